@@ -1,0 +1,75 @@
+// Context management for libob200 (no reference counterpart: Orion keeps no device state).
+#include "ob200_internal.cuh"
+
+extern "C" {
+
+int ob200_version(void) { return OB200_ABI_VERSION; }
+
+int ob200_ctx_create(int device, ob200_ctx** out) {
+  if (!out) return OB200_EINVAL;
+  *out = nullptr;
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || device < 0 || device >= count) return OB200_ECUDA;
+  ob200_ctx* ctx = new ob200_ctx();
+  ctx->device = device;
+  if (cudaSetDevice(device) != cudaSuccess) { delete ctx; return OB200_ECUDA; }
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) { delete ctx; return OB200_ECUDA; }
+  if (prop.major != 10) {  // sm_100a cubin only; fail loudly instead of falling back
+    fprintf(stderr, "libob200: device %d is sm_%d%d, this library is built for sm_100a only\n", device,
+            prop.major, prop.minor);
+    delete ctx;
+    return OB200_ECUDA;
+  }
+  ctx->num_sms = prop.multiProcessorCount;
+  if (cudaMalloc((void**)&ctx->status_dev, sizeof(int)) != cudaSuccess ||
+      cudaMemset(ctx->status_dev, 0, sizeof(int)) != cudaSuccess ||
+      cudaMalloc((void**)&ctx->best_dev, 3 * sizeof(ob200_best)) != cudaSuccess ||
+      cudaMallocHost((void**)&ctx->best_pinned, 3 * sizeof(ob200_best)) != cudaSuccess) {
+    ob200_ctx_destroy(ctx);
+    return OB200_ENOMEM;
+  }
+  *out = ctx;
+  return OB200_OK;
+}
+
+void ob200_ctx_destroy(ob200_ctx* ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  cudaDeviceSynchronize();
+  cudaFree(ctx->slots_dev);
+  cudaFree(ctx->cdf_dev);
+  cudaFree(ctx->col_nlo_dev);
+  cudaFree(ctx->col_nhi_dev);
+  cudaFree(ctx->status_dev);
+  cudaFree(ctx->blob);
+  cudaFree(ctx->L_dev);
+  cudaFree(ctx->work_dev);
+  cudaFree(ctx->kstar_dev);
+  cudaFree(ctx->cand_tmp);
+  cudaFree(ctx->dense_tmp);
+  cudaFree(ctx->partial_dev);
+  cudaFree(ctx->best_dev);
+  if (ctx->best_pinned) cudaFreeHost(ctx->best_pinned);
+  if (ctx->pinned) cudaFreeHost(ctx->pinned);
+  delete ctx;
+}
+
+const char* ob200_last_error(const ob200_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+
+int ob200_set_stream(ob200_ctx* ctx, void* cuda_stream) {
+  if (!ctx) return OB200_EINVAL;
+  ctx->stream = (cudaStream_t)cuda_stream;
+  return OB200_OK;
+}
+
+int ob200_sync(ob200_ctx* ctx) {
+  if (!ctx) return OB200_EINVAL;
+  OB_CUDA(ctx, cudaSetDevice(ctx->device));
+  OB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return OB200_OK;
+}
+
+int64_t ob200_launch_count(const ob200_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+}  // extern "C"

@@ -1,0 +1,611 @@
+// a13: GP fit on the device -- y statistics, Gram matrix, blocked FP64 Cholesky, inv(L), alpha.
+//
+// Replaces GaussianProcessRegressor.fit with fixed hyper-parameters
+// (sklearn/gaussian_process/_gpr.py:233-368): y normalisation :275-280 (population std,
+// _handle_zeros_in_scale), K = kernel(X) :349 (Matern nu=2.5 kernels.py:1720-1729 via pdist-style
+// direct differences, RBF :1569-1570), K[diag] += alpha :350, L = cholesky(K, lower) :352,
+// alpha_ = cho_solve((L, True), y) :363-367, and log_marginal_likelihood value :541-656.
+//
+// B200 design: everything n x n is tiled in 64 x 64 blocks of FP64 and every O(n^3) step is a
+// DMMA (mma.sync m8n8k4 f64 -> SASS DMMA.8x8x4) tile GEMM:
+//   * right-looking Cholesky: 64x64 diagonal factor + its inverse in one CTA (shared memory),
+//     panel = A21 * inv(L11)^T (GEMM), trailing A22 -= P P^T (GEMM, lower tiles only);
+//   * inv(L) by recursive doubling: X21 = -inv(C) (B inv(A)), two batched GEMMs per level;
+//   * alpha by blocked forward/back substitution in one CTA (n^2 work, bandwidth trivial).
+// inv(L) is then written in the tile-packed layout the score kernel streams with bulk copies.
+#include <math.h>
+
+#include "ob200_internal.cuh"
+
+#define FB 64            // block size of the fit algorithms
+#define GEMM_BK 16
+#define OB200_FIT_MAGIC 0x0b200f17
+
+namespace {
+
+// ------------------------------------------------------------------------------------------
+// y statistics + normalised y.  Single CTA, deterministic tree reductions.
+// stats_out: [0]=mean, [1]=std (zero-scale guarded), [2]=min(y)
+__global__ void __launch_bounds__(1024) ystats_kernel(const double* __restrict__ y, int n, int n_pad, int normalize,
+                                                      double* __restrict__ y_norm, double* __restrict__ stats_out) {
+  __shared__ double red[1024];
+  __shared__ double s_mean, s_std;
+  const int t = threadIdx.x;
+  double acc = 0.0, mn = INFINITY;
+  for (int i = t; i < n; i += 1024) { acc += y[i]; mn = fmin(mn, y[i]); }
+  red[t] = acc;
+  __syncthreads();
+  for (int s = 512; s > 0; s >>= 1) { if (t < s) red[t] += red[t + s]; __syncthreads(); }
+  if (t == 0) s_mean = red[0] / (double)n;
+  __syncthreads();
+  const double mean = s_mean;
+  acc = 0.0;
+  for (int i = t; i < n; i += 1024) { double d = y[i] - mean; acc += d * d; }
+  __syncthreads();
+  red[t] = acc;
+  __syncthreads();
+  for (int s = 512; s > 0; s >>= 1) { if (t < s) red[t] += red[t + s]; __syncthreads(); }
+  if (t == 0) {
+    double sd = sqrt(red[0] / (double)n);
+    if (sd < 10.0 * 2.220446049250313e-16) sd = 1.0;  // sklearn _handle_zeros_in_scale
+    s_std = sd;
+  }
+  __syncthreads();
+  red[t] = mn;
+  __syncthreads();
+  for (int s = 512; s > 0; s >>= 1) { if (t < s) red[t] = fmin(red[t], red[t + s]); __syncthreads(); }
+  const double m_use = normalize ? mean : 0.0, s_use = normalize ? s_std : 1.0;
+  if (t == 0) { stats_out[0] = m_use; stats_out[1] = s_use; stats_out[2] = red[0]; }
+  for (int i = t; i < n_pad; i += 1024) y_norm[i] = i < n ? (y[i] - m_use) / s_use : 0.0;
+}
+
+// Xs = X / length_scale (row-major [n_pad x D_pad], zero padded) and xx = ||Xs_i||^2
+__global__ void scale_x_kernel(const double* __restrict__ X, int n, int D, int n_pad, int D_pad,
+                               const double* __restrict__ ls, int n_ls,
+                               double* __restrict__ Xs, double* __restrict__ xx) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_pad) return;
+  double acc = 0.0;
+  for (int d = 0; d < D_pad; ++d) {
+    double v = 0.0;
+    if (i < n && d < D) v = X[(size_t)i * D + d] / ls[n_ls == 1 ? 0 : d];
+    Xs[(size_t)i * D_pad + d] = v;
+    acc = fma(v, v, acc);
+  }
+  xx[i] = acc;
+}
+
+__device__ __forceinline__ double kernel_from_d2(int kind, double d2, double amplitude) {
+  if (kind == OB200_KERNEL_MATERN52) {
+    const double k = sqrt(d2) * 2.23606797749979;  // sqrt(5)
+    return amplitude * ((1.0 + k + k * k / 3.0) * exp(-k));
+  }
+  return amplitude * exp(-0.5 * d2);
+}
+
+// Lower triangle of K (+ alpha on the diagonal) with pdist-style direct differences; identity pad.
+__global__ void __launch_bounds__(256) gram_kernel(const double* __restrict__ Xs, int n, int n_pad, int D_pad, int kind,
+                                                   double amplitude, double alpha, double* __restrict__ K) {
+  const int ti = blockIdx.y, tj = blockIdx.x;
+  if (tj > ti) return;
+  extern __shared__ double sm[];
+  double* xi = sm;                       // [32][D_pad+1]
+  double* xj = sm + 32 * (D_pad + 1);
+  const int ldx = D_pad + 1;
+  for (int e = threadIdx.x; e < 32 * D_pad; e += 256) {
+    const int r = e / D_pad, d = e - r * D_pad;
+    xi[r * ldx + d] = Xs[(size_t)(ti * 32 + r) * D_pad + d];
+    xj[r * ldx + d] = Xs[(size_t)(tj * 32 + r) * D_pad + d];
+  }
+  __syncthreads();
+  for (int e = threadIdx.x; e < 1024; e += 256) {
+    const int r = e >> 5, c = e & 31;
+    const int i = ti * 32 + r, j = tj * 32 + c;
+    double v;
+    if (i >= n || j >= n) {
+      v = (i == j) ? 1.0 : 0.0;
+    } else if (j > i) {
+      v = 0.0;
+    } else {
+      double d2 = 0.0;
+      for (int d = 0; d < D_pad; ++d) { const double df = xi[r * ldx + d] - xj[c * ldx + d]; d2 = fma(df, df, d2); }
+      v = kernel_from_d2(kind, d2, amplitude);
+      if (i == j) v += alpha;
+    }
+    K[(size_t)i * n_pad + j] = v;
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// Generic DMMA tile GEMM for the fit:  C[z] = alpha * A[z] * op(B[z]) + beta * C[z]
+//   tile 64x64 per CTA, 4 warps (2x2), warp tile 32x32 = 4x4 DMMA fragments, K step 16.
+//   All extents are multiples of 64 (M,N) / 16 (K).  TRANS_B: B is [N x K] row-major ("NT").
+//   lower_only: skip tiles strictly above the diagonal (SYRK).  m_last: M of the last batch entry.
+struct gemm_args {
+  const double *A, *B;
+  double* C;
+  int M, N, K, lda, ldb, ldc;
+  long long strideA, strideB, strideC;
+  int m_last, k_eq_m;  // k_eq_m: K follows the batch entry's M (TRTRI second product)
+  double alpha, beta;
+  int lower_only;
+};
+
+template <bool TRANS_B>
+__global__ void __launch_bounds__(128) gemm64_kernel(gemm_args g) {
+  const int z = blockIdx.z;
+  int M = g.M, K = g.K;
+  if (z == (int)gridDim.z - 1 && g.m_last > 0) { M = g.m_last; if (g.k_eq_m) K = g.m_last; }
+  const int tm = blockIdx.y, tn = blockIdx.x;
+  if (tm * 64 >= M) return;
+  if (g.lower_only && tn > tm) return;
+  const double* __restrict__ A = g.A + z * g.strideA + (size_t)tm * 64 * g.lda;
+  const double* __restrict__ B = g.B + z * g.strideB + (TRANS_B ? (size_t)tn * 64 * g.ldb : (size_t)tn * 64);
+  double* C = g.C + z * g.strideC + (size_t)tm * 64 * g.ldc + (size_t)tn * 64;
+
+  __shared__ double As[64][GEMM_BK + 4];
+  __shared__ double Bs[TRANS_B ? 64 : GEMM_BK][TRANS_B ? GEMM_BK + 4 : 64 + 4];
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int gq = lane >> 2, q = lane & 3;
+  const int wm = warp >> 1, wn = warp & 1;
+  double acc[4][4][2];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+
+  for (int k0 = 0; k0 < K; k0 += GEMM_BK) {
+    {  // A tile 64 x 16: thread -> row tid/2, 8 contiguous doubles
+      const int r = tid >> 1, c = (tid & 1) * 8;
+      const double2* src = reinterpret_cast<const double2*>(A + (size_t)r * g.lda + k0 + c);
+#pragma unroll
+      for (int v = 0; v < 4; ++v) { double2 t = src[v]; As[r][c + 2 * v] = t.x; As[r][c + 2 * v + 1] = t.y; }
+    }
+    if (TRANS_B) {
+      const int r = tid >> 1, c = (tid & 1) * 8;
+      const double2* src = reinterpret_cast<const double2*>(B + (size_t)r * g.ldb + k0 + c);
+#pragma unroll
+      for (int v = 0; v < 4; ++v) { double2 t = src[v]; Bs[r][c + 2 * v] = t.x; Bs[r][c + 2 * v + 1] = t.y; }
+    } else {
+      const int r = tid >> 3, c = (tid & 7) * 8;
+      const double2* src = reinterpret_cast<const double2*>(B + (size_t)(k0 + r) * g.ldb + c);
+#pragma unroll
+      for (int v = 0; v < 4; ++v) { double2 t = src[v]; Bs[r][c + 2 * v] = t.x; Bs[r][c + 2 * v + 1] = t.y; }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < GEMM_BK; kk += 4) {
+      double a[4], b[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) a[i] = As[wm * 32 + i * 8 + gq][kk + q];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) b[j] = TRANS_B ? Bs[wn * 32 + j * 8 + gq][kk + q] : Bs[kk + q][wn * 32 + j * 8 + gq];
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      double2* dst = reinterpret_cast<double2*>(C + (size_t)(wm * 32 + i * 8 + gq) * g.ldc + wn * 32 + j * 8 + 2 * q);
+      double2 out;
+      if (g.beta != 0.0) {
+        double2 old = *dst;
+        out.x = g.alpha * acc[i][j][0] + g.beta * old.x;
+        out.y = g.alpha * acc[i][j][1] + g.beta * old.y;
+      } else {
+        out.x = g.alpha * acc[i][j][0];
+        out.y = g.alpha * acc[i][j][1];
+      }
+      *dst = out;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// Diagonal block: factor A[kb,kb] (64x64) in shared memory, write L back (upper zeroed), and
+// write inv(L_kk) to Dinv[kb].  info: 0 ok, else 1-based index of the failing pivot.
+__global__ void __launch_bounds__(256) chol_diag_kernel(double* __restrict__ A, int ld, int kb, double* __restrict__ Dinv,
+                                                        int* __restrict__ info) {
+  extern __shared__ double diag_sm[];
+  double (*S)[FB + 1] = reinterpret_cast<double (*)[FB + 1]>(diag_sm);
+  double (*Inv)[FB + 1] = reinterpret_cast<double (*)[FB + 1]>(diag_sm + FB * (FB + 1));
+  __shared__ int bad;
+  double* blk = A + (size_t)kb * FB * ld + (size_t)kb * FB;
+  const int tid = threadIdx.x;
+  if (tid == 0) bad = 0;
+  for (int e = tid; e < FB * FB; e += 256) { const int r = e >> 6, c = e & 63; S[r][c] = (c <= r) ? blk[(size_t)r * ld + c] : 0.0; }
+  __syncthreads();
+  if (*info != 0) return;  // an earlier block already failed
+  for (int j = 0; j < FB; ++j) {
+    const double piv = S[j][j];
+    if (!(piv > 0.0)) {  // also catches NaN
+      if (tid == 0) { bad = 1; *info = kb * FB + j + 1; }
+      break;
+    }
+    const double d = sqrt(piv);
+    __syncthreads();
+    if (tid == 0) S[j][j] = d;
+    for (int i = j + 1 + tid; i < FB; i += 256) S[i][j] = S[i][j] / d;
+    __syncthreads();
+    // trailing update of the lower triangle: S[i][c] -= S[i][j]*S[c][j], j < c <= i
+    const int rem = FB - j - 1;
+    for (int e = tid; e < rem * rem; e += 256) {
+      const int i = j + 1 + e / rem, c = j + 1 + e % rem;
+      if (c <= i) S[i][c] = fma(-S[i][j], S[c][j], S[i][c]);
+    }
+    __syncthreads();
+  }
+  __syncthreads();
+  if (bad) return;
+  // inverse of the lower-triangular block, one column per thread (forward substitution)
+  if (tid < FB) {
+    const int c = tid;
+    for (int i = 0; i < c; ++i) Inv[i][c] = 0.0;
+    Inv[c][c] = 1.0 / S[c][c];
+    for (int i = c + 1; i < FB; ++i) {
+      double acc = 0.0;
+      for (int k = c; k < i; ++k) acc = fma(S[i][k], Inv[k][c], acc);
+      Inv[i][c] = -acc / S[i][i];
+    }
+  }
+  __syncthreads();
+  double* dinv = Dinv + (size_t)kb * FB * FB;
+  for (int e = tid; e < FB * FB; e += 256) {
+    const int r = e >> 6, c = e & 63;
+    blk[(size_t)r * ld + c] = S[r][c];
+    dinv[e] = Inv[r][c];
+  }
+}
+
+// zero the strict upper triangle tiles left over from the Gram/SYRK (they hold garbage-free zeros
+// already from gram_kernel; SYRK only touches lower tiles) -- nothing to do.  X (inverse) init:
+// X = 0 except diagonal blocks = Dinv.
+__global__ void trtri_init_kernel(double* __restrict__ X, int ld, const double* __restrict__ Dinv) {
+  const int kb = blockIdx.x;
+  double* blk = X + (size_t)kb * FB * ld + (size_t)kb * FB;
+  const double* d = Dinv + (size_t)kb * FB * FB;
+  for (int e = threadIdx.x; e < FB * FB; e += blockDim.x) blk[(size_t)(e >> 6) * ld + (e & 63)] = d[e];
+}
+
+// alpha = L^-T L^-1 y by blocked substitution with the inverted diagonal blocks; also
+// lml = -0.5 y^T alpha - sum log L_ii - n/2 log(2 pi).  One CTA of 1024 threads.
+__global__ void __launch_bounds__(1024) chol_solve_kernel(const double* __restrict__ L, int ld, int n, int n_pad,
+                                                          const double* __restrict__ Dinv, const double* __restrict__ y,
+                                                          double* __restrict__ tvec, double* __restrict__ alpha_out,
+                                                          double* __restrict__ lml_out) {
+  __shared__ double part[16][FB + 1];
+  __shared__ double r[FB];
+  const int tid = threadIdx.x;
+  const int nb = n_pad / FB;
+  // forward: t_i = Dinv_i (y_i - L[i, :64 i] t[:64 i])
+  for (int ib = 0; ib < nb; ++ib) {
+    {
+      const int row = tid >> 4, g = tid & 15;  // 64 rows x 16 column lanes
+      const double* Lr = L + (size_t)(ib * FB + row) * ld;
+      double acc = 0.0;
+      for (int j = g; j < ib * FB; j += 16) acc = fma(Lr[j], tvec[j], acc);
+      part[g][row] = acc;
+    }
+    __syncthreads();
+    if (tid < FB) {
+      double s = 0.0;
+      for (int g = 0; g < 16; ++g) s += part[g][tid];
+      r[tid] = y[ib * FB + tid] - s;
+    }
+    __syncthreads();
+    if (tid < FB) {
+      const double* d = Dinv + (size_t)ib * FB * FB + (size_t)tid * FB;
+      double s = 0.0;
+      for (int k = 0; k <= tid; ++k) s = fma(d[k], r[k], s);
+      tvec[ib * FB + tid] = s;
+    }
+    __threadfence_block();
+    __syncthreads();
+  }
+  // backward: alpha_i = Dinv_i^T (t_i - sum_{k >= 64(i+1)} L[k, i-block]^T alpha_k)
+  for (int ib = nb - 1; ib >= 0; --ib) {
+    {
+      const int c = tid & 63, g = tid >> 6;  // 64 columns x 16 row lanes
+      double acc = 0.0;
+      for (int k = (ib + 1) * FB + g; k < n_pad; k += 16) acc = fma(L[(size_t)k * ld + ib * FB + c], alpha_out[k], acc);
+      part[g][c] = acc;
+    }
+    __syncthreads();
+    if (tid < FB) {
+      double s = 0.0;
+      for (int g = 0; g < 16; ++g) s += part[g][tid];
+      r[tid] = tvec[ib * FB + tid] - s;
+    }
+    __syncthreads();
+    if (tid < FB) {
+      const double* d = Dinv + (size_t)ib * FB * FB;
+      double s = 0.0;
+      for (int m = tid; m < FB; ++m) s = fma(d[(size_t)m * FB + tid], r[m], s);
+      alpha_out[ib * FB + tid] = (ib * FB + tid < n) ? s : 0.0;
+    }
+    __threadfence_block();
+    __syncthreads();
+  }
+  // lml
+  double a = 0.0, b = 0.0;
+  for (int i = tid; i < n; i += 1024) { a = fma(y[i], alpha_out[i], a); b += log(L[(size_t)i * ld + i]); }
+  __shared__ double ra[1024], rb[1024];
+  ra[tid] = a; rb[tid] = b;
+  __syncthreads();
+  for (int s = 512; s > 0; s >>= 1) { if (tid < s) { ra[tid] += ra[tid + s]; rb[tid] += rb[tid + s]; } __syncthreads(); }
+  if (tid == 0) *lml_out = -0.5 * ra[0] - rb[0] - 0.5 * (double)n * 1.8378770664093453;  // log(2 pi)
+}
+
+// Pack inv(L) (dense row-major X, ld = n_pad) into the score kernel's tile layout:
+//   tile (I, J) = rows [I*SC_BM, +SC_BM) x cols [J*SC_BK, +SC_BK), stored contiguously as
+//   [slot (SC_BM/8)][k8 (SC_BK/8)][8 rows][8 cols]; slot = wm*8 + t holds the 8 rows of original
+//   row fragment f = 4*t + wm (cyclic assignment of row fragments to the 4 warp rows).
+// Rows/cols >= n are written as zeros.
+__global__ void pack_linv_kernel(const double* __restrict__ X, int n, int n_pad, double* __restrict__ out) {
+  const int64_t total = (int64_t)n_pad * n_pad;
+  const int nJ = n_pad / SC_BK;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+    int64_t rem = e;
+    const int col8 = rem & 7; rem >>= 3;
+    const int row8 = rem & 7; rem >>= 3;
+    const int k8 = rem % (SC_BK / 8); rem /= (SC_BK / 8);
+    const int slot = rem % (SC_BM / 8); rem /= (SC_BM / 8);
+    const int J = rem % nJ;
+    const int I = (int)(rem / nJ);
+    const int wm = slot >> 3, t = slot & 7;
+    const int row = I * SC_BM + (4 * t + wm) * 8 + row8;
+    const int col = J * SC_BK + k8 * 8 + col8;
+    out[e] = (row < n && col < n && col <= row) ? X[(size_t)row * n_pad + col] : 0.0;
+  }
+}
+
+// Pack Xs into DMMA fragment order: [obs8][d4][8 obs][4 dims]
+__global__ void pack_xs_kernel(const double* __restrict__ Xs, int n_pad, int D_pad, double* __restrict__ out) {
+  const int64_t total = (int64_t)n_pad * D_pad;
+  const int nd4 = D_pad / 4;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+    int64_t rem = e;
+    const int dq = rem & 3; rem >>= 2;
+    const int o8 = rem & 7; rem >>= 3;
+    const int d4 = rem % nd4;
+    const int ob = (int)(rem / nd4);
+    out[e] = Xs[(size_t)(ob * 8 + o8) * D_pad + d4 * 4 + dq];
+  }
+}
+
+__global__ void write_header_kernel(ob200_fit_header* hdr_dev, ob200_fit_header h, const double* stats, const double* lml,
+                                    double* inv_ls_out, const double* ls, int n_ls, int D, int D_pad) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) {
+    h.y_mean = stats[0]; h.y_std = stats[1]; h.y_min = stats[2]; h.lml = *lml;
+    *hdr_dev = h;
+  }
+  for (int d = threadIdx.x; d < D_pad; d += blockDim.x) inv_ls_out[d] = d < D ? ls[n_ls == 1 ? 0 : d] : 1.0;
+}
+
+int launch_gemm(ob200_ctx* ctx, bool trans_b, const gemm_args& g, int batch) {
+  dim3 grid(g.N / 64, g.M / 64, batch);
+  if (grid.x == 0 || grid.y == 0 || batch == 0) return OB200_OK;
+  if (trans_b) gemm64_kernel<true><<<grid, 128, 0, ctx->stream>>>(g);
+  else gemm64_kernel<false><<<grid, 128, 0, ctx->stream>>>(g);
+  OB_LAUNCH_CHECK(ctx);
+  return OB200_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int ob200_gp_state_bytes(ob200_ctx* ctx, int n, int D, int64_t* bytes) {
+  if (!ctx || !bytes) return OB200_EINVAL;
+  if (n < 1 || n > OB200_MAX_N || D < 1) OB_FAIL(ctx, OB200_EINVAL, "n must be in [1, %d], D >= 1", OB200_MAX_N);
+  const int n_pad = (int)ob_round_up(n, SC_BM), D_pad = (int)ob_round_up(D, 4);
+  *bytes = ob_blob_layout(n_pad, D_pad).total;
+  return OB200_OK;
+}
+
+int ob200_gp_fit(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n, int D, const ob200_kernel* kernel,
+                 double alpha, int normalize_y) {
+  if (!ctx) return OB200_EINVAL;
+  if (!X_dev || !y_dev || !kernel) OB_FAIL(ctx, OB200_EINVAL, "null argument");
+  if (n < 1 || n > OB200_MAX_N) OB_FAIL(ctx, OB200_EINVAL, "n_obs=%d outside [1, %d]", n, OB200_MAX_N);
+  if (D < 1 || D > 384) OB_FAIL(ctx, OB200_EINVAL, "D=%d outside [1, 384]", D);
+  if (kernel->kind != OB200_KERNEL_MATERN52 && kernel->kind != OB200_KERNEL_RBF) OB_FAIL(ctx, OB200_EINVAL, "unknown kernel kind");
+  if (kernel->n_length_scale != 1 && kernel->n_length_scale != D) OB_FAIL(ctx, OB200_EINVAL, "length_scale must have 1 or D entries");
+  if (!kernel->length_scale_host) OB_FAIL(ctx, OB200_EINVAL, "length_scale_host is null");
+  for (int i = 0; i < kernel->n_length_scale; ++i)
+    if (!(kernel->length_scale_host[i] > 0.0)) OB_FAIL(ctx, OB200_EINVAL, "length_scale[%d] must be > 0", i);
+  if (!(kernel->amplitude > 0.0) || !(alpha >= 0.0)) OB_FAIL(ctx, OB200_EINVAL, "amplitude must be > 0 and alpha >= 0");
+  OB_CUDA(ctx, cudaSetDevice(ctx->device));
+  ctx->fitted = false;
+
+  const int n_pad = (int)ob_round_up(n, SC_BM), D_pad = (int)ob_round_up(D, 4);
+  const int nb = n_pad / FB;
+  const ob200_blob_layout lay = ob_blob_layout(n_pad, D_pad);
+  int rc;
+  if ((rc = ob_reserve(ctx, &ctx->blob, &ctx->blob_cap, lay.total))) return rc;
+  if ((rc = ob_reserve(ctx, &ctx->L_dev, &ctx->L_cap, (int64_t)n_pad * n_pad))) return rc;
+  // workspace: X (n_pad^2) | T (n_pad^2 / 2) | Dinv (nb*64*64) | Xs (n_pad*D_pad) | y_norm | tvec | ls | stats(4) | info
+  const int64_t w_X = 0, w_T = w_X + (int64_t)n_pad * n_pad, w_Dinv = w_T + (int64_t)n_pad * n_pad / 2,
+                w_Xs = w_Dinv + (int64_t)nb * FB * FB, w_y = w_Xs + (int64_t)n_pad * D_pad, w_t = w_y + n_pad,
+                w_ls = w_t + n_pad, w_stats = w_ls + D_pad, w_end = w_stats + 8;
+  if ((rc = ob_reserve(ctx, &ctx->work_dev, &ctx->work_cap, w_end))) return rc;
+  double* W = ctx->work_dev;
+  double *Xinv = W + w_X, *T = W + w_T, *Dinv = W + w_Dinv, *Xs = W + w_Xs, *ynorm = W + w_y, *tvec = W + w_t,
+         *ls_dev = W + w_ls, *stats = W + w_stats;
+  int* info_dev = reinterpret_cast<int*>(stats + 6);
+  double* lml_dev = stats + 4;
+  cudaStream_t st = ctx->stream;
+  char* blob = ctx->blob;
+  double* b_invls = reinterpret_cast<double*>(blob + lay.off_invls);
+  double* b_xs = reinterpret_cast<double*>(blob + lay.off_xs);
+  double* b_xx = reinterpret_cast<double*>(blob + lay.off_xx);
+  double* b_alpha = reinterpret_cast<double*>(blob + lay.off_alpha);
+  double* b_linv = reinterpret_cast<double*>(blob + lay.off_linv);
+
+  OB_CUDA(ctx, cudaMemcpyAsync(ls_dev, kernel->length_scale_host, (size_t)kernel->n_length_scale * 8, cudaMemcpyHostToDevice, st));
+  OB_CUDA(ctx, cudaMemsetAsync(stats, 0, 8 * sizeof(double), st));
+
+  ystats_kernel<<<1, 1024, 0, st>>>(y_dev, n, n_pad, normalize_y, ynorm, stats);
+  OB_LAUNCH_CHECK(ctx);
+  scale_x_kernel<<<(n_pad + 127) / 128, 128, 0, st>>>(X_dev, n, D, n_pad, D_pad, ls_dev, kernel->n_length_scale, Xs, b_xx);
+  OB_LAUNCH_CHECK(ctx);
+  {
+    const size_t smem = (size_t)2 * 32 * (D_pad + 1) * sizeof(double);
+    OB_CUDA(ctx, cudaFuncSetAttribute(gram_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem > 49152 ? smem : 49152)));
+    dim3 grid(n_pad / 32, n_pad / 32);
+    gram_kernel<<<grid, 256, smem, st>>>(Xs, n, n_pad, D_pad, kernel->kind, kernel->amplitude, alpha, ctx->L_dev);
+    OB_LAUNCH_CHECK(ctx);
+  }
+  // ---- right-looking blocked Cholesky ----------------------------------------------------
+  double* Lm = ctx->L_dev;
+  const size_t diag_smem = (size_t)2 * FB * (FB + 1) * sizeof(double);
+  OB_CUDA(ctx, cudaFuncSetAttribute(chol_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)diag_smem));
+  for (int kb = 0; kb < nb; ++kb) {
+    chol_diag_kernel<<<1, 256, diag_smem, st>>>(Lm, n_pad, kb, Dinv, info_dev);
+    OB_LAUNCH_CHECK(ctx);
+    const int rem = n_pad - (kb + 1) * FB;
+    if (rem <= 0) break;
+    gemm_args p{};
+    p.A = Lm + (size_t)(kb + 1) * FB * n_pad + (size_t)kb * FB; p.lda = n_pad;
+    p.B = Dinv + (size_t)kb * FB * FB; p.ldb = FB;
+    p.C = const_cast<double*>(p.A); p.ldc = n_pad;
+    p.M = rem; p.N = FB; p.K = FB; p.alpha = 1.0; p.beta = 0.0;
+    if ((rc = launch_gemm(ctx, true, p, 1))) return rc;
+    gemm_args s{};
+    s.A = p.A; s.lda = n_pad; s.B = p.A; s.ldb = n_pad;
+    s.C = Lm + (size_t)(kb + 1) * FB * n_pad + (size_t)(kb + 1) * FB; s.ldc = n_pad;
+    s.M = rem; s.N = rem; s.K = FB; s.alpha = -1.0; s.beta = 1.0; s.lower_only = 1;
+    if ((rc = launch_gemm(ctx, true, s, 1))) return rc;
+  }
+  int info = 0;
+  OB_CUDA(ctx, cudaMemcpyAsync(&info, info_dev, sizeof(int), cudaMemcpyDeviceToHost, st));
+  OB_CUDA(ctx, cudaStreamSynchronize(st));
+  if (info != 0)
+    OB_FAIL(ctx, OB200_ENOTSPD,
+            "The kernel is not returning a positive definite matrix (pivot %d of %d). Try gradually increasing the 'alpha' "
+            "parameter of your GaussianProcessRegressor estimator.", info, n);
+
+  // ---- alpha, lml ----------------------------------------------------------------------------
+  chol_solve_kernel<<<1, 1024, 0, st>>>(Lm, n_pad, n, n_pad, Dinv, ynorm, tvec, b_alpha, lml_dev);
+  OB_LAUNCH_CHECK(ctx);
+
+  // ---- inv(L) by recursive doubling ----------------------------------------------------------
+  OB_CUDA(ctx, cudaMemsetAsync(Xinv, 0, (size_t)n_pad * n_pad * 8, st));
+  trtri_init_kernel<<<nb, 256, 0, st>>>(Xinv, n_pad, Dinv);
+  OB_LAUNCH_CHECK(ctx);
+  for (int s = FB; s < n_pad; s *= 2) {
+    int pairs = 0, c_last = 0;
+    for (int lo = 0; lo + s < n_pad; lo += 2 * s) { ++pairs; c_last = (lo + 2 * s <= n_pad ? s : n_pad - lo - s); }
+    if (pairs == 0) break;
+    const long long stride = (long long)2 * s * (n_pad + 1);
+    gemm_args g1{};  // T_z = L[mid:hi, lo:mid] * X[lo:mid, lo:mid]
+    g1.A = Lm + (size_t)s * n_pad; g1.lda = n_pad; g1.strideA = stride;
+    g1.B = Xinv; g1.ldb = n_pad; g1.strideB = stride;
+    g1.C = T; g1.ldc = s; g1.strideC = (long long)s * s;
+    g1.M = s; g1.N = s; g1.K = s; g1.m_last = c_last; g1.alpha = 1.0; g1.beta = 0.0;
+    if ((rc = launch_gemm(ctx, false, g1, pairs))) return rc;
+    gemm_args g2{};  // X[mid:hi, lo:mid] = -X[mid:hi, mid:hi] * T_z
+    g2.A = Xinv + (size_t)s * n_pad + s; g2.lda = n_pad; g2.strideA = stride;
+    g2.B = T; g2.ldb = s; g2.strideB = (long long)s * s;
+    g2.C = Xinv + (size_t)s * n_pad; g2.ldc = n_pad; g2.strideC = stride;
+    g2.M = s; g2.N = s; g2.K = s; g2.m_last = c_last; g2.k_eq_m = 1; g2.alpha = -1.0; g2.beta = 0.0;
+    if ((rc = launch_gemm(ctx, false, g2, pairs))) return rc;
+  }
+  pack_linv_kernel<<<ctx->num_sms * 8, 256, 0, st>>>(Xinv, n, n_pad, b_linv);
+  OB_LAUNCH_CHECK(ctx);
+  pack_xs_kernel<<<ctx->num_sms * 2, 256, 0, st>>>(Xs, n_pad, D_pad, b_xs);
+  OB_LAUNCH_CHECK(ctx);
+  ob200_fit_header h{};
+  h.magic = OB200_FIT_MAGIC; h.n = n; h.D = D; h.n_pad = n_pad; h.D_pad = D_pad; h.kernel_kind = kernel->kind;
+  h.amplitude = kernel->amplitude;
+  write_header_kernel<<<1, 128, 0, st>>>(reinterpret_cast<ob200_fit_header*>(blob), h, stats, lml_dev, b_invls, ls_dev,
+                                         kernel->n_length_scale, D, D_pad);
+  OB_LAUNCH_CHECK(ctx);
+  OB_CUDA(ctx, cudaMemcpyAsync(&ctx->hdr, blob, sizeof(ob200_fit_header), cudaMemcpyDeviceToHost, st));
+  OB_CUDA(ctx, cudaStreamSynchronize(st));
+  ctx->blob_bytes = lay.total;
+  ctx->fitted = true;
+  return OB200_OK;
+}
+
+int ob200_gp_fit_host(ob200_ctx* ctx, const double* X_host, const double* y_host, int n, int D, const ob200_kernel* kernel,
+                      double alpha, int normalize_y) {
+  if (!ctx) return OB200_EINVAL;
+  if (!X_host || !y_host || n < 1 || D < 1) OB_FAIL(ctx, OB200_EINVAL, "bad X/y/n/D");
+  OB_CUDA(ctx, cudaSetDevice(ctx->device));
+  int rc = ob_reserve(ctx, &ctx->cand_tmp, &ctx->cand_cap, (int64_t)n * D + n);
+  if (rc) return rc;
+  OB_CUDA(ctx, cudaMemcpyAsync(ctx->cand_tmp, X_host, (size_t)n * D * 8, cudaMemcpyHostToDevice, ctx->stream));
+  OB_CUDA(ctx, cudaMemcpyAsync(ctx->cand_tmp + (size_t)n * D, y_host, (size_t)n * 8, cudaMemcpyHostToDevice, ctx->stream));
+  return ob200_gp_fit(ctx, ctx->cand_tmp, ctx->cand_tmp + (size_t)n * D, n, D, kernel, alpha, normalize_y);
+}
+
+int ob200_gp_lml(ob200_ctx* ctx, double* lml_host) {
+  if (!ctx || !lml_host) return OB200_EINVAL;
+  if (!ctx->fitted) OB_FAIL(ctx, OB200_ESTATE, "no fit");
+  *lml_host = ctx->hdr.lml;
+  return OB200_OK;
+}
+
+int ob200_gp_get_ystats(ob200_ctx* ctx, double* y_mean, double* y_std, double* y_min) {
+  if (!ctx) return OB200_EINVAL;
+  if (!ctx->fitted) OB_FAIL(ctx, OB200_ESTATE, "no fit");
+  if (y_mean) *y_mean = ctx->hdr.y_mean;
+  if (y_std) *y_std = ctx->hdr.y_std;
+  if (y_min) *y_min = ctx->hdr.y_min;
+  return OB200_OK;
+}
+
+int ob200_gp_get_factor(ob200_ctx* ctx, double* L_host, double* alpha_host) {
+  if (!ctx) return OB200_EINVAL;
+  if (!ctx->fitted) OB_FAIL(ctx, OB200_ESTATE, "no fit");
+  if (L_host && !ctx->L_dev) OB_FAIL(ctx, OB200_ESTATE, "L is not kept on contexts that imported their fit");
+  OB_CUDA(ctx, cudaSetDevice(ctx->device));
+  const int n = ctx->hdr.n, n_pad = ctx->hdr.n_pad;
+  if (L_host)
+    OB_CUDA(ctx, cudaMemcpy2DAsync(L_host, (size_t)n * 8, ctx->L_dev, (size_t)n_pad * 8, (size_t)n * 8, (size_t)n,
+                                   cudaMemcpyDeviceToHost, ctx->stream));
+  if (alpha_host) {
+    const ob200_blob_layout lay = ob_blob_layout(n_pad, ctx->hdr.D_pad);
+    OB_CUDA(ctx, cudaMemcpyAsync(alpha_host, ctx->blob + lay.off_alpha, (size_t)n * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  }
+  OB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return OB200_OK;
+}
+
+int ob200_gp_export(ob200_ctx* ctx, void* blob_dev, int64_t bytes) {
+  if (!ctx || !blob_dev) return OB200_EINVAL;
+  if (!ctx->fitted) OB_FAIL(ctx, OB200_ESTATE, "no fit to export");
+  if (bytes < ctx->blob_bytes) OB_FAIL(ctx, OB200_EINVAL, "blob too small: %lld < %lld", (long long)bytes, (long long)ctx->blob_bytes);
+  OB_CUDA(ctx, cudaSetDevice(ctx->device));
+  OB_CUDA(ctx, cudaMemcpyAsync(blob_dev, ctx->blob, (size_t)ctx->blob_bytes, cudaMemcpyDeviceToDevice, ctx->stream));
+  return OB200_OK;
+}
+
+int ob200_gp_import(ob200_ctx* ctx, const void* blob_dev, int64_t bytes) {
+  if (!ctx || !blob_dev) return OB200_EINVAL;
+  if (bytes < 256) OB_FAIL(ctx, OB200_EINVAL, "blob too small");
+  OB_CUDA(ctx, cudaSetDevice(ctx->device));
+  ob200_fit_header h{};
+  OB_CUDA(ctx, cudaMemcpyAsync(&h, blob_dev, sizeof h, cudaMemcpyDeviceToHost, ctx->stream));
+  OB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  if (h.magic != OB200_FIT_MAGIC || h.n < 1 || h.n > OB200_MAX_N || h.n_pad % SC_BM || h.D_pad % 4)
+    OB_FAIL(ctx, OB200_EINVAL, "not a fit blob");
+  const ob200_blob_layout lay = ob_blob_layout(h.n_pad, h.D_pad);
+  if (bytes < lay.total) OB_FAIL(ctx, OB200_EINVAL, "blob truncated");
+  ctx->fitted = false;
+  int rc = ob_reserve(ctx, &ctx->blob, &ctx->blob_cap, lay.total);
+  if (rc) return rc;
+  OB_CUDA(ctx, cudaMemcpyAsync(ctx->blob, blob_dev, (size_t)lay.total, cudaMemcpyDeviceToDevice, ctx->stream));
+  ctx->hdr = h;
+  ctx->blob_bytes = lay.total;
+  ctx->fitted = true;
+  return OB200_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,208 @@
+// Internal definitions shared by the libob200 translation units (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <string>
+#include <vector>
+
+#include "ob200.h"
+
+#define OB200_ABI_VERSION 1
+#define OB200_MAX_N 8192      // observed points (n_obs) supported by the fit
+#define OB200_NUM_SMS_FALLBACK 148
+
+// ---- tiling constants of the score kernel (see DESIGN.md "score kernel") ------------------
+#define SC_BM 256        // rows of inv(L) per row block (4 warp-rows x 8 fragments x 8 rows)
+#define SC_BN 64         // candidates per CTA tile (2 warp-cols x 4 fragments x 8 candidates)
+#define SC_BK 16         // k (observed-point) extent of one pipeline stage
+#define SC_STAGES 4
+#define SC_CONSUMER_WARPS 8
+#define SC_PRODUCER_WARPS 4   // a full warpgroup so that setmaxnreg can rebalance registers
+#define SC_THREADS ((SC_CONSUMER_WARPS + SC_PRODUCER_WARPS) * 32)
+
+struct ob200_fit_header {   // first bytes of the exported fit blob
+  int32_t magic, n, D, n_pad, D_pad, kernel_kind;
+  double amplitude, y_mean, y_std, y_min, lml;
+};
+
+struct ob200_ctx {
+  int device = 0;
+  int num_sms = OB200_NUM_SMS_FALLBACK;
+  cudaStream_t stream = 0;
+  std::string err;
+  int64_t launches = 0;
+
+  // space
+  int n_slots = 0, d_out = 0, n_cdf = 0;
+  ob200_slot* slots_dev = nullptr;
+  double* cdf_dev = nullptr;
+  double* col_nlo_dev = nullptr;   // per output column normalisation bounds
+  double* col_nhi_dev = nullptr;
+  int* status_dev = nullptr;       // latched sampler status
+
+  // fit state: one device blob [header | inv_ls[D_pad] | Xs packed | xx | alpha | Linv packed]
+  bool fitted = false;
+  ob200_fit_header hdr{};
+  char* blob = nullptr;
+  int64_t blob_bytes = 0, blob_cap = 0;
+  double* L_dev = nullptr;         // dense L (n_pad x n_pad) kept for read-back / lml
+  int64_t L_cap = 0;
+  double* work_dev = nullptr;      // fit workspace
+  int64_t work_cap = 0;
+
+  // score scratch
+  double* kstar_dev = nullptr;     // per-CTA K* slices
+  int64_t kstar_cap = 0;
+  double* cand_tmp = nullptr;      // candidates generated on device / staged from host
+  int64_t cand_cap = 0;
+  double* dense_tmp = nullptr;     // staged dense outputs for the host entry point
+  int64_t dense_cap = 0;
+  char* partial_dev = nullptr;     // per-CTA argmax partials (bytes)
+  int64_t partial_cap = 0;
+  ob200_best* best_dev = nullptr;  // [3]
+  ob200_best* best_pinned = nullptr;
+  double* pinned = nullptr;        // pinned staging for host entry points
+  int64_t pinned_cap = 0;
+};
+
+#define OB_FAIL(ctx, code, ...)                               \
+  do {                                                        \
+    char _b[512];                                             \
+    snprintf(_b, sizeof _b, __VA_ARGS__);                     \
+    (ctx)->err = _b;                                          \
+    return (code);                                            \
+  } while (0)
+
+#define OB_CUDA(ctx, expr)                                                              \
+  do {                                                                                  \
+    cudaError_t _e = (expr);                                                            \
+    if (_e != cudaSuccess)                                                              \
+      OB_FAIL(ctx, _e == cudaErrorMemoryAllocation ? OB200_ENOMEM : OB200_ECUDA,        \
+              "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+  } while (0)
+
+#define OB_LAUNCH_CHECK(ctx)        \
+  do {                              \
+    (ctx)->launches++;              \
+    OB_CUDA(ctx, cudaGetLastError()); \
+  } while (0)
+
+// grow-only device buffer helper
+template <typename T>
+static inline int ob_reserve(ob200_ctx* ctx, T** ptr, int64_t* cap, int64_t want_elems) {
+  if (*cap >= want_elems && *ptr) return OB200_OK;
+  if (*ptr) {
+    OB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    OB_CUDA(ctx, cudaFree(*ptr));
+    *ptr = nullptr;
+    *cap = 0;
+  }
+  OB_CUDA(ctx, cudaMalloc((void**)ptr, (size_t)want_elems * sizeof(T)));
+  *cap = want_elems;
+  return OB200_OK;
+}
+
+static inline int64_t ob_round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
+
+// blob layout (all offsets in bytes, 256-aligned)
+struct ob200_blob_layout {
+  int64_t off_invls, off_xs, off_xx, off_alpha, off_linv, total;
+};
+static inline ob200_blob_layout ob_blob_layout(int n_pad, int D_pad) {
+  ob200_blob_layout l;
+  int64_t o = 256;  // header
+  l.off_invls = o; o += ob_round_up((int64_t)D_pad * 8, 256);
+  l.off_xs = o;    o += ob_round_up((int64_t)n_pad * D_pad * 8, 256);
+  l.off_xx = o;    o += ob_round_up((int64_t)n_pad * 8, 256);
+  l.off_alpha = o; o += ob_round_up((int64_t)n_pad * 8, 256);
+  l.off_linv = o;  o += (int64_t)n_pad * n_pad * 8;
+  l.total = o;
+  return l;
+}
+
+#ifdef __CUDACC__
+// ---- device helpers -----------------------------------------------------------------------
+// D(8x8) += A(8x4, row) * B(4x8, col), FP64 tensor core (SASS: DMMA.8x8x4).
+// lane l: a = A[l/4][l%4], b = B[l%4][l/4], c0/c1 = C[l/4][2*(l%4) + {0,1}]
+__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+               : "+d"(c0), "+d"(c1)
+               : "d"(a), "d"(b));
+}
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_LOOP:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra WAIT_DONE;\n"
+      "bra WAIT_LOOP;\n"
+      "WAIT_DONE:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+// 1-D bulk async copy global -> shared (TMA engine; SASS: UBLKCP), completion on an mbarrier.
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes,
+                                         uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+          smem_u32(dst_smem)),
+      "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
+// 1-D bulk async copy shared -> global (TMA engine), bulk-group completion.
+__device__ __forceinline__ void bulk_s2g(void* dst_gmem, const void* src_smem, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst_gmem),
+               "r"(smem_u32(src_smem)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read0() {
+  asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+__device__ __forceinline__ void bulk_wait_read1() {
+  asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+}
+__device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async;" ::: "memory"); }
+
+// ---- Philox4x32-10 (Salmon et al. 2011); restated bit-for-bit in oracle/philox.py -----------
+struct philox_out { uint32_t r0, r1, r2, r3; };
+__device__ __forceinline__ philox_out philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                                    uint32_t k0, uint32_t k1) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+    uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+    uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
+    c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+    k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+  }
+  return philox_out{c0, c1, c2, c3};
+}
+__device__ __forceinline__ double u53(uint32_t lo, uint32_t hi) {
+  uint64_t x = ((uint64_t)hi << 32) | lo;
+  return (double)(x >> 11) * 0x1.0p-53;
+}
+#endif  // __CUDACC__
+
+// internal cross-TU entry points
+int ob200_sample_launch(ob200_ctx* ctx, uint64_t seed, uint64_t first_index, int64_t count, int normalise,
+                        double* out_dev, int64_t ld, const double* variates_dev);

@@ -1,0 +1,593 @@
+// a14-a17: fused cross-kernel + posterior mean/variance + acquisition + argmax.
+//
+// Replaces, per candidate x (sklearn/gaussian_process/_gpr.py:444-500, kernels.py:1720-1729 /
+// :1569-1570, skopt.acquisition.gaussian_ei/pi/lcb, numpy.argmin):
+//     k*   = amplitude * m(|| (x - X_j)/ls ||)            j = 1..n
+//     mu   = y_std * (k* . alpha) + y_mean
+//     v    = inv(L) k*            (== solve_triangular(L, k*))
+//     var  = max(amplitude - sum v^2, 0) * y_std^2 ; sigma = sqrt(var)
+//     EI / PI / -LCB, first-occurrence argmax
+//
+// One persistent CTA per SM owns tiles of SC_BN = 64 candidates and runs three phases per tile:
+//   phase 1  cross-kernel: the pairwise term cand.X^T is a DMMA (FP64 tensor core) contraction over
+//            the D columns, with observed-point tiles (fragment-packed X/ls, ||X||^2, alpha) staged
+//            into shared memory by bulk async copies (TMA engine) through an mbarrier ring; the
+//            Matern/RBF nonlinearity and the k*.alpha mean are fused into its epilogue.  k* for the
+//            tile (n_pad x 64 doubles) is written once, already in DMMA B-fragment order, to the
+//            CTA's private scratch slice (L2-resident).
+//   phase 2  variance: V = inv(L) K*^T as a lower-triangular DMMA GEMM, 256 rows x 64 candidates
+//            per row block, inv(L) tiles (32 KB) and k* tiles (8 KB) streamed by a dedicated
+//            producer warp with cp.async.bulk into a 4-stage ring; row fragments above the
+//            diagonal / beyond n are skipped; the result is never stored, only sum v^2.
+//   phase 3  posterior + acquisition + running argmax in registers; per-CTA partials at the end.
+#include <math.h>
+
+#include "ob200_internal.cuh"
+
+namespace {
+
+struct best_t {
+  double value;
+  long long index;
+  double mu, sigma;
+};
+
+__device__ __forceinline__ bool better(double v, long long i, double bv, long long bi) {
+  return (v > bv) || (v == bv && i < bi);
+}
+
+struct score_args {
+  const double* cand; long long ldc; long long M; unsigned long long first_index;
+  const double* ls; const double* xs; const double* xx; const double* alpha; const double* linv;
+  int n, n_pad, D, D_pad, kind;
+  double amplitude, y_mean, y_std;
+  int acq_mask; double y_opt, xi, kappa;
+  double* kstar;
+  double *mu_out, *sigma_out, *acq_out;
+  best_t* partials;  // [grid][3]
+  long long n_tiles;
+  int accumulate;    // 1: fold the partials already stored (multi-chunk calls)
+};
+
+__device__ __forceinline__ double kernel_from_d2(int kind, double d2, double amplitude) {
+  if (kind == OB200_KERNEL_MATERN52) {
+    const double k = sqrt(d2) * 2.23606797749979;
+    return amplitude * ((1.0 + k + k * k / 3.0) * exp(-k));
+  }
+  return amplitude * exp(-0.5 * d2);
+}
+
+__device__ __forceinline__ void acquisition(double mu, double sigma, double y_opt, double xi, double kappa, double out[3]) {
+  double ei = 0.0, pi = 0.0;
+  if (sigma > 0.0) {
+    const double imp = y_opt - xi - mu;
+    const double z = imp / sigma;
+    const double cdf = 0.5 * erfc(-z * 0.7071067811865476);
+    const double pdf = exp(-0.5 * z * z) * 0.3989422804014327;
+    ei = imp * cdf + sigma * pdf;
+    pi = cdf;
+  }
+  out[OB200_ACQ_EI] = ei;
+  out[OB200_ACQ_PI] = pi;
+  out[OB200_ACQ_LCB] = -(mu - kappa * sigma);
+}
+
+__device__ __forceinline__ void consumer_bar() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+
+#define P1_STAGES 2
+#define P1_OBS 64
+
+__global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  const int D_pad = a.D_pad, nd4 = D_pad >> 2;
+  const int p1_stage_elems = P1_OBS * D_pad + 2 * P1_OBS;
+  double* un = reinterpret_cast<double*>(smem_raw);
+  // phase-1 view of the union
+  double* Cs = un;                                // [8 cf][nd4][32]
+  double* p1buf = un + SC_BN * D_pad;             // P1_STAGES x (Xs chunk | xx | alpha)
+  // phase-2 view
+  double* Abuf = un;                              // SC_STAGES x (SC_BM*SC_BK)
+  double* Bbuf = un + SC_STAGES * SC_BM * SC_BK;  // SC_STAGES x (SC_BK*SC_BN)
+  size_t un_elems = (size_t)SC_STAGES * (SC_BM * SC_BK + SC_BK * SC_BN);
+  {
+    const size_t p1 = (size_t)SC_BN * D_pad + (size_t)P1_STAGES * p1_stage_elems;
+    if (p1 > un_elems) un_elems = p1;
+  }
+  double* small = un + un_elems;
+  double* cc = small;                     // [64]
+  double* mured = cc + SC_BN;             // [8][64]
+  double* ssred = mured + 8 * SC_BN;      // [4][64]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(ssred + 4 * SC_BN);
+  uint64_t* full1 = bars;                 // [P1_STAGES]
+  uint64_t* empty1 = full1 + P1_STAGES;
+  uint64_t* full2 = empty1 + P1_STAGES;   // [SC_STAGES]
+  uint64_t* empty2 = full2 + SC_STAGES;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int g = lane >> 2, q = lane & 3;
+  const bool is_producer = (warp >= SC_CONSUMER_WARPS);   // warps 8..11; only warp 8 lane 0 issues copies
+  const bool is_issuer = (warp == SC_CONSUMER_WARPS) && (lane == 0);
+
+  if (tid == 0) {
+    for (int s = 0; s < P1_STAGES; ++s) { mbar_init(&full1[s], 1); mbar_init(&empty1[s], SC_CONSUMER_WARPS); }
+    for (int s = 0; s < SC_STAGES; ++s) { mbar_init(&full2[s], 1); mbar_init(&empty2[s], SC_CONSUMER_WARPS); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  double* kslice = a.kstar + (size_t)blockIdx.x * a.n_pad * SC_BN;
+  const int n_chunks1 = (a.n + P1_OBS - 1) / P1_OBS;          // observed-point chunks that hold real rows
+  const int n_rb = (a.n + SC_BM - 1) / SC_BM;                 // row blocks of inv(L) that hold real rows
+  const int k_lim = (int)(((long long)a.n + SC_BK - 1) / SC_BK);  // stages with real columns
+
+  // running ring positions (continue across tiles)
+  uint32_t it1 = 0, it2 = 0;
+
+  // running best per acquisition (threads 0..63)
+  best_t best[3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) { best[k].value = -INFINITY; best[k].index = 0x7fffffffffffffffLL; best[k].mu = 0.0; best[k].sigma = 0.0; }
+  if (a.accumulate && tid == 0) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) best[k] = a.partials[(size_t)blockIdx.x * 3 + k];
+  }
+
+  if (is_producer) {
+    // register rebalancing (3 warps per SM sub-partition: 2 consumers x 232 + 1 producer x 40 = 504);
+    // each role keeps its own tile loop so the register budget is decided by dominance.
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+    for (long long tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+      if (is_issuer) {
+        // ---- phase 1 producer: observed-point chunks
+        const uint32_t xs_bytes = (uint32_t)(P1_OBS * D_pad * 8);
+        for (int c = 0; c < n_chunks1; ++c, ++it1) {
+          const int s = it1 % P1_STAGES;
+          const uint32_t ph = (it1 / P1_STAGES) & 1;
+          mbar_wait(&empty1[s], ph ^ 1);
+          double* dst = p1buf + (size_t)s * p1_stage_elems;
+          mbar_expect_tx(&full1[s], xs_bytes + 2 * P1_OBS * 8);
+          bulk_g2s(dst, a.xs + (size_t)c * P1_OBS * D_pad, xs_bytes, &full1[s]);
+          bulk_g2s(dst + P1_OBS * D_pad, a.xx + (size_t)c * P1_OBS, P1_OBS * 8, &full1[s]);
+          bulk_g2s(dst + P1_OBS * D_pad + P1_OBS, a.alpha + (size_t)c * P1_OBS, P1_OBS * 8, &full1[s]);
+        }
+      }
+      __syncthreads();  // (A) consumers finished phase 1, k* slice written
+      if (is_issuer) {
+        // ---- phase 2 producer: inv(L) tiles + k* tiles
+        const int nJ = a.n_pad / SC_BK;
+        for (int I = 0; I < n_rb; ++I) {
+          int jend = (I + 1) * (SC_BM / SC_BK);
+          if (jend > k_lim) jend = k_lim;
+          for (int J = 0; J < jend; ++J, ++it2) {
+            const int s = it2 % SC_STAGES;
+            const uint32_t ph = (it2 / SC_STAGES) & 1;
+            mbar_wait(&empty2[s], ph ^ 1);
+            mbar_expect_tx(&full2[s], (SC_BM * SC_BK + SC_BK * SC_BN) * 8);
+            bulk_g2s(Abuf + (size_t)s * SC_BM * SC_BK, a.linv + ((size_t)I * nJ + J) * (SC_BM * SC_BK), SC_BM * SC_BK * 8, &full2[s]);
+            bulk_g2s(Bbuf + (size_t)s * SC_BK * SC_BN, kslice + (size_t)J * SC_BK * SC_BN, SC_BK * SC_BN * 8, &full2[s]);
+          }
+        }
+      }
+      __syncthreads();  // (B) end of tile
+    }
+    return;
+  }
+
+  // =============================== consumers (warps 0..7) ===============================
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+  for (long long tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+    const long long row0 = tile * SC_BN;
+    // ---- stage the candidate tile: Cs = cand / ls in A-fragment order, cc = ||Cs||^2
+    for (int e = tid; e < SC_BN * D_pad; e += SC_CONSUMER_WARPS * 32) {
+      const int r = e / D_pad, d = e - r * D_pad;
+      double v = 0.0;
+      if (d < a.D && row0 + r < a.M) v = a.cand[(size_t)(row0 + r) * a.ldc + d] / a.ls[d];
+      Cs[((size_t)(r >> 3) * nd4 + (d >> 2)) * 32 + (r & 7) * 4 + (d & 3)] = v;
+    }
+    consumer_bar();
+    if (tid < SC_BN) {
+      const int r = tid;
+      double acc = 0.0;
+      for (int d = 0; d < D_pad; ++d) {
+        const double v = Cs[((size_t)(r >> 3) * nd4 + (d >> 2)) * 32 + (r & 7) * 4 + (d & 3)];
+        acc = fma(v, v, acc);
+      }
+      cc[r] = acc;
+    }
+    consumer_bar();
+
+    // ---- phase 1: k* = kernel(cand, X) and mu partials
+    double ccr[8], mup[8];
+#pragma unroll
+    for (int cf = 0; cf < 8; ++cf) { ccr[cf] = cc[cf * 8 + g]; mup[cf] = 0.0; }
+    for (int c = 0; c < n_chunks1; ++c, ++it1) {
+      const int s = it1 % P1_STAGES;
+      const uint32_t ph = (it1 / P1_STAGES) & 1;
+      mbar_wait(&full1[s], ph);
+      const double* xs_s = p1buf + (size_t)s * p1_stage_elems + (size_t)warp * nd4 * 32;  // this warp's obs8 block
+      const double* xx_s = p1buf + (size_t)s * p1_stage_elems + P1_OBS * D_pad + warp * 8;
+      const double* al_s = xx_s + P1_OBS;
+      double acc[8][2];
+#pragma unroll
+      for (int cf = 0; cf < 8; ++cf) acc[cf][0] = acc[cf][1] = 0.0;
+      for (int d4 = 0; d4 < nd4; ++d4) {
+        const double b = xs_s[d4 * 32 + lane];
+#pragma unroll
+        for (int cf = 0; cf < 8; ++cf) dmma884(acc[cf][0], acc[cf][1], Cs[((size_t)cf * nd4 + d4) * 32 + lane], b);
+      }
+      const double xx0 = xx_s[2 * q], xx1 = xx_s[2 * q + 1];
+      const double al0 = al_s[2 * q], al1 = al_s[2 * q + 1];
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty1[s]);
+      const int ob = c * 8 + warp;  // global obs8 block
+      double2* dst = reinterpret_cast<double2*>(kslice + (size_t)ob * 8 * 64) + lane;
+#pragma unroll
+      for (int cf = 0; cf < 8; ++cf) {
+        const double d20 = fmax(ccr[cf] + xx0 - 2.0 * acc[cf][0], 0.0);
+        const double d21 = fmax(ccr[cf] + xx1 - 2.0 * acc[cf][1], 0.0);
+        double2 kv;
+        kv.x = kernel_from_d2(a.kind, d20, a.amplitude);
+        kv.y = kernel_from_d2(a.kind, d21, a.amplitude);
+        mup[cf] = fma(kv.x, al0, mup[cf]);
+        mup[cf] = fma(kv.y, al1, mup[cf]);
+        dst[cf * 32] = kv;
+      }
+    }
+    // mu: reduce over q (4 lanes) then across warps through shared memory
+#pragma unroll
+    for (int cf = 0; cf < 8; ++cf) {
+      double v = mup[cf];
+      v += __shfl_xor_sync(0xffffffffu, v, 1);
+      v += __shfl_xor_sync(0xffffffffu, v, 2);
+      if (q == 0) mured[warp * SC_BN + cf * 8 + g] = v;
+    }
+    fence_proxy_async();  // k* global writes (generic proxy) -> bulk reads (async proxy)
+    __syncthreads();      // (A)
+
+    // ---- phase 2: sum v^2 with v = inv(L) k*
+    const int wm = warp >> 1, wn = warp & 1;
+    double ss[4][2];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) ss[j][0] = ss[j][1] = 0.0;
+    for (int I = 0; I < n_rb; ++I) {
+      double acc[8][4][2];
+#pragma unroll
+      for (int t = 0; t < 8; ++t)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[t][j][0] = acc[t][j][1] = 0.0;
+      int jend = (I + 1) * (SC_BM / SC_BK);
+      if (jend > k_lim) jend = k_lim;
+      const int rbase = I * SC_BM + wm * 8;  // first row of fragment t is rbase + 32 t
+      for (int J = 0; J < jend; ++J, ++it2) {
+        const int s = it2 % SC_STAGES;
+        const uint32_t ph = (it2 / SC_STAGES) & 1;
+        mbar_wait(&full2[s], ph);
+        const double2* As = reinterpret_cast<const double2*>(Abuf + (size_t)s * SC_BM * SC_BK) + (size_t)wm * 8 * (SC_BK / 8) * 32 + lane;
+        const double2* Bs = reinterpret_cast<const double2*>(Bbuf + (size_t)s * SC_BK * SC_BN) + (size_t)wn * 4 * 32 + lane;
+#pragma unroll
+        for (int k8 = 0; k8 < SC_BK / 8; ++k8) {
+          const int k0 = J * SC_BK + k8 * 8;
+          double2 b[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) b[j] = Bs[(k8 * 8 + j) * 32];
+#pragma unroll
+          for (int t = 0; t < 8; ++t) {
+            const int r0 = rbase + 32 * t;
+            if (r0 < a.n && r0 + 7 >= k0) {
+              const double2 av = As[(t * (SC_BK / 8) + k8) * 32];
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                dmma884(acc[t][j][0], acc[t][j][1], av.x, b[j].x);
+                dmma884(acc[t][j][0], acc[t][j][1], av.y, b[j].y);
+              }
+            }
+          }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty2[s]);
+      }
+#pragma unroll
+      for (int t = 0; t < 8; ++t)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          ss[j][0] = fma(acc[t][j][0], acc[t][j][0], ss[j][0]);
+          ss[j][1] = fma(acc[t][j][1], acc[t][j][1], ss[j][1]);
+        }
+    }
+    // reduce over the 8 row lanes (g), then across the 4 row warps via shared memory
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        double v = ss[j][e];
+        v += __shfl_xor_sync(0xffffffffu, v, 4);
+        v += __shfl_xor_sync(0xffffffffu, v, 8);
+        v += __shfl_xor_sync(0xffffffffu, v, 16);
+        if (g == 0) ssred[wm * SC_BN + wn * 32 + j * 8 + 2 * q + e] = v;
+      }
+    consumer_bar();
+
+    // ---- phase 3: posterior, acquisition, running argmax (one thread per candidate)
+    if (tid < SC_BN && row0 + tid < a.M) {
+      double s2 = ((ssred[tid] + ssred[SC_BN + tid]) + ssred[2 * SC_BN + tid]) + ssred[3 * SC_BN + tid];
+      double m = 0.0;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) m += mured[w * SC_BN + tid];
+      const double mu = a.y_std * m + a.y_mean;
+      double var = a.amplitude - s2;
+      if (var < 0.0) var = 0.0;
+      var = var * (a.y_std * a.y_std);
+      const double sigma = sqrt(var);
+      double acq[3];
+      acquisition(mu, sigma, a.y_opt, a.xi, a.kappa, acq);
+      const long long row = row0 + tid;
+      if (a.mu_out) a.mu_out[row] = mu;
+      if (a.sigma_out) a.sigma_out[row] = sigma;
+      const long long gidx = (long long)a.first_index + row;
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        if (!(a.acq_mask & (1 << k))) continue;
+        if (a.acq_out) a.acq_out[(size_t)k * a.M + row] = acq[k];
+        if (better(acq[k], gidx, best[k].value, best[k].index)) { best[k].value = acq[k]; best[k].index = gidx; best[k].mu = mu; best[k].sigma = sigma; }
+      }
+    }
+    fence_proxy_async();
+    __syncthreads();  // (B) end of tile: smem union and the k* slice may be reused
+  }
+
+  // ---- per-CTA winner: warp-shuffle argmax over threads 0..63, then two warps through smem
+  if (warp < 2) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      double v = best[k].value, m = best[k].mu, sg = best[k].sigma;
+      long long i = best[k].index;
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1) {
+        const double ov = __shfl_xor_sync(0xffffffffu, v, off);
+        const long long oi = __shfl_xor_sync(0xffffffffu, i, off);
+        const double om = __shfl_xor_sync(0xffffffffu, m, off);
+        const double os = __shfl_xor_sync(0xffffffffu, sg, off);
+        if (better(ov, oi, v, i)) { v = ov; i = oi; m = om; sg = os; }
+      }
+      if (lane == 0) {
+        double* slot = mured + (warp * 3 + k) * 4;
+        slot[0] = v; slot[1] = __longlong_as_double(i); slot[2] = m; slot[3] = sg;
+      }
+    }
+  }
+  consumer_bar();
+  if (tid < 3) {
+    const double* s0 = mured + (0 * 3 + tid) * 4;
+    const double* s1 = mured + (1 * 3 + tid) * 4;
+    best_t b;
+    b.value = s0[0]; b.index = __double_as_longlong(s0[1]); b.mu = s0[2]; b.sigma = s0[3];
+    const double v1 = s1[0];
+    const long long i1 = __double_as_longlong(s1[1]);
+    if (better(v1, i1, b.value, b.index)) { b.value = v1; b.index = i1; b.mu = s1[2]; b.sigma = s1[3]; }
+    a.partials[(size_t)blockIdx.x * 3 + tid] = b;
+  }
+}
+
+// final reduction of per-CTA partials -> best[3]
+__global__ void __launch_bounds__(256) reduce_best_kernel(const best_t* __restrict__ partials, int n_part, int acq_mask,
+                                                          ob200_best* __restrict__ out) {
+  __shared__ best_t sm[256];
+  for (int k = 0; k < 3; ++k) {
+    best_t b;
+    b.value = -INFINITY; b.index = 0x7fffffffffffffffLL; b.mu = 0.0; b.sigma = 0.0;
+    for (int p = threadIdx.x; p < n_part; p += 256) {
+      const best_t o = partials[(size_t)p * 3 + k];
+      if (better(o.value, o.index, b.value, b.index)) b = o;
+    }
+    sm[threadIdx.x] = b;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+      if (threadIdx.x < s) {
+        const best_t o = sm[threadIdx.x + s];
+        if (better(o.value, o.index, sm[threadIdx.x].value, sm[threadIdx.x].index)) sm[threadIdx.x] = o;
+      }
+      __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+      ob200_best r;
+      const bool on = (acq_mask >> k) & 1;
+      r.value = on ? sm[0].value : 0.0;
+      r.index = on ? sm[0].index : -1;
+      r.mu = on ? sm[0].mu : 0.0;
+      r.sigma = on ? sm[0].sigma : 0.0;
+      out[k] = r;
+    }
+    __syncthreads();
+  }
+}
+
+// a16-a17 alone: acquisition + argmax over given mu/sigma; per-CTA partials in scratch
+__global__ void __launch_bounds__(256) acq_partial_kernel(const double* __restrict__ mu, const double* __restrict__ sigma, long long M,
+                                                          unsigned long long first_index, int acq_mask, double y_opt, double xi,
+                                                          double kappa, double* __restrict__ acq_out, best_t* __restrict__ partials) {
+  __shared__ best_t sm[256];
+  best_t best[3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) { best[k].value = -INFINITY; best[k].index = 0x7fffffffffffffffLL; best[k].mu = 0.0; best[k].sigma = 0.0; }
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < M; i += (long long)gridDim.x * blockDim.x) {
+    const double m = mu[i], s = sigma[i];
+    double acq[3];
+    acquisition(m, s, y_opt, xi, kappa, acq);
+    const long long gi = (long long)first_index + i;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      if (!(acq_mask & (1 << k))) continue;
+      if (acq_out) acq_out[(size_t)k * M + i] = acq[k];
+      if (better(acq[k], gi, best[k].value, best[k].index)) { best[k].value = acq[k]; best[k].index = gi; best[k].mu = m; best[k].sigma = s; }
+    }
+  }
+  for (int k = 0; k < 3; ++k) {
+    sm[threadIdx.x] = best[k];
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+      if (threadIdx.x < s) {
+        const best_t o = sm[threadIdx.x + s];
+        if (better(o.value, o.index, sm[threadIdx.x].value, sm[threadIdx.x].index)) sm[threadIdx.x] = o;
+      }
+      __syncthreads();
+    }
+    if (threadIdx.x == 0) partials[(size_t)blockIdx.x * 3 + k] = sm[0];
+    __syncthreads();
+  }
+}
+
+size_t score_smem_bytes(int D_pad) {
+  size_t un = (size_t)SC_STAGES * (SC_BM * SC_BK + SC_BK * SC_BN);
+  const size_t p1 = (size_t)SC_BN * D_pad + (size_t)P1_STAGES * (P1_OBS * D_pad + 2 * P1_OBS);
+  if (p1 > un) un = p1;
+  return (un + SC_BN + 8 * SC_BN + 4 * SC_BN) * sizeof(double) + (2 * P1_STAGES + 2 * SC_STAGES) * sizeof(uint64_t) + 128;
+}
+
+int score_launch(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M, uint64_t first_index, int acq_mask,
+                 double y_opt, double xi, double kappa, double* mu_dev, double* sigma_dev, double* acq_dev, int accumulate,
+                 int* grid_out) {
+  const ob200_fit_header& h = ctx->hdr;
+  const ob200_blob_layout lay = ob_blob_layout(h.n_pad, h.D_pad);
+  const size_t smem = score_smem_bytes(h.D_pad);
+  if (smem > 227 * 1024) OB_FAIL(ctx, OB200_EINVAL, "D=%d too wide for the score kernel's shared-memory tile (max 128)", h.D);
+  const int64_t n_tiles = (M + SC_BN - 1) / SC_BN;
+  const int grid = (int)(n_tiles < ctx->num_sms ? n_tiles : ctx->num_sms);
+  int rc;
+  if ((rc = ob_reserve(ctx, &ctx->kstar_dev, &ctx->kstar_cap, (int64_t)ctx->num_sms * h.n_pad * SC_BN))) return rc;
+  if ((rc = ob_reserve(ctx, &ctx->partial_dev, &ctx->partial_cap, (int64_t)4096 * 3 * (int64_t)sizeof(best_t)))) return rc;
+  score_args a{};
+  a.cand = cand_dev; a.ldc = ldc; a.M = M; a.first_index = first_index;
+  a.ls = reinterpret_cast<const double*>(ctx->blob + lay.off_invls);
+  a.xs = reinterpret_cast<const double*>(ctx->blob + lay.off_xs);
+  a.xx = reinterpret_cast<const double*>(ctx->blob + lay.off_xx);
+  a.alpha = reinterpret_cast<const double*>(ctx->blob + lay.off_alpha);
+  a.linv = reinterpret_cast<const double*>(ctx->blob + lay.off_linv);
+  a.n = h.n; a.n_pad = h.n_pad; a.D = h.D; a.D_pad = h.D_pad; a.kind = h.kernel_kind;
+  a.amplitude = h.amplitude; a.y_mean = h.y_mean; a.y_std = h.y_std;
+  a.acq_mask = acq_mask; a.y_opt = y_opt; a.xi = xi; a.kappa = kappa;
+  a.kstar = ctx->kstar_dev;
+  a.mu_out = mu_dev; a.sigma_out = sigma_dev; a.acq_out = acq_dev;
+  a.partials = reinterpret_cast<best_t*>(ctx->partial_dev);
+  a.n_tiles = n_tiles;
+  a.accumulate = accumulate;
+  OB_CUDA(ctx, cudaFuncSetAttribute(score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  score_kernel<<<grid, SC_THREADS, smem, ctx->stream>>>(a);
+  OB_LAUNCH_CHECK(ctx);
+  *grid_out = grid;
+  return OB200_OK;
+}
+
+int check_score_args(ob200_ctx* ctx, int64_t M, int acq_mask, const void* best) {
+  if (!ctx->fitted) OB_FAIL(ctx, OB200_ESTATE, "ob200_score called before ob200_gp_fit / ob200_gp_import");
+  if (M < 1) OB_FAIL(ctx, OB200_EINVAL, "M must be >= 1");
+  if ((acq_mask & 7) == 0 || (acq_mask & ~7)) OB_FAIL(ctx, OB200_EINVAL, "acq_mask must select EI(1), PI(2) and/or LCB(4)");
+  if (!best) OB_FAIL(ctx, OB200_EINVAL, "best is null");
+  return OB200_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int ob200_score_async(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M, uint64_t seed, uint64_t first_index,
+                      int acq_mask, double y_opt, double xi, double kappa, ob200_best* best_dev, double* mu_dev,
+                      double* sigma_dev, double* acq_dev) {
+  if (!ctx) return OB200_EINVAL;
+  int rc = check_score_args(ctx, M, acq_mask, best_dev);
+  if (rc) return rc;
+  OB_CUDA(ctx, cudaSetDevice(ctx->device));
+  const int D = ctx->hdr.D;
+  int grid = 0;
+  if (cand_dev) {
+    if (ldc < D) OB_FAIL(ctx, OB200_EINVAL, "ldc=%lld < D=%d", (long long)ldc, D);
+    if ((rc = score_launch(ctx, cand_dev, ldc, M, first_index, acq_mask, y_opt, xi, kappa, mu_dev, sigma_dev, acq_dev, 0, &grid))) return rc;
+  } else {
+    // candidates from the registered space: generate (normalised) in chunks, fold the argmax
+    if (ctx->n_slots <= 0) OB_FAIL(ctx, OB200_ESTATE, "cand_dev is NULL and no space was set");
+    if (ctx->d_out != D) OB_FAIL(ctx, OB200_EINVAL, "space width %d != fitted D %d", ctx->d_out, D);
+    const int64_t chunk_rows = ((int64_t)1 << 31) / ((int64_t)D * 8) / SC_BN * SC_BN;  // <= 2 GiB of candidates at a time
+    if (acq_dev && M > chunk_rows) OB_FAIL(ctx, OB200_EINVAL, "dense acquisition output needs M <= %lld when candidates are generated", (long long)chunk_rows);
+    const int64_t rows_cap = M < chunk_rows ? M : chunk_rows;
+    if ((rc = ob_reserve(ctx, &ctx->cand_tmp, &ctx->cand_cap, rows_cap * D))) return rc;
+    int grid_max = 0;
+    for (int64_t r0 = 0; r0 < M; r0 += chunk_rows) {
+      const int64_t rows = (M - r0 < chunk_rows) ? M - r0 : chunk_rows;
+      if ((rc = ob200_sample_launch(ctx, seed, first_index + (uint64_t)r0, rows, 1, ctx->cand_tmp, D, nullptr))) return rc;
+      // every chunk but the last is full-size, so the first launch has the widest grid and
+      // initialises every partial the final reduction reads; later launches fold into their own.
+      if ((rc = score_launch(ctx, ctx->cand_tmp, D, rows, first_index + (uint64_t)r0, acq_mask, y_opt, xi, kappa,
+                             mu_dev ? mu_dev + r0 : nullptr, sigma_dev ? sigma_dev + r0 : nullptr, acq_dev, r0 == 0 ? 0 : 1, &grid)))
+        return rc;
+      if (grid > grid_max) grid_max = grid;
+    }
+    grid = grid_max;
+  }
+  reduce_best_kernel<<<1, 256, 0, ctx->stream>>>(reinterpret_cast<const best_t*>(ctx->partial_dev), grid, acq_mask, best_dev);
+  OB_LAUNCH_CHECK(ctx);
+  return OB200_OK;
+}
+
+int ob200_score(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M, uint64_t seed, uint64_t first_index,
+                int acq_mask, double y_opt, double xi, double kappa, ob200_best* best_host, double* mu_dev,
+                double* sigma_dev, double* acq_dev) {
+  if (!ctx) return OB200_EINVAL;
+  if (!best_host) OB_FAIL(ctx, OB200_EINVAL, "best_host is null");
+  int rc = ob200_score_async(ctx, cand_dev, ldc, M, seed, first_index, acq_mask, y_opt, xi, kappa, ctx->best_dev, mu_dev,
+                             sigma_dev, acq_dev);
+  if (rc) return rc;
+  OB_CUDA(ctx, cudaMemcpyAsync(ctx->best_pinned, ctx->best_dev, 3 * sizeof(ob200_best), cudaMemcpyDeviceToHost, ctx->stream));
+  OB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  memcpy(best_host, ctx->best_pinned, 3 * sizeof(ob200_best));
+  if (!cand_dev) return ob200_sample_status(ctx);
+  return OB200_OK;
+}
+
+int ob200_score_host(ob200_ctx* ctx, const double* cand_host, int64_t ldc, int64_t M, int acq_mask, double y_opt, double xi,
+                     double kappa, ob200_best* best_host, double* mu_host, double* sigma_host, double* acq_host) {
+  if (!ctx) return OB200_EINVAL;
+  if (!cand_host) OB_FAIL(ctx, OB200_EINVAL, "cand_host is null");
+  int rc = check_score_args(ctx, M, acq_mask, best_host);
+  if (rc) return rc;
+  const int D = ctx->hdr.D;
+  if (ldc < D) OB_FAIL(ctx, OB200_EINVAL, "ldc=%lld < D=%d", (long long)ldc, D);
+  OB_CUDA(ctx, cudaSetDevice(ctx->device));
+  if ((rc = ob_reserve(ctx, &ctx->cand_tmp, &ctx->cand_cap, M * D))) return rc;
+  const int64_t dense = (mu_host ? M : 0) + (sigma_host ? M : 0) + (acq_host ? 3 * M : 0);
+  if (dense && (rc = ob_reserve(ctx, &ctx->dense_tmp, &ctx->dense_cap, dense))) return rc;
+  double* p = ctx->dense_tmp;
+  double* mu_dev = mu_host ? p : nullptr; if (mu_host) p += M;
+  double* sg_dev = sigma_host ? p : nullptr; if (sigma_host) p += M;
+  double* aq_dev = acq_host ? p : nullptr;
+  OB_CUDA(ctx, cudaMemcpy2DAsync(ctx->cand_tmp, (size_t)D * 8, cand_host, (size_t)ldc * 8, (size_t)D * 8, (size_t)M,
+                                 cudaMemcpyHostToDevice, ctx->stream));
+  if ((rc = ob200_score_async(ctx, ctx->cand_tmp, D, M, 0, 0, acq_mask, y_opt, xi, kappa, ctx->best_dev, mu_dev, sg_dev, aq_dev))) return rc;
+  OB_CUDA(ctx, cudaMemcpyAsync(ctx->best_pinned, ctx->best_dev, 3 * sizeof(ob200_best), cudaMemcpyDeviceToHost, ctx->stream));
+  if (mu_host) OB_CUDA(ctx, cudaMemcpyAsync(mu_host, mu_dev, (size_t)M * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  if (sigma_host) OB_CUDA(ctx, cudaMemcpyAsync(sigma_host, sg_dev, (size_t)M * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  if (acq_host) OB_CUDA(ctx, cudaMemcpyAsync(acq_host, aq_dev, (size_t)3 * M * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  OB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  memcpy(best_host, ctx->best_pinned, 3 * sizeof(ob200_best));
+  return OB200_OK;
+}
+
+int ob200_acq_argmax(ob200_ctx* ctx, const double* mu_dev, const double* sigma_dev, int64_t M, uint64_t first_index,
+                     int acq_mask, double y_opt, double xi, double kappa, ob200_best* best_host, double* acq_dev) {
+  if (!ctx) return OB200_EINVAL;
+  if (!mu_dev || !sigma_dev || !best_host || M < 1) OB_FAIL(ctx, OB200_EINVAL, "bad mu/sigma/best/M");
+  if ((acq_mask & 7) == 0 || (acq_mask & ~7)) OB_FAIL(ctx, OB200_EINVAL, "acq_mask must select EI(1), PI(2) and/or LCB(4)");
+  OB_CUDA(ctx, cudaSetDevice(ctx->device));
+  int rc;
+  if ((rc = ob_reserve(ctx, &ctx->partial_dev, &ctx->partial_cap, (int64_t)4096 * 3 * (int64_t)sizeof(best_t)))) return rc;
+  int64_t blocks = (M + 255) / 256;
+  const int grid = (int)(blocks < (int64_t)ctx->num_sms * 8 ? blocks : (int64_t)ctx->num_sms * 8);
+  acq_partial_kernel<<<grid, 256, 0, ctx->stream>>>(mu_dev, sigma_dev, M, first_index, acq_mask, y_opt, xi, kappa, acq_dev,
+                                                    reinterpret_cast<best_t*>(ctx->partial_dev));
+  OB_LAUNCH_CHECK(ctx);
+  reduce_best_kernel<<<1, 256, 0, ctx->stream>>>(reinterpret_cast<const best_t*>(ctx->partial_dev), grid, acq_mask, ctx->best_dev);
+  OB_LAUNCH_CHECK(ctx);
+  OB_CUDA(ctx, cudaMemcpyAsync(ctx->best_pinned, ctx->best_dev, 3 * sizeof(ob200_best), cudaMemcpyDeviceToHost, ctx->stream));
+  OB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  memcpy(best_host, ctx->best_pinned, 3 * sizeof(ob200_best));
+  return OB200_OK;
+}
+
+}  // extern "C"

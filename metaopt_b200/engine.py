@@ -1,0 +1,226 @@
+"""Device engine: thin Python wrapper over the C ABI (include/ob200.h) using torch tensors for
+device memory and streams.  One engine per CUDA device, cached at module level (the algorithm
+object is deep-copied by Orion on every update, `src/orion/core/worker/producer.py:161`, so no
+device handle may live inside it)."""
+import atexit
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import Best, Kernel, Slot
+
+_ENGINES = {}
+
+
+def get_engine(device=None):
+    """Process-wide engine for a CUDA device index (default: torch's current device)."""
+    if not torch.cuda.is_available():
+        raise RuntimeError("metaopt_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
+    if device is None:
+        device = torch.cuda.current_device()
+    device = int(device)
+    if device not in _ENGINES:
+        _ENGINES[device] = Engine(device)
+    return _ENGINES[device]
+
+
+@atexit.register
+def _shutdown():
+    for eng in list(_ENGINES.values()):
+        eng.close()
+    _ENGINES.clear()
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else None
+
+
+class Engine:
+    def __init__(self, device):
+        self.lib = _lib.load()
+        self.device = int(device)
+        self.tdev = torch.device("cuda", self.device)
+        ctx = C.c_void_p()
+        rc = self.lib.ob200_ctx_create(self.device, C.byref(ctx))
+        if rc != 0:
+            raise _lib.Ob200Error(rc, "ob200_ctx_create(device=%d) failed (needs an sm_100a GPU)" % self.device)
+        self.ctx = ctx
+        self.d_out = 0
+        self.n_slots = 0
+        self.n = self.D = 0
+        self.use_torch_stream()
+
+    def close(self):
+        if self.ctx is not None:
+            self.lib.ob200_ctx_destroy(self.ctx)
+            self.ctx = None
+
+    def _check(self, rc):
+        _lib.check(self.ctx, rc)
+
+    def use_torch_stream(self):
+        """Enqueue on torch's current stream of this device, so torch ops and ours are ordered."""
+        s = torch.cuda.current_stream(self.tdev).cuda_stream
+        self._check(self.lib.ob200_set_stream(self.ctx, C.c_void_p(s)))
+
+    def sync(self):
+        self._check(self.lib.ob200_sync(self.ctx))
+
+    @property
+    def launches(self):
+        return int(self.lib.ob200_launch_count(self.ctx))
+
+    # ---- space ---------------------------------------------------------------------------
+    def set_space(self, slots, cdf):
+        """slots: list of dicts with the fields of `ob200_slot`; cdf: flat list of floats."""
+        arr = (Slot * len(slots))()
+        for i, s in enumerate(slots):
+            for k, _ in Slot._fields_:
+                setattr(arr[i], k, s[k])
+        cdf_arr = (C.c_double * max(len(cdf), 1))(*cdf)
+        self._check(self.lib.ob200_space_set(self.ctx, arr, len(slots), cdf_arr, len(cdf)))
+        self.n_slots = len(slots)
+        self.d_out = max(s["out_col"] + s["width"] for s in slots)
+
+    def sample(self, seed, first_index, count, normalise=True, variates=None, out=None, check=True):
+        """[count x D_out] float64 device tensor of sampled+transformed(+normalised) points."""
+        self.use_torch_stream()
+        if out is None:
+            out = torch.empty((count, self.d_out), dtype=torch.float64, device=self.tdev)
+        assert out.dtype == torch.float64 and out.is_cuda and out.stride(1) == 1
+        var = None
+        if variates is not None:
+            var = torch.as_tensor(variates, dtype=torch.float64).to(self.tdev).contiguous()
+            assert var.shape == (count, self.n_slots)
+        self._check(self.lib.ob200_sample_transform(self.ctx, seed, first_index, count, int(bool(normalise)),
+                                                    _ptr(out), out.stride(0), _ptr(var)))
+        if check:
+            self._check(self.lib.ob200_sample_status(self.ctx))
+        return out
+
+    def sample_host(self, seed, first_index, count, normalise=True, variates=None):
+        out = np.empty((count, self.d_out), dtype=np.float64)
+        var = None
+        if variates is not None:
+            var = np.ascontiguousarray(variates, dtype=np.float64)
+            assert var.shape == (count, self.n_slots)
+        self._check(self.lib.ob200_sample_transform_host(
+            self.ctx, seed, first_index, count, int(bool(normalise)), out.ctypes.data_as(C.c_void_p), self.d_out,
+            var.ctypes.data_as(C.c_void_p) if var is not None else None))
+        self._check(self.lib.ob200_sample_status(self.ctx))
+        return out
+
+    # ---- fit -------------------------------------------------------------------------------
+    def fit(self, X, y, kind=_lib.KERNEL_MATERN52, amplitude=1.0, length_scale=1.0, alpha=1e-10, normalize_y=False):
+        self.use_torch_stream()
+        ls = np.atleast_1d(np.asarray(length_scale, dtype=np.float64)).copy()
+        k = Kernel(kind, len(ls), float(amplitude), ls.ctypes.data_as(C.POINTER(C.c_double)))
+        if isinstance(X, torch.Tensor):
+            X = X.to(self.tdev, torch.float64).contiguous()
+            y = torch.as_tensor(y).to(self.tdev, torch.float64).contiguous()
+            n, D = X.shape
+            rc = self.lib.ob200_gp_fit(self.ctx, _ptr(X), _ptr(y), n, D, C.byref(k), float(alpha), int(bool(normalize_y)))
+        else:
+            X = np.ascontiguousarray(X, dtype=np.float64)
+            y = np.ascontiguousarray(y, dtype=np.float64)
+            n, D = X.shape
+            rc = self.lib.ob200_gp_fit_host(self.ctx, X.ctypes.data_as(C.c_void_p), y.ctypes.data_as(C.c_void_p), n, D,
+                                            C.byref(k), float(alpha), int(bool(normalize_y)))
+        self._check(rc)
+        self.n, self.D = n, D
+
+    def ystats(self):
+        a, b, c = C.c_double(), C.c_double(), C.c_double()
+        self._check(self.lib.ob200_gp_get_ystats(self.ctx, C.byref(a), C.byref(b), C.byref(c)))
+        return a.value, b.value, c.value
+
+    def lml(self):
+        v = C.c_double()
+        self._check(self.lib.ob200_gp_lml(self.ctx, C.byref(v)))
+        return v.value
+
+    def get_factor(self):
+        L = np.empty((self.n, self.n), dtype=np.float64)
+        al = np.empty(self.n, dtype=np.float64)
+        self._check(self.lib.ob200_gp_get_factor(self.ctx, L.ctypes.data_as(C.c_void_p), al.ctypes.data_as(C.c_void_p)))
+        return L, al
+
+    def export_state(self):
+        """Opaque fit state as a uint8 device tensor (to be broadcast to the other ranks)."""
+        self.use_torch_stream()
+        nbytes = C.c_int64()
+        self._check(self.lib.ob200_gp_state_bytes(self.ctx, self.n, self.D, C.byref(nbytes)))
+        blob = torch.empty(nbytes.value, dtype=torch.uint8, device=self.tdev)
+        self._check(self.lib.ob200_gp_export(self.ctx, _ptr(blob), nbytes.value))
+        return blob
+
+    def state_bytes(self, n, D):
+        nbytes = C.c_int64()
+        self._check(self.lib.ob200_gp_state_bytes(self.ctx, n, D, C.byref(nbytes)))
+        return nbytes.value
+
+    def import_state(self, blob, n, D):
+        self.use_torch_stream()
+        assert blob.dtype == torch.uint8 and blob.is_cuda and blob.is_contiguous()
+        self._check(self.lib.ob200_gp_import(self.ctx, _ptr(blob), blob.numel()))
+        self.n, self.D = n, D
+
+    # ---- score -----------------------------------------------------------------------------
+    @staticmethod
+    def _bests(arr, mask):
+        names = {0: "EI", 1: "PI", 2: "LCB"}
+        return {names[k]: dict(value=arr[k].value, index=int(arr[k].index), mu=arr[k].mu, sigma=arr[k].sigma)
+                for k in range(3) if mask & (1 << k)}
+
+    def score(self, cand=None, M=None, seed=0, first_index=0, acq_mask=1, y_opt=0.0, xi=0.01, kappa=1.96, dense=False):
+        """Score candidates on the device.  cand: [M x >=D] float64 CUDA tensor (normalised), or None
+        to generate candidate i from (seed, first_index+i) with the registered space."""
+        self.use_torch_stream()
+        ldc = 0
+        if cand is not None:
+            assert cand.dtype == torch.float64 and cand.is_cuda and cand.stride(1) == 1
+            M, ldc = cand.shape[0], cand.stride(0)
+        mu = sg = aq = None
+        if dense:
+            mu = torch.empty(M, dtype=torch.float64, device=self.tdev)
+            sg = torch.empty(M, dtype=torch.float64, device=self.tdev)
+            aq = torch.zeros((3, M), dtype=torch.float64, device=self.tdev)
+        best = (Best * 3)()
+        self._check(self.lib.ob200_score(self.ctx, _ptr(cand), ldc, M, seed, first_index, acq_mask, y_opt, xi, kappa,
+                                         best, _ptr(mu), _ptr(sg), _ptr(aq)))
+        res = self._bests(best, acq_mask)
+        if dense:
+            res.update(mu=mu, sigma=sg, acq=aq)
+        return res
+
+    def score_host(self, cand, acq_mask=1, y_opt=0.0, xi=0.01, kappa=1.96, dense=False):
+        """Same through host buffers (numpy in, numpy out): H2D/D2H copies happen inside the call."""
+        self.use_torch_stream()
+        cand = np.asarray(cand, dtype=np.float64)
+        assert cand.ndim == 2 and cand.strides[1] == 8
+        M, ldc = cand.shape[0], cand.strides[0] // 8
+        mu = sg = aq = None
+        if dense:
+            mu, sg, aq = np.empty(M), np.empty(M), np.zeros((3, M))
+        best = (Best * 3)()
+        vp = lambda x: x.ctypes.data_as(C.c_void_p) if x is not None else None
+        self._check(self.lib.ob200_score_host(self.ctx, vp(cand), ldc, M, acq_mask, y_opt, xi, kappa, best,
+                                              vp(mu), vp(sg), vp(aq)))
+        res = self._bests(best, acq_mask)
+        if dense:
+            res.update(mu=mu, sigma=sg, acq=aq)
+        return res
+
+    def acq_argmax(self, mu, sigma, first_index=0, acq_mask=1, y_opt=0.0, xi=0.01, kappa=1.96, dense=False):
+        self.use_torch_stream()
+        M = mu.numel()
+        aq = torch.zeros((3, M), dtype=torch.float64, device=self.tdev) if dense else None
+        best = (Best * 3)()
+        self._check(self.lib.ob200_acq_argmax(self.ctx, _ptr(mu), _ptr(sigma), M, first_index, acq_mask, y_opt, xi, kappa,
+                                              best, _ptr(aq)))
+        res = self._bests(best, acq_mask)
+        if dense:
+            res["acq"] = aq
+        return res
