@@ -1,0 +1,272 @@
+"""`BayesianOptimizer`: the B200 plugin behind Orion's unchanged algorithm API.
+
+Drop-in for the reference's documented skopt wrapper (`orion.algo.skopt.BayesianOptimizer`,
+`/root/reference/docs/src/user/algorithms.rst:136-217`): same class name (so the same
+`algorithms: {BayesianOptimizer: {...}}` config key, matched case-insensitively by
+`orion.core.utils.Factory`, `src/orion/core/utils/__init__.py:151-153`), same config keys and
+defaults (`seed, n_initial_points, acq_func, alpha, n_restarts_optimizer, noise, normalize_y`;
+also pinned by `tests/unittests/core/cli/test_info.py:89-98`), `requires = 'real'`.
+
+Contract with Orion:
+  * `BaseAlgorithm.__init__(space, **kwargs)` (`src/orion/algo/base.py:87-119`) turns every kwarg
+    into an attribute and into `configuration`; a `seed` kwarg calls `seed_rng`.
+  * the object is constructed several times at start-up and `copy.deepcopy`'d on every producer
+    update (`src/orion/core/worker/producer.py:161`): no CUDA work in `__init__`, no device handle
+    in `__dict__` -- the engine lives in `metaopt_b200.engine._ENGINES`.
+  * `suggest(num)` returns points of the transformed ('real') space; Orion then checks
+    `point in transformed_space` and reverses it (`src/orion/core/worker/primary_algo.py:61-81`).
+  * `observe(points, results)` may deliver the whole history at once (`producer.py:107-132`) or one
+    point; results are dicts with an `objective` key (`core/utils/format_trials.py:53-72`).
+  * `state_dict` / `set_state` carry the Philox stream position (`producer.py:84`).
+
+When Orion is importable the class derives from `orion.algo.base.BaseAlgorithm`; otherwise from a
+minimal mirror with the same behaviour, so the GPU box (no Orion install) runs the same code.
+"""
+import copy
+import hashlib
+
+import numpy as np
+
+from . import _lib, compiler
+
+try:  # the real thing, when the plugin runs under Orion
+    from orion.algo.base import BaseAlgorithm  # pylint: disable=import-error
+    HAVE_ORION = True
+except Exception:  # pragma: no cover - exercised on the GPU box
+    HAVE_ORION = False
+
+    class BaseAlgorithm:
+        """Mirror of `orion.algo.base.BaseAlgorithm` (`base.py:21-270`) for Orion-less hosts."""
+
+        requires = []
+
+        def __init__(self, space, **kwargs):
+            self._space = space
+            self._param_names = list(kwargs.keys())
+            for name, value in kwargs.items():
+                if name == "seed":
+                    self.seed_rng(value)
+                setattr(self, name, value)
+
+        def seed_rng(self, seed):
+            pass
+
+        @property
+        def state_dict(self):
+            return {}
+
+        def set_state(self, state_dict):
+            pass
+
+        @property
+        def is_done(self):
+            return False
+
+        def score(self, point):
+            return 0
+
+        def judge(self, point, measurements):
+            return None
+
+        @property
+        def should_suspend(self):
+            return False
+
+        @property
+        def configuration(self):
+            conf = {k: getattr(self, k) for k in self._param_names if not k.startswith("_")}
+            return {self.__class__.__name__.lower(): conf}
+
+        @property
+        def space(self):
+            return self._space
+
+        @space.setter
+        def space(self, space_):
+            self._space = space_
+
+
+_ACQ = {"EI": _lib.ACQ_EI, "PI": _lib.ACQ_PI, "LCB": _lib.ACQ_LCB}
+_KERNELS = {"matern52": _lib.KERNEL_MATERN52, "matern": _lib.KERNEL_MATERN52, "rbf": _lib.KERNEL_RBF}
+
+
+class BayesianOptimizer(BaseAlgorithm):
+    """GP-based Bayesian optimiser whose candidate scoring runs on one B200.
+
+    Reference keys (same meaning as the skopt wrapper): `seed`, `n_initial_points`, `acq_func`
+    ('EI' | 'PI' | 'LCB' | 'gp_hedge'), `alpha`, `n_restarts_optimizer`, `noise`, `normalize_y`.
+    Additive keys (defaults keep reference behaviour): `n_points` (candidates per suggest, skopt's
+    default 10000), `xi`, `kappa`, `kernel` ('matern52' | 'rbf'), `length_scale`, `amplitude`,
+    `noise_level` (variance folded into the diagonal when `noise == 'gaussian'`), `device`.
+    """
+
+    requires = "real"
+
+    # pylint: disable=too-many-arguments
+    def __init__(self, space, seed=None, n_initial_points=10, acq_func="gp_hedge", alpha=1e-10,
+                 n_restarts_optimizer=0, noise="gaussian", normalize_y=False, n_points=10000, xi=0.01,
+                 kappa=1.96, kernel="matern52", length_scale=1.0, amplitude=1.0, noise_level=1e-4, device=0):
+        self._seed = None
+        self._offset = 0          # next unused global candidate index of the Philox stream
+        self._X = []              # observed points, flat + normalised
+        self._y = []
+        self._compiled = None
+        self._hedge_gains = [0.0, 0.0, 0.0]
+        self._hedge_pending = None
+        super().__init__(space, seed=seed, n_initial_points=n_initial_points, acq_func=acq_func, alpha=alpha,
+                         n_restarts_optimizer=n_restarts_optimizer, noise=noise, normalize_y=normalize_y,
+                         n_points=n_points, xi=xi, kappa=kappa, kernel=kernel, length_scale=length_scale,
+                         amplitude=amplitude, noise_level=noise_level, device=device)
+        if str(acq_func) not in ("EI", "PI", "LCB", "gp_hedge"):
+            raise ValueError("acq_func must be one of 'EI', 'PI', 'LCB', 'gp_hedge' (EIps/PIps need timings "
+                             "that Orion does not pass); got %r" % (acq_func,))
+        if str(kernel).lower() not in _KERNELS:
+            raise ValueError("kernel must be 'matern52' or 'rbf'; got %r" % (kernel,))
+        if self._seed is None:
+            self.seed_rng(None)
+
+    # ---- BaseAlgorithm API ---------------------------------------------------------------
+    def seed_rng(self, seed):
+        """Select the Philox stream (None = fresh entropy) and rewind it."""
+        self._seed = compiler.fold_seed(seed)
+        self._offset = 0
+
+    @property
+    def state_dict(self):
+        return {"seed": self._seed, "offset": self._offset, "hedge_gains": list(self._hedge_gains),
+                "hedge_pending": copy.deepcopy(self._hedge_pending)}
+
+    def set_state(self, state_dict):
+        self._seed = state_dict["seed"]
+        self._offset = state_dict["offset"]
+        self._hedge_gains = list(state_dict.get("hedge_gains", [0.0, 0.0, 0.0]))
+        self._hedge_pending = copy.deepcopy(state_dict.get("hedge_pending"))
+
+    @property
+    def space(self):
+        return self._space
+
+    @space.setter
+    def space(self, space_):
+        """Orion assigns the transformed space right after construction (`primary_algo.py:43`)."""
+        self._space = space_
+        self._compiled = None
+
+    def __deepcopy__(self, memo):
+        new = copy.copy(self)  # shallow: config scalars, the shared space object, the compiled table
+        new._X = list(self._X)
+        new._y = list(self._y)
+        new._hedge_gains = list(self._hedge_gains)
+        new._hedge_pending = copy.deepcopy(self._hedge_pending)
+        memo[id(self)] = new
+        return new
+
+    def suggest(self, num=1):
+        """`num` points of the transformed space (tuples; 1-D arrays for one-hot / shaped dims)."""
+        comp = self._get_compiled()
+        eng = self._engine()
+        compiler.upload(eng, comp)
+        points = []
+        for _ in range(int(num)):
+            if len(self._y) < max(int(self.n_initial_points), 1):
+                row = eng.sample(self._seed, self._offset, 1, normalise=False).cpu().numpy()[0]
+                self._offset += 1
+            else:
+                row = self._suggest_gp(eng, comp)
+            points.append(compiler.regroup_row(comp, row, transformed=True))
+        return points
+
+    def observe(self, points, results):
+        """Record evaluated points; the GP is refitted lazily at the next `suggest`."""
+        comp = self._get_compiled()
+        for point, result in zip(points, results):
+            objective = result.get("objective") if isinstance(result, dict) else result
+            if objective is None:
+                continue
+            flat = np.asarray(compiler.flatten_point(comp, point), dtype=float)
+            self._X.append(comp.normalise(flat))
+            self._y.append(float(objective))
+        self._settle_hedge()
+
+    # ---- internals -------------------------------------------------------------------------
+    def _engine(self):
+        from .engine import get_engine
+        return get_engine(int(self.device))
+
+    def _get_compiled(self):
+        if self._compiled is None:
+            if self._space is None:
+                raise RuntimeError("no space set")
+            comp = compiler.compile_space(self._space)
+            if not comp.normalisable:
+                raise ValueError("BayesianOptimizer needs a finite interval() for every real/integer dimension "
+                                 "(unbounded priors need low/high), like the reference skopt wrapper")
+            self._compiled = comp
+        return self._compiled
+
+    def _diag_noise(self):
+        return float(self.alpha) + (float(self.noise_level) if self.noise == "gaussian" else 0.0)
+
+    def _ensure_fit(self, eng):
+        X = np.asarray(self._X, dtype=np.float64)
+        y = np.asarray(self._y, dtype=np.float64)
+        ls = np.atleast_1d(np.asarray(self.length_scale, dtype=np.float64))
+        h = hashlib.blake2b(digest_size=16)
+        for part in (X.tobytes(), y.tobytes(), ls.tobytes(),
+                     repr((self.kernel, self.amplitude, self._diag_noise(), bool(self.normalize_y))).encode()):
+            h.update(part)
+        token = h.digest()
+        if getattr(eng, "_fit_token", None) != token:
+            eng.fit(X, y, kind=_KERNELS[str(self.kernel).lower()], amplitude=float(self.amplitude), length_scale=ls,
+                    alpha=self._diag_noise(), normalize_y=bool(self.normalize_y))
+            eng._fit_token = token
+        return float(y.min())
+
+    def _suggest_gp(self, eng, comp):
+        y_opt = self._ensure_fit(eng)
+        M = int(self.n_points)
+        hedge = self.acq_func == "gp_hedge"
+        mask = 7 if hedge else (1 << _ACQ[self.acq_func])
+        res = eng.score(None, M=M, seed=self._seed, first_index=self._offset, acq_mask=mask, y_opt=y_opt,
+                        xi=float(self.xi), kappa=float(self.kappa))
+        self._offset += M
+        if hedge:
+            # skopt's gp_hedge: draw one of the three proposals with probability softmax(eta * gains);
+            # the draw itself uses the Philox stream so that it follows state_dict/set_state.
+            names = ("EI", "LCB", "PI")
+            gains = np.asarray(self._hedge_gains)
+            logits = gains - gains.max()
+            probs = np.exp(logits) / np.exp(logits).sum()
+            u = float(self._uniform())
+            pick = int(min(np.searchsorted(np.cumsum(probs), u, side="right"), 2))
+            self._hedge_pending = [(res[n]["index"], res[n]["mu"]) for n in names]
+            winner = res[names[pick]]
+        else:
+            winner = res[self.acq_func]
+        return eng.sample(self._seed, winner["index"], 1, normalise=False).cpu().numpy()[0]
+
+    def _uniform(self):
+        """One host-side uniform from the same counter-based stream (stream position = offset)."""
+        from .philox_host import uniform01
+        u = uniform01(self._seed, self._offset)
+        self._offset += 1
+        return u
+
+    def _settle_hedge(self):
+        # gains_ -= predicted mean of each proposal (skopt: `self.gains_ -= est.predict(next_xs)`)
+        if self._hedge_pending:
+            for k, (_, mu) in enumerate(self._hedge_pending):
+                self._hedge_gains[k] -= float(mu)
+            self._hedge_pending = None
+
+
+def register():
+    """Make the plugin discoverable without a pip install (what `tests/conftest.py:114-116` of the
+    reference does for its own fake algorithm); an installed distribution uses the entry point."""
+    if not HAVE_ORION:
+        raise RuntimeError("Orion is not importable")
+    from orion.algo.base import OptimizationAlgorithm  # pylint: disable=import-error
+    name = BayesianOptimizer.__name__.lower()
+    if name not in OptimizationAlgorithm.typenames:
+        OptimizationAlgorithm.types.append(BayesianOptimizer)
+        OptimizationAlgorithm.typenames.append(name)

@@ -33,7 +33,7 @@ def _compare(engine, X, y, C, kind=0, amp=1.0, ls=1.0, alpha=1e-10 + 1e-4, norma
         mu, sd, acq = out["mu"].cpu().numpy(), out["sigma"].cpu().numpy(), out["acq"].cpu().numpy()
     np.testing.assert_allclose(mu, mu_r, rtol=RTOL, atol=RTOL * np.abs(mu_r).max())
     # std: relative where sigma is not cancellation-dominated, absolute otherwise
-    floor = 1e-6 * np.sqrt(amp) * ref.gpr._y_train_std
+    floor = float(1e-6 * np.sqrt(amp) * np.ravel(ref.gpr._y_train_std)[0])
     np.testing.assert_allclose(sd, sd_r, rtol=RTOL, atol=floor)
     for k, name in ((0, "EI"), (1, "PI"), (2, "LCB")):
         util = oacq.utility(k, mu_r, sd_r, y_opt, xi, kappa)
