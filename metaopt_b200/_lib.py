@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libob200.so")
+LIB_PATH = os.environ.get("OB200_LIB") or os.path.join(HERE, "libob200.so")  # OB200_LIB: tuning variants
 
 OK, EINVAL, ECUDA, ENOTSPD, ENOMEM, ESTATE, EBOUNDS = 0, -1, -2, -3, -4, -5, -6
 KIND_REAL, KIND_INT, KIND_CAT = 0, 1, 2

@@ -23,18 +23,23 @@ def needs_build():
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force=False, verbose=False):
-    """Compile every .cu for sm_100a (cross-compiles without a GPU) and link libob200.so in-tree."""
-    if not force and not needs_build():
-        return LIB
+def build(force=False, verbose=False, defines=(), out=None):
+    """Compile every .cu for sm_100a (cross-compiles without a GPU) and link libob200.so in-tree.
+
+    `defines`/`out` build a tuning variant (e.g. defines=["SC_BK=32"], out="libob200_bk32.so")."""
+    lib = os.path.join(HERE, out) if out else LIB
+    if not force and not out and not needs_build():
+        return lib
+    tag = ("_" + os.path.splitext(out)[0]) if out else ""
     objs = []
     for src in SOURCES:
-        obj = os.path.join(CSRC, src.replace(".cu", ".o"))
-        cmd = [NVCC] + FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", os.path.join(CSRC, src), "-o", obj]
+        obj = os.path.join(CSRC, src.replace(".cu", tag + ".o"))
+        cmd = [NVCC] + FLAGS + ["-D" + d for d in defines] + (["-Xptxas", "-v"] if verbose else []) + \
+            ["-c", os.path.join(CSRC, src), "-o", obj]
         subprocess.run(cmd, check=True)
         objs.append(obj)
-    subprocess.run([NVCC, "-shared", "-o", LIB] + objs + ["-lcudart"], check=True)
-    return LIB
+    subprocess.run([NVCC, "-shared", "-o", lib] + objs + ["-lcudart"], check=True)
+    return lib
 
 
 if __name__ == "__main__":

@@ -16,8 +16,15 @@
 // ---- tiling constants of the score kernel (see DESIGN.md "score kernel") ------------------
 #define SC_BM 256        // rows of inv(L) per row block (4 warp-rows x 8 fragments x 8 rows)
 #define SC_BN 64         // candidates per CTA tile (2 warp-cols x 4 fragments x 8 candidates)
+#ifndef SC_BK
 #define SC_BK 16         // k (observed-point) extent of one pipeline stage
+#endif
+#ifndef SC_STAGES
 #define SC_STAGES 4
+#endif
+#ifndef SC_CONSUMER_REGS
+#define SC_CONSUMER_REGS 232
+#endif
 #define SC_CONSUMER_WARPS 8
 #define SC_PRODUCER_WARPS 4   // a full warpgroup so that setmaxnreg can rebalance registers
 #define SC_THREADS ((SC_CONSUMER_WARPS + SC_PRODUCER_WARPS) * 32)
@@ -127,7 +134,7 @@ static inline ob200_blob_layout ob_blob_layout(int n_pad, int D_pad) {
 // D(8x8) += A(8x4, row) * B(4x8, col), FP64 tensor core (SASS: DMMA.8x8x4).
 // lane l: a = A[l/4][l%4], b = B[l%4][l/4], c0/c1 = C[l/4][2*(l%4) + {0,1}]
 __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
-  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+  asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
                : "+d"(c0), "+d"(c1)
                : "d"(a), "d"(b));
 }

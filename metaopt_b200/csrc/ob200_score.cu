@@ -74,7 +74,9 @@ __device__ __forceinline__ void acquisition(double mu, double sigma, double y_op
 
 __device__ __forceinline__ void consumer_bar() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
 
+#ifndef P1_STAGES
 #define P1_STAGES 2
+#endif
 #define P1_OBS 64
 
 __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
@@ -173,7 +175,7 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
   }
 
   // =============================== consumers (warps 0..7) ===============================
-  asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(SC_CONSUMER_REGS));
   for (long long tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
     const long long row0 = tile * SC_BN;
     // ---- stage the candidate tile: Cs = cand / ls in A-fragment order, cc = ||Cs||^2
@@ -263,21 +265,43 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
         mbar_wait(&full2[s], ph);
         const double2* As = reinterpret_cast<const double2*>(Abuf + (size_t)s * SC_BM * SC_BK) + (size_t)wm * 8 * (SC_BK / 8) * 32 + lane;
         const double2* Bs = reinterpret_cast<const double2*>(Bbuf + (size_t)s * SC_BK * SC_BN) + (size_t)wn * 4 * 32 + lane;
+        // Stages strictly below the diagonal with every row fragment inside n need no predicates:
+        // plain unrolled loads + 128 DMMAs.  Diagonal / last-row-block stages predicate each fragment.
+        const bool full = (J * SC_BK + SC_BK - 1 <= I * SC_BM) && (I * SC_BM + SC_BM <= a.n);
+        if (full) {
 #pragma unroll
-        for (int k8 = 0; k8 < SC_BK / 8; ++k8) {
-          const int k0 = J * SC_BK + k8 * 8;
-          double2 b[4];
+          for (int k8 = 0; k8 < SC_BK / 8; ++k8) {
+            double2 b[4], av[8];
 #pragma unroll
-          for (int j = 0; j < 4; ++j) b[j] = Bs[(k8 * 8 + j) * 32];
+            for (int j = 0; j < 4; ++j) b[j] = Bs[(k8 * 8 + j) * 32];
 #pragma unroll
-          for (int t = 0; t < 8; ++t) {
-            const int r0 = rbase + 32 * t;
-            if (r0 < a.n && r0 + 7 >= k0) {
-              const double2 av = As[(t * (SC_BK / 8) + k8) * 32];
+            for (int t = 0; t < 8; ++t) av[t] = As[(t * (SC_BK / 8) + k8) * 32];
 #pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                dmma884(acc[t][j][0], acc[t][j][1], av.x, b[j].x);
-                dmma884(acc[t][j][0], acc[t][j][1], av.y, b[j].y);
+            for (int t = 0; t < 8; ++t)
+#pragma unroll
+              for (int j = 0; j < 4; ++j) dmma884(acc[t][j][0], acc[t][j][1], av[t].x, b[j].x);
+#pragma unroll
+            for (int t = 0; t < 8; ++t)
+#pragma unroll
+              for (int j = 0; j < 4; ++j) dmma884(acc[t][j][0], acc[t][j][1], av[t].y, b[j].y);
+          }
+        } else {
+#pragma unroll
+          for (int k8 = 0; k8 < SC_BK / 8; ++k8) {
+            const int k0 = J * SC_BK + k8 * 8;
+            double2 b[4], av[8];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) b[j] = Bs[(k8 * 8 + j) * 32];
+#pragma unroll
+            for (int t = 0; t < 8; ++t) av[t] = As[(t * (SC_BK / 8) + k8) * 32];
+#pragma unroll
+            for (int t = 0; t < 8; ++t) {
+              const int r0 = rbase + 32 * t;
+              if (r0 < a.n && r0 + 7 >= k0) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) dmma884(acc[t][j][0], acc[t][j][1], av[t].x, b[j].x);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) dmma884(acc[t][j][0], acc[t][j][1], av[t].y, b[j].y);
               }
             }
           }
@@ -557,8 +581,11 @@ int ob200_score_host(ob200_ctx* ctx, const double* cand_host, int64_t ldc, int64
   double* mu_dev = mu_host ? p : nullptr; if (mu_host) p += M;
   double* sg_dev = sigma_host ? p : nullptr; if (sigma_host) p += M;
   double* aq_dev = acq_host ? p : nullptr;
-  OB_CUDA(ctx, cudaMemcpy2DAsync(ctx->cand_tmp, (size_t)D * 8, cand_host, (size_t)ldc * 8, (size_t)D * 8, (size_t)M,
-                                 cudaMemcpyHostToDevice, ctx->stream));
+  if (ldc == D)  // contiguous rows: one flat DMA (a 2-D copy of 8*D-byte rows is an order of magnitude slower)
+    OB_CUDA(ctx, cudaMemcpyAsync(ctx->cand_tmp, cand_host, (size_t)M * D * 8, cudaMemcpyHostToDevice, ctx->stream));
+  else
+    OB_CUDA(ctx, cudaMemcpy2DAsync(ctx->cand_tmp, (size_t)D * 8, cand_host, (size_t)ldc * 8, (size_t)D * 8, (size_t)M,
+                                   cudaMemcpyHostToDevice, ctx->stream));
   if ((rc = ob200_score_async(ctx, ctx->cand_tmp, D, M, 0, 0, acq_mask, y_opt, xi, kappa, ctx->best_dev, mu_dev, sg_dev, aq_dev))) return rc;
   OB_CUDA(ctx, cudaMemcpyAsync(ctx->best_pinned, ctx->best_dev, 3 * sizeof(ob200_best), cudaMemcpyDeviceToHost, ctx->stream));
   if (mu_host) OB_CUDA(ctx, cudaMemcpyAsync(mu_host, mu_dev, (size_t)M * 8, cudaMemcpyDeviceToHost, ctx->stream));

@@ -1,0 +1,74 @@
+"""Import the UNMODIFIED reference (Orion) from /root/reference with harness-side shims.
+
+Test infrastructure only (see oracle/__init__.py).  Nothing is copied or edited: the reference's
+`src/` is put on `sys.path` and three things it expects from its 2019 environment are supplied
+in memory:
+  1. `appdirs`  -> the reference's own vendored `src/orion/core/utils/_appdirs.py`, loaded by path;
+  2. `pymongo`  -> a stub with the names `core/io/database/mongodb.py` imports (never used with
+                   PickledDB / EphemeralDB);
+  3. `numpy.object` -> `object` (removed in numpy >= 1.24; used at `algo/space.py:549,572`).
+The reference does not exist on the GPU box: `available()` is False there and every user of this
+module skips.
+"""
+import importlib.util
+import os
+import sys
+import types
+
+REF_ROOT = "/root/reference"
+REF_SRC = os.path.join(REF_ROOT, "src")
+
+
+def available():
+    return os.path.isdir(os.path.join(REF_SRC, "orion"))
+
+
+def _install_shims():
+    import numpy
+    if not hasattr(numpy, "object"):
+        numpy.object = object
+    if "appdirs" not in sys.modules:
+        path = os.path.join(REF_SRC, "orion", "core", "utils", "_appdirs.py")
+        spec = importlib.util.spec_from_file_location("appdirs", path)
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        sys.modules["appdirs"] = mod
+    if "pymongo" not in sys.modules:
+        pm = types.ModuleType("pymongo")
+        errors = types.ModuleType("pymongo.errors")
+        for name in ("DuplicateKeyError", "BulkWriteError", "ConnectionFailure", "OperationFailure", "InvalidURI",
+                     "ConfigurationError"):
+            setattr(errors, name, type(name, (Exception,), {}))
+        uri_parser = types.ModuleType("pymongo.uri_parser")
+        uri_parser.parse_uri = lambda uri, *a, **k: {"nodelist": [("localhost", 27017)], "database": None,
+                                                     "username": None, "password": None, "options": {}}
+
+        class MongoClient:  # pragma: no cover - never instantiated
+            HOST, PORT = "localhost", 27017
+
+            def __init__(self, *a, **k):
+                raise errors.ConnectionFailure("pymongo stub: no MongoDB in the oracle harness")
+
+        class ReturnDocument:
+            BEFORE, AFTER = False, True
+
+        pm.errors, pm.uri_parser, pm.MongoClient, pm.ReturnDocument = errors, uri_parser, MongoClient, ReturnDocument
+        pm.ASCENDING, pm.DESCENDING = 1, -1
+        sys.modules["pymongo"] = pm
+        sys.modules["pymongo.errors"] = errors
+        sys.modules["pymongo.uri_parser"] = uri_parser
+
+
+def load():
+    """Return the reference's `orion` package (or None when /root/reference is absent)."""
+    if not available():
+        return None
+    sys.dont_write_bytecode = True  # the reference tree is read-only
+    _install_shims()
+    if REF_SRC not in sys.path:
+        sys.path.insert(0, REF_SRC)
+    import orion  # noqa: F401
+    import orion.algo.space  # noqa: F401
+    import orion.algo.base  # noqa: F401
+    import orion.core.worker.transformer  # noqa: F401
+    return sys.modules["orion"]

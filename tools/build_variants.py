@@ -1,0 +1,16 @@
+"""Build tuning variants of libob200 (different tile/stage/register settings) next to the main one."""
+import sys
+sys.path.insert(0, ".")
+from metaopt_b200 import build as b
+
+VARIANTS = {
+    "bk32s2": ["SC_BK=32", "SC_STAGES=2"],
+    "bk16s5": ["SC_BK=16", "SC_STAGES=5"],
+    "bk8s8": ["SC_BK=8", "SC_STAGES=8"],
+    "r224": ["SC_CONSUMER_REGS=224"],
+    "p1s3": ["P1_STAGES=3"],
+}
+if __name__ == "__main__":
+    names = sys.argv[1:] or list(VARIANTS)
+    for name in names:
+        print(b.build(force=True, defines=VARIANTS[name], out="libob200_%s.so" % name))
