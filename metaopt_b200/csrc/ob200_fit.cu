@@ -87,7 +87,10 @@ __device__ __forceinline__ double kernel_from_d2(int kind, double d2, double amp
 __global__ void __launch_bounds__(256) gram_kernel(const double* __restrict__ Xs, int n, int n_pad, int D_pad, int kind,
                                                    double amplitude, double alpha, double* __restrict__ K) {
   const int ti = blockIdx.y, tj = blockIdx.x;
-  if (tj > ti) return;
+  if (tj > ti) {  // strictly upper tiles: zero (the buffer is reused across fits of different n_pad)
+    for (int e = threadIdx.x; e < 1024; e += 256) K[(size_t)(ti * 32 + (e >> 5)) * n_pad + tj * 32 + (e & 31)] = 0.0;
+    return;
+  }
   extern __shared__ double sm[];
   double* xi = sm;                       // [32][D_pad+1]
   double* xj = sm + 32 * (D_pad + 1);
@@ -343,8 +346,9 @@ __global__ void __launch_bounds__(1024) chol_solve_kernel(const double* __restri
 
 // Pack inv(L) (dense row-major X, ld = n_pad) into the score kernel's tile layout:
 //   tile (I, J) = rows [I*SC_BM, +SC_BM) x cols [J*SC_BK, +SC_BK), stored contiguously as
-//   [slot (SC_BM/8)][k8 (SC_BK/8)][8 rows][8 cols]; slot = wm*8 + t holds the 8 rows of original
-//   row fragment f = 4*t + wm (cyclic assignment of row fragments to the 4 warp rows).
+//   [slot (SC_BM/8)][k8 (SC_BK/8)][8 rows][8 cols]; slot = wm*SC_FM + t holds the 8 rows of original
+//   row fragment f = SC_WM*t + (t odd ? SC_WM-1-wm : wm): row fragments are dealt to the SC_WM warp rows
+//   back and forth, so every warp row owns the same amount of work inside the triangular diagonal block.
 // Rows/cols >= n are written as zeros.
 __global__ void pack_linv_kernel(const double* __restrict__ X, int n, int n_pad, double* __restrict__ out) {
   const int64_t total = (int64_t)n_pad * n_pad;
@@ -357,8 +361,8 @@ __global__ void pack_linv_kernel(const double* __restrict__ X, int n, int n_pad,
     const int slot = rem % (SC_BM / 8); rem /= (SC_BM / 8);
     const int J = rem % nJ;
     const int I = (int)(rem / nJ);
-    const int wm = slot >> 3, t = slot & 7;
-    const int row = I * SC_BM + (4 * t + wm) * 8 + row8;
+    const int wm = slot / SC_FM, t = slot % SC_FM;
+    const int row = I * SC_BM + (SC_WM * t + ((t & 1) ? SC_WM - 1 - wm : wm)) * 8 + row8;
     const int col = J * SC_BK + k8 * 8 + col8;
     out[e] = (row < n && col < n && col <= row) ? X[(size_t)row * n_pad + col] : 0.0;
   }

@@ -14,20 +14,37 @@
 #define OB200_NUM_SMS_FALLBACK 148
 
 // ---- tiling constants of the score kernel (see DESIGN.md "score kernel") ------------------
-#define SC_BM 256        // rows of inv(L) per row block (4 warp-rows x 8 fragments x 8 rows)
-#define SC_BN 64         // candidates per CTA tile (2 warp-cols x 4 fragments x 8 candidates)
+// Consumer warps form a SC_WM x SC_WN grid; each owns SC_FM row fragments (8 rows of inv(L)) x
+// SC_FN candidate fragments (8 candidates).  Defaults: 6x2 warps, 4x4 fragments -> 192 x 64 tile
+// (3 consumer warps per SM sub-partition keep the DMMA pipe fed better than 2 fat ones).
+#ifndef SC_WM
+#define SC_WM 6
+#endif
+#ifndef SC_WN
+#define SC_WN 2
+#endif
+#ifndef SC_FM
+#define SC_FM 4
+#endif
+#ifndef SC_FN
+#define SC_FN 4
+#endif
+#define SC_BM (SC_WM * SC_FM * 8)   // rows of inv(L) per row block
+#define SC_BN (SC_WN * SC_FN * 8)   // candidates per CTA tile
+#define SC_NCF (SC_BN / 8)          // candidate fragments per tile
 #ifndef SC_BK
 #define SC_BK 16         // k (observed-point) extent of one pipeline stage
 #endif
 #ifndef SC_STAGES
 #define SC_STAGES 4
 #endif
-#ifndef SC_CONSUMER_REGS
-#define SC_CONSUMER_REGS 232
-#endif
-#define SC_CONSUMER_WARPS 8
+#define SC_CONSUMER_WARPS (SC_WM * SC_WN)
 #define SC_PRODUCER_WARPS 4   // a full warpgroup so that setmaxnreg can rebalance registers
 #define SC_THREADS ((SC_CONSUMER_WARPS + SC_PRODUCER_WARPS) * 32)
+#ifndef SC_CONSUMER_REGS      // per-SMSP budget: (consumer warps / 4) * regs + 40 <= 512
+#define SC_CONSUMER_REGS ((SC_CONSUMER_WARPS == 8) ? 232 : 152)
+#endif
+#define SC_P1_OBS (SC_CONSUMER_WARPS * 8)   // observed points per phase-1 chunk (one obs8 block per warp)
 
 struct ob200_fit_header {   // first bytes of the exported fit blob
   int32_t magic, n, D, n_pad, D_pad, kernel_kind;

@@ -47,14 +47,61 @@ struct score_args {
   best_t* partials;  // [grid][3]
   long long n_tiles;
   int accumulate;    // 1: fold the partials already stored (multi-chunk calls)
+  int p1_stages;     // phase-1 ring depth (2, or 1 when D is too wide for two stages)
 };
+
+// ---- branch-free FP64 math for the cross-kernel epilogue ------------------------------------
+// The library exp()/sqrt() cost ~150 issued instructions per kernel evaluation (special-case
+// paths, integer fix-ups); phase 1 was issue-bound on them.  These straight-line versions are
+// ~35 instructions, accurate to ~1-2 ulp on the domain that can occur here, and interleave
+// freely across the 16 evaluations each lane owns.
+
+// sqrt(x) for finite x >= 0 (x = 0 and x below 1e-30 return a tiny finite value <= 1e-15,
+// which the Matern polynomial maps to amplitude * (1 + O(1e-30))).
+__device__ __forceinline__ double sqrt_pos(double x) {
+  const double xm = fmax(x, 1e-30);
+  double y = (double)rsqrtf((float)xm);          // 23-bit seed (MUFU.RSQ)
+  double h = 0.5 * xm;
+  y = y * fma(-h * y, y, 1.5);                     // Newton on 1/sqrt: 46 bits
+  y = y * fma(-h * y, y, 1.5);                     // ~full precision
+  double s = x * y;
+  const double e = fma(-s, s, x);                  // residual (only meaningful when xm == x)
+  return (x >= 1e-30) ? fma(e, 0.5 * y, s) : s;
+}
+
+// exp(t) for t <= 0.  Cody-Waite reduction t = n ln2 + r, |r| <= ln2/2, degree-13 Taylor
+// (truncation 4e-18 relative), scaling by exponent-field addition; below 2^-1021 returns 0.
+__device__ __forceinline__ double exp_neg(double t) {
+  const double magic = 6755399441055744.0;         // 1.5 * 2^52: round-to-nearest-integer trick
+  const double nd_biased = fma(t, 1.4426950408889634, magic);
+  const int n = __double2loint(nd_biased);
+  const double nd = nd_biased - magic;
+  double r = fma(nd, -6.93147180369123816490e-01, t);
+  r = fma(nd, -1.90821492927058770002e-10, r);
+  double p = 1.6059043836821613e-10;               // 1/13!
+  p = fma(p, r, 2.08767569878681e-09);             // 1/12!
+  p = fma(p, r, 2.505210838544172e-08);            // 1/11!
+  p = fma(p, r, 2.755731922398589e-07);            // 1/10!
+  p = fma(p, r, 2.7557319223985893e-06);           // 1/9!
+  p = fma(p, r, 2.48015873015873e-05);             // 1/8!
+  p = fma(p, r, 0.0001984126984126984);            // 1/7!
+  p = fma(p, r, 0.001388888888888889);             // 1/6!
+  p = fma(p, r, 0.008333333333333333);             // 1/5!
+  p = fma(p, r, 0.041666666666666664);             // 1/4!
+  p = fma(p, r, 0.16666666666666666);              // 1/3!
+  p = fma(p, r, 0.5);
+  p = fma(p, r, 1.0);
+  p = fma(p, r, 1.0);
+  const double scaled = __hiloint2double(__double2hiint(p) + (n << 20), __double2loint(p));
+  return (n >= -1021) ? scaled : 0.0;
+}
 
 __device__ __forceinline__ double kernel_from_d2(int kind, double d2, double amplitude) {
   if (kind == OB200_KERNEL_MATERN52) {
-    const double k = sqrt(d2) * 2.23606797749979;
-    return amplitude * ((1.0 + k + k * k / 3.0) * exp(-k));
+    const double k = sqrt_pos(d2) * 2.23606797749979;  // sqrt(5) * dist
+    return amplitude * (fma(k, fma(k, 0.3333333333333333, 1.0), 1.0) * exp_neg(-k));
   }
-  return amplitude * exp(-0.5 * d2);
+  return amplitude * exp_neg(-0.5 * d2);
 }
 
 __device__ __forceinline__ void acquisition(double mu, double sigma, double y_opt, double xi, double kappa, double out[3]) {
@@ -72,34 +119,41 @@ __device__ __forceinline__ void acquisition(double mu, double sigma, double y_op
   out[OB200_ACQ_LCB] = -(mu - kappa * sigma);
 }
 
-__device__ __forceinline__ void consumer_bar() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+__device__ __forceinline__ void consumer_bar() {
+  asm volatile("bar.sync 1, %0;" ::"n"(SC_CONSUMER_WARPS * 32) : "memory");
+}
 
 #ifndef P1_STAGES
 #define P1_STAGES 2
 #endif
-#define P1_OBS 64
+static_assert(SC_BM % 64 == 0, "row block must be a multiple of the fit block");
+static_assert(SC_BM % SC_P1_OBS == 0, "row block must be a multiple of the phase-1 chunk");
+static_assert(SC_BN % 32 == 0 && SC_BN <= SC_CONSUMER_WARPS * 32, "candidate tile shape");
+static_assert(SC_BK % 8 == 0, "stage depth");
+
+__host__ __device__ inline size_t score_union_elems(int D_pad, int p1_stages) {
+  size_t un = (size_t)SC_STAGES * (SC_BM * SC_BK + SC_BK * SC_BN);
+  const size_t p1 = (size_t)SC_BN * D_pad + (size_t)p1_stages * (SC_P1_OBS * D_pad + 2 * SC_P1_OBS);
+  return p1 > un ? p1 : un;
+}
 
 __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int D_pad = a.D_pad, nd4 = D_pad >> 2;
-  const int p1_stage_elems = P1_OBS * D_pad + 2 * P1_OBS;
+  const int p1_stage_elems = SC_P1_OBS * D_pad + 2 * SC_P1_OBS;
   double* un = reinterpret_cast<double*>(smem_raw);
   // phase-1 view of the union
-  double* Cs = un;                                // [8 cf][nd4][32]
+  double* Cs = un;                                // [SC_NCF][nd4][32]
   double* p1buf = un + SC_BN * D_pad;             // P1_STAGES x (Xs chunk | xx | alpha)
   // phase-2 view
   double* Abuf = un;                              // SC_STAGES x (SC_BM*SC_BK)
   double* Bbuf = un + SC_STAGES * SC_BM * SC_BK;  // SC_STAGES x (SC_BK*SC_BN)
-  size_t un_elems = (size_t)SC_STAGES * (SC_BM * SC_BK + SC_BK * SC_BN);
-  {
-    const size_t p1 = (size_t)SC_BN * D_pad + (size_t)P1_STAGES * p1_stage_elems;
-    if (p1 > un_elems) un_elems = p1;
-  }
-  double* small = un + un_elems;
-  double* cc = small;                     // [64]
-  double* mured = cc + SC_BN;             // [8][64]
-  double* ssred = mured + 8 * SC_BN;      // [4][64]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(ssred + 4 * SC_BN);
+  const int P1S = a.p1_stages;
+  double* small = un + score_union_elems(D_pad, P1S);
+  double* cc = small;                                   // [SC_BN]
+  double* mured = cc + SC_BN;                           // [SC_CONSUMER_WARPS][SC_BN]
+  double* ssred = mured + SC_CONSUMER_WARPS * SC_BN;    // [SC_WM][SC_BN]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(ssred + SC_WM * SC_BN);
   uint64_t* full1 = bars;                 // [P1_STAGES]
   uint64_t* empty1 = full1 + P1_STAGES;
   uint64_t* full2 = empty1 + P1_STAGES;   // [SC_STAGES]
@@ -107,7 +161,7 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int g = lane >> 2, q = lane & 3;
-  const bool is_producer = (warp >= SC_CONSUMER_WARPS);   // warps 8..11; only warp 8 lane 0 issues copies
+  const bool is_producer = (warp >= SC_CONSUMER_WARPS);   // last warpgroup; only its first lane issues copies
   const bool is_issuer = (warp == SC_CONSUMER_WARPS) && (lane == 0);
 
   if (tid == 0) {
@@ -116,40 +170,40 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
+
   double* kslice = a.kstar + (size_t)blockIdx.x * a.n_pad * SC_BN;
-  const int n_chunks1 = (a.n + P1_OBS - 1) / P1_OBS;          // observed-point chunks that hold real rows
+#ifdef SC_DEBUG_SKIP_PHASE1
+  const int n_chunks1 = 0;  // timing experiment only: phase 2 + 3 on stale k*
+#else
+  const int n_chunks1 = (a.n + SC_P1_OBS - 1) / SC_P1_OBS;    // observed-point chunks that hold real rows
+#endif
+#ifdef SC_DEBUG_SKIP_PHASE2
+  const int n_rb = 0;   // timing experiment only: phase 1 + 3
+#else
   const int n_rb = (a.n + SC_BM - 1) / SC_BM;                 // row blocks of inv(L) that hold real rows
+#endif
   const int k_lim = (int)(((long long)a.n + SC_BK - 1) / SC_BK);  // stages with real columns
 
   // running ring positions (continue across tiles)
   uint32_t it1 = 0, it2 = 0;
 
-  // running best per acquisition (threads 0..63)
-  best_t best[3];
-#pragma unroll
-  for (int k = 0; k < 3; ++k) { best[k].value = -INFINITY; best[k].index = 0x7fffffffffffffffLL; best[k].mu = 0.0; best[k].sigma = 0.0; }
-  if (a.accumulate && tid == 0) {
-#pragma unroll
-    for (int k = 0; k < 3; ++k) best[k] = a.partials[(size_t)blockIdx.x * 3 + k];
-  }
-
   if (is_producer) {
-    // register rebalancing (3 warps per SM sub-partition: 2 consumers x 232 + 1 producer x 40 = 504);
-    // each role keeps its own tile loop so the register budget is decided by dominance.
+    // register rebalancing: each role keeps its own tile loop so the register budget is decided by
+    // dominance (per SM sub-partition: consumers x SC_CONSUMER_REGS + 1 producer x 40 <= 512).
     asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
     for (long long tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
       if (is_issuer) {
         // ---- phase 1 producer: observed-point chunks
-        const uint32_t xs_bytes = (uint32_t)(P1_OBS * D_pad * 8);
+        const uint32_t xs_bytes = (uint32_t)(SC_P1_OBS * D_pad * 8);
         for (int c = 0; c < n_chunks1; ++c, ++it1) {
-          const int s = it1 % P1_STAGES;
-          const uint32_t ph = (it1 / P1_STAGES) & 1;
+          const int s = it1 % P1S;
+          const uint32_t ph = (it1 / P1S) & 1;
           mbar_wait(&empty1[s], ph ^ 1);
           double* dst = p1buf + (size_t)s * p1_stage_elems;
-          mbar_expect_tx(&full1[s], xs_bytes + 2 * P1_OBS * 8);
-          bulk_g2s(dst, a.xs + (size_t)c * P1_OBS * D_pad, xs_bytes, &full1[s]);
-          bulk_g2s(dst + P1_OBS * D_pad, a.xx + (size_t)c * P1_OBS, P1_OBS * 8, &full1[s]);
-          bulk_g2s(dst + P1_OBS * D_pad + P1_OBS, a.alpha + (size_t)c * P1_OBS, P1_OBS * 8, &full1[s]);
+          mbar_expect_tx(&full1[s], xs_bytes + 2 * SC_P1_OBS * 8);
+          bulk_g2s(dst, a.xs + (size_t)c * SC_P1_OBS * D_pad, xs_bytes, &full1[s]);
+          bulk_g2s(dst + SC_P1_OBS * D_pad, a.xx + (size_t)c * SC_P1_OBS, SC_P1_OBS * 8, &full1[s]);
+          bulk_g2s(dst + SC_P1_OBS * D_pad + SC_P1_OBS, a.alpha + (size_t)c * SC_P1_OBS, SC_P1_OBS * 8, &full1[s]);
         }
       }
       __syncthreads();  // (A) consumers finished phase 1, k* slice written
@@ -174,8 +228,18 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
     return;
   }
 
-  // =============================== consumers (warps 0..7) ===============================
+  // =============================== consumers ===============================
   asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(SC_CONSUMER_REGS));
+
+  // running best per acquisition (threads 0..SC_BN-1 own one candidate column each)
+  best_t best[3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) { best[k].value = -INFINITY; best[k].index = 0x7fffffffffffffffLL; best[k].mu = 0.0; best[k].sigma = 0.0; }
+  if (a.accumulate && tid == 0) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) best[k] = a.partials[(size_t)blockIdx.x * 3 + k];
+  }
+
   for (long long tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
     const long long row0 = tile * SC_BN;
     // ---- stage the candidate tile: Cs = cand / ls in A-fragment order, cc = ||Cs||^2
@@ -197,111 +261,114 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
     }
     consumer_bar();
 
-    // ---- phase 1: k* = kernel(cand, X) and mu partials
-    double ccr[8], mup[8];
+    // ---- phase 1: k* = kernel(cand, X) and mu partials; warp w owns obs8 block w of each chunk
+    {
+      double ccr[SC_NCF], mup[SC_NCF];
 #pragma unroll
-    for (int cf = 0; cf < 8; ++cf) { ccr[cf] = cc[cf * 8 + g]; mup[cf] = 0.0; }
-    for (int c = 0; c < n_chunks1; ++c, ++it1) {
-      const int s = it1 % P1_STAGES;
-      const uint32_t ph = (it1 / P1_STAGES) & 1;
-      mbar_wait(&full1[s], ph);
-      const double* xs_s = p1buf + (size_t)s * p1_stage_elems + (size_t)warp * nd4 * 32;  // this warp's obs8 block
-      const double* xx_s = p1buf + (size_t)s * p1_stage_elems + P1_OBS * D_pad + warp * 8;
-      const double* al_s = xx_s + P1_OBS;
-      double acc[8][2];
+      for (int cf = 0; cf < SC_NCF; ++cf) { ccr[cf] = cc[cf * 8 + g]; mup[cf] = 0.0; }
+      for (int c = 0; c < n_chunks1; ++c, ++it1) {
+        const int s = it1 % P1S;
+        const uint32_t ph = (it1 / P1S) & 1;
+        mbar_wait(&full1[s], ph);
+        const double* xs_s = p1buf + (size_t)s * p1_stage_elems + (size_t)warp * nd4 * 32;  // this warp's obs8 block
+        const double* xx_s = p1buf + (size_t)s * p1_stage_elems + SC_P1_OBS * D_pad + warp * 8;
+        const double* al_s = xx_s + SC_P1_OBS;
+        double acc[SC_NCF][2];
 #pragma unroll
-      for (int cf = 0; cf < 8; ++cf) acc[cf][0] = acc[cf][1] = 0.0;
-      for (int d4 = 0; d4 < nd4; ++d4) {
-        const double b = xs_s[d4 * 32 + lane];
+        for (int cf = 0; cf < SC_NCF; ++cf) acc[cf][0] = acc[cf][1] = 0.0;
+        for (int d4 = 0; d4 < nd4; ++d4) {
+          const double b = xs_s[d4 * 32 + lane];
 #pragma unroll
-        for (int cf = 0; cf < 8; ++cf) dmma884(acc[cf][0], acc[cf][1], Cs[((size_t)cf * nd4 + d4) * 32 + lane], b);
+          for (int cf = 0; cf < SC_NCF; ++cf) dmma884(acc[cf][0], acc[cf][1], Cs[((size_t)cf * nd4 + d4) * 32 + lane], b);
+        }
+        const double xx0 = xx_s[2 * q], xx1 = xx_s[2 * q + 1];
+        const double al0 = al_s[2 * q], al1 = al_s[2 * q + 1];
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty1[s]);
+        const int ob = c * SC_CONSUMER_WARPS + warp;  // global obs8 block
+        double2* dst = reinterpret_cast<double2*>(kslice + (size_t)ob * SC_NCF * 64) + lane;
+#pragma unroll
+        for (int cf = 0; cf < SC_NCF; ++cf) {
+          const double d20 = fmax(ccr[cf] + xx0 - 2.0 * acc[cf][0], 0.0);
+          const double d21 = fmax(ccr[cf] + xx1 - 2.0 * acc[cf][1], 0.0);
+          double2 kv;
+          kv.x = kernel_from_d2(a.kind, d20, a.amplitude);
+          kv.y = kernel_from_d2(a.kind, d21, a.amplitude);
+          mup[cf] = fma(kv.x, al0, mup[cf]);
+          mup[cf] = fma(kv.y, al1, mup[cf]);
+          dst[cf * 32] = kv;
+        }
       }
-      const double xx0 = xx_s[2 * q], xx1 = xx_s[2 * q + 1];
-      const double al0 = al_s[2 * q], al1 = al_s[2 * q + 1];
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&empty1[s]);
-      const int ob = c * 8 + warp;  // global obs8 block
-      double2* dst = reinterpret_cast<double2*>(kslice + (size_t)ob * 8 * 64) + lane;
+      // mu: reduce over q (4 lanes) then across warps through shared memory
 #pragma unroll
-      for (int cf = 0; cf < 8; ++cf) {
-        const double d20 = fmax(ccr[cf] + xx0 - 2.0 * acc[cf][0], 0.0);
-        const double d21 = fmax(ccr[cf] + xx1 - 2.0 * acc[cf][1], 0.0);
-        double2 kv;
-        kv.x = kernel_from_d2(a.kind, d20, a.amplitude);
-        kv.y = kernel_from_d2(a.kind, d21, a.amplitude);
-        mup[cf] = fma(kv.x, al0, mup[cf]);
-        mup[cf] = fma(kv.y, al1, mup[cf]);
-        dst[cf * 32] = kv;
+      for (int cf = 0; cf < SC_NCF; ++cf) {
+        double v = mup[cf];
+        v += __shfl_xor_sync(0xffffffffu, v, 1);
+        v += __shfl_xor_sync(0xffffffffu, v, 2);
+        if (q == 0) mured[warp * SC_BN + cf * 8 + g] = v;
       }
-    }
-    // mu: reduce over q (4 lanes) then across warps through shared memory
-#pragma unroll
-    for (int cf = 0; cf < 8; ++cf) {
-      double v = mup[cf];
-      v += __shfl_xor_sync(0xffffffffu, v, 1);
-      v += __shfl_xor_sync(0xffffffffu, v, 2);
-      if (q == 0) mured[warp * SC_BN + cf * 8 + g] = v;
     }
     fence_proxy_async();  // k* global writes (generic proxy) -> bulk reads (async proxy)
     __syncthreads();      // (A)
 
     // ---- phase 2: sum v^2 with v = inv(L) k*
-    const int wm = warp >> 1, wn = warp & 1;
-    double ss[4][2];
+    const int wm = warp / SC_WN, wn = warp % SC_WN;
+    double ss[SC_FN][2];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) ss[j][0] = ss[j][1] = 0.0;
+    for (int j = 0; j < SC_FN; ++j) ss[j][0] = ss[j][1] = 0.0;
     for (int I = 0; I < n_rb; ++I) {
-      double acc[8][4][2];
+      double acc[SC_FM][SC_FN][2];
 #pragma unroll
-      for (int t = 0; t < 8; ++t)
+      for (int t = 0; t < SC_FM; ++t)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) acc[t][j][0] = acc[t][j][1] = 0.0;
+        for (int j = 0; j < SC_FN; ++j) acc[t][j][0] = acc[t][j][1] = 0.0;
       int jend = (I + 1) * (SC_BM / SC_BK);
       if (jend > k_lim) jend = k_lim;
-      const int rbase = I * SC_BM + wm * 8;  // first row of fragment t is rbase + 32 t
+      // first row of fragment t: row fragments are dealt back and forth over the warp rows (see pack_linv_kernel)
+      const int rb_even = I * SC_BM + wm * 8, rb_odd = I * SC_BM + (SC_WM - 1 - wm) * 8;
       for (int J = 0; J < jend; ++J, ++it2) {
         const int s = it2 % SC_STAGES;
         const uint32_t ph = (it2 / SC_STAGES) & 1;
         mbar_wait(&full2[s], ph);
-        const double2* As = reinterpret_cast<const double2*>(Abuf + (size_t)s * SC_BM * SC_BK) + (size_t)wm * 8 * (SC_BK / 8) * 32 + lane;
-        const double2* Bs = reinterpret_cast<const double2*>(Bbuf + (size_t)s * SC_BK * SC_BN) + (size_t)wn * 4 * 32 + lane;
+        const double2* As = reinterpret_cast<const double2*>(Abuf + (size_t)s * SC_BM * SC_BK) + (size_t)wm * SC_FM * (SC_BK / 8) * 32 + lane;
+        const double2* Bs = reinterpret_cast<const double2*>(Bbuf + (size_t)s * SC_BK * SC_BN) + (size_t)wn * SC_FN * 32 + lane;
         // Stages strictly below the diagonal with every row fragment inside n need no predicates:
-        // plain unrolled loads + 128 DMMAs.  Diagonal / last-row-block stages predicate each fragment.
+        // plain unrolled loads + DMMAs.  Diagonal / last-row-block stages predicate each fragment.
         const bool full = (J * SC_BK + SC_BK - 1 <= I * SC_BM) && (I * SC_BM + SC_BM <= a.n);
         if (full) {
 #pragma unroll
           for (int k8 = 0; k8 < SC_BK / 8; ++k8) {
-            double2 b[4], av[8];
+            double2 b[SC_FN], av[SC_FM];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) b[j] = Bs[(k8 * 8 + j) * 32];
+            for (int j = 0; j < SC_FN; ++j) b[j] = Bs[(k8 * SC_NCF + j) * 32];
 #pragma unroll
-            for (int t = 0; t < 8; ++t) av[t] = As[(t * (SC_BK / 8) + k8) * 32];
+            for (int t = 0; t < SC_FM; ++t) av[t] = As[(t * (SC_BK / 8) + k8) * 32];
 #pragma unroll
-            for (int t = 0; t < 8; ++t)
+            for (int t = 0; t < SC_FM; ++t)
 #pragma unroll
-              for (int j = 0; j < 4; ++j) dmma884(acc[t][j][0], acc[t][j][1], av[t].x, b[j].x);
+              for (int j = 0; j < SC_FN; ++j) dmma884(acc[t][j][0], acc[t][j][1], av[t].x, b[j].x);
 #pragma unroll
-            for (int t = 0; t < 8; ++t)
+            for (int t = 0; t < SC_FM; ++t)
 #pragma unroll
-              for (int j = 0; j < 4; ++j) dmma884(acc[t][j][0], acc[t][j][1], av[t].y, b[j].y);
+              for (int j = 0; j < SC_FN; ++j) dmma884(acc[t][j][0], acc[t][j][1], av[t].y, b[j].y);
           }
         } else {
 #pragma unroll
           for (int k8 = 0; k8 < SC_BK / 8; ++k8) {
             const int k0 = J * SC_BK + k8 * 8;
-            double2 b[4], av[8];
+            double2 b[SC_FN], av[SC_FM];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) b[j] = Bs[(k8 * 8 + j) * 32];
+            for (int j = 0; j < SC_FN; ++j) b[j] = Bs[(k8 * SC_NCF + j) * 32];
 #pragma unroll
-            for (int t = 0; t < 8; ++t) av[t] = As[(t * (SC_BK / 8) + k8) * 32];
+            for (int t = 0; t < SC_FM; ++t) av[t] = As[(t * (SC_BK / 8) + k8) * 32];
 #pragma unroll
-            for (int t = 0; t < 8; ++t) {
-              const int r0 = rbase + 32 * t;
+            for (int t = 0; t < SC_FM; ++t) {
+              const int r0 = ((t & 1) ? rb_odd : rb_even) + 8 * SC_WM * t;
               if (r0 < a.n && r0 + 7 >= k0) {
 #pragma unroll
-                for (int j = 0; j < 4; ++j) dmma884(acc[t][j][0], acc[t][j][1], av[t].x, b[j].x);
+                for (int j = 0; j < SC_FN; ++j) dmma884(acc[t][j][0], acc[t][j][1], av[t].x, b[j].x);
 #pragma unroll
-                for (int j = 0; j < 4; ++j) dmma884(acc[t][j][0], acc[t][j][1], av[t].y, b[j].y);
+                for (int j = 0; j < SC_FN; ++j) dmma884(acc[t][j][0], acc[t][j][1], av[t].y, b[j].y);
               }
             }
           }
@@ -310,32 +377,34 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
         if (lane == 0) mbar_arrive(&empty2[s]);
       }
 #pragma unroll
-      for (int t = 0; t < 8; ++t)
+      for (int t = 0; t < SC_FM; ++t)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
+        for (int j = 0; j < SC_FN; ++j) {
           ss[j][0] = fma(acc[t][j][0], acc[t][j][0], ss[j][0]);
           ss[j][1] = fma(acc[t][j][1], acc[t][j][1], ss[j][1]);
         }
     }
-    // reduce over the 8 row lanes (g), then across the 4 row warps via shared memory
+    // reduce over the 8 row lanes (g), then across the SC_WM row warps via shared memory
 #pragma unroll
-    for (int j = 0; j < 4; ++j)
+    for (int j = 0; j < SC_FN; ++j)
 #pragma unroll
       for (int e = 0; e < 2; ++e) {
         double v = ss[j][e];
         v += __shfl_xor_sync(0xffffffffu, v, 4);
         v += __shfl_xor_sync(0xffffffffu, v, 8);
         v += __shfl_xor_sync(0xffffffffu, v, 16);
-        if (g == 0) ssred[wm * SC_BN + wn * 32 + j * 8 + 2 * q + e] = v;
+        if (g == 0) ssred[wm * SC_BN + wn * SC_FN * 8 + j * 8 + 2 * q + e] = v;
       }
     consumer_bar();
 
     // ---- phase 3: posterior, acquisition, running argmax (one thread per candidate)
     if (tid < SC_BN && row0 + tid < a.M) {
-      double s2 = ((ssred[tid] + ssred[SC_BN + tid]) + ssred[2 * SC_BN + tid]) + ssred[3 * SC_BN + tid];
+      double s2 = 0.0;
+#pragma unroll
+      for (int w = 0; w < SC_WM; ++w) s2 += ssred[w * SC_BN + tid];
       double m = 0.0;
 #pragma unroll
-      for (int w = 0; w < 8; ++w) m += mured[w * SC_BN + tid];
+      for (int w = 0; w < SC_CONSUMER_WARPS; ++w) m += mured[w * SC_BN + tid];
       const double mu = a.y_std * m + a.y_mean;
       double var = a.amplitude - s2;
       if (var < 0.0) var = 0.0;
@@ -358,8 +427,8 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
     __syncthreads();  // (B) end of tile: smem union and the k* slice may be reused
   }
 
-  // ---- per-CTA winner: warp-shuffle argmax over threads 0..63, then two warps through smem
-  if (warp < 2) {
+  // ---- per-CTA winner: warp-shuffle argmax inside the SC_BN/32 owner warps, then through smem
+  if (warp < SC_BN / 32) {
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
       double v = best[k].value, m = best[k].mu, sg = best[k].sigma;
@@ -380,13 +449,13 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
   }
   consumer_bar();
   if (tid < 3) {
-    const double* s0 = mured + (0 * 3 + tid) * 4;
-    const double* s1 = mured + (1 * 3 + tid) * 4;
     best_t b;
-    b.value = s0[0]; b.index = __double_as_longlong(s0[1]); b.mu = s0[2]; b.sigma = s0[3];
-    const double v1 = s1[0];
-    const long long i1 = __double_as_longlong(s1[1]);
-    if (better(v1, i1, b.value, b.index)) { b.value = v1; b.index = i1; b.mu = s1[2]; b.sigma = s1[3]; }
+    b.value = -INFINITY; b.index = 0x7fffffffffffffffLL; b.mu = 0.0; b.sigma = 0.0;
+    for (int w = 0; w < SC_BN / 32; ++w) {
+      const double* sl = mured + (w * 3 + tid) * 4;
+      const long long i1 = __double_as_longlong(sl[1]);
+      if (better(sl[0], i1, b.value, b.index)) { b.value = sl[0]; b.index = i1; b.mu = sl[2]; b.sigma = sl[3]; }
+    }
     a.partials[(size_t)blockIdx.x * 3 + tid] = b;
   }
 }
@@ -459,11 +528,9 @@ __global__ void __launch_bounds__(256) acq_partial_kernel(const double* __restri
   }
 }
 
-size_t score_smem_bytes(int D_pad) {
-  size_t un = (size_t)SC_STAGES * (SC_BM * SC_BK + SC_BK * SC_BN);
-  const size_t p1 = (size_t)SC_BN * D_pad + (size_t)P1_STAGES * (P1_OBS * D_pad + 2 * P1_OBS);
-  if (p1 > un) un = p1;
-  return (un + SC_BN + 8 * SC_BN + 4 * SC_BN) * sizeof(double) + (2 * P1_STAGES + 2 * SC_STAGES) * sizeof(uint64_t) + 128;
+size_t score_smem_bytes(int D_pad, int p1_stages) {
+  return (score_union_elems(D_pad, p1_stages) + SC_BN + SC_CONSUMER_WARPS * SC_BN + SC_WM * SC_BN) * sizeof(double) +
+         (2 * P1_STAGES + 2 * SC_STAGES) * sizeof(uint64_t) + 128;
 }
 
 int score_launch(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M, uint64_t first_index, int acq_mask,
@@ -471,8 +538,10 @@ int score_launch(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M,
                  int* grid_out) {
   const ob200_fit_header& h = ctx->hdr;
   const ob200_blob_layout lay = ob_blob_layout(h.n_pad, h.D_pad);
-  const size_t smem = score_smem_bytes(h.D_pad);
-  if (smem > 227 * 1024) OB_FAIL(ctx, OB200_EINVAL, "D=%d too wide for the score kernel's shared-memory tile (max 128)", h.D);
+  int p1_stages = P1_STAGES;
+  size_t smem = score_smem_bytes(h.D_pad, p1_stages);
+  if (smem > 227 * 1024) { p1_stages = 1; smem = score_smem_bytes(h.D_pad, 1); }
+  if (smem > 227 * 1024) OB_FAIL(ctx, OB200_EINVAL, "D=%d too wide for the score kernel's shared-memory tile", h.D);
   const int64_t n_tiles = (M + SC_BN - 1) / SC_BN;
   const int grid = (int)(n_tiles < ctx->num_sms ? n_tiles : ctx->num_sms);
   int rc;
@@ -493,6 +562,7 @@ int score_launch(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M,
   a.partials = reinterpret_cast<best_t*>(ctx->partial_dev);
   a.n_tiles = n_tiles;
   a.accumulate = accumulate;
+  a.p1_stages = p1_stages;
   OB_CUDA(ctx, cudaFuncSetAttribute(score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   score_kernel<<<grid, SC_THREADS, smem, ctx->stream>>>(a);
   OB_LAUNCH_CHECK(ctx);

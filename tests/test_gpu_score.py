@@ -55,7 +55,7 @@ def _compare(engine, X, y, C, kind=0, amp=1.0, ls=1.0, alpha=1e-10 + 1e-4, norma
 
 @pytest.mark.parametrize("n,d,M,kind,normalize_y", [
     (5, 2, 1, 0, True), (5, 2, 63, 0, False), (50, 2, 1000, 0, True), (64, 3, 64, 1, True),
-    (200, 20, 777, 0, True), (257, 7, 2049, 1, False), (700, 60, 1500, 0, True), (1030, 100, 513, 0, True)])
+    (200, 20, 777, 0, True), (257, 7, 2049, 1, False), (100, 150, 300, 0, True), (193, 9, 129, 0, True), (700, 60, 1500, 0, True), (1030, 100, 513, 0, True)])
 def test_posterior_and_acquisition_match_sklearn(engine, n, d, M, kind, normalize_y):
     X, y = gp_problem(n, d, seed=n + d)
     C = np.random.RandomState(1).uniform(size=(M, d))

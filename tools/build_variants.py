@@ -9,6 +9,11 @@ VARIANTS = {
     "bk8s8": ["SC_BK=8", "SC_STAGES=8"],
     "r224": ["SC_CONSUMER_REGS=224"],
     "p1s3": ["P1_STAGES=3"],
+    "w42": ["SC_WM=4", "SC_WN=2", "SC_FM=8", "SC_FN=4"],
+    "w62bk32": ["SC_BK=32", "SC_STAGES=2"],
+    "w62bk32s3": ["SC_BK=32", "SC_STAGES=3"],
+    "skip2": ["SC_DEBUG_SKIP_PHASE2"],
+    "skip1": ["SC_DEBUG_SKIP_PHASE1"],
 }
 if __name__ == "__main__":
     names = sys.argv[1:] or list(VARIANTS)
