@@ -169,6 +169,26 @@ int ob200_acq_argmax(ob200_ctx* ctx, const double* mu_dev, const double* sigma_d
                      uint64_t first_index, int acq_mask, double y_opt, double xi, double kappa,
                      ob200_best* best_host, double* acq_dev);
 
+/* Allocation-free variant of ob200_acq_argmax.  It has no counterpart in the reference; it exists
+ * for callers that must not allocate device memory when they call in -- services that reserve all
+ * GPU memory up front and treat a later cudaMalloc as a fault, or code running after its host
+ * framework has frozen allocation -- and so can neither create a context nor let one grow.
+ *   - no context: works on the calling thread's CURRENT device; mu_dev, sigma_dev [M], best_dev [3]
+ *     and the optional acq_dev [3 x M] are caller-owned device buffers on that device; the result
+ *     is written to best_dev asynchronously on cuda_stream (a cudaStream_t, 0 = default stream).
+ *   - the per-block scratch is a fixed 384 KiB array inside the library's device image (held by
+ *     every GPU that loads the library until exit); it limits one call to 2^24 = 16,777,216
+ *     candidates, larger M is refused with OB200_EINVAL and a message in errbuf (may be NULL).
+ *   - it calls no cudaMalloc / cudaFree or any other allocating routine.  The first call on each
+ *     device looks the scratch array's device address up once; make that first call outside any
+ *     stream capture.
+ *   - all calls share the one scratch array (it keeps the previous call's records, none of which
+ *     a later call reads before overwriting): two calls that overlap on the GPU -- different
+ *     streams or host threads -- race on it; serialise them. */
+int ob200_acq_argmax_static(const double* mu_dev, const double* sigma_dev, int64_t M, uint64_t first_index,
+                            int acq_mask, double y_opt, double xi, double kappa, ob200_best* best_dev,
+                            double* acq_dev, void* cuda_stream, char* errbuf, int errbuf_len);
+
 #ifdef __cplusplus
 }
 #endif

@@ -688,3 +688,89 @@ int ob200_acq_argmax(ob200_ctx* ctx, const double* mu_dev, const double* sigma_d
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// Allocation-free acquisition + argmax.
+//
+// Some hosts of this library may not allocate device memory when they call into it: a real-time
+// or latency-critical service that reserves all of its GPU memory at start-up and treats any
+// later cudaMalloc as a fault (it can stall on the driver's allocator lock or fail under a full
+// memory pool), and code that runs in a phase where allocation is simply forbidden, e.g. between
+// a framework's "memory frozen" point and shutdown.  ob200_acq_argmax needs a context (whose
+// creation allocates) and grows a scratch buffer for the per-block winners on first use; this
+// variant needs neither.  Its scratch is the fixed array below, which lives in the library's
+// device image: every GPU that loads libob200.so holds these 384 KiB until the process exits.
+//
+// The array's name is only meaningful to device code.  On the host it is a placeholder symbol,
+// not a device address, so its address is looked up once per device with cudaGetSymbolAddress
+// (with that device current) and the looked-up pointer is what the kernels receive.
+#define OB200_STATIC_ITEMS_PER_BLOCK 4096                 /* 256 threads x 16 candidates */
+#define OB200_STATIC_MAX_BLOCKS 4096
+#define OB200_STATIC_MAX_M ((int64_t)OB200_STATIC_ITEMS_PER_BLOCK * OB200_STATIC_MAX_BLOCKS) /* 2^24 */
+#define OB200_STATIC_MAX_DEVICES 64
+
+static __device__ __align__(256) unsigned char g_static_partials[OB200_STATIC_MAX_BLOCKS * 3 * sizeof(best_t)];
+
+namespace {
+best_t* g_static_addr[OB200_STATIC_MAX_DEVICES];  // per-device address of g_static_partials (0 = not looked up yet)
+
+void static_fail(char* errbuf, int errbuf_len, const char* msg) {
+  if (errbuf && errbuf_len > 0) snprintf(errbuf, (size_t)errbuf_len, "%s", msg);
+}
+}  // namespace
+
+extern "C" int ob200_acq_argmax_static(const double* mu_dev, const double* sigma_dev, int64_t M, uint64_t first_index,
+                                       int acq_mask, double y_opt, double xi, double kappa, ob200_best* best_dev,
+                                       double* acq_dev, void* cuda_stream, char* errbuf, int errbuf_len) {
+  char msg[256];
+  if (!mu_dev || !sigma_dev || !best_dev || M < 1) {
+    static_fail(errbuf, errbuf_len, "ob200_acq_argmax_static: mu_dev, sigma_dev and best_dev must be non-null and M >= 1");
+    return OB200_EINVAL;
+  }
+  if ((acq_mask & 7) == 0 || (acq_mask & ~7)) {
+    static_fail(errbuf, errbuf_len, "ob200_acq_argmax_static: acq_mask must select EI(1), PI(2) and/or LCB(4)");
+    return OB200_EINVAL;
+  }
+  if (M > OB200_STATIC_MAX_M) {
+    snprintf(msg, sizeof msg,
+             "ob200_acq_argmax_static: M=%lld exceeds the fixed scratch (at most %lld candidates per call); "
+             "split the call or use ob200_acq_argmax", (long long)M, (long long)OB200_STATIC_MAX_M);
+    static_fail(errbuf, errbuf_len, msg);
+    return OB200_EINVAL;
+  }
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= OB200_STATIC_MAX_DEVICES) {
+    static_fail(errbuf, errbuf_len, "ob200_acq_argmax_static: cannot identify the current CUDA device");
+    return OB200_ECUDA;
+  }
+  best_t* scratch = g_static_addr[dev];
+  if (!scratch) {  // first call on this device: resolve the symbol (do this before any stream capture)
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_static_partials);
+    if (e != cudaSuccess || !p) {
+      snprintf(msg, sizeof msg, "ob200_acq_argmax_static: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+      static_fail(errbuf, errbuf_len, msg);
+      return OB200_ECUDA;
+    }
+    scratch = static_cast<best_t*>(p);
+    g_static_addr[dev] = scratch;
+  }
+  cudaStream_t st = (cudaStream_t)cuda_stream;
+  const int grid = (int)((M + OB200_STATIC_ITEMS_PER_BLOCK - 1) / OB200_STATIC_ITEMS_PER_BLOCK);
+  // Nothing in the scratch has to start at zero: each of the `grid` blocks overwrites its own three
+  // records, and the reduction reads exactly those `grid` records, so whatever an earlier (possibly
+  // larger) call left behind is never read.
+  acq_partial_kernel<<<grid, 256, 0, st>>>(mu_dev, sigma_dev, M, first_index, acq_mask, y_opt, xi, kappa, acq_dev, scratch);
+  e = cudaGetLastError();
+  if (e == cudaSuccess) {
+    reduce_best_kernel<<<1, 256, 0, st>>>(scratch, grid, acq_mask, best_dev);
+    e = cudaGetLastError();
+  }
+  if (e != cudaSuccess) {
+    snprintf(msg, sizeof msg, "ob200_acq_argmax_static: kernel launch failed: %s", cudaGetErrorString(e));
+    static_fail(errbuf, errbuf_len, msg);
+    return OB200_ECUDA;
+  }
+  return OB200_OK;
+}
