@@ -61,3 +61,16 @@ def gp_problem(n, d, seed=0, noise=0.01):
     X = rs.uniform(size=(n, d))
     y = ((X - 0.5) ** 2).sum(axis=1) + noise * rs.randn(n)
     return X, y
+
+
+def space_from_spec(spec):
+    """Rebuild a golden-fixture space (tests/golden/sampling_ref.json) with the mirror classes."""
+    s = Space()
+    for item in spec:
+        if item[0] == "categorical":
+            _, name, cats, probs = item
+            s.register(Categorical(name, dict(zip(cats, probs)) if probs else cats))
+        else:
+            kind, name, prior, a, b = item
+            s.register((Real if kind == "real" else Integer)(name, prior, a, b))
+    return s

@@ -1,0 +1,110 @@
+"""Plugin host logic (no GPU): configuration keys, state, deepcopy, observe bookkeeping, the suggest
+flow.  The device is replaced by the oracle-backed `OracleEngine` stand-in (tests only)."""
+import copy
+
+import numpy as np
+import pytest
+
+from metaopt_b200 import engine as engine_mod
+from metaopt_b200.algo import BayesianOptimizer
+from metaopt_b200.space import Categorical, Integer, Real, Space, build_required_space
+
+from fake_engine import OracleEngine
+
+
+@pytest.fixture()
+def fake(monkeypatch):
+    eng = OracleEngine()
+    monkeypatch.setattr(engine_mod, "get_engine", lambda device=None: eng)
+    return eng
+
+
+def small_space():
+    s = Space()
+    s.register(Real("x", "uniform", -2, 4))
+    s.register(Integer("n", "uniform", 1, 8))
+    s.register(Categorical("act", ["relu", "tanh", "gelu"]))
+    return s
+
+
+def objective(point):
+    act, n, x = point  # dimensions come in sorted-name order: act, n, x
+    return (x - 0.5) ** 2 + 0.1 * (n - 3) ** 2 + {"relu": 0.0, "tanh": 0.3, "gelu": 0.1}[act]
+
+
+def test_reference_config_keys_and_defaults():
+    # docs/src/user/algorithms.rst:157-167 and tests/unittests/core/cli/test_info.py:89-98
+    a = BayesianOptimizer(None)
+    conf = a.configuration["bayesianoptimizer"]
+    for key, default in dict(n_initial_points=10, acq_func="gp_hedge", alpha=1e-10, n_restarts_optimizer=0,
+                             noise="gaussian", normalize_y=False).items():
+        assert conf[key] == default
+    assert "seed" in conf and conf["n_points"] == 10000
+    assert BayesianOptimizer.requires == "real"
+    with pytest.raises(ValueError):
+        BayesianOptimizer(None, acq_func="EIps")
+
+
+def test_no_device_work_in_constructor_and_cheap_deepcopy(fake):
+    a = BayesianOptimizer(build_required_space("real", small_space()), seed=3)
+    assert fake.calls == {"sample": 0, "fit": 0, "score": 0}
+    b = copy.deepcopy(a)
+    assert b is not a and b._space is a._space and b.state_dict == a.state_dict
+    b._X.append(np.zeros(3))
+    assert len(a._X) == 0
+    assert "engine" not in " ".join(a.__dict__).lower()  # no device handle inside the instance
+
+
+def test_seeded_suggestions_are_reproducible_and_state_follows(fake):
+    t = build_required_space("real", small_space())
+    a, b = BayesianOptimizer(t, seed=7), BayesianOptimizer(t, seed=7)
+    pa, pb = a.suggest(3), b.suggest(3)
+    assert repr(pa) == repr(pb)
+    for p in pa:
+        assert p in t
+    c = BayesianOptimizer(t, seed=1)
+    c.set_state(a.state_dict)
+    assert repr(c.suggest(1)) == repr(a.suggest(1))
+    a.seed_rng(7)
+    assert repr(a.suggest(3)) == repr(pa)
+
+
+@pytest.mark.parametrize("acq", ["EI", "PI", "LCB", "gp_hedge"])
+def test_observe_then_gp_suggest(fake, acq):
+    space = small_space()
+    t = build_required_space("real", space)
+    a = BayesianOptimizer(t, seed=11, n_initial_points=5, acq_func=acq, n_points=500, normalize_y=True)
+    for _ in range(8):
+        (tp,) = a.suggest(1)
+        assert tp in t
+        a.observe([tp], [{"objective": objective(t.reverse(tp)), "constraint": [], "gradient": None}])
+    assert len(a._y) == 8 and fake.calls["fit"] == 3 and fake.calls["score"] == 3
+    # lies without an objective are ignored, whole-history observe is accepted
+    a.observe([tp], [{"objective": None}])
+    assert len(a._y) == 8
+    d = copy.deepcopy(a)
+    d.observe([tp], [{"objective": 1.0}])
+    assert len(a._y) == 8 and len(d._y) == 9
+    # the engine's fit is keyed by the data: the copy refits, the original reuses
+    n_fit = fake.calls["fit"]
+    d.suggest(1)
+    assert fake.calls["fit"] == n_fit + 1
+    a.suggest(1)
+    assert fake.calls["fit"] == n_fit + 2  # engine now holds the copy's fit -> original refits once
+    a.suggest(1)
+    assert fake.calls["fit"] == n_fit + 2
+
+
+def test_unbounded_space_is_rejected(fake):
+    s = Space()
+    s.register(Real("x", "norm", 0, 1))
+    a = BayesianOptimizer(build_required_space("real", s), seed=1)
+    with pytest.raises(ValueError, match="finite interval"):
+        a.suggest(1)
+
+
+def test_mirror_base_matches_reference_base_behaviour():
+    a = BayesianOptimizer(None, seed=5, n_points=123)
+    assert a.n_points == 123 and a.is_done is False and a.score(None) == 0 and a.judge(None, None) is None
+    assert a.should_suspend is False
+    assert list(a.configuration) == ["bayesianoptimizer"]
