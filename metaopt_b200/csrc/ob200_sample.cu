@@ -5,11 +5,15 @@
 // build_required_space(requires='real') (src/orion/core/worker/transformer.py:51-66, :219-221,
 // :252-254, :269-282, :304-323) plus the skopt-side `(x-low)/(high-low)` normalisation.
 //
-// Layout: output is dense row-major [count x ld] float64.  A CTA produces a tile of R rows into
-// shared memory (one thread per (row, slot pair): one Philox4x32-10 call yields the first-try
-// uniforms of two slots), then the whole contiguous tile leaves with ONE bulk async copy
-// (cp.async.bulk shared->global, TMA engine) when ld == D_out, else with coalesced stores.
-// Two tiles of shared memory are in flight so generation overlaps the store.
+// Layout: output is dense row-major [count x ld] float64.  A CTA produces a tile of 128 rows in
+// shared memory; inside the tile a WARP owns one slot pair for 32 consecutive rows (lane = row), so
+// control flow (kind / prior / number of categories) is warp-uniform and one Philox4x32-10 call
+// yields the first-try uniforms of both slots.  The shared-memory row stride is the row width
+// padded to 2 (mod 4) doubles: rows stay 16-byte aligned and the lane-per-row stores are at most
+// 2-way bank conflicted.  The tile then leaves through the TMA engine: one bulk async copy per row
+// (cp.async.bulk shared->global), or a single one for the whole tile when it is contiguous on both
+// sides.  Odd widths / unaligned outputs fall back to coalesced scalar stores.  Two CTAs of 16
+// warps fit per SM, so one CTA's generation overlaps the other's store phase.
 //
 // RNG contract (restated in oracle/philox.py + oracle/sampling.py, checked bit-exactly):
 //   key = (seed_lo, seed_hi); counter = (index_lo, index_hi, c2, try)
@@ -20,138 +24,202 @@
 
 namespace {
 
-__device__ __forceinline__ int cdf_search_right(const double* __restrict__ cdf, int k, double u) {
-  // numpy searchsorted(cdf, u, side='right'): number of entries <= u
-  int lo = 0, hi = k;
-  while (lo < hi) {
-    int mid = (lo + hi) >> 1;
-    if (cdf[mid] <= u) lo = mid + 1; else hi = mid;
+#define ST_ROWS 128      // rows per tile
+#define ST_THREADS 512
+
+struct philox_keys { uint32_t k0[10], k1[10]; };  // round keys, precomputed on the host (constant bank operands)
+
+__device__ __forceinline__ philox_out philox_rk(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, const philox_keys& rk) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+    const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+    const uint32_t n0 = hi1 ^ c1 ^ rk.k0[r], n2 = hi0 ^ c3 ^ rk.k1[r];
+    c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
   }
-  return lo < k - 1 ? lo : k - 1;
+  return philox_out{c0, c1, c2, c3};
 }
 
-__device__ __forceinline__ double draw_value(const ob200_slot& s, double u, double z) {
-  // no FMA contraction: the reference rounds the product and the sum separately
-  if (s.prior == OB200_PRIOR_UNIFORM) return __dadd_rn(s.p0, __dmul_rn(s.p1, u));
-  if (s.prior == OB200_PRIOR_LOGUNIFORM) return exp(__dadd_rn(s.p0, __dmul_rn(u, s.p1)));
-  return __dadd_rn(s.p0, __dmul_rn(s.p1, z));
+// (hi:lo >> 11) * 2^-53 without a 64-bit integer conversion: both halves convert exactly and the
+// fused sum of two exact products of powers of two is exact, so this equals u53() bit for bit.
+__device__ __forceinline__ double u53_fast(uint32_t lo, uint32_t hi) {
+  const uint32_t top = hi >> 11;                           // 21 bits
+  const uint32_t bot = (hi << 21) | (lo >> 11);            // 32 bits
+  return fma((double)top, 0x1.0p-21, (double)bot * 0x1.0p-53);
 }
 
-__device__ __forceinline__ void emit_slot(const ob200_slot& s, double value, int normalise,
-                                          double* __restrict__ row_out) {
-  const double span = __dsub_rn(s.nhi, s.nlo);
-  if (s.kind == OB200_KIND_CAT && s.ncat > 2) {
-    const int hot = (int)value;
-    for (int j = 0; j < s.width; ++j) {
-      double v = (j == hot) ? 1.0 : 0.0;
-      if (normalise) v = __ddiv_rn(__dsub_rn(v, s.nlo), span);
-      row_out[s.out_col + j] = v;
-    }
+__device__ __forceinline__ double box_muller(philox_out r) {
+  const double ua = u53_fast(r.r0, r.r1), ub = u53_fast(r.r2, r.r3);
+  return __dmul_rn(sqrt(__dmul_rn(-2.0, log(__dsub_rn(1.0, ua)))), cos(__dmul_rn(6.283185307179586, ub)));
+}
+
+// value of a real / integer slot from a uniform u or a standard normal z; never contracted to FMA:
+// the reference rounds the product and the sum separately (scipy: loc + scale * U)
+__device__ __forceinline__ double draw_value(int prior, double p0, double p1, double u, double z) {
+  if (prior == OB200_PRIOR_UNIFORM) return __dadd_rn(p0, __dmul_rn(p1, u));
+  if (prior == OB200_PRIOR_LOGUNIFORM) return exp(__dadd_rn(p0, __dmul_rn(u, p1)));
+  return __dadd_rn(p0, __dmul_rn(p1, z));
+}
+
+// numpy searchsorted(cdf, u, side='right') clamped to k-1: number of entries <= u
+__device__ __forceinline__ int cdf_count(const double* __restrict__ cdf, int k, double u) {
+  int n = 0;
+  if (k <= 8) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) n += (j < k && cdf[j] <= u) ? 1 : 0;
   } else {
-    double v = (s.kind == OB200_KIND_CAT && s.ncat == 1) ? 0.0 : value;
-    if (normalise) v = __ddiv_rn(__dsub_rn(v, s.nlo), span);
-    row_out[s.out_col] = v;
+    int lo = 0, hi = k;
+    while (lo < hi) { const int mid = (lo + hi) >> 1; if (cdf[mid] <= u) lo = mid + 1; else hi = mid; }
+    n = lo;
   }
+  return n < k - 1 ? n : k - 1;
 }
 
-// one slot of one point; u0 = first-try uniform already drawn (non-normal priors)
-__device__ __forceinline__ void do_slot(const ob200_slot& s, int si, const double* __restrict__ cdf,
-                                        uint64_t index, uint32_t k0, uint32_t k1, double u0,
-                                        const double* __restrict__ variate, int normalise,
-                                        double* __restrict__ row_out, int* __restrict__ status) {
-  double value = 0.0;
-  bool done = false;
-  const int tries = variate ? 1 : 4;
-  for (int t = 0; t < tries && !done; ++t) {
-    double u = u0, z = 0.0;
-    if (variate) {
-      u = z = *variate;
-    } else if (s.prior == OB200_PRIOR_NORMAL) {
-      philox_out r = philox4x32_10((uint32_t)index, (uint32_t)(index >> 32), 0x80000000u | (uint32_t)si,
-                                   (uint32_t)t, k0, k1);
-      double ua = u53(r.r0, r.r1), ub = u53(r.r2, r.r3);
-      z = __dmul_rn(sqrt(__dmul_rn(-2.0, log(__dsub_rn(1.0, ua)))), cos(__dmul_rn(6.283185307179586, ub)));
-    } else if (t > 0) {
-      philox_out r = philox4x32_10((uint32_t)index, (uint32_t)(index >> 32), (uint32_t)(si >> 1),
-                                   (uint32_t)t, k0, k1);
-      u = (si & 1) ? u53(r.r2, r.r3) : u53(r.r0, r.r1);
-    }
-    double x;
-    bool ok;
-    if (s.kind == OB200_KIND_CAT) {
-      x = (double)cdf_search_right(cdf + s.cdf_off, s.ncat, u);
-      ok = true;
+// Real.sample's retries (space.py:379-389), tries 1..3.  Rare: kept out of line so the common path
+// stays short and convergent.  Returns the accepted value, or NaN when all tries were rejected.
+__device__ __noinline__ double retry_slot(const ob200_slot* s, int si, uint64_t index, const philox_keys* rk) {
+  const bool is_int = (s->kind == OB200_KIND_INT);
+  for (int t = 1; t < 4; ++t) {
+    double u = 0.0, z = 0.0;
+    if (s->prior == OB200_PRIOR_NORMAL) {
+      z = box_muller(philox_rk((uint32_t)index, (uint32_t)(index >> 32), 0x80000000u | (uint32_t)si, (uint32_t)t, *rk));
     } else {
-      x = draw_value(s, u, z);
-      if (s.kind == OB200_KIND_INT) x = floor(x);
-      ok = (x >= s.low) && (x < s.high);
+      const philox_out r = philox_rk((uint32_t)index, (uint32_t)(index >> 32), (uint32_t)(si >> 1), (uint32_t)t, *rk);
+      u = (si & 1) ? u53_fast(r.r2, r.r3) : u53_fast(r.r0, r.r1);
     }
-    if (ok) { value = x; done = true; }
+    double xt = draw_value(s->prior, s->p0, s->p1, u, z);
+    if (is_int) xt = floor(xt);
+    if ((xt >= s->low) && (xt < s->high)) return xt;
   }
-  if (!done) atomicOr(status, 1);
-  emit_slot(s, value, normalise, row_out);
+  return __longlong_as_double(0x7ff8000000000000LL);
 }
 
-__global__ void __launch_bounds__(256)
-sample_transform_kernel(const ob200_slot* __restrict__ slots, int n_slots, const double* __restrict__ cdf,
-                        int d_out, uint64_t seed, uint64_t first_index, int64_t count, int normalise,
-                        double* __restrict__ out, int64_t ld, const double* __restrict__ variates,
-                        int rows_per_tile, int use_bulk, int* __restrict__ status) {
+// One slot for the 32 rows of a warp (lane = row).  Everything that depends only on the slot is
+// warp-uniform; only the rare rejection retries diverge.
+__device__ __forceinline__ void do_slot(const ob200_slot* __restrict__ sp, int si, const double* __restrict__ cdf, uint64_t index,
+                                        const philox_keys& rk, double u0, const double* __restrict__ variate,
+                                        bool active, int normalise, double* __restrict__ row_out, int* __restrict__ status) {
+  const int kind = sp->kind;
+  const double nlo = sp->nlo, span = __dsub_rn(sp->nhi, nlo);
+  const int col = sp->out_col;
+  if (kind == OB200_KIND_CAT) {
+    const int k = sp->ncat;
+    const double u = variate ? (active ? *variate : 0.0) : u0;
+    const int hot = cdf_count(cdf + sp->cdf_off, k, u);
+    if (k > 2) {
+      double v0 = 0.0, v1 = 1.0;
+      if (normalise) { v0 = __ddiv_rn(__dsub_rn(0.0, nlo), span); v1 = __ddiv_rn(__dsub_rn(1.0, nlo), span); }
+      if (active)
+        for (int j = 0; j < k; ++j) row_out[col + j] = (j == hot) ? v1 : v0;
+    } else {
+      double v = (k == 1) ? 0.0 : (double)hot;
+      if (normalise) v = __ddiv_rn(__dsub_rn(v, nlo), span);
+      if (active) row_out[col] = v;
+    }
+    return;
+  }
+  const int prior = sp->prior;
+  const double p0 = sp->p0, p1 = sp->p1, low = sp->low, high = sp->high;
+  double x;
+  bool ok;
+  if (variate) {  // parity mode: one host-supplied variate, no resampling
+    const double v = active ? *variate : 0.5;
+    x = draw_value(prior, p0, p1, v, v);
+    if (kind == OB200_KIND_INT) x = floor(x);
+    ok = (x >= low) && (x < high);
+  } else {
+    double z = 0.0;
+    if (prior == OB200_PRIOR_NORMAL)
+      z = box_muller(philox_rk((uint32_t)index, (uint32_t)(index >> 32), 0x80000000u | (uint32_t)si, 0u, rk));
+    x = draw_value(prior, p0, p1, u0, z);
+    if (kind == OB200_KIND_INT) x = floor(x);
+    ok = (x >= low) && (x < high);
+    if (__any_sync(0xffffffffu, active && !ok)) {
+      if (active && !ok) {
+        x = retry_slot(sp, si, index, &rk);
+        ok = (x == x);
+      }
+    }
+  }
+  if (active && !ok) { atomicOr(status, 1); x = 0.0; }
+  if (normalise) x = __ddiv_rn(__dsub_rn(x, nlo), span);
+  if (active) row_out[col] = x;
+}
+
+__global__ void __launch_bounds__(ST_THREADS, 2)
+sample_transform_kernel(const ob200_slot* __restrict__ slots_g, int n_slots, const double* __restrict__ cdf_g, int n_cdf,
+                        int d_out, int stride, const __grid_constant__ philox_keys rk, uint64_t first_index, int64_t count,
+                        int normalise, double* __restrict__ out, int64_t ld, const double* __restrict__ variates,
+                        int bulk_ok, int vec_lanes, int* __restrict__ status) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  double* tile[2];
-  tile[0] = reinterpret_cast<double*>(smem_raw);
-  tile[1] = tile[0] + (size_t)rows_per_tile * d_out;
-  const uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+  double* tile = reinterpret_cast<double*>(smem_raw);                        // [ST_ROWS][stride]
+  ob200_slot* slots = reinterpret_cast<ob200_slot*>(tile + (size_t)ST_ROWS * stride);
+  double* cdf = reinterpret_cast<double*>(slots + n_slots);
+  for (int i = threadIdx.x; i < n_slots * (int)(sizeof(ob200_slot) / 8); i += ST_THREADS)
+    reinterpret_cast<double*>(slots)[i] = reinterpret_cast<const double*>(slots_g)[i];
+  for (int i = threadIdx.x; i < n_cdf; i += ST_THREADS) cdf[i] = cdf_g[i];
+  __syncthreads();
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n_pairs = (n_slots + 1) >> 1;
-  const int64_t n_tiles = (count + rows_per_tile - 1) / rows_per_tile;
-  int buf = 0;
-  for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x, buf ^= 1) {
-    const int64_t row0 = t * rows_per_tile;
-    const int rows = (int)min((int64_t)rows_per_tile, count - row0);
-    double* sm = tile[buf];
-    // the bulk store that last read this buffer (two iterations ago) must have drained
-    if (use_bulk && threadIdx.x == 0) bulk_wait_read1();
-    __syncthreads();
-    const int items = rows * n_pairs;
-    for (int it = threadIdx.x; it < items; it += blockDim.x) {
-      const int r = it / n_pairs, p = it - r * n_pairs;
+  const int64_t n_tiles = (count + ST_ROWS - 1) / ST_ROWS;
+  const uint32_t row_bytes = (uint32_t)d_out * 8u;
+
+  for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+    const int64_t row0 = t * ST_ROWS;
+    const int rows = (int)min((int64_t)ST_ROWS, count - row0);
+    for (int rg = 0; rg * 32 < rows; ++rg) {
+      const int r = rg * 32 + lane;
+      const bool active = r < rows;
       const uint64_t index = first_index + (uint64_t)(row0 + r);
-      double* row_out = sm + (size_t)r * d_out;
-      const int s0 = 2 * p, s1 = 2 * p + 1;
-      double ua = 0.0, ub = 0.0;
-      if (!variates) {
-        philox_out pr = philox4x32_10((uint32_t)index, (uint32_t)(index >> 32), (uint32_t)p, 0u, k0, k1);
-        ua = u53(pr.r0, pr.r1);
-        ub = u53(pr.r2, pr.r3);
-      }
-      const double* v0 = variates ? variates + (size_t)(row0 + r) * n_slots + s0 : nullptr;
-      {
-        const ob200_slot s = slots[s0];
-        do_slot(s, s0, cdf, index, k0, k1, ua, v0, normalise, row_out, status);
-      }
-      if (s1 < n_slots) {
-        const ob200_slot s = slots[s1];
-        do_slot(s, s1, cdf, index, k0, k1, ub, v0 ? v0 + 1 : nullptr, normalise, row_out, status);
+      double* row_out = tile + (size_t)r * stride;
+      for (int p = warp; p < n_pairs; p += ST_THREADS / 32) {
+        const int s0 = 2 * p, s1 = 2 * p + 1;
+        double ua = 0.0, ub = 0.0;
+        if (!variates) {
+          const philox_out pr = philox_rk((uint32_t)index, (uint32_t)(index >> 32), (uint32_t)p, 0u, rk);
+          ua = u53_fast(pr.r0, pr.r1);
+          ub = u53_fast(pr.r2, pr.r3);
+        }
+        const double* v0 = variates ? variates + (size_t)(row0 + r) * n_slots + s0 : nullptr;
+        do_slot(slots + s0, s0, cdf, index, rk, ua, v0, active, normalise, row_out, status);
+        if (s1 < n_slots) do_slot(slots + s1, s1, cdf, index, rk, ub, v0 ? v0 + 1 : nullptr, active, normalise, row_out, status);
       }
     }
-    const bool bulk_ok = use_bulk && ((((int64_t)rows * d_out) & 1) == 0);
     if (bulk_ok) {
-      fence_proxy_async();  // make generic-proxy smem writes visible to the async proxy
+      fence_proxy_async();  // generic-proxy smem writes -> async-proxy (TMA) reads
       __syncthreads();
-      if (threadIdx.x == 0) {
-        bulk_s2g(out + row0 * ld, sm, (uint32_t)((size_t)rows * d_out * sizeof(double)));
+      if (warp == 0) {
+        if (bulk_ok == 2) {
+          if (lane == 0) bulk_s2g(out + row0 * ld, tile, (uint32_t)rows * row_bytes);
+        } else {
+          for (int r = lane; r < rows; r += 32) bulk_s2g(out + (row0 + r) * ld, tile + (size_t)r * stride, row_bytes);
+        }
         bulk_commit();
+        bulk_wait_read0();  // the tile is rewritten next iteration
       }
+      __syncthreads();
+    } else if (vec_lanes) {
+      __syncthreads();
+      // 16-byte coalesced stores: a power-of-two group of lanes per row
+      const int sub = lane / vec_lanes, l = lane - sub * vec_lanes, rows_per_iter = 32 / vec_lanes;
+      for (int r = warp * rows_per_iter + sub; r < rows; r += (ST_THREADS / 32) * rows_per_iter) {
+        const double2* src = reinterpret_cast<const double2*>(tile + (size_t)r * stride);
+        double2* dst = reinterpret_cast<double2*>(out + (row0 + r) * ld);
+        for (int c = l; c < (d_out >> 1); c += vec_lanes) dst[c] = src[c];
+      }
+      __syncthreads();
     } else {
       __syncthreads();
-      const int elems = rows * d_out;
-      for (int e = threadIdx.x; e < elems; e += blockDim.x) {
-        const int r = e / d_out, c = e - r * d_out;
-        out[(row0 + r) * ld + c] = sm[e];
+      for (int r = warp; r < rows; r += ST_THREADS / 32) {
+        const double* src = tile + (size_t)r * stride;
+        double* dst = out + (row0 + r) * ld;
+        for (int c = lane; c < d_out; c += 32) dst[c] = src[c];
       }
+      __syncthreads();
     }
   }
-  if (use_bulk && threadIdx.x == 0) bulk_wait0();
+  if (bulk_ok && warp == 0) bulk_wait0();
 }
 
 }  // namespace
@@ -162,18 +230,33 @@ int ob200_sample_launch(ob200_ctx* ctx, uint64_t seed, uint64_t first_index, int
   if (count < 0 || !out_dev || ld < ctx->d_out) OB_FAIL(ctx, OB200_EINVAL, "bad count/out/ld (ld=%lld, D_out=%d)", (long long)ld, ctx->d_out);
   if (count == 0) return OB200_OK;
   const int d_out = ctx->d_out;
-  int rows = (int)(49152 / ((int64_t)d_out * 8));  // 48 KiB per buffer, two buffers
-  if (rows > 128) rows = 128;
-  if (rows < 1) OB_FAIL(ctx, OB200_EINVAL, "D_out=%d too wide for the sampler tile", d_out);
-  if (rows > 1) rows &= ~1;
-  const size_t smem = (size_t)2 * rows * d_out * sizeof(double);
-  const int use_bulk = (ld == d_out) && ((reinterpret_cast<uintptr_t>(out_dev) & 15) == 0) && (rows % 2 == 0 || d_out % 2 == 0);
-  const int64_t n_tiles = (count + rows - 1) / rows;
-  int grid = (int)(n_tiles < (int64_t)ctx->num_sms * 4 ? n_tiles : (int64_t)ctx->num_sms * 4);
-  OB_CUDA(ctx, cudaFuncSetAttribute(sample_transform_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 49152));
-  sample_transform_kernel<<<grid, 256, smem, ctx->stream>>>(ctx->slots_dev, ctx->n_slots, ctx->cdf_dev, d_out,
-                                                            seed, first_index, count, normalise, out_dev, ld,
-                                                            variates_dev, rows, use_bulk, ctx->status_dev);
+  // 16-byte paths need an even width, an even leading dimension and a 16-byte aligned base.  Shared-memory
+  // row stride: width padded to 2 (mod 4) doubles (16-byte aligned rows, <= 2-way conflicts); else odd stride.
+  const int aligned = (d_out % 2 == 0) && (ld % 2 == 0) && ((reinterpret_cast<uintptr_t>(out_dev) & 15) == 0);
+  const int stride = aligned ? ((d_out % 4 == 2) ? d_out : d_out + 2) : (d_out | 1);
+  // copy-out: 2 = one bulk copy per tile (contiguous both sides), 1 = one bulk copy per row (rows >= 512 B),
+  // 0 = cooperative stores (16-byte vectors when aligned)
+  int bulk_ok = 0, vec_lanes = 0;
+  if (aligned && stride == d_out && ld == d_out) bulk_ok = 2;
+  else if (aligned && d_out * 8 >= 512) bulk_ok = 1;
+  else if (aligned) { vec_lanes = 1; while (vec_lanes < 32 && vec_lanes < d_out / 2) vec_lanes <<= 1; }
+  const size_t smem = ((size_t)ST_ROWS * stride + (size_t)ctx->n_cdf) * sizeof(double) + (size_t)ctx->n_slots * sizeof(ob200_slot);
+  if (smem > 227 * 1024) OB_FAIL(ctx, OB200_EINVAL, "D_out=%d too wide for the sampler tile", d_out);
+  const int64_t n_tiles = (count + ST_ROWS - 1) / ST_ROWS;
+  int per_sm = (int)((227 * 1024) / (smem + 1024));
+  if (per_sm > 2048 / ST_THREADS) per_sm = 2048 / ST_THREADS;
+  if (per_sm < 1) per_sm = 1;
+  const int64_t max_grid = (int64_t)ctx->num_sms * per_sm;
+  const int grid = (int)(n_tiles < max_grid ? n_tiles : max_grid);
+  philox_keys rk;
+  {
+    uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+    for (int r = 0; r < 10; ++r) { rk.k0[r] = k0; rk.k1[r] = k1; k0 += 0x9E3779B9u; k1 += 0xBB67AE85u; }
+  }
+  OB_CUDA(ctx, cudaFuncSetAttribute(sample_transform_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  sample_transform_kernel<<<grid, ST_THREADS, smem, ctx->stream>>>(ctx->slots_dev, ctx->n_slots, ctx->cdf_dev, ctx->n_cdf, d_out,
+                                                                   stride, rk, first_index, count, normalise, out_dev, ld,
+                                                                   variates_dev, bulk_ok, vec_lanes, ctx->status_dev);
   OB_LAUNCH_CHECK(ctx);
   return OB200_OK;
 }
