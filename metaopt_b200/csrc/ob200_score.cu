@@ -353,6 +353,10 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
               for (int j = 0; j < SC_FN; ++j) dmma884(acc[t][j][0], acc[t][j][1], av[t].y, b[j].y);
           }
         } else {
+          // Row fragments of a warp are ordered by row, so the active ones form a range [t0, t1):
+          // t >= t0 lies on/below the diagonal of this 8-column block, t < t1 lies inside n.  The
+          // fall-through switch makes the skip a real (warp-uniform) branch; predicated-off DMMAs
+          // would still occupy the tensor pipe.
 #pragma unroll
           for (int k8 = 0; k8 < SC_BK / 8; ++k8) {
             const int k0 = J * SC_BK + k8 * 8;
@@ -361,16 +365,36 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
             for (int j = 0; j < SC_FN; ++j) b[j] = Bs[(k8 * SC_NCF + j) * 32];
 #pragma unroll
             for (int t = 0; t < SC_FM; ++t) av[t] = As[(t * (SC_BK / 8) + k8) * 32];
+            int t0 = SC_FM, t1 = 0;
 #pragma unroll
-            for (int t = 0; t < SC_FM; ++t) {
+            for (int t = SC_FM - 1; t >= 0; --t) {
               const int r0 = ((t & 1) ? rb_odd : rb_even) + 8 * SC_WM * t;
-              if (r0 < a.n && r0 + 7 >= k0) {
-#pragma unroll
-                for (int j = 0; j < SC_FN; ++j) dmma884(acc[t][j][0], acc[t][j][1], av[t].x, b[j].x);
-#pragma unroll
-                for (int j = 0; j < SC_FN; ++j) dmma884(acc[t][j][0], acc[t][j][1], av[t].y, b[j].y);
+              if (r0 + 7 >= k0) t0 = t;
+              if (r0 < a.n && t1 == 0) t1 = t + 1;
+            }
+#define SC_FRAG(T)                                                                                   \
+  {                                                                                                  \
+    _Pragma("unroll") for (int j = 0; j < SC_FN; ++j) dmma884(acc[T][j][0], acc[T][j][1], av[T].x, b[j].x); \
+    _Pragma("unroll") for (int j = 0; j < SC_FN; ++j) dmma884(acc[T][j][0], acc[T][j][1], av[T].y, b[j].y); \
+  }
+            static_assert(SC_FM == 4 || SC_FM == 8, "fragment switch is written for 4 or 8 row fragments per warp");
+            if (t0 < t1) {
+              switch (t0) {
+                case 0: SC_FRAG(0) if (t1 == 1) break;
+                case 1: SC_FRAG(1) if (t1 == 2) break;
+                case 2: SC_FRAG(2) if (t1 == 3) break;
+                case 3: SC_FRAG(3)
+#if SC_FM == 8
+                  if (t1 == 4) break;
+                case 4: SC_FRAG(4) if (t1 == 5) break;
+                case 5: SC_FRAG(5) if (t1 == 6) break;
+                case 6: SC_FRAG(6) if (t1 == 7) break;
+                case 7: SC_FRAG(7)
+#endif
+                default: break;
               }
             }
+#undef SC_FRAG
           }
         }
         __syncwarp();
