@@ -102,8 +102,11 @@ def cpu_reference_rate(X, y, candidates, repeats=1):
     """The reference's CPU path on `candidates`: sklearn predict(return_std) + restated EI + argmin."""
     from oracle import acquisition as oacq
     from oracle import gp as ogp
+    import sklearn  # noqa: F401  (loads the BLAS/OpenMP runtimes that threadpoolctl then finds)
     try:
-        from threadpoolctl import threadpool_info
+        from threadpoolctl import threadpool_info, threadpool_limits
+        # torchrun exports OMP_NUM_THREADS=1; the CPU baseline is entitled to every host core
+        threadpool_limits(limits=os.cpu_count() or 1)
         threads = max([p.get("num_threads", 1) for p in threadpool_info()] or [1])
     except Exception:
         threads = os.cpu_count() or 1
@@ -144,7 +147,7 @@ def run_reference(args):
         "e2e": {"value": value, "unit": "candidates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def run_ours(args):
@@ -311,12 +314,30 @@ def run_ours(args):
     }
     if cpu_baseline:
         line["cpu_baseline"] = cpu_baseline
-    print(json.dumps(line), flush=True)
+    emit(line)
     if multi:
         dist.destroy_process_group()
 
 
+_REAL_STDOUT = None
+
+
+def emit(line):
+    """Print the ONE JSON line on the real stdout (fd 1 is redirected to stderr while running, so that
+    banners printed by native libraries such as NCCL cannot end up in the result stream)."""
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is not None:
+        os.write(_REAL_STDOUT, data)
+    else:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+
+
 def main():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
