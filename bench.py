@@ -250,6 +250,28 @@ def run_ours(args):
         e2e_s = obdist.max_over_ranks(e2e_s, device=dev)
     e2e_value = total / e2e_s
 
+    # ---- exact pruned scoring (same winner, reported separately: `value` stays the dense number) --------
+    pr_rec, n_scored = eng.score_pruned(cand, acq="EI", y_opt=y_opt, xi=XI, first_index=start)
+    pr_steps = max(1, min(args.steps, 5))
+    if multi:
+        dist.barrier()
+    torch.cuda.synchronize()
+    p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    p0.record()
+    for _ in range(pr_steps):
+        pr_rec, n_scored = eng.score_pruned(cand, acq="EI", y_opt=y_opt, xi=XI, first_index=start)
+        if multi:
+            pr_rec = obdist.allgather_best(pr_rec, device=dev)
+    p1.record()
+    torch.cuda.synchronize()
+    pr_ms = p0.elapsed_time(p1) / pr_steps
+    if multi:
+        pr_ms = obdist.max_over_ranks(pr_ms, device=dev)
+    pruned = {"value": total / (pr_ms * 1e-3), "unit": "candidates/s", "ms_per_step": pr_ms,
+              "fully_scored_fraction_rank0": n_scored / count, "same_winner_as_dense": pr_rec.get("EI") == rec.get("EI"),
+              "note": "exact mean-only upper-bound pruning (ob200_score_pruned): identical argmax and values; "
+                      "data-dependent, therefore NOT the headline value"}
+
     if rank != 0:
         if multi:
             dist.destroy_process_group()
@@ -311,6 +333,7 @@ def run_ours(args):
         "gpu_launches": int(launches),
         "roofline": roofline,
         "best": rec.get("EI"),
+        "pruned": pruned,
     }
     if cpu_baseline:
         line["cpu_baseline"] = cpu_baseline

@@ -97,7 +97,8 @@ class BayesianOptimizer(BaseAlgorithm):
     ('EI' | 'PI' | 'LCB' | 'gp_hedge'), `alpha`, `n_restarts_optimizer`, `noise`, `normalize_y`.
     Additive keys (defaults keep reference behaviour): `n_points` (candidates per suggest, skopt's
     default 10000), `xi`, `kappa`, `kernel` ('matern52' | 'rbf'), `length_scale`, `amplitude`,
-    `noise_level` (variance folded into the diagonal when `noise == 'gaussian'`), `device`.
+    `noise_level` (variance folded into the diagonal when `noise == 'gaussian'`), `device`, `prune`
+    (exact mean-only pruning of hopeless candidates for single acquisitions; same winner, faster).
     """
 
     requires = "real"
@@ -105,7 +106,8 @@ class BayesianOptimizer(BaseAlgorithm):
     # pylint: disable=too-many-arguments
     def __init__(self, space, seed=None, n_initial_points=10, acq_func="gp_hedge", alpha=1e-10,
                  n_restarts_optimizer=0, noise="gaussian", normalize_y=False, n_points=10000, xi=0.01,
-                 kappa=1.96, kernel="matern52", length_scale=1.0, amplitude=1.0, noise_level=1e-4, device=0):
+                 kappa=1.96, kernel="matern52", length_scale=1.0, amplitude=1.0, noise_level=1e-4, device=0,
+                 prune=True):
         self._seed = None
         self._offset = 0          # next unused global candidate index of the Philox stream
         self._X = []              # observed points, flat + normalised
@@ -116,7 +118,7 @@ class BayesianOptimizer(BaseAlgorithm):
         super().__init__(space, seed=seed, n_initial_points=n_initial_points, acq_func=acq_func, alpha=alpha,
                          n_restarts_optimizer=n_restarts_optimizer, noise=noise, normalize_y=normalize_y,
                          n_points=n_points, xi=xi, kappa=kappa, kernel=kernel, length_scale=length_scale,
-                         amplitude=amplitude, noise_level=noise_level, device=device)
+                         amplitude=amplitude, noise_level=noise_level, device=device, prune=prune)
         if str(acq_func) not in ("EI", "PI", "LCB", "gp_hedge"):
             raise ValueError("acq_func must be one of 'EI', 'PI', 'LCB', 'gp_hedge' (EIps/PIps need timings "
                              "that Orion does not pass); got %r" % (acq_func,))
@@ -227,8 +229,12 @@ class BayesianOptimizer(BaseAlgorithm):
         M = int(self.n_points)
         hedge = self.acq_func == "gp_hedge"
         mask = 7 if hedge else (1 << _ACQ[self.acq_func])
-        res = eng.score(None, M=M, seed=self._seed, first_index=self._offset, acq_mask=mask, y_opt=y_opt,
-                        xi=float(self.xi), kappa=float(self.kappa))
+        if not hedge and self.prune:
+            res, _ = eng.score_pruned(None, M=M, seed=self._seed, first_index=self._offset, acq=self.acq_func,
+                                      y_opt=y_opt, xi=float(self.xi), kappa=float(self.kappa))
+        else:
+            res = eng.score(None, M=M, seed=self._seed, first_index=self._offset, acq_mask=mask, y_opt=y_opt,
+                            xi=float(self.xi), kappa=float(self.kappa))
         self._offset += M
         if hedge:
             # skopt's gp_hedge: draw one of the three proposals with probability softmax(eta * gains);

@@ -49,6 +49,10 @@ void ob200_ctx_destroy(ob200_ctx* ctx) {
   cudaFree(ctx->cand_tmp);
   cudaFree(ctx->dense_tmp);
   cudaFree(ctx->partial_dev);
+  cudaFree(ctx->ub_dev);
+  cudaFree(ctx->idx_dev);
+  cudaFree(ctx->gather_dev);
+  cudaFree(ctx->prune_small_dev);
   cudaFree(ctx->best_dev);
   if (ctx->best_pinned) cudaFreeHost(ctx->best_pinned);
   if (ctx->pinned) cudaFreeHost(ctx->pinned);

@@ -87,6 +87,14 @@ struct ob200_ctx {
   int64_t partial_cap = 0;
   ob200_best* best_dev = nullptr;  // [3]
   ob200_best* best_pinned = nullptr;
+  double* ub_dev = nullptr;        // pruned scoring: mu / upper bound per candidate
+  int64_t ub_cap = 0;
+  long long* idx_dev = nullptr;    // pruned scoring: compacted survivor indices
+  int64_t idx_cap = 0;
+  double* gather_dev = nullptr;    // pruned scoring: gathered survivor rows
+  int64_t gather_cap = 0;
+  char* prune_small_dev = nullptr; // histogram, counters, block min/max
+  int64_t prune_small_cap = 0;
   double* pinned = nullptr;        // pinned staging for host entry points
   int64_t pinned_cap = 0;
 };

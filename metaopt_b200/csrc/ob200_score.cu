@@ -48,6 +48,8 @@ struct score_args {
   long long n_tiles;
   int accumulate;    // 1: fold the partials already stored (multi-chunk calls)
   int p1_stages;     // phase-1 ring depth (2, or 1 when D is too wide for two stages)
+  int mean_only;     // 1: phase 1 only, write mu_out (pruned scoring, pass 1)
+  const long long* index_map;  // optional: global index of row r (gathered survivors); else first_index + r
 };
 
 // ---- branch-free FP64 math for the cross-kernel epilogue ------------------------------------
@@ -207,7 +209,7 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
         }
       }
       __syncthreads();  // (A) consumers finished phase 1, k* slice written
-      if (is_issuer) {
+      if (is_issuer && !a.mean_only) {
         // ---- phase 2 producer: inv(L) tiles + k* tiles
         const int nJ = a.n_pad / SC_BK;
         for (int I = 0; I < n_rb; ++I) {
@@ -296,7 +298,7 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
           kv.y = kernel_from_d2(a.kind, d21, a.amplitude);
           mup[cf] = fma(kv.x, al0, mup[cf]);
           mup[cf] = fma(kv.y, al1, mup[cf]);
-          dst[cf * 32] = kv;
+          if (!a.mean_only) dst[cf * 32] = kv;
         }
       }
       // mu: reduce over q (4 lanes) then across warps through shared memory
@@ -316,7 +318,7 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
     double ss[SC_FN][2];
 #pragma unroll
     for (int j = 0; j < SC_FN; ++j) ss[j][0] = ss[j][1] = 0.0;
-    for (int I = 0; I < n_rb; ++I) {
+    for (int I = 0; I < (a.mean_only ? 0 : n_rb); ++I) {
       double acc[SC_FM][SC_FN][2];
 #pragma unroll
       for (int t = 0; t < SC_FM; ++t)
@@ -430,21 +432,25 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
 #pragma unroll
       for (int w = 0; w < SC_CONSUMER_WARPS; ++w) m += mured[w * SC_BN + tid];
       const double mu = a.y_std * m + a.y_mean;
-      double var = a.amplitude - s2;
-      if (var < 0.0) var = 0.0;
-      var = var * (a.y_std * a.y_std);
-      const double sigma = sqrt(var);
-      double acq[3];
-      acquisition(mu, sigma, a.y_opt, a.xi, a.kappa, acq);
       const long long row = row0 + tid;
-      if (a.mu_out) a.mu_out[row] = mu;
-      if (a.sigma_out) a.sigma_out[row] = sigma;
-      const long long gidx = (long long)a.first_index + row;
+      if (a.mean_only) {
+        a.mu_out[row] = mu;
+      } else {
+        double var = a.amplitude - s2;
+        if (var < 0.0) var = 0.0;
+        var = var * (a.y_std * a.y_std);
+        const double sigma = sqrt(var);
+        double acq[3];
+        acquisition(mu, sigma, a.y_opt, a.xi, a.kappa, acq);
+        if (a.mu_out) a.mu_out[row] = mu;
+        if (a.sigma_out) a.sigma_out[row] = sigma;
+        const long long gidx = a.index_map ? a.index_map[row] : (long long)a.first_index + row;
 #pragma unroll
-      for (int k = 0; k < 3; ++k) {
-        if (!(a.acq_mask & (1 << k))) continue;
-        if (a.acq_out) a.acq_out[(size_t)k * a.M + row] = acq[k];
-        if (better(acq[k], gidx, best[k].value, best[k].index)) { best[k].value = acq[k]; best[k].index = gidx; best[k].mu = mu; best[k].sigma = sigma; }
+        for (int k = 0; k < 3; ++k) {
+          if (!(a.acq_mask & (1 << k))) continue;
+          if (a.acq_out) a.acq_out[(size_t)k * a.M + row] = acq[k];
+          if (better(acq[k], gidx, best[k].value, best[k].index)) { best[k].value = acq[k]; best[k].index = gidx; best[k].mu = mu; best[k].sigma = sigma; }
+        }
       }
     }
     fence_proxy_async();
@@ -559,7 +565,7 @@ size_t score_smem_bytes(int D_pad, int p1_stages) {
 
 int score_launch(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M, uint64_t first_index, int acq_mask,
                  double y_opt, double xi, double kappa, double* mu_dev, double* sigma_dev, double* acq_dev, int accumulate,
-                 int* grid_out) {
+                 int* grid_out, int mean_only = 0, const long long* index_map = nullptr) {
   const ob200_fit_header& h = ctx->hdr;
   const ob200_blob_layout lay = ob_blob_layout(h.n_pad, h.D_pad);
   int p1_stages = P1_STAGES;
@@ -587,6 +593,8 @@ int score_launch(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M,
   a.n_tiles = n_tiles;
   a.accumulate = accumulate;
   a.p1_stages = p1_stages;
+  a.mean_only = mean_only;
+  a.index_map = index_map;
   OB_CUDA(ctx, cudaFuncSetAttribute(score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   score_kernel<<<grid, SC_THREADS, smem, ctx->stream>>>(a);
   OB_LAUNCH_CHECK(ctx);
@@ -712,6 +720,220 @@ int ob200_acq_argmax(ob200_ctx* ctx, const double* mu_dev, const double* sigma_d
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// Exact pruned scoring.  EI, PI (for y_opt - xi - mu <= 0) and -LCB are increasing in
+// sigma, and sigma^2 <= amplitude * y_std^2 (the prior variance), so U(mu, sigma_max) is an upper
+// bound of the utility that needs only the O(nD) mean.  Pass 1 computes mu for every candidate
+// (phase 1 of the score kernel), a first batch with the largest bounds is scored in full to get an
+// incumbent, and only candidates whose bound reaches the incumbent are scored after that.  Every
+// candidate left out has utility <= bound < incumbent <= maximum, so the argmax (ties included) and
+// the winner's values are bit-identical to the dense call.
+namespace {
+
+#define PR_BINS 2048
+
+__device__ __forceinline__ double upper_bound_utility(int acq, double mu, double sigma_max, double y_opt, double xi, double kappa) {
+  double u[3];
+  acquisition(mu, sigma_max, y_opt, xi, kappa, u);
+  if (acq == OB200_ACQ_PI && (y_opt - xi - mu) > 0.0) return 1.0;  // PI decreases in sigma when the mean already improves
+  return u[acq];
+}
+
+__global__ void __launch_bounds__(256) ub_kernel(const double* __restrict__ mu, long long M, int acq, double sigma_max, double y_opt,
+                                                 double xi, double kappa, double* __restrict__ ub, double* __restrict__ blk_minmax) {
+  __shared__ double smin[256], smax[256];
+  double lo = INFINITY, hi = -INFINITY;
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < M; i += (long long)gridDim.x * 256) {
+    const double v = upper_bound_utility(acq, mu[i], sigma_max, y_opt, xi, kappa);
+    ub[i] = v;
+    if (v == v) { lo = fmin(lo, v); hi = fmax(hi, v); }
+  }
+  smin[threadIdx.x] = lo; smax[threadIdx.x] = hi;
+  __syncthreads();
+  for (int s = 128; s > 0; s >>= 1) {
+    if (threadIdx.x < s) { smin[threadIdx.x] = fmin(smin[threadIdx.x], smin[threadIdx.x + s]); smax[threadIdx.x] = fmax(smax[threadIdx.x], smax[threadIdx.x + s]); }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) { blk_minmax[2 * blockIdx.x] = smin[0]; blk_minmax[2 * blockIdx.x + 1] = smax[0]; }
+}
+
+__global__ void __launch_bounds__(256) hist_kernel(const double* __restrict__ ub, long long M, double lo, double inv_width, int* __restrict__ hist) {
+  __shared__ int sh[PR_BINS];
+  for (int b = threadIdx.x; b < PR_BINS; b += 256) sh[b] = 0;
+  __syncthreads();
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < M; i += (long long)gridDim.x * 256) {
+    const double v = ub[i];
+    int b = (int)((v - lo) * inv_width);
+    b = b < 0 ? 0 : (b >= PR_BINS ? PR_BINS - 1 : b);
+    if (v == v) atomicAdd(&sh[b], 1);
+  }
+  __syncthreads();
+  for (int b = threadIdx.x; b < PR_BINS; b += 256) if (sh[b]) atomicAdd(&hist[b], sh[b]);
+}
+
+// indices with lo <= ub < hi (NaN bounds are always kept: they must be scored), order irrelevant
+__global__ void __launch_bounds__(256) compact_kernel(const double* __restrict__ ub, long long M, double lo, double hi,
+                                                      unsigned long long first_index, long long* __restrict__ rows,
+                                                      unsigned long long* __restrict__ counter) {
+  for (long long i0 = (long long)blockIdx.x * 256; i0 < M; i0 += (long long)gridDim.x * 256) {
+    const long long i = i0 + threadIdx.x;
+    bool keep = false;
+    if (i < M) { const double v = ub[i]; keep = !(v == v) ? (hi == INFINITY) : (v >= lo && v < hi); }
+    const unsigned mask = __ballot_sync(0xffffffffu, keep);
+    if (mask) {
+      const int lane = threadIdx.x & 31, leader = __ffs(mask) - 1;
+      unsigned long long base = 0;
+      if (lane == leader) base = atomicAdd(counter, (unsigned long long)__popc(mask));
+      base = __shfl_sync(0xffffffffu, base, leader);
+      if (keep) rows[base + __popc(mask & ((1u << lane) - 1))] = i;
+    }
+  }
+}
+
+// gather survivor rows into a dense [count x D] matrix and turn row numbers into global indices
+__global__ void __launch_bounds__(256) gather_kernel(const double* __restrict__ cand, long long ldc, int D, long long* __restrict__ rows,
+                                                     long long count, unsigned long long first_index, double* __restrict__ out) {
+  const long long total = count * D;
+  for (long long e = (long long)blockIdx.x * 256 + threadIdx.x; e < total; e += (long long)gridDim.x * 256) {
+    const long long r = e / D;
+    const int d = (int)(e - r * D);
+    out[e] = cand[rows[r] * ldc + d];
+  }
+}
+__global__ void __launch_bounds__(256) globalise_kernel(long long* __restrict__ rows, long long count, unsigned long long first_index) {
+  for (long long r = (long long)blockIdx.x * 256 + threadIdx.x; r < count; r += (long long)gridDim.x * 256) rows[r] += (long long)first_index;
+}
+
+}  // namespace
+
+extern "C" int ob200_score_pruned(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M, uint64_t seed, uint64_t first_index,
+                                  int acq, double y_opt, double xi, double kappa, ob200_best* best_host, int64_t* n_scored_host) {
+  if (!ctx) return OB200_EINVAL;
+  if (acq < 0 || acq > 2) OB_FAIL(ctx, OB200_EINVAL, "acq must be OB200_ACQ_EI, _PI or _LCB");
+  const int mask = 1 << acq;
+  int rc = check_score_args(ctx, M, mask, best_host);
+  if (rc) return rc;
+  OB_CUDA(ctx, cudaSetDevice(ctx->device));
+  const int D = ctx->hdr.D;
+  const int64_t batch = (int64_t)ctx->num_sms * SC_BN;  // one tile per CTA
+  cudaStream_t st = ctx->stream;
+  // small problems, or candidate sets that do not fit in one resident buffer: dense path
+  const bool too_big = !cand_dev && (M * (int64_t)D * 8 > ((int64_t)1 << 31));
+  if (M <= 4 * batch || too_big) {
+    ob200_best tmp[3];
+    rc = ob200_score(ctx, cand_dev, ldc, M, seed, first_index, mask, y_opt, xi, kappa, tmp, nullptr, nullptr, nullptr);
+    if (rc) return rc;
+    best_host[0] = tmp[acq];
+    if (n_scored_host) *n_scored_host = M;
+    return OB200_OK;
+  }
+  if (cand_dev) {
+    if (ldc < D) OB_FAIL(ctx, OB200_EINVAL, "ldc=%lld < D=%d", (long long)ldc, D);
+  } else {
+    if (ctx->n_slots <= 0) OB_FAIL(ctx, OB200_ESTATE, "cand_dev is NULL and no space was set");
+    if (ctx->d_out != D) OB_FAIL(ctx, OB200_EINVAL, "space width %d != fitted D %d", ctx->d_out, D);
+    if ((rc = ob_reserve(ctx, &ctx->cand_tmp, &ctx->cand_cap, M * D))) return rc;
+    if ((rc = ob200_sample_launch(ctx, seed, first_index, M, 1, ctx->cand_tmp, D, nullptr))) return rc;
+    cand_dev = ctx->cand_tmp;
+    ldc = D;
+  }
+  if ((rc = ob_reserve(ctx, &ctx->ub_dev, &ctx->ub_cap, 2 * M))) return rc;
+  if ((rc = ob_reserve(ctx, &ctx->idx_dev, &ctx->idx_cap, M))) return rc;
+  const int nblk = ctx->num_sms * 8;
+  const int64_t small_bytes = (int64_t)nblk * 16 + PR_BINS * 4 + 64;
+  if ((rc = ob_reserve(ctx, &ctx->prune_small_dev, &ctx->prune_small_cap, small_bytes))) return rc;
+  double* mu = ctx->ub_dev;
+  double* ub = ctx->ub_dev + M;
+  double* blk = reinterpret_cast<double*>(ctx->prune_small_dev);
+  int* hist = reinterpret_cast<int*>(ctx->prune_small_dev + (size_t)nblk * 16);
+  unsigned long long* counter = reinterpret_cast<unsigned long long*>(ctx->prune_small_dev + (size_t)nblk * 16 + PR_BINS * 4);
+
+  // pass 1: posterior mean of every candidate
+  int grid = 0;
+  if ((rc = score_launch(ctx, cand_dev, ldc, M, first_index, mask, y_opt, xi, kappa, mu, nullptr, nullptr, 0, &grid, 1, nullptr))) return rc;
+  const double sigma_max = sqrt(ctx->hdr.amplitude) * ctx->hdr.y_std;
+  ub_kernel<<<nblk, 256, 0, st>>>(mu, M, acq, sigma_max, y_opt, xi, kappa, ub, blk);
+  OB_LAUNCH_CHECK(ctx);
+  std::vector<double> h_blk((size_t)nblk * 2);
+  OB_CUDA(ctx, cudaMemcpyAsync(h_blk.data(), blk, (size_t)nblk * 16, cudaMemcpyDeviceToHost, st));
+  OB_CUDA(ctx, cudaMemsetAsync(hist, 0, PR_BINS * 4 + 64, st));
+  OB_CUDA(ctx, cudaStreamSynchronize(st));
+  double lo = INFINITY, hi = -INFINITY;
+  for (int b = 0; b < nblk; ++b) { if (h_blk[2 * b] < lo) lo = h_blk[2 * b]; if (h_blk[2 * b + 1] > hi) hi = h_blk[2 * b + 1]; }
+  double tau = -INFINITY;  // first batch = {ub >= tau}
+  if (hi > lo && lo > -INFINITY && hi < INFINITY) {
+    const double width = (hi - lo) / PR_BINS;
+    hist_kernel<<<nblk, 256, 0, st>>>(ub, M, lo, 1.0 / width, hist);
+    OB_LAUNCH_CHECK(ctx);
+    std::vector<int> h_hist(PR_BINS);
+    OB_CUDA(ctx, cudaMemcpyAsync(h_hist.data(), hist, PR_BINS * 4, cudaMemcpyDeviceToHost, st));
+    OB_CUDA(ctx, cudaStreamSynchronize(st));
+    int64_t acc_count = 0;
+    for (int b = PR_BINS - 1; b >= 0; --b) {
+      acc_count += h_hist[b];
+      if (acc_count >= batch) { tau = lo + width * b; break; }
+    }
+    tau = tau - 1e-9 * fabs(tau);  // bin edges are computed differently on the device: err on the inclusive side
+  }
+  // batch A: the candidates with the largest bounds
+  int64_t n_scored = 0;
+  unsigned long long h_count = 0;
+  compact_kernel<<<nblk, 256, 0, st>>>(ub, M, tau, INFINITY, first_index, ctx->idx_dev, counter);
+  OB_LAUNCH_CHECK(ctx);
+  OB_CUDA(ctx, cudaMemcpyAsync(&h_count, counter, 8, cudaMemcpyDeviceToHost, st));
+  OB_CUDA(ctx, cudaStreamSynchronize(st));
+  int grid_max = 0;
+  ob200_best incumbent{};
+  incumbent.value = -INFINITY;
+  if (h_count > 0) {
+    const int64_t nA = (int64_t)h_count;
+    if ((rc = ob_reserve(ctx, &ctx->gather_dev, &ctx->gather_cap, nA * D))) return rc;
+    gather_kernel<<<nblk, 256, 0, st>>>(cand_dev, ldc, D, ctx->idx_dev, nA, first_index, ctx->gather_dev);
+    OB_LAUNCH_CHECK(ctx);
+    globalise_kernel<<<nblk, 256, 0, st>>>(ctx->idx_dev, nA, first_index);
+    OB_LAUNCH_CHECK(ctx);
+    if ((rc = score_launch(ctx, ctx->gather_dev, D, nA, 0, mask, y_opt, xi, kappa, nullptr, nullptr, nullptr, 0, &grid, 0, ctx->idx_dev))) return rc;
+    grid_max = grid;
+    reduce_best_kernel<<<1, 256, 0, st>>>(reinterpret_cast<const best_t*>(ctx->partial_dev), grid, mask, ctx->best_dev);
+    OB_LAUNCH_CHECK(ctx);
+    OB_CUDA(ctx, cudaMemcpyAsync(ctx->best_pinned, ctx->best_dev, 3 * sizeof(ob200_best), cudaMemcpyDeviceToHost, st));
+    OB_CUDA(ctx, cudaStreamSynchronize(st));
+    incumbent = ctx->best_pinned[acq];
+    n_scored += nA;
+  }
+  // batch B: everything else whose bound still reaches the incumbent (with a rounding margin)
+  const double thr = incumbent.value - 1e-12 * fabs(incumbent.value) - 1e-300;
+  if (thr < tau) {
+    OB_CUDA(ctx, cudaMemsetAsync(counter, 0, 8, st));
+    compact_kernel<<<nblk, 256, 0, st>>>(ub, M, thr, tau, first_index, ctx->idx_dev, counter);
+    OB_LAUNCH_CHECK(ctx);
+    OB_CUDA(ctx, cudaMemcpyAsync(&h_count, counter, 8, cudaMemcpyDeviceToHost, st));
+    OB_CUDA(ctx, cudaStreamSynchronize(st));
+    if (h_count > 0) {
+      const int64_t nB = (int64_t)h_count;
+      if ((rc = ob_reserve(ctx, &ctx->gather_dev, &ctx->gather_cap, nB * D))) return rc;
+      gather_kernel<<<nblk, 256, 0, st>>>(cand_dev, ldc, D, ctx->idx_dev, nB, first_index, ctx->gather_dev);
+      OB_LAUNCH_CHECK(ctx);
+      globalise_kernel<<<nblk, 256, 0, st>>>(ctx->idx_dev, nB, first_index);
+      OB_LAUNCH_CHECK(ctx);
+      // a wider grid than batch A's would read uninitialised partials: run it as a fresh launch and merge on the host
+      if ((rc = score_launch(ctx, ctx->gather_dev, D, nB, 0, mask, y_opt, xi, kappa, nullptr, nullptr, nullptr, 0, &grid, 0, ctx->idx_dev))) return rc;
+      reduce_best_kernel<<<1, 256, 0, st>>>(reinterpret_cast<const best_t*>(ctx->partial_dev), grid, mask, ctx->best_dev);
+      OB_LAUNCH_CHECK(ctx);
+      OB_CUDA(ctx, cudaMemcpyAsync(ctx->best_pinned, ctx->best_dev, 3 * sizeof(ob200_best), cudaMemcpyDeviceToHost, st));
+      OB_CUDA(ctx, cudaStreamSynchronize(st));
+      const ob200_best b = ctx->best_pinned[acq];
+      if (b.value > incumbent.value || (b.value == incumbent.value && b.index < incumbent.index)) incumbent = b;
+      n_scored += nB;
+    }
+  }
+  (void)grid_max;
+  best_host[0] = incumbent;
+  if (n_scored_host) *n_scored_host = n_scored;
+  if (cand_dev == ctx->cand_tmp) return ob200_sample_status(ctx);
+  return OB200_OK;
+}
 
 // ---------------------------------------------------------------------------------------------
 // Allocation-free acquisition + argmax.

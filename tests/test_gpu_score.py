@@ -117,6 +117,34 @@ def test_generated_candidates_equal_explicit_ones(engine):
     assert best == a["EI"]
 
 
+@pytest.mark.parametrize("acq", ["EI", "PI", "LCB"])
+def test_pruned_scoring_is_bit_identical_to_dense(engine, acq):
+    X, y = gp_problem(500, 6, seed=12)
+    engine.fit(X, y, alpha=1e-10 + 1e-4, normalize_y=True, length_scale=0.7)
+    C = torch.as_tensor(np.random.RandomState(4).uniform(size=(150_001, 6))).cuda()
+    k = {"EI": 0, "PI": 1, "LCB": 2}[acq]
+    dense = engine.score(C, acq_mask=1 << k, y_opt=float(y.min()), first_index=77)
+    pruned, n_scored = engine.score_pruned(C, acq=acq, y_opt=float(y.min()), first_index=77)
+    assert pruned == dense
+    assert 0 < n_scored <= C.shape[0]
+    if acq != "PI":
+        assert n_scored < C.shape[0] // 2  # the bound really prunes on this problem
+    # small call falls back to the dense path
+    small, n_small = engine.score_pruned(C[:1000], acq=acq, y_opt=float(y.min()), first_index=77)
+    assert small == engine.score(C[:1000], acq_mask=1 << k, y_opt=float(y.min()), first_index=77) and n_small == 1000
+
+
+def test_pruned_scoring_with_generated_candidates(engine):
+    comp = compiler.compile_space(transformed(cfg3_space()))
+    compiler.upload(engine, comp)
+    X = engine.sample(99, 0, 300).cpu().numpy()
+    y = ((X - 0.5) ** 2).sum(axis=1)
+    engine.fit(X, y, alpha=1e-6, normalize_y=True)
+    dense = engine.score(None, M=120_000, seed=5, first_index=10_000, acq_mask=1, y_opt=float(y.min()))
+    pruned, n_scored = engine.score_pruned(None, M=120_000, seed=5, first_index=10_000, acq="EI", y_opt=float(y.min()))
+    assert pruned == dense and n_scored <= 120_000
+
+
 def test_export_import_roundtrip(engine):
     X, y = gp_problem(260, 6, seed=8)
     engine.fit(X, y, alpha=1e-6, normalize_y=True)
