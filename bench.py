@@ -272,6 +272,29 @@ def run_ours(args):
               "note": "exact mean-only upper-bound pruning (ob200_score_pruned): identical argmax and values; "
                       "data-dependent, therefore NOT the headline value"}
 
+    # ---- suggest() latency through the plugin API (BaseAlgorithm.suggest), rank 0 only --------------------
+    suggest_latency = None
+    if rank == 0:
+        from metaopt_b200.algo import BayesianOptimizer
+        tspace = build_required_space("real", space)
+
+        def plugin_latency(**extra):
+            algo = BayesianOptimizer(tspace, seed=1, n_initial_points=10, acq_func="EI", alpha=ALPHA, noise="gaussian",
+                                     noise_level=NOISE, normalize_y=True, n_points=M, xi=XI, device=local, **extra)
+            pts = [tuple(float(v) for v in row) for row in X]
+            algo.observe(pts, [{"objective": float(v)} for v in y])
+            algo.suggest(1)  # fit + first suggest
+            lat = []
+            for _ in range(max(5, min(20, args.steps * 2))):
+                t1 = time.perf_counter()
+                algo.suggest(1)
+                lat.append((time.perf_counter() - t1) * 1e3)
+            return statistics.median(lat), len(lat)
+        p50_dense, n_calls = plugin_latency(prune=False)
+        p50_pruned, _ = plugin_latency(prune=True)
+        suggest_latency = {"p50_ms_dense": p50_dense, "p50_ms_pruned": p50_pruned, "calls": n_calls, "n_points": M,
+                           "n_obs": N_OBS, "api": "BayesianOptimizer.suggest(1) (host wall clock, fit cached)"}
+
     if rank != 0:
         if multi:
             dist.destroy_process_group()
@@ -334,6 +357,7 @@ def run_ours(args):
         "roofline": roofline,
         "best": rec.get("EI"),
         "pruned": pruned,
+        "suggest_latency": suggest_latency,
     }
     if cpu_baseline:
         line["cpu_baseline"] = cpu_baseline

@@ -38,6 +38,7 @@ void ob200_ctx_destroy(ob200_ctx* ctx) {
   cudaSetDevice(ctx->device);
   cudaDeviceSynchronize();
   cudaFree(ctx->slots_dev);
+  cudaFree(ctx->dslots_dev);
   cudaFree(ctx->cdf_dev);
   cudaFree(ctx->col_nlo_dev);
   cudaFree(ctx->col_nhi_dev);

@@ -17,8 +17,11 @@
 //
 // RNG contract (restated in oracle/philox.py + oracle/sampling.py, checked bit-exactly):
 //   key = (seed_lo, seed_hi); counter = (index_lo, index_hi, c2, try)
-//   uniform / loguniform / choice slot s: c2 = s>>1, uniform = component (s&1) of the pair
-//   normal slot s: c2 = 0x80000000|s, Box-Muller of the pair
+//   Slots are grouped by operation (uniform real, uniform int, loguniform real, loguniform int,
+//   normal real, normal int, one-hot, small categorical -- in that order, table order inside a
+//   group, each group padded to an even size); q = position of the slot in that grouped order.
+//   uniform / loguniform / choice slot: c2 = q>>1, uniform = component (q&1) of the pair
+//   normal slot: c2 = 0x80000000|q, Box-Muller of the pair
 //   try t = 0..3 (Real.sample's 4-try rejection, space.py:379-389); exhausted -> status latch.
 #include "ob200_internal.cuh"
 
@@ -26,6 +29,22 @@ namespace {
 
 #define ST_ROWS 128      // rows per tile
 #define ST_THREADS 512
+
+// Slot as the kernel reads it: 64 bytes = four 16-byte shared-memory loads, everything that only
+// depends on the slot precomputed on the host (ob200_space_set).
+struct __align__(16) dslot {
+  double p0, p1;      // real/int: prior parameters; categorical: normalised values of 0.0 and 1.0
+  double low, high;   // acceptance interval [low, high)
+  double nlo, rspan;  // normalisation: (x - nlo) / span, rspan = RN(1 / span)
+  double span;
+  int col_src;        // out_col | (original slot index << 16)
+  int op;             // OP_* below
+};
+static_assert(sizeof(dslot) == 64, "device slot must be 64 bytes");
+struct dslot_cat { int ncat, cdf_off; };  // categorical slots reinterpret (low) as these two ints
+
+enum { OP_UNIFORM = 0, OP_UNIFORM_INT = 1, OP_LOGUNIFORM = 2, OP_LOGUNIFORM_INT = 3, OP_NORMAL = 4, OP_NORMAL_INT = 5,
+       OP_ONEHOT = 6, OP_CAT_SMALL = 7, OP_NONE = 8 };
 
 struct philox_keys { uint32_t k0[10], k1[10]; };  // round keys, precomputed on the host (constant bank operands)
 
@@ -53,20 +72,83 @@ __device__ __forceinline__ double box_muller(philox_out r) {
   return __dmul_rn(sqrt(__dmul_rn(-2.0, log(__dsub_rn(1.0, ua)))), cos(__dmul_rn(6.283185307179586, ub)));
 }
 
-// value of a real / integer slot from a uniform u or a standard normal z; never contracted to FMA:
-// the reference rounds the product and the sum separately (scipy: loc + scale * U)
-__device__ __forceinline__ double draw_value(int prior, double p0, double p1, double u, double z) {
-  if (prior == OB200_PRIOR_UNIFORM) return __dadd_rn(p0, __dmul_rn(p1, u));
-  if (prior == OB200_PRIOR_LOGUNIFORM) return exp(__dadd_rn(p0, __dmul_rn(u, p1)));
-  return __dadd_rn(p0, __dmul_rn(p1, z));
+// a / b for a slot-constant divisor b with rb = RN(1/b) from the host: q0 = RN(a rb), exact residual
+// r = a - q0 b (one FMA), q = RN(q0 + r rb).  With a correctly rounded reciprocal this final
+// correction step returns the correctly rounded quotient (Markstein 1990), i.e. the same bits as the
+// IEEE division numpy performs, at 3 instructions instead of ~21; tests compare against numpy.
+__device__ __forceinline__ double div_const(double a, double b, double rb) {
+  const double q0 = __dmul_rn(a, rb);
+  const double r = fma(-q0, b, a);
+  return fma(r, rb, q0);
+}
+
+// value of a real / integer slot; products and sums rounded separately like scipy (loc + scale * U)
+template <int OP>
+__device__ __forceinline__ double draw_op(const dslot& s, double u, double z) {
+  double x;
+  if (OP == OP_UNIFORM || OP == OP_UNIFORM_INT) x = __dadd_rn(s.p0, __dmul_rn(s.p1, u));
+  else if (OP == OP_LOGUNIFORM || OP == OP_LOGUNIFORM_INT) x = exp(__dadd_rn(s.p0, __dmul_rn(u, s.p1)));
+  else x = __dadd_rn(s.p0, __dmul_rn(s.p1, z));
+  if (OP & 1) x = floor(x);
+  return x;
+}
+
+// Real.sample's retries (space.py:379-389), tries 1..3.  Rare: out of line.  NaN = all rejected.
+__device__ __noinline__ double retry_slot(const dslot* s, int q, uint64_t index, const philox_keys* rk) {
+  for (int t = 1; t < 4; ++t) {
+    double u = 0.0, z = 0.0;
+    if (s->op == OP_NORMAL || s->op == OP_NORMAL_INT) {
+      z = box_muller(philox_rk((uint32_t)index, (uint32_t)(index >> 32), 0x80000000u | (uint32_t)q, (uint32_t)t, *rk));
+    } else {
+      const philox_out r = philox_rk((uint32_t)index, (uint32_t)(index >> 32), (uint32_t)(q >> 1), (uint32_t)t, *rk);
+      u = (q & 1) ? u53_fast(r.r2, r.r3) : u53_fast(r.r0, r.r1);
+    }
+    double xt;
+    switch (s->op) {
+      case OP_UNIFORM: xt = draw_op<OP_UNIFORM>(*s, u, z); break;
+      case OP_UNIFORM_INT: xt = draw_op<OP_UNIFORM_INT>(*s, u, z); break;
+      case OP_LOGUNIFORM: xt = draw_op<OP_LOGUNIFORM>(*s, u, z); break;
+      case OP_LOGUNIFORM_INT: xt = draw_op<OP_LOGUNIFORM_INT>(*s, u, z); break;
+      case OP_NORMAL: xt = draw_op<OP_NORMAL>(*s, u, z); break;
+      default: xt = draw_op<OP_NORMAL_INT>(*s, u, z); break;
+    }
+    if ((xt >= s->low) && (xt < s->high)) return xt;
+  }
+  return __longlong_as_double(0x7ff8000000000000LL);
+}
+
+template <int OP>
+__device__ __forceinline__ void real_slot(const dslot* __restrict__ sp, int q, uint64_t index, const philox_keys& rk, double u0,
+                                          const double* __restrict__ var_row, bool active, int normalise,
+                                          double* __restrict__ row_out, int* __restrict__ status) {
+  const dslot s = *sp;  // four LDS.128, broadcast
+  double x;
+  bool ok;
+  if (var_row) {  // parity mode: one host-supplied variate, no resampling
+    const double v = active ? var_row[s.col_src >> 16] : 0.5;
+    x = draw_op<OP>(s, v, v);
+    ok = (x >= s.low) && (x < s.high);
+  } else {
+    double z = 0.0;
+    if (OP == OP_NORMAL || OP == OP_NORMAL_INT)
+      z = box_muller(philox_rk((uint32_t)index, (uint32_t)(index >> 32), 0x80000000u | (uint32_t)q, 0u, rk));
+    x = draw_op<OP>(s, u0, z);
+    ok = (x >= s.low) && (x < s.high);
+    if (__any_sync(0xffffffffu, active && !ok)) {
+      if (active && !ok) { x = retry_slot(sp, q, index, &rk); ok = (x == x); }
+    }
+  }
+  if (active && !ok) { atomicOr(status, 1); x = 0.0; }
+  if (normalise) x = div_const(__dsub_rn(x, s.nlo), s.span, s.rspan);
+  if (active) row_out[s.col_src & 0xffff] = x;
 }
 
 // numpy searchsorted(cdf, u, side='right') clamped to k-1: number of entries <= u
 __device__ __forceinline__ int cdf_count(const double* __restrict__ cdf, int k, double u) {
   int n = 0;
-  if (k <= 8) {
+  if (k <= 4) {
 #pragma unroll
-    for (int j = 0; j < 8; ++j) n += (j < k && cdf[j] <= u) ? 1 : 0;
+    for (int j = 0; j < 4; ++j) n += (j < k && cdf[j] <= u) ? 1 : 0;
   } else {
     int lo = 0, hi = k;
     while (lo < hi) { const int mid = (lo + hi) >> 1; if (cdf[mid] <= u) lo = mid + 1; else hi = mid; }
@@ -75,116 +157,91 @@ __device__ __forceinline__ int cdf_count(const double* __restrict__ cdf, int k, 
   return n < k - 1 ? n : k - 1;
 }
 
-// Real.sample's retries (space.py:379-389), tries 1..3.  Rare: kept out of line so the common path
-// stays short and convergent.  Returns the accepted value, or NaN when all tries were rejected.
-__device__ __noinline__ double retry_slot(const ob200_slot* s, int si, uint64_t index, const philox_keys* rk) {
-  const bool is_int = (s->kind == OB200_KIND_INT);
-  for (int t = 1; t < 4; ++t) {
-    double u = 0.0, z = 0.0;
-    if (s->prior == OB200_PRIOR_NORMAL) {
-      z = box_muller(philox_rk((uint32_t)index, (uint32_t)(index >> 32), 0x80000000u | (uint32_t)si, (uint32_t)t, *rk));
+template <bool ONEHOT>
+__device__ __forceinline__ void cat_slot(const dslot* __restrict__ sp, const double* __restrict__ cdf, double u0,
+                                         const double* __restrict__ var_row, bool active, int normalise,
+                                         double* __restrict__ row_out) {
+  const dslot s = *sp;
+  const dslot_cat c = *reinterpret_cast<const dslot_cat*>(&sp->low);
+  const double u = var_row ? (active ? var_row[s.col_src >> 16] : 0.0) : u0;
+  const int hot = cdf_count(cdf + c.cdf_off, c.ncat, u);
+  const double v0 = normalise ? s.p0 : 0.0, v1 = normalise ? s.p1 : 1.0;
+  const int col = s.col_src & 0xffff;
+  if (active) {
+    if (ONEHOT) {
+      for (int j = 0; j < c.ncat; ++j) row_out[col + j] = (j == hot) ? v1 : v0;
     } else {
-      const philox_out r = philox_rk((uint32_t)index, (uint32_t)(index >> 32), (uint32_t)(si >> 1), (uint32_t)t, *rk);
-      u = (si & 1) ? u53_fast(r.r2, r.r3) : u53_fast(r.r0, r.r1);
+      row_out[col] = hot ? v1 : v0;  // k == 2: float(index); k == 1: 0.0
     }
-    double xt = draw_value(s->prior, s->p0, s->p1, u, z);
-    if (is_int) xt = floor(xt);
-    if ((xt >= s->low) && (xt < s->high)) return xt;
   }
-  return __longlong_as_double(0x7ff8000000000000LL);
 }
 
-// One slot for the 32 rows of a warp (lane = row).  Everything that depends only on the slot is
-// warp-uniform; only the rare rejection retries diverge.
-__device__ __forceinline__ void do_slot(const ob200_slot* __restrict__ sp, int si, const double* __restrict__ cdf, uint64_t index,
-                                        const philox_keys& rk, double u0, const double* __restrict__ variate,
+// Both slots of a pair share the operation (groups are padded to even size), so one warp-uniform
+// switch per pair selects straight-line code for the two of them.
+template <int OP>
+__device__ __forceinline__ void pair_op(const dslot* __restrict__ sp, const double* __restrict__ cdf, int q, uint64_t index,
+                                        const philox_keys& rk, double ua, double ub, const double* __restrict__ var_row,
                                         bool active, int normalise, double* __restrict__ row_out, int* __restrict__ status) {
-  const int kind = sp->kind;
-  const double nlo = sp->nlo, span = __dsub_rn(sp->nhi, nlo);
-  const int col = sp->out_col;
-  if (kind == OB200_KIND_CAT) {
-    const int k = sp->ncat;
-    const double u = variate ? (active ? *variate : 0.0) : u0;
-    const int hot = cdf_count(cdf + sp->cdf_off, k, u);
-    if (k > 2) {
-      double v0 = 0.0, v1 = 1.0;
-      if (normalise) { v0 = __ddiv_rn(__dsub_rn(0.0, nlo), span); v1 = __ddiv_rn(__dsub_rn(1.0, nlo), span); }
-      if (active)
-        for (int j = 0; j < k; ++j) row_out[col + j] = (j == hot) ? v1 : v0;
-    } else {
-      double v = (k == 1) ? 0.0 : (double)hot;
-      if (normalise) v = __ddiv_rn(__dsub_rn(v, nlo), span);
-      if (active) row_out[col] = v;
-    }
-    return;
-  }
-  const int prior = sp->prior;
-  const double p0 = sp->p0, p1 = sp->p1, low = sp->low, high = sp->high;
-  double x;
-  bool ok;
-  if (variate) {  // parity mode: one host-supplied variate, no resampling
-    const double v = active ? *variate : 0.5;
-    x = draw_value(prior, p0, p1, v, v);
-    if (kind == OB200_KIND_INT) x = floor(x);
-    ok = (x >= low) && (x < high);
+  if (OP == OP_ONEHOT || OP == OP_CAT_SMALL) {
+    cat_slot<OP == OP_ONEHOT>(sp, cdf, ua, var_row, active, normalise, row_out);
+    if (sp[1].op != OP_NONE) cat_slot<OP == OP_ONEHOT>(sp + 1, cdf, ub, var_row, active, normalise, row_out);
   } else {
-    double z = 0.0;
-    if (prior == OB200_PRIOR_NORMAL)
-      z = box_muller(philox_rk((uint32_t)index, (uint32_t)(index >> 32), 0x80000000u | (uint32_t)si, 0u, rk));
-    x = draw_value(prior, p0, p1, u0, z);
-    if (kind == OB200_KIND_INT) x = floor(x);
-    ok = (x >= low) && (x < high);
-    if (__any_sync(0xffffffffu, active && !ok)) {
-      if (active && !ok) {
-        x = retry_slot(sp, si, index, &rk);
-        ok = (x == x);
-      }
-    }
+    real_slot<OP>(sp, q, index, rk, ua, var_row, active, normalise, row_out, status);
+    if (sp[1].op != OP_NONE) real_slot<OP>(sp + 1, q + 1, index, rk, ub, var_row, active, normalise, row_out, status);
   }
-  if (active && !ok) { atomicOr(status, 1); x = 0.0; }
-  if (normalise) x = __ddiv_rn(__dsub_rn(x, nlo), span);
-  if (active) row_out[col] = x;
 }
 
 __global__ void __launch_bounds__(ST_THREADS, 2)
-sample_transform_kernel(const ob200_slot* __restrict__ slots_g, int n_slots, const double* __restrict__ cdf_g, int n_cdf,
+sample_transform_kernel(const dslot* __restrict__ slots_g, int n_dslots, int n_slots, const double* __restrict__ cdf_g, int n_cdf,
                         int d_out, int stride, const __grid_constant__ philox_keys rk, uint64_t first_index, int64_t count,
                         int normalise, double* __restrict__ out, int64_t ld, const double* __restrict__ variates,
                         int bulk_ok, int vec_lanes, int* __restrict__ status) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  double* tile = reinterpret_cast<double*>(smem_raw);                        // [ST_ROWS][stride]
-  ob200_slot* slots = reinterpret_cast<ob200_slot*>(tile + (size_t)ST_ROWS * stride);
-  double* cdf = reinterpret_cast<double*>(slots + n_slots);
-  for (int i = threadIdx.x; i < n_slots * (int)(sizeof(ob200_slot) / 8); i += ST_THREADS)
+  double* tile = reinterpret_cast<double*>(smem_raw);                                   // [ST_ROWS][stride]
+  dslot* slots = reinterpret_cast<dslot*>(tile + (((size_t)ST_ROWS * stride + 1) & ~(size_t)1));  // 16-byte aligned
+  double* cdf = reinterpret_cast<double*>(slots + n_dslots);
+  for (int i = threadIdx.x; i < n_dslots * (int)(sizeof(dslot) / 8); i += ST_THREADS)
     reinterpret_cast<double*>(slots)[i] = reinterpret_cast<const double*>(slots_g)[i];
   for (int i = threadIdx.x; i < n_cdf; i += ST_THREADS) cdf[i] = cdf_g[i];
   __syncthreads();
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n_pairs = (n_slots + 1) >> 1;
+  const int n_pairs = n_dslots >> 1;
   const int64_t n_tiles = (count + ST_ROWS - 1) / ST_ROWS;
   const uint32_t row_bytes = (uint32_t)d_out * 8u;
 
   for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
     const int64_t row0 = t * ST_ROWS;
     const int rows = (int)min((int64_t)ST_ROWS, count - row0);
-    for (int rg = 0; rg * 32 < rows; ++rg) {
+    const int n_rg = (rows + 31) >> 5;
+    // items = (row group, pair), dealt round-robin to the warps without an integer division
+    int rg = 0, p = warp;
+    while (p >= n_pairs) { p -= n_pairs; ++rg; }
+    while (rg < n_rg) {
       const int r = rg * 32 + lane;
       const bool active = r < rows;
       const uint64_t index = first_index + (uint64_t)(row0 + r);
       double* row_out = tile + (size_t)r * stride;
-      for (int p = warp; p < n_pairs; p += ST_THREADS / 32) {
-        const int s0 = 2 * p, s1 = 2 * p + 1;
-        double ua = 0.0, ub = 0.0;
-        if (!variates) {
-          const philox_out pr = philox_rk((uint32_t)index, (uint32_t)(index >> 32), (uint32_t)p, 0u, rk);
-          ua = u53_fast(pr.r0, pr.r1);
-          ub = u53_fast(pr.r2, pr.r3);
-        }
-        const double* v0 = variates ? variates + (size_t)(row0 + r) * n_slots + s0 : nullptr;
-        do_slot(slots + s0, s0, cdf, index, rk, ua, v0, active, normalise, row_out, status);
-        if (s1 < n_slots) do_slot(slots + s1, s1, cdf, index, rk, ub, v0 ? v0 + 1 : nullptr, active, normalise, row_out, status);
+      const dslot* sp = slots + 2 * p;
+      const double* var_row = variates ? variates + (size_t)(row0 + (active ? r : 0)) * n_slots : nullptr;
+      double ua = 0.0, ub = 0.0;
+      if (!variates) {
+        const philox_out pr = philox_rk((uint32_t)index, (uint32_t)(index >> 32), (uint32_t)p, 0u, rk);
+        ua = u53_fast(pr.r0, pr.r1);
+        ub = u53_fast(pr.r2, pr.r3);
       }
+      switch (sp->op) {
+        case OP_UNIFORM: pair_op<OP_UNIFORM>(sp, cdf, 2 * p, index, rk, ua, ub, var_row, active, normalise, row_out, status); break;
+        case OP_UNIFORM_INT: pair_op<OP_UNIFORM_INT>(sp, cdf, 2 * p, index, rk, ua, ub, var_row, active, normalise, row_out, status); break;
+        case OP_LOGUNIFORM: pair_op<OP_LOGUNIFORM>(sp, cdf, 2 * p, index, rk, ua, ub, var_row, active, normalise, row_out, status); break;
+        case OP_LOGUNIFORM_INT: pair_op<OP_LOGUNIFORM_INT>(sp, cdf, 2 * p, index, rk, ua, ub, var_row, active, normalise, row_out, status); break;
+        case OP_NORMAL: pair_op<OP_NORMAL>(sp, cdf, 2 * p, index, rk, ua, ub, var_row, active, normalise, row_out, status); break;
+        case OP_NORMAL_INT: pair_op<OP_NORMAL_INT>(sp, cdf, 2 * p, index, rk, ua, ub, var_row, active, normalise, row_out, status); break;
+        case OP_ONEHOT: pair_op<OP_ONEHOT>(sp, cdf, 2 * p, index, rk, ua, ub, var_row, active, normalise, row_out, status); break;
+        default: pair_op<OP_CAT_SMALL>(sp, cdf, 2 * p, index, rk, ua, ub, var_row, active, normalise, row_out, status); break;
+      }
+      p += ST_THREADS / 32;
+      while (p >= n_pairs) { p -= n_pairs; ++rg; }
     }
     if (bulk_ok) {
       fence_proxy_async();  // generic-proxy smem writes -> async-proxy (TMA) reads
@@ -222,6 +279,27 @@ sample_transform_kernel(const ob200_slot* __restrict__ slots_g, int n_slots, con
   if (bulk_ok && warp == 0) bulk_wait0();
 }
 
+// host: ABI slot -> device slot
+dslot make_dslot(const ob200_slot& s, int src) {
+  dslot d{};
+  d.col_src = s.out_col | (src << 16);
+  d.nlo = s.nlo;
+  d.span = s.nhi - s.nlo;
+  d.rspan = 1.0 / d.span;
+  if (s.kind == OB200_KIND_CAT) {
+    d.op = s.ncat > 2 ? OP_ONEHOT : OP_CAT_SMALL;
+    d.p0 = (0.0 - s.nlo) / d.span;  // same IEEE operations as numpy's (x - low) / (high - low)
+    d.p1 = (1.0 - s.nlo) / d.span;
+    dslot_cat c{s.ncat, s.cdf_off};
+    memcpy(&d.low, &c, sizeof c);
+  } else {
+    const int base = s.prior == OB200_PRIOR_UNIFORM ? OP_UNIFORM : (s.prior == OB200_PRIOR_LOGUNIFORM ? OP_LOGUNIFORM : OP_NORMAL);
+    d.op = base + (s.kind == OB200_KIND_INT ? 1 : 0);
+    d.p0 = s.p0; d.p1 = s.p1; d.low = s.low; d.high = s.high;
+  }
+  return d;
+}
+
 }  // namespace
 
 int ob200_sample_launch(ob200_ctx* ctx, uint64_t seed, uint64_t first_index, int64_t count, int normalise,
@@ -240,7 +318,7 @@ int ob200_sample_launch(ob200_ctx* ctx, uint64_t seed, uint64_t first_index, int
   if (aligned && stride == d_out && ld == d_out) bulk_ok = 2;
   else if (aligned && d_out * 8 >= 512) bulk_ok = 1;
   else if (aligned) { vec_lanes = 1; while (vec_lanes < 32 && vec_lanes < d_out / 2) vec_lanes <<= 1; }
-  const size_t smem = ((size_t)ST_ROWS * stride + (size_t)ctx->n_cdf) * sizeof(double) + (size_t)ctx->n_slots * sizeof(ob200_slot);
+  const size_t smem = ((((size_t)ST_ROWS * stride + 1) & ~(size_t)1) + (size_t)ctx->n_cdf) * sizeof(double) + (size_t)ctx->n_dslots * sizeof(dslot);
   if (smem > 227 * 1024) OB_FAIL(ctx, OB200_EINVAL, "D_out=%d too wide for the sampler tile", d_out);
   const int64_t n_tiles = (count + ST_ROWS - 1) / ST_ROWS;
   int per_sm = (int)((227 * 1024) / (smem + 1024));
@@ -254,7 +332,7 @@ int ob200_sample_launch(ob200_ctx* ctx, uint64_t seed, uint64_t first_index, int
     for (int r = 0; r < 10; ++r) { rk.k0[r] = k0; rk.k1[r] = k1; k0 += 0x9E3779B9u; k1 += 0xBB67AE85u; }
   }
   OB_CUDA(ctx, cudaFuncSetAttribute(sample_transform_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  sample_transform_kernel<<<grid, ST_THREADS, smem, ctx->stream>>>(ctx->slots_dev, ctx->n_slots, ctx->cdf_dev, ctx->n_cdf, d_out,
+  sample_transform_kernel<<<grid, ST_THREADS, smem, ctx->stream>>>(reinterpret_cast<const dslot*>(ctx->dslots_dev), ctx->n_dslots, ctx->n_slots, ctx->cdf_dev, ctx->n_cdf, d_out,
                                                                    stride, rk, first_index, count, normalise, out_dev, ld,
                                                                    variates_dev, bulk_ok, vec_lanes, ctx->status_dev);
   OB_LAUNCH_CHECK(ctx);
@@ -285,12 +363,29 @@ int ob200_space_set(ob200_ctx* ctx, const ob200_slot* slots_host, int n_slots, c
   }
   OB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   cudaFree(ctx->slots_dev); ctx->slots_dev = nullptr;
+  cudaFree(ctx->dslots_dev); ctx->dslots_dev = nullptr;
   cudaFree(ctx->cdf_dev); ctx->cdf_dev = nullptr;
   cudaFree(ctx->col_nlo_dev); ctx->col_nlo_dev = nullptr;
   cudaFree(ctx->col_nhi_dev); ctx->col_nhi_dev = nullptr;
   ctx->n_slots = 0;
   OB_CUDA(ctx, cudaMalloc((void**)&ctx->slots_dev, (size_t)n_slots * sizeof(ob200_slot)));
   OB_CUDA(ctx, cudaMemcpy(ctx->slots_dev, slots_host, (size_t)n_slots * sizeof(ob200_slot), cudaMemcpyHostToDevice));
+  int n_dslots = 0;
+  {
+    if (n_slots >= 32768 || d_out >= 65536) OB_FAIL(ctx, OB200_EINVAL, "space too wide (slots < 32768, columns < 65536)");
+    // group by operation (even-padded with no-op slots) -- this order defines the RNG position of a slot
+    std::vector<dslot> ds;
+    for (int op = 0; op < OP_NONE; ++op) {
+      for (int i = 0; i < n_slots; ++i) {
+        const dslot d = make_dslot(slots_host[i], i);
+        if (d.op == op) ds.push_back(d);
+      }
+      if (ds.size() & 1) { dslot pad{}; pad.op = OP_NONE; ds.push_back(pad); }
+    }
+    n_dslots = (int)ds.size();
+    OB_CUDA(ctx, cudaMalloc((void**)&ctx->dslots_dev, ds.size() * sizeof(dslot)));
+    OB_CUDA(ctx, cudaMemcpy(ctx->dslots_dev, ds.data(), ds.size() * sizeof(dslot), cudaMemcpyHostToDevice));
+  }
   OB_CUDA(ctx, cudaMalloc((void**)&ctx->cdf_dev, (size_t)(n_cdf > 0 ? n_cdf : 1) * sizeof(double)));
   if (n_cdf > 0) OB_CUDA(ctx, cudaMemcpy(ctx->cdf_dev, cdf_host, (size_t)n_cdf * sizeof(double), cudaMemcpyHostToDevice));
   std::vector<double> lo(d_out, 0.0), hi(d_out, 1.0);
@@ -304,6 +399,7 @@ int ob200_space_set(ob200_ctx* ctx, const ob200_slot* slots_host, int n_slots, c
   OB_CUDA(ctx, cudaMemcpy(ctx->col_nlo_dev, lo.data(), (size_t)d_out * sizeof(double), cudaMemcpyHostToDevice));
   OB_CUDA(ctx, cudaMemcpy(ctx->col_nhi_dev, hi.data(), (size_t)d_out * sizeof(double), cudaMemcpyHostToDevice));
   ctx->n_slots = n_slots;
+  ctx->n_dslots = n_dslots;
   ctx->n_cdf = n_cdf;
   ctx->d_out = d_out;
   return OB200_OK;

@@ -9,8 +9,9 @@ sampled integers/uniforms can be checked exactly.
 
 Counter layout used by `ob200_sample_transform` (metaopt_b200/csrc/ob200_sample.cu):
   counter = (index_lo, index_hi, c2, try), key = (seed_lo, seed_hi)
-  c2 = slot>>1 for uniform/loguniform/choice slots (component slot&1 of the pair),
-  c2 = 0x80000000|slot for normal slots (Box-Muller of the pair)
+  q = position of the slot in the device's grouped order (oracle.sampling.rng_positions)
+  c2 = q>>1 for uniform/loguniform/choice slots (component q&1 of the pair),
+  c2 = 0x80000000|q for normal slots (Box-Muller of the pair)
   -> 4 x uint32 (r0..r3) -> two 53-bit uniforms in [0,1):
        u_a = ((r1<<32 | r0) >> 11) * 2**-53 ,  u_b = ((r3<<32 | r2) >> 11) * 2**-53
 """

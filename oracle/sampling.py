@@ -68,6 +68,27 @@ def one_hot_reverse(x, k):
     return x.argmax(axis=-1)
 
 
+def slot_op(s):
+    """Operation code of a slot (same numbering as the device kernel)."""
+    if s['kind'] == KIND_CAT:
+        return 6 if s['ncat'] > 2 else 7
+    base = {PRIOR_UNIFORM: 0, PRIOR_LOGUNIFORM: 2, PRIOR_NORMAL: 4}[s['prior']]
+    return base + (1 if s['kind'] == KIND_INT else 0)
+
+
+def rng_positions(slots):
+    """Position q of every slot in the device's RNG order: slots grouped by operation (0..7), table
+    order inside a group, each group padded to an even size (device contract, ob200_sample.cu)."""
+    pos, q = [0] * len(slots), 0
+    for op in range(8):
+        members = [i for i, s in enumerate(slots) if slot_op(s) == op]
+        for i in members:
+            pos[i] = q
+            q += 1
+        q += q & 1
+    return pos
+
+
 def sample_transform(slots, cdf, seed, first_index, count, normalise=True, variates=None):
     """Return (out [count x D_out] float64, status).
 
@@ -79,7 +100,9 @@ def sample_transform(slots, cdf, seed, first_index, count, normalise=True, varia
     out = np.zeros((count, d_out))
     status = STATUS_OK
     idx = np.arange(first_index, first_index + count, dtype=np.uint64)
+    qpos = rng_positions(slots)
     for si, s in enumerate(slots):
+        q = qpos[si]
         value = np.zeros(count)
         done = np.zeros(count, dtype=bool)
         tries = 1 if variates is not None else 4
@@ -87,11 +110,11 @@ def sample_transform(slots, cdf, seed, first_index, count, normalise=True, varia
             if variates is not None:
                 u = z = np.asarray(variates[:, si], dtype=np.float64)
             elif s['prior'] == PRIOR_NORMAL:
-                ua, ub = philox.uniform_pair(seed, idx, 0x80000000 | si, t)
+                ua, ub = philox.uniform_pair(seed, idx, 0x80000000 | q, t)
                 u, z = None, box_muller(ua, ub)
             else:
-                ua, ub = philox.uniform_pair(seed, idx, si >> 1, t)
-                u, z = (ua if si % 2 == 0 else ub), None
+                ua, ub = philox.uniform_pair(seed, idx, q >> 1, t)
+                u, z = (ua if q % 2 == 0 else ub), None
             if s['kind'] == KIND_CAT:
                 c = np.asarray(cdf[s['cdf_off']:s['cdf_off'] + s['ncat']])
                 x = np.searchsorted(c, u, side='right').astype(np.float64)

@@ -143,3 +143,25 @@ def test_distribution_of_generated_samples(engine):
     assert np.all(x[:, c0:c0 + 4].sum(axis=1) == 1.0)
     ci = x[:, by_name["c_int"]["col"]]
     assert set(np.unique(ci)) == {-3.0, -2.0, -1.0, 0.0, 1.0, 2.0}
+
+
+def test_normalisation_division_is_ieee_exact_at_scale(engine):
+    """The kernel divides by each slot's constant span with a reciprocal + exact-residual correction
+    instead of an IEEE division; numpy divides.  Check bit equality on 24M quotients over awkward spans."""
+    from metaopt_b200.space import Categorical, Integer, Real, Space
+    s = Space()
+    spans = [(0.0, 1.0), (-3.0, 9.0), (0.1, 0.30000000000000004), (-1e-3, 7e5), (2.0, 2.0000000000000004 + 1e-9),
+             (-0.1, 1.1), (1e-5, 1.0), (123.456, 789.0123), (0.3333333333333333, 0.6666666666666666), (-7.0, 1e-7),
+             (5e-324 + 1.0, 3.0), (1.0, 1.9999999999999998)]
+    for i, (a, b) in enumerate(spans):
+        s.register(Real("r%02d" % i, "uniform", a, b - a))
+    for i in range(6):
+        s.register(Integer("i%02d" % i, "uniform", -5 * i, 17 + 100 * i))
+    for i in range(6):
+        s.register(Categorical("c%02d" % i, list(range(2 + i))))
+    comp = compiler.compile_space(transformed(s))
+    compiler.upload(engine, comp)
+    n = 1_000_000
+    dev = engine.sample(31337, 5, n, normalise=True).cpu().numpy()
+    ref, status = sampling.sample_transform(comp.slots, comp.cdf, 31337, 5, n, normalise=True)
+    assert np.array_equal(dev, ref)
