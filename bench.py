@@ -280,7 +280,8 @@ def run_ours(args):
 
         def plugin_latency(**extra):
             algo = BayesianOptimizer(tspace, seed=1, n_initial_points=10, acq_func="EI", alpha=ALPHA, noise="gaussian",
-                                     noise_level=NOISE, normalize_y=True, n_points=M, xi=XI, device=local, **extra)
+                                     noise_level=NOISE, normalize_y=True, n_points=M, xi=XI, device=local,
+                                     fit_hyperparameters=False, **extra)
             pts = [tuple(float(v) for v in row) for row in X]
             algo.observe(pts, [{"objective": float(v)} for v in y])
             algo.suggest(1)  # fit + first suggest

@@ -129,6 +129,12 @@ int ob200_gp_fit_host(ob200_ctx* ctx, const double* X_host, const double* y_host
                       const ob200_kernel* kernel, double alpha, int normalize_y);
 /* log marginal likelihood of the current fit (sklearn:_gpr.py:541-656, value only). */
 int ob200_gp_lml(ob200_ctx* ctx, double* lml_host);
+/* Gradient of the log marginal likelihood of the current fit (sklearn:_gpr.py:541-656,
+ * log_marginal_likelihood(theta, eval_gradient=True)): grad_host[0] = d/dlog(amplitude),
+ * grad_host[1..D] = d/dlog(length_scale_d) (sum them for an isotropic kernel), grad_host[D+1] =
+ * d/d(diagonal term) (multiply by the noise level for d/dlog(noise)).  n_grad must be D+2.  Needs a
+ * fit made on this context (not an imported one).  Synchronous. */
+int ob200_gp_lml_grad(ob200_ctx* ctx, double* lml_host, double* grad_host, int n_grad);
 /* Parity/debug read-back of L [n x n] (lower, row-major, upper = 0) and alpha_ [n] (either may be NULL). */
 int ob200_gp_get_factor(ob200_ctx* ctx, double* L_host, double* alpha_host);
 /* y statistics used by the fit: y_mean, y_std (after _handle_zeros_in_scale), min(y). */

@@ -98,7 +98,11 @@ class BayesianOptimizer(BaseAlgorithm):
     Additive keys (defaults keep reference behaviour): `n_points` (candidates per suggest, skopt's
     default 10000), `xi`, `kappa`, `kernel` ('matern52' | 'rbf'), `length_scale`, `amplitude`,
     `noise_level` (variance folded into the diagonal when `noise == 'gaussian'`), `device`, `prune`
-    (exact mean-only pruning of hopeless candidates for single acquisitions; same winner, faster).
+    (exact mean-only pruning of hopeless candidates for single acquisitions; same winner, faster),
+    `fit_hyperparameters` (maximise the log marginal likelihood over amplitude, per-dimension length
+    scales and -- when `noise == 'gaussian'` -- the noise level, like the reference's scikit-learn
+    estimator does, with `n_restarts_optimizer` extra starts; `length_scale`/`amplitude`/`noise_level`
+    are then the starting point).
     """
 
     requires = "real"
@@ -107,7 +111,7 @@ class BayesianOptimizer(BaseAlgorithm):
     def __init__(self, space, seed=None, n_initial_points=10, acq_func="gp_hedge", alpha=1e-10,
                  n_restarts_optimizer=0, noise="gaussian", normalize_y=False, n_points=10000, xi=0.01,
                  kappa=1.96, kernel="matern52", length_scale=1.0, amplitude=1.0, noise_level=1e-4, device=0,
-                 prune=True):
+                 prune=True, fit_hyperparameters=True):
         self._seed = None
         self._offset = 0          # next unused global candidate index of the Philox stream
         self._X = []              # observed points, flat + normalised
@@ -115,10 +119,12 @@ class BayesianOptimizer(BaseAlgorithm):
         self._compiled = None
         self._hedge_gains = [0.0, 0.0, 0.0]
         self._hedge_pending = None
+        self._theta = None        # last fitted (amplitude, length_scale[D], noise): warm start of the next fit
         super().__init__(space, seed=seed, n_initial_points=n_initial_points, acq_func=acq_func, alpha=alpha,
                          n_restarts_optimizer=n_restarts_optimizer, noise=noise, normalize_y=normalize_y,
                          n_points=n_points, xi=xi, kappa=kappa, kernel=kernel, length_scale=length_scale,
-                         amplitude=amplitude, noise_level=noise_level, device=device, prune=prune)
+                         amplitude=amplitude, noise_level=noise_level, device=device, prune=prune,
+                         fit_hyperparameters=fit_hyperparameters)
         if str(acq_func) not in ("EI", "PI", "LCB", "gp_hedge"):
             raise ValueError("acq_func must be one of 'EI', 'PI', 'LCB', 'gp_hedge' (EIps/PIps need timings "
                              "that Orion does not pass); got %r" % (acq_func,))
@@ -160,6 +166,7 @@ class BayesianOptimizer(BaseAlgorithm):
         new._y = list(self._y)
         new._hedge_gains = list(self._hedge_gains)
         new._hedge_pending = copy.deepcopy(self._hedge_pending)
+        new._theta = copy.deepcopy(self._theta)
         memo[id(self)] = new
         return new
 
@@ -213,14 +220,28 @@ class BayesianOptimizer(BaseAlgorithm):
         X = np.asarray(self._X, dtype=np.float64)
         y = np.asarray(self._y, dtype=np.float64)
         ls = np.atleast_1d(np.asarray(self.length_scale, dtype=np.float64))
+        kind = _KERNELS[str(self.kernel).lower()]
         h = hashlib.blake2b(digest_size=16)
         for part in (X.tobytes(), y.tobytes(), ls.tobytes(),
-                     repr((self.kernel, self.amplitude, self._diag_noise(), bool(self.normalize_y))).encode()):
+                     repr((self.kernel, self.amplitude, self._diag_noise(), bool(self.normalize_y),
+                           bool(self.fit_hyperparameters), int(self.n_restarts_optimizer))).encode()):
             h.update(part)
         token = h.digest()
         if getattr(eng, "_fit_token", None) != token:
-            eng.fit(X, y, kind=_KERNELS[str(self.kernel).lower()], amplitude=float(self.amplitude), length_scale=ls,
-                    alpha=self._diag_noise(), normalize_y=bool(self.normalize_y))
+            if self.fit_hyperparameters and len(y) >= 2:
+                from . import hyperopt
+                amp0, ls0, nz0 = self._theta if self._theta is not None else (
+                    float(self.amplitude), np.broadcast_to(ls, (X.shape[1],)).copy(), float(self.noise_level))
+                gaussian = self.noise == "gaussian"
+                rng = np.random.RandomState(self._seed % (2 ** 32))
+                Xd, yd = eng.to_device(X), eng.to_device(y)
+                res = hyperopt.optimise(eng, Xd, yd, kind, amp0, ls0, nz0 if gaussian else 0.0, float(self.alpha),
+                                        bool(self.normalize_y), anisotropic=True, optimise_noise=gaussian,
+                                        n_restarts=int(self.n_restarts_optimizer), rng=rng)
+                self._theta = (res.amplitude, np.asarray(res.length_scale), res.noise if gaussian else float(self.noise_level))
+            else:
+                eng.fit(X, y, kind=kind, amplitude=float(self.amplitude), length_scale=ls,
+                        alpha=self._diag_noise(), normalize_y=bool(self.normalize_y))
             eng._fit_token = token
         return float(y.min())
 

@@ -391,6 +391,124 @@ __global__ void write_header_kernel(ob200_fit_header* hdr_dev, ob200_fit_header 
   for (int d = threadIdx.x; d < D_pad; d += blockDim.x) inv_ls_out[d] = d < D ? ls[n_ls == 1 ? 0 : d] : 1.0;
 }
 
+// ------------------------------------------------------------------------------------------
+// Gradient of the log marginal likelihood w.r.t. log(amplitude), log(length_scale_d) and the diagonal
+// term (sklearn/gaussian_process/_gpr.py:541-656: 0.5 tr((alpha alpha^T - K^-1) dK/dtheta)).
+//   W = alpha alpha^T - K^-1 ;  T_ij = W_ij * g(r_ij) with dk/dlog(ls_d) = g(r) * (dx_d/ls_d)^2
+//   d/dlog(ls_d)  = sum_i t_i xs_id^2 - sum_i xs_id (T Xs)_id      (t = row sums of T, Xs = X/ls)
+//   d/dlog(amp)   = 0.5 sum_ij W_ij k_f(r_ij) ;  d/d(diag) = 0.5 tr(W)
+__global__ void transpose_kernel(const double* __restrict__ A, int n_pad, double* __restrict__ At) {
+  __shared__ double t[32][33];
+  const int bx = blockIdx.x * 32, by = blockIdx.y * 32;
+  for (int r = threadIdx.y; r < 32; r += 8) t[r][threadIdx.x] = A[(size_t)(by + r) * n_pad + bx + threadIdx.x];
+  __syncthreads();
+  for (int r = threadIdx.y; r < 32; r += 8) At[(size_t)(bx + r) * n_pad + by + threadIdx.x] = t[threadIdx.x][r];
+}
+
+// one 32x32 tile (tj <= ti): T both triangles, per-tile partial of sum W k_f (off-diagonal tiles count twice)
+__global__ void __launch_bounds__(256) lml_t_kernel(const double* __restrict__ Xs, const double* __restrict__ alpha,
+                                                    const double* __restrict__ Kinv, int n, int n_pad, int D_pad, int kind,
+                                                    double amplitude, double* __restrict__ T, double* __restrict__ amp_part) {
+  const int ti = blockIdx.y, tj = blockIdx.x;
+  const int tile_id = ti * gridDim.x + tj;
+  __shared__ double red[256];
+  if (tj > ti) { if (threadIdx.x == 0) amp_part[tile_id] = 0.0; return; }
+  extern __shared__ double sm[];
+  double* xi = sm;
+  double* xj = sm + 32 * (D_pad + 1);
+  const int ldx = D_pad + 1;
+  for (int e = threadIdx.x; e < 32 * D_pad; e += 256) {
+    const int r = e / D_pad, d = e - r * D_pad;
+    xi[r * ldx + d] = Xs[(size_t)(ti * 32 + r) * D_pad + d];
+    xj[r * ldx + d] = Xs[(size_t)(tj * 32 + r) * D_pad + d];
+  }
+  __syncthreads();
+  double part = 0.0;
+  for (int e = threadIdx.x; e < 1024; e += 256) {
+    const int r = e >> 5, c = e & 31;
+    const int i = ti * 32 + r, j = tj * 32 + c;
+    double tv = 0.0;
+    if (i < n && j < n && (ti != tj || j <= i)) {
+      double d2 = 0.0;
+      for (int d = 0; d < D_pad; ++d) { const double df = xi[r * ldx + d] - xj[c * ldx + d]; d2 = fma(df, df, d2); }
+      const double w = alpha[i] * alpha[j] - Kinv[(size_t)i * n_pad + j];
+      double kf, g;
+      if (kind == OB200_KERNEL_MATERN52) {
+        const double k5 = sqrt(d2) * 2.23606797749979, ex = exp(-k5);
+        kf = amplitude * (1.0 + k5 + k5 * k5 / 3.0) * ex;
+        g = amplitude * (5.0 / 3.0) * (1.0 + k5) * ex;
+      } else {
+        kf = amplitude * exp(-0.5 * d2);
+        g = kf;
+      }
+      tv = w * g;
+      part += (i == j ? 1.0 : 2.0) * w * kf;
+    }
+    if (i < n_pad && j < n_pad) {
+      if (ti != tj || j <= i) {
+        T[(size_t)i * n_pad + j] = tv;
+        if (i != j) T[(size_t)j * n_pad + i] = tv;
+      }
+    }
+  }
+  red[threadIdx.x] = part;
+  __syncthreads();
+  for (int s = 128; s > 0; s >>= 1) { if (threadIdx.x < s) red[threadIdx.x] += red[threadIdx.x + s]; __syncthreads(); }
+  if (threadIdx.x == 0) amp_part[tile_id] = red[0];
+}
+
+// one warp per row i: t_i = sum_j T_ij and P[i][d] = sum_j T_ij Xs[j][d]; then the row's contribution
+// c[i][d] = t_i xs_id^2 - xs_id P_id (deterministic: fixed lane striding, shuffle tree)
+__global__ void __launch_bounds__(256) lml_row_kernel(const double* __restrict__ T, const double* __restrict__ Xs, int n, int n_pad,
+                                                      int D_pad, double* __restrict__ contrib) {
+  const int warp = (blockIdx.x * 256 + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= n) return;
+  const double* Tr = T + (size_t)warp * n_pad;
+  double t = 0.0;
+  for (int j = lane; j < n; j += 32) t += Tr[j];
+  for (int off = 16; off > 0; off >>= 1) t += __shfl_xor_sync(0xffffffffu, t, off);
+  for (int d0 = 0; d0 < D_pad; d0 += 4) {
+    double p0 = 0, p1 = 0, p2 = 0, p3 = 0;
+    for (int j = lane; j < n; j += 32) {
+      const double tv = Tr[j];
+      const double* x = Xs + (size_t)j * D_pad + d0;
+      p0 = fma(tv, x[0], p0); p1 = fma(tv, x[1], p1); p2 = fma(tv, x[2], p2); p3 = fma(tv, x[3], p3);
+    }
+    for (int off = 16; off > 0; off >>= 1) {
+      p0 += __shfl_xor_sync(0xffffffffu, p0, off); p1 += __shfl_xor_sync(0xffffffffu, p1, off);
+      p2 += __shfl_xor_sync(0xffffffffu, p2, off); p3 += __shfl_xor_sync(0xffffffffu, p3, off);
+    }
+    if (lane == 0) {
+      const double* xi = Xs + (size_t)warp * D_pad + d0;
+      double* c = contrib + (size_t)warp * D_pad + d0;
+      c[0] = t * xi[0] * xi[0] - xi[0] * p0; c[1] = t * xi[1] * xi[1] - xi[1] * p1;
+      c[2] = t * xi[2] * xi[2] - xi[2] * p2; c[3] = t * xi[3] * xi[3] - xi[3] * p3;
+    }
+  }
+}
+
+// out[0] = d/dlog(amp), out[1 + d] = d/dlog(ls_d) (d < D_pad), out[1 + D_pad] = d/d(diag)
+__global__ void __launch_bounds__(256) lml_final_kernel(const double* __restrict__ contrib, const double* __restrict__ amp_part,
+                                                        int n_tiles, const double* __restrict__ alpha, const double* __restrict__ Kinv,
+                                                        int n, int n_pad, int D_pad, double* __restrict__ out) {
+  __shared__ double red[256];
+  const int which = blockIdx.x;  // 0: amp, 1..D_pad: ls, D_pad+1: diag
+  double acc = 0.0;
+  if (which == 0) {
+    for (int t = threadIdx.x; t < n_tiles; t += 256) acc += amp_part[t];
+    acc *= 0.5;
+  } else if (which <= D_pad) {
+    for (int i = threadIdx.x; i < n; i += 256) acc += contrib[(size_t)i * D_pad + which - 1];
+  } else {
+    for (int i = threadIdx.x; i < n; i += 256) acc += alpha[i] * alpha[i] - Kinv[(size_t)i * n_pad + i];
+    acc *= 0.5;
+  }
+  red[threadIdx.x] = acc;
+  __syncthreads();
+  for (int s = 128; s > 0; s >>= 1) { if (threadIdx.x < s) red[threadIdx.x] += red[threadIdx.x + s]; __syncthreads(); }
+  if (threadIdx.x == 0) out[which] = red[0];
+}
+
 int launch_gemm(ob200_ctx* ctx, bool trans_b, const gemm_args& g, int batch) {
   dim3 grid(g.N / 64, g.M / 64, batch);
   if (grid.x == 0 || grid.y == 0 || batch == 0) return OB200_OK;
@@ -426,6 +544,7 @@ int ob200_gp_fit(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n
   if (!(kernel->amplitude > 0.0) || !(alpha >= 0.0)) OB_FAIL(ctx, OB200_EINVAL, "amplitude must be > 0 and alpha >= 0");
   OB_CUDA(ctx, cudaSetDevice(ctx->device));
   ctx->fitted = false;
+  ctx->have_local_fit = false;
 
   const int n_pad = (int)ob_round_up(n, SC_BM), D_pad = (int)ob_round_up(D, 4);
   const int nb = n_pad / FB;
@@ -534,6 +653,9 @@ int ob200_gp_fit(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n
   OB_CUDA(ctx, cudaStreamSynchronize(st));
   ctx->blob_bytes = lay.total;
   ctx->fitted = true;
+  ctx->have_local_fit = true;
+  ctx->w_Xs_off = w_Xs;
+  ctx->w_y_off = w_y;
   return OB200_OK;
 }
 
@@ -556,6 +678,49 @@ int ob200_gp_lml(ob200_ctx* ctx, double* lml_host) {
   return OB200_OK;
 }
 
+int ob200_gp_lml_grad(ob200_ctx* ctx, double* lml_host, double* grad_host, int n_grad) {
+  if (!ctx || !grad_host) return OB200_EINVAL;
+  if (!ctx->fitted || !ctx->have_local_fit) OB_FAIL(ctx, OB200_ESTATE, "the gradient needs a fit made on this context");
+  const int n = ctx->hdr.n, n_pad = ctx->hdr.n_pad, D = ctx->hdr.D, D_pad = ctx->hdr.D_pad;
+  if (n_grad != D + 2) OB_FAIL(ctx, OB200_EINVAL, "n_grad must be D + 2 = %d (amplitude, D length scales, diagonal)", D + 2);
+  OB_CUDA(ctx, cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
+  const ob200_blob_layout lay = ob_blob_layout(n_pad, D_pad);
+  const double* alpha = reinterpret_cast<const double*>(ctx->blob + lay.off_alpha);
+  const double* Xinv = ctx->work_dev;                 // dense inv(L), row-major (fit workspace, offset 0)
+  const double* Xs = ctx->work_dev + ctx->w_Xs_off;   // X / ls, row-major [n_pad x D_pad]
+  const int nt = n_pad / 32;
+  const int64_t g_M = 0, g_Kinv = g_M + (int64_t)n_pad * n_pad, g_T = g_Kinv + (int64_t)n_pad * n_pad,
+                g_contrib = g_T + (int64_t)n_pad * n_pad, g_part = g_contrib + (int64_t)n_pad * D_pad,
+                g_out = g_part + (int64_t)nt * nt, g_end = g_out + D_pad + 8;
+  int rc = ob_reserve(ctx, &ctx->grad_dev, &ctx->grad_cap, g_end);
+  if (rc) return rc;
+  double* G = ctx->grad_dev;
+  transpose_kernel<<<dim3(nt, nt), dim3(32, 8), 0, st>>>(Xinv, n_pad, G + g_M);
+  OB_LAUNCH_CHECK(ctx);
+  gemm_args k{};  // K^-1 = inv(L)^T inv(L) = M M^T, lower tiles
+  k.A = G + g_M; k.lda = n_pad; k.B = G + g_M; k.ldb = n_pad; k.C = G + g_Kinv; k.ldc = n_pad;
+  k.M = n_pad; k.N = n_pad; k.K = n_pad; k.alpha = 1.0; k.beta = 0.0; k.lower_only = 1;
+  if ((rc = launch_gemm(ctx, true, k, 1))) return rc;
+  const size_t smem = (size_t)2 * 32 * (D_pad + 1) * sizeof(double);
+  OB_CUDA(ctx, cudaFuncSetAttribute(lml_t_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem > 49152 ? smem : 49152)));
+  lml_t_kernel<<<dim3(nt, nt), 256, smem, st>>>(Xs, alpha, G + g_Kinv, n, n_pad, D_pad, ctx->hdr.kernel_kind, ctx->hdr.amplitude,
+                                                 G + g_T, G + g_part);
+  OB_LAUNCH_CHECK(ctx);
+  lml_row_kernel<<<(n * 32 + 255) / 256, 256, 0, st>>>(G + g_T, Xs, n, n_pad, D_pad, G + g_contrib);
+  OB_LAUNCH_CHECK(ctx);
+  lml_final_kernel<<<D_pad + 2, 256, 0, st>>>(G + g_contrib, G + g_part, nt * nt, alpha, G + g_Kinv, n, n_pad, D_pad, G + g_out);
+  OB_LAUNCH_CHECK(ctx);
+  std::vector<double> h((size_t)D_pad + 2);
+  OB_CUDA(ctx, cudaMemcpyAsync(h.data(), G + g_out, (size_t)(D_pad + 2) * 8, cudaMemcpyDeviceToHost, st));
+  OB_CUDA(ctx, cudaStreamSynchronize(st));
+  grad_host[0] = h[0];
+  for (int d = 0; d < D; ++d) grad_host[1 + d] = h[1 + d];
+  grad_host[1 + D] = h[1 + D_pad];
+  if (lml_host) *lml_host = ctx->hdr.lml;
+  return OB200_OK;
+}
+
 int ob200_gp_get_ystats(ob200_ctx* ctx, double* y_mean, double* y_std, double* y_min) {
   if (!ctx) return OB200_EINVAL;
   if (!ctx->fitted) OB_FAIL(ctx, OB200_ESTATE, "no fit");
@@ -568,7 +733,7 @@ int ob200_gp_get_ystats(ob200_ctx* ctx, double* y_mean, double* y_std, double* y
 int ob200_gp_get_factor(ob200_ctx* ctx, double* L_host, double* alpha_host) {
   if (!ctx) return OB200_EINVAL;
   if (!ctx->fitted) OB_FAIL(ctx, OB200_ESTATE, "no fit");
-  if (L_host && !ctx->L_dev) OB_FAIL(ctx, OB200_ESTATE, "L is not kept on contexts that imported their fit");
+  if (L_host && !ctx->have_local_fit) OB_FAIL(ctx, OB200_ESTATE, "L is not kept on contexts that imported their fit");
   OB_CUDA(ctx, cudaSetDevice(ctx->device));
   const int n = ctx->hdr.n, n_pad = ctx->hdr.n_pad;
   if (L_host)
@@ -603,6 +768,7 @@ int ob200_gp_import(ob200_ctx* ctx, const void* blob_dev, int64_t bytes) {
   const ob200_blob_layout lay = ob_blob_layout(h.n_pad, h.D_pad);
   if (bytes < lay.total) OB_FAIL(ctx, OB200_EINVAL, "blob truncated");
   ctx->fitted = false;
+  ctx->have_local_fit = false;
   int rc = ob_reserve(ctx, &ctx->blob, &ctx->blob_cap, lay.total);
   if (rc) return rc;
   OB_CUDA(ctx, cudaMemcpyAsync(ctx->blob, blob_dev, (size_t)lay.total, cudaMemcpyDeviceToDevice, ctx->stream));

@@ -76,6 +76,10 @@ struct ob200_ctx {
   int64_t L_cap = 0;
   double* work_dev = nullptr;      // fit workspace
   int64_t work_cap = 0;
+  bool have_local_fit = false;     // work_dev / L_dev hold the factors of the current fit (not an imported one)
+  int64_t w_Xs_off = 0, w_y_off = 0;  // offsets (doubles) of X/ls and normalised y inside work_dev
+  double* grad_dev = nullptr;      // LML-gradient workspace
+  int64_t grad_cap = 0;
 
   // score scratch
   double* kstar_dev = nullptr;     // per-CTA K* slices

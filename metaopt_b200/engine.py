@@ -65,6 +65,10 @@ class Engine:
         s = torch.cuda.current_stream(self.tdev).cuda_stream
         self._check(self.lib.ob200_set_stream(self.ctx, C.c_void_p(s)))
 
+    def to_device(self, array):
+        """numpy -> float64 tensor on this engine's device (kept resident across repeated fits)."""
+        return torch.as_tensor(np.ascontiguousarray(array, dtype=np.float64)).to(self.tdev)
+
     def sync(self):
         self._check(self.lib.ob200_sync(self.ctx))
 
@@ -140,6 +144,14 @@ class Engine:
         v = C.c_double()
         self._check(self.lib.ob200_gp_lml(self.ctx, C.byref(v)))
         return v.value
+
+    def lml_grad(self):
+        """(lml, grad) of the current fit; grad = [dlog(amplitude), dlog(ls_0..D-1), d(diagonal)]."""
+        self.use_torch_stream()
+        v = C.c_double()
+        g = (C.c_double * (self.D + 2))()
+        self._check(self.lib.ob200_gp_lml_grad(self.ctx, C.byref(v), g, self.D + 2))
+        return v.value, np.asarray(list(g))
 
     def get_factor(self):
         L = np.empty((self.n, self.n), dtype=np.float64)

@@ -47,7 +47,34 @@ class OracleEngine:
         self.calls["fit"] += 1
         X = np.asarray(X, float)
         ls = np.broadcast_to(np.asarray(length_scale, float), (X.shape[1],)).copy()
-        self.model = ogp.NumpyGP(kind, amplitude, ls, alpha, normalize_y).fit(X, np.asarray(y, float))
+        self._y_raw = np.asarray(y, float)
+        self.model = ogp.NumpyGP(kind, amplitude, ls, alpha, normalize_y).fit(X, self._y_raw)
+
+    def to_device(self, array):
+        return np.asarray(array, dtype=float)
+
+    def lml(self):
+        return float(self._gpr().log_marginal_likelihood_value_)
+
+    def _gpr(self):
+        from sklearn.gaussian_process import GaussianProcessRegressor
+        from sklearn.gaussian_process.kernels import RBF, ConstantKernel, Matern
+        m = self.model
+        base = Matern(length_scale=m.length_scale, nu=2.5) if m.kind == 0 else RBF(length_scale=m.length_scale)
+        return GaussianProcessRegressor(kernel=ConstantKernel(m.amplitude) * base, alpha=m.alpha, optimizer=None,
+                                        normalize_y=m.normalize_y).fit(m.X, self._y_raw)
+
+    def lml_grad(self):
+        """[dlog amp, dlog ls_d..., d(diag)] from sklearn's analytic gradient (+ a numeric diagonal term)."""
+        g = self._gpr()
+        lml, grad = g.log_marginal_likelihood(g.kernel_.theta, eval_gradient=True)
+        m = self.model
+        y = (self._y_raw - m.y_mean) / m.y_std
+        import numpy.linalg as la
+        Kinv = la.inv(m.L @ m.L.T)
+        a = Kinv @ y
+        d_diag = 0.5 * (a @ a - np.trace(Kinv))
+        return float(lml), np.concatenate([grad, [d_diag]])
 
     def score(self, cand=None, M=None, seed=0, first_index=0, acq_mask=1, y_opt=0.0, xi=0.01, kappa=1.96, dense=False):
         self.calls["score"] += 1

@@ -73,7 +73,8 @@ def test_seeded_suggestions_are_reproducible_and_state_follows(fake):
 def test_observe_then_gp_suggest(fake, acq):
     space = small_space()
     t = build_required_space("real", space)
-    a = BayesianOptimizer(t, seed=11, n_initial_points=5, acq_func=acq, n_points=500, normalize_y=True)
+    a = BayesianOptimizer(t, seed=11, n_initial_points=5, acq_func=acq, n_points=500, normalize_y=True,
+                          fit_hyperparameters=False)
     for _ in range(8):
         (tp,) = a.suggest(1)
         assert tp in t
@@ -108,3 +109,18 @@ def test_mirror_base_matches_reference_base_behaviour():
     assert a.n_points == 123 and a.is_done is False and a.score(None) == 0 and a.judge(None, None) is None
     assert a.should_suspend is False
     assert list(a.configuration) == ["bayesianoptimizer"]
+
+
+def test_hyperparameters_are_fitted_and_warm_started(fake):
+    space = small_space()
+    t = build_required_space("real", space)
+    a = BayesianOptimizer(t, seed=2, n_initial_points=6, acq_func="EI", n_points=300, normalize_y=True)
+    assert a.configuration["bayesianoptimizer"]["fit_hyperparameters"] is True
+    for _ in range(9):
+        (tp,) = a.suggest(1)
+        a.observe([tp], [{"objective": objective(t.reverse(tp))}])
+    amp, ls, noise = a._theta
+    assert len(ls) == 5 and 1e-2 <= amp <= 1e3 and np.all((ls >= 1e-2 * (1 - 1e-9)) & (ls <= 1e2 * (1 + 1e-9))) and 1e-5 * (1 - 1e-9) <= noise <= 1e5 * (1 + 1e-9)
+    assert fake.calls["fit"] > 3  # several likelihood evaluations per refit
+    b = copy.deepcopy(a)
+    assert b._theta[0] == a._theta[0] and b._theta[1] is not a._theta[1]

@@ -45,7 +45,8 @@ def test_cfg1_rosenbrock_50_trials_with_per_suggest_parity(engine):
         if trial >= 10:
             # oracle replay of this suggestion on the SAME candidates (Philox restated in numpy)
             C, _ = osamp.sample_transform(comp.slots, comp.cdf, a._seed, offset_before, 10000, True)
-            model = ogp.SklearnGP(0, 1.0, 0.3 * np.ones(2), 1e-10 + 1e-4, True).fit(np.asarray(a._X), np.asarray(a._y))
+            amp, ls, noise = a._theta  # hyper-parameters the plugin fitted for this suggest (device L-BFGS-B)
+            model = ogp.SklearnGP(0, amp, ls, 1e-10 + noise, True).fit(np.asarray(a._X), np.asarray(a._y))
             mu, sd = model.predict(C)
             pick = oacq.pick(oacq.ACQ_EI, mu, sd, float(min(a._y)))
             want = comp.denormalise(C[pick])
@@ -57,6 +58,24 @@ def test_cfg1_rosenbrock_50_trials_with_per_suggest_parity(engine):
     rnd = [rosen(p) for p in space.sample(50, seed=1)]
     assert min(ys) < min(rnd)
     assert min(ys[10:]) < min(ys[:10])
+
+
+def test_fixed_hyperparameters_mode_matches_oracle(engine):
+    space = rosen_space()
+    t = build_required_space("real", space)
+    a = BayesianOptimizer(t, seed=4, n_initial_points=8, acq_func="LCB", n_points=20000, normalize_y=True, length_scale=0.3,
+                          fit_hyperparameters=False)
+    comp = compiler.compile_space(t)
+    for trial in range(14):
+        off = a._offset
+        (tp,) = a.suggest(1)
+        if trial >= 8:
+            C, _ = osamp.sample_transform(comp.slots, comp.cdf, a._seed, off, 20000, True)
+            model = ogp.SklearnGP(0, 1.0, 0.3 * np.ones(2), 1e-10 + 1e-4, True).fit(np.asarray(a._X), np.asarray(a._y))
+            mu, sd = model.predict(C)
+            want = comp.denormalise(C[oacq.pick(oacq.ACQ_LCB, mu, sd, float(min(a._y)))])
+            np.testing.assert_allclose(np.asarray(tp, dtype=float), want, rtol=1e-12, atol=1e-12)
+        a.observe([tp], [{"objective": rosen(t.reverse(tp))}])
 
 
 def test_mixed_space_suggestions_are_valid_and_reproducible(engine):

@@ -71,3 +71,40 @@ def test_bad_arguments(engine):
         engine.fit(X, y, amplitude=-1.0)
     with pytest.raises(_lib.Ob200Error):
         engine.fit(np.zeros((9000, 2)), np.zeros(9000))  # n > 8192
+
+
+@pytest.mark.parametrize("kind,n,d,normalize_y", [(0, 120, 3, True), (1, 90, 5, False), (0, 300, 20, True)])
+def test_lml_gradient_matches_sklearn(engine, kind, n, d, normalize_y):
+    from sklearn.gaussian_process import GaussianProcessRegressor
+    from sklearn.gaussian_process.kernels import RBF, ConstantKernel, Matern, WhiteKernel
+    X, y = gp_problem(n, d, seed=20 + n)
+    ls = np.linspace(0.5, 1.7, d)
+    amp, noise, alpha = 1.8, 3e-3, 1e-10
+    base = Matern(length_scale=ls, nu=2.5) if kind == 0 else RBF(length_scale=ls)
+    kernel = ConstantKernel(amp) * base + WhiteKernel(noise)
+    gpr = GaussianProcessRegressor(kernel=kernel, alpha=alpha, optimizer=None, normalize_y=normalize_y).fit(X, y)
+    lml_ref, grad_ref = gpr.log_marginal_likelihood(gpr.kernel_.theta, eval_gradient=True)
+    engine.fit(X, y, kind=kind, amplitude=amp, length_scale=ls, alpha=alpha + noise, normalize_y=normalize_y)
+    lml, g = engine.lml_grad()
+    ours = np.concatenate([[g[0]], g[1:1 + d], [noise * g[1 + d]]])  # theta = log c, log ls, log noise
+    np.testing.assert_allclose(lml, lml_ref, rtol=1e-9)
+    np.testing.assert_allclose(ours, grad_ref, rtol=1e-6, atol=1e-6 * np.abs(grad_ref).max())
+
+
+def test_hyperparameter_optimisation_reaches_sklearn_optimum(engine):
+    import warnings
+    from sklearn.gaussian_process import GaussianProcessRegressor
+    from sklearn.gaussian_process.kernels import ConstantKernel, Matern, WhiteKernel
+    from metaopt_b200 import hyperopt
+    X, y = gp_problem(150, 4, seed=77, noise=0.05)
+    kernel = ConstantKernel(1.0, (1e-2, 1e3)) * Matern(length_scale=np.ones(4), length_scale_bounds=(1e-2, 1e2), nu=2.5) + \
+        WhiteKernel(1.0, (1e-5, 1e5))
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        gpr = GaussianProcessRegressor(kernel=kernel, alpha=1e-10, normalize_y=True, n_restarts_optimizer=0).fit(X, y)
+    res = hyperopt.optimise(engine, torch.as_tensor(X).cuda(), torch.as_tensor(y).cuda(), kind=0, amplitude=1.0,
+                            length_scale=np.ones(4), noise=1.0, alpha=1e-10, normalize_y=True)
+    assert res.lml >= gpr.log_marginal_likelihood_value_ - 1e-3 * abs(gpr.log_marginal_likelihood_value_) - 1e-3
+    assert res.n_evals < 200 and 1e-5 <= res.noise <= 1e5
+    # the engine is left fitted at the optimum
+    np.testing.assert_allclose(engine.lml(), res.lml, rtol=1e-12)

@@ -68,7 +68,8 @@ def test_primary_algo_drives_the_plugin(orion_env):
     from orion.core.worker.primary_algo import PrimaryAlgo
     space = _space()
     palgo = PrimaryAlgo(space, {"bayesianoptimizer": {"seed": 3, "n_initial_points": 4, "acq_func": "EI",
-                                                      "n_points": 200, "normalize_y": True}})
+                                                      "n_points": 200, "normalize_y": True,
+                                                      "fit_hyperparameters": False}})
     assert palgo.algorithm.space is palgo.transformed_space
     assert palgo.configuration["bayesianoptimizer"]["n_points"] == 200
     seen = []
