@@ -278,7 +278,7 @@ def run_ours(args):
         from metaopt_b200.algo import BayesianOptimizer
         tspace = build_required_space("real", space)
 
-        def plugin_latency(**extra):
+        def plugin_latency(calls, **extra):
             algo = BayesianOptimizer(tspace, seed=1, n_initial_points=10, acq_func="EI", alpha=ALPHA, noise="gaussian",
                                      noise_level=NOISE, normalize_y=True, n_points=M, xi=XI, device=local,
                                      fit_hyperparameters=False, **extra)
@@ -286,14 +286,14 @@ def run_ours(args):
             algo.observe(pts, [{"objective": float(v)} for v in y])
             algo.suggest(1)  # fit + first suggest
             lat = []
-            for _ in range(max(5, min(20, args.steps * 2))):
+            for _ in range(calls):
                 t1 = time.perf_counter()
                 algo.suggest(1)
                 lat.append((time.perf_counter() - t1) * 1e3)
             return statistics.median(lat), len(lat)
-        p50_dense, n_calls = plugin_latency(prune=False)
-        p50_pruned, _ = plugin_latency(prune=True)
-        suggest_latency = {"p50_ms_dense": p50_dense, "p50_ms_pruned": p50_pruned, "calls": n_calls, "n_points": M,
+        p50_dense, n_dense = plugin_latency(max(5, min(20, args.steps * 2)), prune=False)
+        p50_pruned, n_calls = plugin_latency(50, prune=True)
+        suggest_latency = {"p50_ms_dense": p50_dense, "p50_ms_pruned": p50_pruned, "calls_dense": n_dense, "calls_pruned": n_calls, "n_points": M,
                            "n_obs": N_OBS, "api": "BayesianOptimizer.suggest(1) (host wall clock, fit cached)"}
 
     if rank != 0:

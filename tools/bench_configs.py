@@ -55,6 +55,33 @@ def main():
     out["real20_sampler"] = dict(points=1 << 24, ms=ms2, achieved_gbs=(1 << 24) * 160 / ms2 / 1e6)
     del buf, buf2
     print(json.dumps(out), flush=True)
+    # CPU restatement (numpy, vectorised Philox) of the same sampler on a bounded sample, single core
+    from oracle import sampling as osamp
+    t0 = time.perf_counter()
+    osamp.sample_transform(comp.slots, comp.cdf, 7, 0, 20000, True)
+    out["cfg5_sampler"]["cpu_port_points_per_s"] = 20000 / (time.perf_counter() - t0)
+    # small-problem latency (BASELINE config 1 shape): n_obs = 50, D = 2, 10k candidates, through the plugin
+    from metaopt_b200.algo import BayesianOptimizer
+    t2 = transformed(real_space(2))
+    algo = BayesianOptimizer(t2, seed=1, n_initial_points=5, acq_func="EI", n_points=10000, normalize_y=True)
+    rs = np.random.RandomState(0)
+    pts = [tuple(float(v) for v in rs.uniform(size=2)) for _ in range(50)]
+    algo.observe(pts, [{"objective": float((p[0] - 0.3) ** 2 + (p[1] - 0.6) ** 2)} for p in pts])
+    t0 = time.perf_counter()
+    algo.suggest(1)
+    first = (time.perf_counter() - t0) * 1e3
+    lat = []
+    for _ in range(30):
+        t0 = time.perf_counter()
+        algo.suggest(1)
+        lat.append((time.perf_counter() - t0) * 1e3)
+    algo.observe(pts[:1], [{"objective": 0.5}])
+    t0 = time.perf_counter()
+    algo.suggest(1)
+    refit = (time.perf_counter() - t0) * 1e3
+    out["cfg1_plugin_latency_ms"] = dict(first_suggest_with_hyperfit=first, p50_cached_fit=float(np.median(lat)),
+                                         suggest_after_one_new_observation=refit, n_obs=50, n_points=10000)
+    print(json.dumps(out), flush=True)
     if "--sampler-only" in sys.argv:
         return
     # ---- cfg3 / cfg4 scoring shapes (reduced candidate counts, same n and D)
