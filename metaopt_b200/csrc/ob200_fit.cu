@@ -220,6 +220,7 @@ __global__ void __launch_bounds__(256) chol_diag_kernel(double* __restrict__ A, 
   __shared__ int bad;
   double* blk = A + (size_t)kb * FB * ld + (size_t)kb * FB;
   const int tid = threadIdx.x;
+  const int ty = tid >> 4, tx = tid & 15;  // 16 x 16 thread grid over the trailing block
   if (tid == 0) bad = 0;
   for (int e = tid; e < FB * FB; e += 256) { const int r = e >> 6, c = e & 63; S[r][c] = (c <= r) ? blk[(size_t)r * ld + c] : 0.0; }
   __syncthreads();
@@ -231,29 +232,37 @@ __global__ void __launch_bounds__(256) chol_diag_kernel(double* __restrict__ A, 
       break;
     }
     const double d = sqrt(piv);
-    __syncthreads();
+    __syncthreads();  // everybody has read the pivot
+    // scale column j (one division per row), then the rank-1 update of the trailing lower triangle
     if (tid == 0) S[j][j] = d;
     for (int i = j + 1 + tid; i < FB; i += 256) S[i][j] = S[i][j] / d;
     __syncthreads();
-    // trailing update of the lower triangle: S[i][c] -= S[i][j]*S[c][j], j < c <= i
-    const int rem = FB - j - 1;
-    for (int e = tid; e < rem * rem; e += 256) {
-      const int i = j + 1 + e / rem, c = j + 1 + e % rem;
-      if (c <= i) S[i][c] = fma(-S[i][j], S[c][j], S[i][c]);
+    for (int i = j + 1 + ty; i < FB; i += 16) {
+      const double li = S[i][j];
+      for (int c = j + 1 + tx; c <= i; c += 16) S[i][c] = fma(-li, S[c][j], S[i][c]);
     }
     __syncthreads();
   }
   __syncthreads();
   if (bad) return;
-  // inverse of the lower-triangular block, one column per thread (forward substitution)
-  if (tid < FB) {
-    const int c = tid;
-    for (int i = 0; i < c; ++i) Inv[i][c] = 0.0;
-    Inv[c][c] = 1.0 / S[c][c];
-    for (int i = c + 1; i < FB; ++i) {
+  // inverse of the lower-triangular block: column c by forward substitution, 4 lanes per column
+  // splitting the inner sum (fixed split + shuffle tree: deterministic)
+  {
+    const int c = tid >> 2, sub = tid & 3;
+    const int c_first = (tid >> 5) * 8;  // first column of this warp: uniform trip count for the shuffles
+    if (sub == 0) {
+      for (int i = 0; i < c; ++i) Inv[i][c] = 0.0;
+      Inv[c][c] = 1.0 / S[c][c];
+    }
+    __syncwarp();
+    for (int i = c_first + 1; i < FB; ++i) {
       double acc = 0.0;
-      for (int k = c; k < i; ++k) acc = fma(S[i][k], Inv[k][c], acc);
-      Inv[i][c] = -acc / S[i][i];
+      if (i > c)
+        for (int k = c + sub; k < i; k += 4) acc = fma(S[i][k], Inv[k][c], acc);
+      acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+      acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+      if (sub == 0 && i > c) Inv[i][c] = -acc / S[i][i];
+      __syncwarp();
     }
   }
   __syncthreads();

@@ -21,6 +21,7 @@
 //            diagonal / beyond n are skipped; the result is never stored, only sum v^2.
 //   phase 3  posterior + acquisition + running argmax in registers; per-CTA partials at the end.
 #include <math.h>
+#include <stdlib.h>
 
 #include "ob200_internal.cuh"
 
@@ -630,7 +631,11 @@ int ob200_score_async(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64
     // candidates from the registered space: generate (normalised) in chunks, fold the argmax
     if (ctx->n_slots <= 0) OB_FAIL(ctx, OB200_ESTATE, "cand_dev is NULL and no space was set");
     if (ctx->d_out != D) OB_FAIL(ctx, OB200_EINVAL, "space width %d != fitted D %d", ctx->d_out, D);
-    const int64_t chunk_rows = ((int64_t)1 << 31) / ((int64_t)D * 8) / SC_BN * SC_BN;  // <= 2 GiB of candidates at a time
+    int64_t chunk_rows = ((int64_t)1 << 31) / ((int64_t)D * 8) / SC_BN * SC_BN;  // <= 2 GiB of candidates at a time
+    if (const char* env = getenv("OB200_CHUNK_ROWS")) {  // testing hook: exercise the multi-chunk path at small sizes
+      const long long v = atoll(env);
+      if (v >= SC_BN) chunk_rows = v / SC_BN * SC_BN;
+    }
     if (acq_dev && M > chunk_rows) OB_FAIL(ctx, OB200_EINVAL, "dense acquisition output needs M <= %lld when candidates are generated", (long long)chunk_rows);
     const int64_t rows_cap = M < chunk_rows ? M : chunk_rows;
     if ((rc = ob_reserve(ctx, &ctx->cand_tmp, &ctx->cand_cap, rows_cap * D))) return rc;

@@ -145,6 +145,23 @@ def test_pruned_scoring_with_generated_candidates(engine):
     assert pruned == dense and n_scored <= 120_000
 
 
+def test_chunked_generation_equals_single_pass(engine, monkeypatch):
+    """Candidate sets larger than 2 GiB are generated and scored chunk by chunk with a running argmax;
+    OB200_CHUNK_ROWS shrinks the chunk so the path is exercised at test size (ragged last chunk included)."""
+    comp = compiler.compile_space(transformed(cfg3_space()))
+    compiler.upload(engine, comp)
+    X = engine.sample(99, 0, 200).cpu().numpy()
+    y = ((X - 0.5) ** 2).sum(axis=1)
+    engine.fit(X, y, alpha=1e-6, normalize_y=True)
+    whole = engine.score(None, M=50_003, seed=8, first_index=123, acq_mask=7, y_opt=float(y.min()), dense=True)
+    monkeypatch.setenv("OB200_CHUNK_ROWS", "12800")
+    parts = engine.score(None, M=50_003, seed=8, first_index=123, acq_mask=7, y_opt=float(y.min()))
+    for k in ("EI", "PI", "LCB"):
+        assert parts[k] == whole[k]
+    mu_only = engine.score(None, M=50_003, seed=8, first_index=123, acq_mask=1, y_opt=float(y.min()), dense=False)
+    assert mu_only["EI"] == whole["EI"]
+
+
 def test_export_import_roundtrip(engine):
     X, y = gp_problem(260, 6, seed=8)
     engine.fit(X, y, alpha=1e-6, normalize_y=True)

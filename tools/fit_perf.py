@@ -1,0 +1,32 @@
+"""GPU box: wall time of one fit and of one fit + LML gradient at several n (after warm-up)."""
+import json
+import sys
+import time
+
+import numpy as np
+import torch
+
+sys.path.insert(0, ".")
+from metaopt_b200.engine import get_engine  # noqa: E402
+
+eng = get_engine(0)
+out = {}
+for n, d in ((50, 2), (200, 10), (500, 20), (2000, 20), (4000, 60), (8000, 100)):
+    rs = np.random.RandomState(0)
+    X = torch.as_tensor(rs.uniform(size=(n, d))).cuda()
+    y = torch.as_tensor(((rs.uniform(size=(n, d)) - 0.5) ** 2).sum(1)).cuda()
+    for _ in range(2):
+        eng.fit(X, y, alpha=1e-4, normalize_y=True)
+        eng.lml_grad()
+    reps = 5 if n <= 2000 else 2
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        eng.fit(X, y, alpha=1e-4, normalize_y=True)
+    fit_ms = (time.perf_counter() - t0) / reps * 1e3
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        eng.fit(X, y, alpha=1e-4, normalize_y=True)
+        eng.lml_grad()
+    both_ms = (time.perf_counter() - t0) / reps * 1e3
+    out["n%d_d%d" % (n, d)] = dict(fit_ms=round(fit_ms, 3), fit_plus_grad_ms=round(both_ms, 3))
+    print(json.dumps(out), flush=True)
