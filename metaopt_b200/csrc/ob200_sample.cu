@@ -27,8 +27,15 @@
 
 namespace {
 
-#define ST_ROWS 128      // rows per tile
-#define ST_THREADS 512
+#ifndef ST_ROWS
+#define ST_ROWS 32       // rows per tile (one row group)
+#endif
+#ifndef ST_THREADS
+#define ST_THREADS 128   // 4 warps share the slot pairs of the tile; many small independent CTAs per SM
+#endif
+#ifndef ST_MIN_CTAS
+#define ST_MIN_CTAS 8
+#endif
 
 // Slot as the kernel reads it: 64 bytes = four 16-byte shared-memory loads, everything that only
 // depends on the slot precomputed on the host (ob200_space_set).
@@ -191,7 +198,7 @@ __device__ __forceinline__ void pair_op(const dslot* __restrict__ sp, const doub
   }
 }
 
-__global__ void __launch_bounds__(ST_THREADS, 2)
+__global__ void __launch_bounds__(ST_THREADS, ST_MIN_CTAS)
 sample_transform_kernel(const dslot* __restrict__ slots_g, int n_dslots, int n_slots, const double* __restrict__ cdf_g, int n_cdf,
                         int d_out, int stride, const __grid_constant__ philox_keys rk, uint64_t first_index, int64_t count,
                         int normalise, double* __restrict__ out, int64_t ld, const double* __restrict__ variates,

@@ -888,7 +888,6 @@ extern "C" int ob200_score_pruned(ob200_ctx* ctx, const double* cand_dev, int64_
   OB_LAUNCH_CHECK(ctx);
   OB_CUDA(ctx, cudaMemcpyAsync(&h_count, counter, 8, cudaMemcpyDeviceToHost, st));
   OB_CUDA(ctx, cudaStreamSynchronize(st));
-  int grid_max = 0;
   ob200_best incumbent{};
   incumbent.value = -INFINITY;
   if (h_count > 0) {
@@ -899,7 +898,6 @@ extern "C" int ob200_score_pruned(ob200_ctx* ctx, const double* cand_dev, int64_
     globalise_kernel<<<nblk, 256, 0, st>>>(ctx->idx_dev, nA, first_index);
     OB_LAUNCH_CHECK(ctx);
     if ((rc = score_launch(ctx, ctx->gather_dev, D, nA, 0, mask, y_opt, xi, kappa, nullptr, nullptr, nullptr, 0, &grid, 0, ctx->idx_dev))) return rc;
-    grid_max = grid;
     reduce_best_kernel<<<1, 256, 0, st>>>(reinterpret_cast<const best_t*>(ctx->partial_dev), grid, mask, ctx->best_dev);
     OB_LAUNCH_CHECK(ctx);
     OB_CUDA(ctx, cudaMemcpyAsync(ctx->best_pinned, ctx->best_dev, 3 * sizeof(ob200_best), cudaMemcpyDeviceToHost, st));
@@ -933,7 +931,6 @@ extern "C" int ob200_score_pruned(ob200_ctx* ctx, const double* cand_dev, int64_
       n_scored += nB;
     }
   }
-  (void)grid_max;
   best_host[0] = incumbent;
   if (n_scored_host) *n_scored_host = n_scored;
   if (cand_dev == ctx->cand_tmp) return ob200_sample_status(ctx);

@@ -4,6 +4,9 @@ sys.path.insert(0, ".")
 from metaopt_b200 import build as b
 
 VARIANTS = {
+    "st128": ["ST_ROWS=128", "ST_THREADS=512", "ST_MIN_CTAS=2"],
+    "st64": ["ST_ROWS=64", "ST_THREADS=256", "ST_MIN_CTAS=4"],
+    "st32w8": ["ST_ROWS=32", "ST_THREADS=256", "ST_MIN_CTAS=4"],
     "bk32s2": ["SC_BK=32", "SC_STAGES=2"],
     "bk16s5": ["SC_BK=16", "SC_STAGES=5"],
     "bk8s8": ["SC_BK=8", "SC_STAGES=8"],
