@@ -171,18 +171,34 @@ class BayesianOptimizer(BaseAlgorithm):
         return new
 
     def suggest(self, num=1):
-        """`num` points of the transformed space (tuples; 1-D arrays for one-hot / shaped dims)."""
+        """`num` points of the transformed space (tuples; 1-D arrays for one-hot / shaped dims).
+
+        `num > 1` (the reference wrapper only supports 1) uses skopt's constant-liar strategy "cl_min": after
+        each pick the point is added with the best objective seen so far as a stand-in result, the GP is
+        refitted with the hyper-parameters kept, and the next point is picked; the lies are dropped afterwards."""
         comp = self._get_compiled()
         eng = self._engine()
         compiler.upload(eng, comp)
         points = []
-        for _ in range(int(num)):
-            if len(self._y) < max(int(self.n_initial_points), 1):
-                row = eng.sample(self._seed, self._offset, 1, normalise=False).cpu().numpy()[0]
-                self._offset += 1
-            else:
-                row = self._suggest_gp(eng, comp)
-            points.append(compiler.regroup_row(comp, row, transformed=True))
+        n_real = len(self._y)
+        saved_fit = self.fit_hyperparameters
+        try:
+            for k in range(int(num)):
+                if n_real < max(int(self.n_initial_points), 1):
+                    row = eng.sample(self._seed, self._offset, 1, normalise=False).cpu().numpy()[0]
+                    self._offset += 1
+                else:
+                    row = self._suggest_gp(eng, comp)
+                    if k + 1 < int(num):  # constant liar: pretend this point returned the incumbent
+                        self._X.append(comp.normalise(np.asarray(row, dtype=float)))
+                        self._y.append(float(min(self._y[:n_real])))
+                        if self._theta is not None:
+                            self.fit_hyperparameters = False  # lies must not move the hyper-parameters
+                points.append(compiler.regroup_row(comp, row, transformed=True))
+        finally:
+            del self._X[n_real:]
+            del self._y[n_real:]
+            self.fit_hyperparameters = saved_fit
         return points
 
     def observe(self, points, results):
@@ -224,7 +240,9 @@ class BayesianOptimizer(BaseAlgorithm):
         h = hashlib.blake2b(digest_size=16)
         for part in (X.tobytes(), y.tobytes(), ls.tobytes(),
                      repr((self.kernel, self.amplitude, self._diag_noise(), bool(self.normalize_y),
-                           bool(self.fit_hyperparameters), int(self.n_restarts_optimizer))).encode()):
+                           bool(self.fit_hyperparameters), int(self.n_restarts_optimizer),
+                           None if (self._theta is None or self.fit_hyperparameters) else
+                           (self._theta[0], tuple(np.atleast_1d(self._theta[1])), self._theta[2]))).encode()):
             h.update(part)
         token = h.digest()
         if getattr(eng, "_fit_token", None) != token:
@@ -239,10 +257,18 @@ class BayesianOptimizer(BaseAlgorithm):
                                         bool(self.normalize_y), anisotropic=True, optimise_noise=gaussian,
                                         n_restarts=int(self.n_restarts_optimizer), rng=rng)
                 self._theta = (res.amplitude, np.asarray(res.length_scale), res.noise if gaussian else float(self.noise_level))
+            elif self._theta is not None and saved_theta_ok(self._theta, X.shape[1]):
+                amp_t, ls_t, nz_t = self._theta  # hyper-parameters of the last optimisation (constant-liar refits)
+                eng.fit(X, y, kind=kind, amplitude=amp_t, length_scale=ls_t,
+                        alpha=float(self.alpha) + (nz_t if self.noise == "gaussian" else 0.0), normalize_y=bool(self.normalize_y))
             else:
                 eng.fit(X, y, kind=kind, amplitude=float(self.amplitude), length_scale=ls,
                         alpha=self._diag_noise(), normalize_y=bool(self.normalize_y))
             eng._fit_token = token
+            eng._fit_theta = copy.deepcopy(self._theta)
+        elif self.fit_hyperparameters and getattr(eng, "_fit_theta", None) is not None:
+            # another copy of this algorithm (producer.py:161) already fitted these data: adopt its optimum
+            self._theta = copy.deepcopy(eng._fit_theta)
         return float(y.min())
 
     def _suggest_gp(self, eng, comp):
@@ -285,6 +311,11 @@ class BayesianOptimizer(BaseAlgorithm):
             for k, (_, mu) in enumerate(self._hedge_pending):
                 self._hedge_gains[k] -= float(mu)
             self._hedge_pending = None
+
+
+def saved_theta_ok(theta, d):
+    """A stored (amplitude, length_scale, noise) triple matches the current space width."""
+    return len(np.atleast_1d(theta[1])) in (1, d)
 
 
 def register():

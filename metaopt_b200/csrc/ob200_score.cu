@@ -48,7 +48,7 @@ struct score_args {
   best_t* partials;  // [grid][3]
   long long n_tiles;
   int accumulate;    // 1: fold the partials already stored (multi-chunk calls)
-  int p1_stages;     // phase-1 ring depth (2, or 1 when D is too wide for two stages)
+  int p1_stages;     // phase-1 ring depth (1..P1_STAGES, the deepest that fits in shared memory)
   int mean_only;     // 1: phase 1 only, write mu_out (pruned scoring, pass 1)
   const long long* index_map;  // optional: global index of row r (gathered survivors); else first_index + r
 };
@@ -59,52 +59,49 @@ struct score_args {
 // ~35 instructions, accurate to ~1-2 ulp on the domain that can occur here, and interleave
 // freely across the 16 evaluations each lane owns.
 
-// sqrt(x) for finite x >= 0 (x = 0 and x below 1e-30 return a tiny finite value <= 1e-15,
-// which the Matern polynomial maps to amplitude * (1 + O(1e-30))).
+// sqrt(x) for finite x >= 0: float rsqrt seed (23 bits), then two Heron corrections that reuse the
+// seed as the (approximate) derivative: error 1.5 eps^2 after the first, 1.5 eps^3 after the second,
+// i.e. below double rounding (<= 1 ulp measured).  x = 0 gives 0; x below 1e-30 gives a tiny finite
+// value <= 1e-15, which the Matern polynomial maps to amplitude * (1 + O(1e-30)).
 __device__ __forceinline__ double sqrt_pos(double x) {
-  const double xm = fmax(x, 1e-30);
-  double y = (double)rsqrtf((float)xm);          // 23-bit seed (MUFU.RSQ)
-  double h = 0.5 * xm;
-  y = y * fma(-h * y, y, 1.5);                     // Newton on 1/sqrt: 46 bits
-  y = y * fma(-h * y, y, 1.5);                     // ~full precision
-  double s = x * y;
-  const double e = fma(-s, s, x);                  // residual (only meaningful when xm == x)
-  return (x >= 1e-30) ? fma(e, 0.5 * y, s) : s;
+  const float yf = rsqrtf((float)fmax(x, 1e-30));  // MUFU.RSQ
+  const double y0 = (double)yf, hy = (double)(0.5f * yf);
+  double s = x * y0;
+  s = fma(fma(-s, s, x), hy, s);
+  s = fma(fma(-s, s, x), hy, s);
+  return s;
 }
 
-// exp(t) for t <= 0.  Cody-Waite reduction t = n ln2 + r, |r| <= ln2/2, degree-13 Taylor
-// (truncation 4e-18 relative), scaling by exponent-field addition; below 2^-1021 returns 0.
-__device__ __forceinline__ double exp_neg(double t) {
+// exp(t) for t <= 0 with a 32-entry table: t = (32 n + j) ln2/32 + r, |r| <= ln2/64, so
+// exp(t) = 2^n * 2^(j/32) * exp(r) and a degree-6 Taylor polynomial suffices (truncation 3.5e-18);
+// Cody-Waite two-constant reduction, scaling by exponent-field addition.  ~2 ulp; below 2^-1021 -> 0.
+// `tab` = 2^(j/32), j = 0..31, in shared memory.
+__device__ __forceinline__ double exp_neg(double t, const double* __restrict__ tab) {
   const double magic = 6755399441055744.0;         // 1.5 * 2^52: round-to-nearest-integer trick
-  const double nd_biased = fma(t, 1.4426950408889634, magic);
-  const int n = __double2loint(nd_biased);
-  const double nd = nd_biased - magic;
-  double r = fma(nd, -6.93147180369123816490e-01, t);
-  r = fma(nd, -1.90821492927058770002e-10, r);
-  double p = 1.6059043836821613e-10;               // 1/13!
-  p = fma(p, r, 2.08767569878681e-09);             // 1/12!
-  p = fma(p, r, 2.505210838544172e-08);            // 1/11!
-  p = fma(p, r, 2.755731922398589e-07);            // 1/10!
-  p = fma(p, r, 2.7557319223985893e-06);           // 1/9!
-  p = fma(p, r, 2.48015873015873e-05);             // 1/8!
-  p = fma(p, r, 0.0001984126984126984);            // 1/7!
-  p = fma(p, r, 0.001388888888888889);             // 1/6!
-  p = fma(p, r, 0.008333333333333333);             // 1/5!
-  p = fma(p, r, 0.041666666666666664);             // 1/4!
-  p = fma(p, r, 0.16666666666666666);              // 1/3!
+  const double mb = fma(t, 46.16624130844683, magic);  // t * 32 / ln2
+  const int m = __double2loint(mb);
+  const double md = mb - magic;
+  double r = fma(md, -2.16608493865351192653e-02, t);   // ln2/32, high part
+  r = fma(md, -5.96317165397058692146e-12, r);          // ln2/32, low part
+  double p = 1.0 / 720.0;
+  p = fma(p, r, 1.0 / 120.0);
+  p = fma(p, r, 1.0 / 24.0);
+  p = fma(p, r, 1.0 / 6.0);
   p = fma(p, r, 0.5);
   p = fma(p, r, 1.0);
   p = fma(p, r, 1.0);
-  const double scaled = __hiloint2double(__double2hiint(p) + (n << 20), __double2loint(p));
+  const double v = tab[m & 31] * p;
+  const int n = m >> 5;
+  const double scaled = __hiloint2double(__double2hiint(v) + (n << 20), __double2loint(v));
   return (n >= -1021) ? scaled : 0.0;
 }
 
-__device__ __forceinline__ double kernel_from_d2(int kind, double d2, double amplitude) {
+__device__ __forceinline__ double kernel_from_d2(int kind, double d2, double amplitude, const double* __restrict__ tab) {
   if (kind == OB200_KERNEL_MATERN52) {
     const double k = sqrt_pos(d2) * 2.23606797749979;  // sqrt(5) * dist
-    return amplitude * (fma(k, fma(k, 0.3333333333333333, 1.0), 1.0) * exp_neg(-k));
+    return amplitude * (fma(k, fma(k, 0.3333333333333333, 1.0), 1.0) * exp_neg(-k, tab));
   }
-  return amplitude * exp_neg(-0.5 * d2);
+  return amplitude * exp_neg(-0.5 * d2, tab);
 }
 
 __device__ __forceinline__ void acquisition(double mu, double sigma, double y_opt, double xi, double kappa, double out[3]) {
@@ -127,7 +124,7 @@ __device__ __forceinline__ void consumer_bar() {
 }
 
 #ifndef P1_STAGES
-#define P1_STAGES 2
+#define P1_STAGES 6   // maximum depth of the phase-1 ring; the launcher picks the deepest that fits
 #endif
 static_assert(SC_BM % 64 == 0, "row block must be a multiple of the fit block");
 static_assert(SC_BM % SC_P1_OBS == 0, "row block must be a multiple of the phase-1 chunk");
@@ -161,12 +158,14 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
   uint64_t* empty1 = full1 + P1_STAGES;
   uint64_t* full2 = empty1 + P1_STAGES;   // [SC_STAGES]
   uint64_t* empty2 = full2 + SC_STAGES;
+  double* exp_tab = reinterpret_cast<double*>(empty2 + SC_STAGES);  // 2^(j/32), j = 0..31
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int g = lane >> 2, q = lane & 3;
   const bool is_producer = (warp >= SC_CONSUMER_WARPS);   // last warpgroup; only its first lane issues copies
   const bool is_issuer = (warp == SC_CONSUMER_WARPS) && (lane == 0);
 
+  if (tid < 32) exp_tab[tid] = exp2((double)tid * 0.03125);
   if (tid == 0) {
     for (int s = 0; s < P1_STAGES; ++s) { mbar_init(&full1[s], 1); mbar_init(&empty1[s], SC_CONSUMER_WARPS); }
     for (int s = 0; s < SC_STAGES; ++s) { mbar_init(&full2[s], 1); mbar_init(&empty2[s], SC_CONSUMER_WARPS); }
@@ -295,8 +294,8 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
           const double d20 = fmax(ccr[cf] + xx0 - 2.0 * acc[cf][0], 0.0);
           const double d21 = fmax(ccr[cf] + xx1 - 2.0 * acc[cf][1], 0.0);
           double2 kv;
-          kv.x = kernel_from_d2(a.kind, d20, a.amplitude);
-          kv.y = kernel_from_d2(a.kind, d21, a.amplitude);
+          kv.x = kernel_from_d2(a.kind, d20, a.amplitude, exp_tab);
+          kv.y = kernel_from_d2(a.kind, d21, a.amplitude, exp_tab);
           mup[cf] = fma(kv.x, al0, mup[cf]);
           mup[cf] = fma(kv.y, al1, mup[cf]);
           if (!a.mean_only) dst[cf * 32] = kv;
@@ -561,7 +560,7 @@ __global__ void __launch_bounds__(256) acq_partial_kernel(const double* __restri
 
 size_t score_smem_bytes(int D_pad, int p1_stages) {
   return (score_union_elems(D_pad, p1_stages) + SC_BN + SC_CONSUMER_WARPS * SC_BN + SC_WM * SC_BN) * sizeof(double) +
-         (2 * P1_STAGES + 2 * SC_STAGES) * sizeof(uint64_t) + 128;
+         (2 * P1_STAGES + 2 * SC_STAGES) * sizeof(uint64_t) + 32 * sizeof(double) + 128;
 }
 
 int score_launch(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M, uint64_t first_index, int acq_mask,
@@ -569,9 +568,12 @@ int score_launch(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M,
                  int* grid_out, int mean_only = 0, const long long* index_map = nullptr) {
   const ob200_fit_header& h = ctx->hdr;
   const ob200_blob_layout lay = ob_blob_layout(h.n_pad, h.D_pad);
+  // phase-1 ring depth: the deepest that fits (observed-point chunks are small, so the bulk-copy latency has
+  // to be covered by depth, not by chunk size); OB200_P1_STAGES overrides for tuning
   int p1_stages = P1_STAGES;
+  if (const char* env = getenv("OB200_P1_STAGES")) { const int v = atoi(env); if (v >= 1 && v <= P1_STAGES) p1_stages = v; }
   size_t smem = score_smem_bytes(h.D_pad, p1_stages);
-  if (smem > 227 * 1024) { p1_stages = 1; smem = score_smem_bytes(h.D_pad, 1); }
+  while (smem > 227 * 1024 && p1_stages > 1) { --p1_stages; smem = score_smem_bytes(h.D_pad, p1_stages); }
   if (smem > 227 * 1024) OB_FAIL(ctx, OB200_EINVAL, "D=%d too wide for the score kernel's shared-memory tile", h.D);
   const int64_t n_tiles = (M + SC_BN - 1) / SC_BN;
   const int grid = (int)(n_tiles < ctx->num_sms ? n_tiles : ctx->num_sms);

@@ -124,3 +124,20 @@ def test_hyperparameters_are_fitted_and_warm_started(fake):
     assert fake.calls["fit"] > 3  # several likelihood evaluations per refit
     b = copy.deepcopy(a)
     assert b._theta[0] == a._theta[0] and b._theta[1] is not a._theta[1]
+
+
+def test_batch_suggest_uses_constant_liar_and_leaves_no_lies(fake):
+    space = small_space()
+    t = build_required_space("real", space)
+    a = BayesianOptimizer(t, seed=3, n_initial_points=5, acq_func="EI", n_points=400, normalize_y=True)
+    for _ in range(6):
+        (tp,) = a.suggest(1)
+        a.observe([tp], [{"objective": objective(t.reverse(tp))}])
+    b = copy.deepcopy(a)
+    b.suggest(1)                                        # what a plain suggest fits on the real data
+    theta = copy.deepcopy(b._theta)
+    batch = a.suggest(4)
+    assert len(batch) == 4 and all(p in t for p in batch)
+    assert len({repr(p) for p in batch}) == 4          # the lies push the picks apart
+    assert len(a._y) == 6 and len(a._X) == 6           # lies are gone
+    assert a._theta[0] == theta[0] and a.fit_hyperparameters is True  # hyper-parameters untouched by lies

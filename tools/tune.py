@@ -28,8 +28,11 @@ print(json.dumps(out))
 
 if __name__ == "__main__":
     libs = sorted(glob.glob("metaopt_b200/libob200*.so"))
-    for lib in libs:
-        env = dict(os.environ, OB200_LIB=os.path.abspath(lib))
+    envs = [dict(os.environ, OB200_LIB=os.path.abspath(lib)) for lib in libs]
+    if "--p1" in sys.argv:  # sweep the phase-1 ring depth on the main library
+        libs = ["p1_stages=%d" % k for k in (1, 2, 3, 4, 6)]
+        envs = [dict(os.environ, OB200_P1_STAGES=str(k)) for k in (1, 2, 3, 4, 6)]
+    for lib, env in zip(libs, envs):
         try:
             res = subprocess.run([sys.executable, "-c", CHILD], env=env, capture_output=True, text=True, timeout=120)
             print(os.path.basename(lib), res.stdout.strip().splitlines()[-1] if res.stdout.strip() else res.stderr[-400:], flush=True)
