@@ -1,4 +1,6 @@
 // Context management for libob200 (no reference counterpart: Orion keeps no device state).
+#include <stdlib.h>
+
 #include "ob200_internal.cuh"
 
 extern "C" {
@@ -22,6 +24,18 @@ int ob200_ctx_create(int device, ob200_ctx** out) {
     return OB200_ECUDA;
   }
   ctx->num_sms = prop.multiProcessorCount;
+  {
+    // The score kernel's k* slices are written once and re-read several times per tile: keep them in a
+    // persisting L2 set-aside so they never travel to HBM (OB200_L2_PERSIST=0 disables).
+    const char* env = getenv("OB200_L2_PERSIST");
+    if (!(env && env[0] == '0') && prop.persistingL2CacheMaxSize > 0 &&
+        cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t)prop.persistingL2CacheMaxSize) == cudaSuccess) {
+      ctx->l2_persist_max = (size_t)prop.persistingL2CacheMaxSize;
+      ctx->l2_window_max = (size_t)prop.accessPolicyMaxWindowSize;
+    } else {
+      cudaGetLastError();
+    }
+  }
   if (cudaMalloc((void**)&ctx->status_dev, sizeof(int)) != cudaSuccess ||
       cudaMemset(ctx->status_dev, 0, sizeof(int)) != cudaSuccess ||
       cudaMalloc((void**)&ctx->best_dev, 3 * sizeof(ob200_best)) != cudaSuccess ||

@@ -33,6 +33,11 @@ struct best_t {
   double mu, sigma;
 };
 
+// after a synchronised score call: hand the persisting L2 lines back to everybody else
+inline void ob_release_l2(ob200_ctx* ctx) {
+  if (ctx->l2_dirty) { cudaCtxResetPersistingL2Cache(); ctx->l2_dirty = false; }
+}
+
 __device__ __forceinline__ bool better(double v, long long i, double bv, long long bi) {
   return (v > bv) || (v == bv && i < bi);
 }
@@ -379,13 +384,16 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
     _Pragma("unroll") for (int j = 0; j < SC_FN; ++j) dmma884(acc[T][j][0], acc[T][j][1], av[T].x, b[j].x); \
     _Pragma("unroll") for (int j = 0; j < SC_FN; ++j) dmma884(acc[T][j][0], acc[T][j][1], av[T].y, b[j].y); \
   }
-            static_assert(SC_FM == 4 || SC_FM == 8, "fragment switch is written for 4 or 8 row fragments per warp");
+            static_assert(SC_FM == 2 || SC_FM == 4 || SC_FM == 8, "fragment switch is written for 2, 4 or 8 row fragments per warp");
             if (t0 < t1) {
               switch (t0) {
                 case 0: SC_FRAG(0) if (t1 == 1) break;
-                case 1: SC_FRAG(1) if (t1 == 2) break;
+                case 1: SC_FRAG(1)
+#if SC_FM >= 4
+                  if (t1 == 2) break;
                 case 2: SC_FRAG(2) if (t1 == 3) break;
                 case 3: SC_FRAG(3)
+#endif
 #if SC_FM == 8
                   if (t1 == 4) break;
                 case 4: SC_FRAG(4) if (t1 == 5) break;
@@ -599,8 +607,26 @@ int score_launch(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M,
   a.mean_only = mean_only;
   a.index_map = index_map;
   OB_CUDA(ctx, cudaFuncSetAttribute(score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  // k* slices -> persisting L2 lines for this launch (the window is a launch-time stream attribute)
+  const size_t slices = (size_t)grid * h.n_pad * SC_BN * sizeof(double);
+  const bool persist = ctx->l2_persist_max > 0 && !mean_only;
+  if (persist) {
+    cudaStreamAttrValue attr{};
+    attr.accessPolicyWindow.base_ptr = ctx->kstar_dev;
+    attr.accessPolicyWindow.num_bytes = slices < ctx->l2_window_max ? slices : ctx->l2_window_max;
+    attr.accessPolicyWindow.hitRatio = ctx->l2_persist_max >= slices ? 1.0f : (float)ctx->l2_persist_max / (float)slices;
+    attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+    attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+    OB_CUDA(ctx, cudaStreamSetAttribute(ctx->stream, cudaStreamAttributeAccessPolicyWindow, &attr));
+  }
   score_kernel<<<grid, SC_THREADS, smem, ctx->stream>>>(a);
   OB_LAUNCH_CHECK(ctx);
+  if (persist) {  // later launches on this (caller-owned) stream must not inherit the window
+    cudaStreamAttrValue attr{};
+    attr.accessPolicyWindow.num_bytes = 0;
+    OB_CUDA(ctx, cudaStreamSetAttribute(ctx->stream, cudaStreamAttributeAccessPolicyWindow, &attr));
+    ctx->l2_dirty = true;
+  }
   *grid_out = grid;
   return OB200_OK;
 }
@@ -670,6 +696,7 @@ int ob200_score(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M, 
   OB_CUDA(ctx, cudaMemcpyAsync(ctx->best_pinned, ctx->best_dev, 3 * sizeof(ob200_best), cudaMemcpyDeviceToHost, ctx->stream));
   OB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   memcpy(best_host, ctx->best_pinned, 3 * sizeof(ob200_best));
+  ob_release_l2(ctx);
   if (!cand_dev) return ob200_sample_status(ctx);
   return OB200_OK;
 }
@@ -702,6 +729,7 @@ int ob200_score_host(ob200_ctx* ctx, const double* cand_host, int64_t ldc, int64
   if (acq_host) OB_CUDA(ctx, cudaMemcpyAsync(acq_host, aq_dev, (size_t)3 * M * 8, cudaMemcpyDeviceToHost, ctx->stream));
   OB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   memcpy(best_host, ctx->best_pinned, 3 * sizeof(ob200_best));
+  ob_release_l2(ctx);
   return OB200_OK;
 }
 
@@ -935,6 +963,7 @@ extern "C" int ob200_score_pruned(ob200_ctx* ctx, const double* cand_dev, int64_
   }
   best_host[0] = incumbent;
   if (n_scored_host) *n_scored_host = n_scored;
+  ob_release_l2(ctx);
   if (cand_dev == ctx->cand_tmp) return ob200_sample_status(ctx);
   return OB200_OK;
 }

@@ -4,6 +4,8 @@ sys.path.insert(0, ".")
 from metaopt_b200 import build as b
 
 VARIANTS = {
+    "bn64": ["SC_WM=6", "SC_WN=2", "SC_FM=4", "SC_FN=4", "SC_BK=16", "SC_STAGES=4"],
+    "bn32s4": ["SC_STAGES=4"],
     "st128": ["ST_ROWS=128", "ST_THREADS=512", "ST_MIN_CTAS=2"],
     "st64": ["ST_ROWS=64", "ST_THREADS=256", "ST_MIN_CTAS=4"],
     "st32w8": ["ST_ROWS=32", "ST_THREADS=256", "ST_MIN_CTAS=4"],
