@@ -8,18 +8,20 @@
 //     var  = max(amplitude - sum v^2, 0) * y_std^2 ; sigma = sqrt(var)
 //     EI / PI / -LCB, first-occurrence argmax
 //
-// One persistent CTA per SM owns tiles of SC_BN = 64 candidates and runs three phases per tile:
+// One persistent CTA per SM owns tiles of SC_BN candidates (default 32) and runs three phases per tile:
 //   phase 1  cross-kernel: the pairwise term cand.X^T is a DMMA (FP64 tensor core) contraction over
 //            the D columns, with observed-point tiles (fragment-packed X/ls, ||X||^2, alpha) staged
 //            into shared memory by bulk async copies (TMA engine) through an mbarrier ring; the
 //            Matern/RBF nonlinearity and the k*.alpha mean are fused into its epilogue.  k* for the
-//            tile (n_pad x 64 doubles) is written once, already in DMMA B-fragment order, to the
-//            CTA's private scratch slice (L2-resident).
-//   phase 2  variance: V = inv(L) K*^T as a lower-triangular DMMA GEMM, 256 rows x 64 candidates
-//            per row block, inv(L) tiles (32 KB) and k* tiles (8 KB) streamed by a dedicated
-//            producer warp with cp.async.bulk into a 4-stage ring; row fragments above the
-//            diagonal / beyond n are skipped; the result is never stored, only sum v^2.
+//            tile (n_pad x SC_BN doubles) is written once, already in DMMA B-fragment order, to the
+//            CTA's private scratch slice, which is pinned in L2 (persisting access-policy window).
+//   phase 2  variance: V = inv(L) K*^T as a lower-triangular DMMA GEMM, SC_BM (192) rows x SC_BN
+//            candidates per row block, inv(L) tiles (SC_BM x SC_BK doubles, 48 KB) and k* tiles
+//            (SC_BK x SC_BN, 8 KB) streamed by a dedicated producer warp with cp.async.bulk into an
+//            SC_STAGES-deep ring; row fragments above the diagonal / beyond n are skipped; the
+//            result is never stored, only sum v^2.
 //   phase 3  posterior + acquisition + running argmax in registers; per-CTA partials at the end.
+// Tile geometry (SC_*) lives in ob200_internal.cuh; DESIGN.md section 3 has the measurements.
 #include <math.h>
 #include <stdlib.h>
 
