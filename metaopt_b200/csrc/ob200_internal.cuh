@@ -104,6 +104,8 @@ struct ob200_ctx {
   int64_t gather_cap = 0;
   char* prune_small_dev = nullptr; // histogram, counters, block min/max
   int64_t prune_small_cap = 0;
+  cudaStream_t copy_stream = nullptr;  // H2D of the candidate tail overlapped with scoring of the head
+  cudaEvent_t ev_main = nullptr, ev_copy = nullptr;
   double* pinned = nullptr;        // pinned staging for host entry points
   int64_t pinned_cap = 0;
 };

@@ -719,12 +719,38 @@ int ob200_score_host(ob200_ctx* ctx, const double* cand_host, int64_t ldc, int64
   double* mu_dev = mu_host ? p : nullptr; if (mu_host) p += M;
   double* sg_dev = sigma_host ? p : nullptr; if (sigma_host) p += M;
   double* aq_dev = acq_host ? p : nullptr;
-  if (ldc == D)  // contiguous rows: one flat DMA (a 2-D copy of 8*D-byte rows is an order of magnitude slower)
-    OB_CUDA(ctx, cudaMemcpyAsync(ctx->cand_tmp, cand_host, (size_t)M * D * 8, cudaMemcpyHostToDevice, ctx->stream));
-  else
-    OB_CUDA(ctx, cudaMemcpy2DAsync(ctx->cand_tmp, (size_t)D * 8, cand_host, (size_t)ldc * 8, (size_t)D * 8, (size_t)M,
-                                   cudaMemcpyHostToDevice, ctx->stream));
-  if ((rc = ob200_score_async(ctx, ctx->cand_tmp, D, M, 0, 0, acq_mask, y_opt, xi, kappa, ctx->best_dev, mu_dev, sg_dev, aq_dev))) return rc;
+  const int64_t head = (int64_t)ctx->num_sms * SC_BN * 16;  // 16 tiles per CTA: its scoring outlasts the tail's H2D copy
+  if (ldc == D && !dense && M >= 4 * head) {
+    // Overlap: copy the head, score it while the tail travels on a second stream, then score the tail
+    // into the same running argmax.
+    if (!ctx->copy_stream) {
+      OB_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+      OB_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_main, cudaEventDisableTiming));
+      OB_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_copy, cudaEventDisableTiming));
+    }
+    OB_CUDA(ctx, cudaEventRecord(ctx->ev_main, ctx->stream));        // earlier users of cand_tmp are done
+    OB_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_main, 0));
+    OB_CUDA(ctx, cudaMemcpyAsync(ctx->cand_tmp, cand_host, (size_t)head * D * 8, cudaMemcpyHostToDevice, ctx->stream));
+    OB_CUDA(ctx, cudaMemcpyAsync(ctx->cand_tmp + head * D, cand_host + head * D, (size_t)(M - head) * D * 8,
+                                 cudaMemcpyHostToDevice, ctx->copy_stream));
+    OB_CUDA(ctx, cudaEventRecord(ctx->ev_copy, ctx->copy_stream));
+    int grid = 0, grid2 = 0;
+    if ((rc = score_launch(ctx, ctx->cand_tmp, D, head, 0, acq_mask, y_opt, xi, kappa, nullptr, nullptr, nullptr, 0, &grid))) return rc;
+    OB_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_copy, 0));
+    if ((rc = score_launch(ctx, ctx->cand_tmp + head * D, D, M - head, (uint64_t)head, acq_mask, y_opt, xi, kappa, nullptr, nullptr,
+                           nullptr, 1, &grid2)))
+      return rc;
+    reduce_best_kernel<<<1, 256, 0, ctx->stream>>>(reinterpret_cast<const best_t*>(ctx->partial_dev), grid > grid2 ? grid : grid2,
+                                                   acq_mask, ctx->best_dev);
+    OB_LAUNCH_CHECK(ctx);
+  } else {
+    if (ldc == D)  // contiguous rows: one flat DMA (a 2-D copy of 8*D-byte rows is an order of magnitude slower)
+      OB_CUDA(ctx, cudaMemcpyAsync(ctx->cand_tmp, cand_host, (size_t)M * D * 8, cudaMemcpyHostToDevice, ctx->stream));
+    else
+      OB_CUDA(ctx, cudaMemcpy2DAsync(ctx->cand_tmp, (size_t)D * 8, cand_host, (size_t)ldc * 8, (size_t)D * 8, (size_t)M,
+                                     cudaMemcpyHostToDevice, ctx->stream));
+    if ((rc = ob200_score_async(ctx, ctx->cand_tmp, D, M, 0, 0, acq_mask, y_opt, xi, kappa, ctx->best_dev, mu_dev, sg_dev, aq_dev))) return rc;
+  }
   OB_CUDA(ctx, cudaMemcpyAsync(ctx->best_pinned, ctx->best_dev, 3 * sizeof(ob200_best), cudaMemcpyDeviceToHost, ctx->stream));
   if (mu_host) OB_CUDA(ctx, cudaMemcpyAsync(mu_host, mu_dev, (size_t)M * 8, cudaMemcpyDeviceToHost, ctx->stream));
   if (sigma_host) OB_CUDA(ctx, cudaMemcpyAsync(sigma_host, sg_dev, (size_t)M * 8, cudaMemcpyDeviceToHost, ctx->stream));

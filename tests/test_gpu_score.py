@@ -201,3 +201,16 @@ def test_score_before_fit_is_an_error():
             e.score(torch.zeros((4, 2), dtype=torch.float64, device="cuda"))
     finally:
         e.close()
+
+
+def test_host_entry_point_overlapped_copy_equals_device_path(engine):
+    """Large host calls copy the candidate tail on a second stream while the head is scored."""
+    X, y = gp_problem(64, 6, seed=14)
+    engine.fit(X, y, alpha=1e-6, normalize_y=True)
+    M = 148 * 32 * 16 * 4 + 77  # just above the overlap threshold, ragged
+    C = np.random.RandomState(9).uniform(size=(M, 6))
+    pinned = torch.as_tensor(C).pin_memory()
+    a = engine.score_host(pinned.numpy(), acq_mask=7, y_opt=float(y.min()))
+    b = engine.score(torch.as_tensor(C).cuda(), acq_mask=7, y_opt=float(y.min()))
+    assert a == b
+    assert engine.score_host(C, acq_mask=7, y_opt=float(y.min())) == b  # pageable host memory too
