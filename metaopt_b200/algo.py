@@ -276,9 +276,12 @@ class BayesianOptimizer(BaseAlgorithm):
         M = int(self.n_points)
         hedge = self.acq_func == "gp_hedge"
         mask = 7 if hedge else (1 << _ACQ[self.acq_func])
-        if not hedge and self.prune:
-            res, _ = eng.score_pruned(None, M=M, seed=self._seed, first_index=self._offset, acq=self.acq_func,
-                                      y_opt=y_opt, xi=float(self.xi), kappa=float(self.kappa))
+        if self.prune:
+            res = {}
+            for name in (("EI", "LCB", "PI") if hedge else (self.acq_func,)):  # same winners as one dense pass
+                one, _ = eng.score_pruned(None, M=M, seed=self._seed, first_index=self._offset, acq=name,
+                                          y_opt=y_opt, xi=float(self.xi), kappa=float(self.kappa))
+                res.update(one)
         else:
             res = eng.score(None, M=M, seed=self._seed, first_index=self._offset, acq_mask=mask, y_opt=y_opt,
                             xi=float(self.xi), kappa=float(self.kappa))
