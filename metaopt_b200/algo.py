@@ -142,13 +142,15 @@ class BayesianOptimizer(BaseAlgorithm):
     @property
     def state_dict(self):
         return {"seed": self._seed, "offset": self._offset, "hedge_gains": list(self._hedge_gains),
-                "hedge_pending": copy.deepcopy(self._hedge_pending)}
+                "hedge_pending": copy.deepcopy(self._hedge_pending), "theta": copy.deepcopy(self._theta)}
 
     def set_state(self, state_dict):
         self._seed = state_dict["seed"]
         self._offset = state_dict["offset"]
         self._hedge_gains = list(state_dict.get("hedge_gains", [0.0, 0.0, 0.0]))
         self._hedge_pending = copy.deepcopy(state_dict.get("hedge_pending"))
+        if state_dict.get("theta") is not None:  # warm start of the next hyper-parameter fit
+            self._theta = copy.deepcopy(state_dict["theta"])
 
     @property
     def space(self):

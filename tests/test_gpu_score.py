@@ -69,6 +69,31 @@ def test_cfg2_shape_n2000_d20(engine):
     _compare(engine, X, y, C)
 
 
+def test_largest_supported_fit_n8000_d100(engine):
+    """BASELINE config 4 shape at a CPU-checkable candidate count: the n = 8000 Cholesky / inverse / alpha path."""
+    X, y = gp_problem(8000, 100, seed=5)
+    C = np.random.RandomState(2).uniform(size=(257, 100))
+    _compare(engine, X, y, C)
+
+
+def test_ill_conditioned_gram_matrix(engine):
+    """No noise term, alpha = 1e-10 and clustered observations: cond(K) ~ 1e9; the posterior still has to
+    agree with scikit-learn where scikit-learn itself is stable (mean relative to its scale, std above 1e-3)."""
+    rs = np.random.RandomState(3)
+    centres = rs.uniform(size=(20, 3))
+    X = np.concatenate([c + 1e-3 * rs.randn(10, 3) for c in centres])
+    y = np.sin(3 * X).sum(axis=1)
+    C = rs.uniform(size=(500, 3))
+    engine.fit(X, y, alpha=1e-10, normalize_y=True, length_scale=0.5)
+    ref = ogp.SklearnGP(0, 1.0, 0.5 * np.ones(3), 1e-10, True).fit(X, y)
+    mu_r, sd_r = ref.predict(C)
+    out = engine.score(torch.as_tensor(C).cuda(), acq_mask=1, y_opt=float(y.min()), dense=True)
+    mu, sd = out["mu"].cpu().numpy(), out["sigma"].cpu().numpy()
+    np.testing.assert_allclose(mu, mu_r, rtol=1e-4, atol=1e-4 * np.abs(mu_r).max())
+    big = sd_r > 1e-3
+    np.testing.assert_allclose(sd[big], sd_r[big], rtol=1e-3)
+
+
 def test_host_entry_point(engine):
     X, y = gp_problem(300, 8, seed=4)
     C = np.random.RandomState(2).uniform(size=(3001, 8))
