@@ -9,11 +9,13 @@
 // B200 design: everything n x n is tiled in 64 x 64 blocks of FP64 and every O(n^3) step is a
 // DMMA (mma.sync m8n8k4 f64 -> SASS DMMA.8x8x4) tile GEMM:
 //   * right-looking Cholesky: 64x64 diagonal factor + its inverse in one CTA (shared memory),
-//     panel = A21 * inv(L11)^T (GEMM), trailing A22 -= P P^T (GEMM, lower tiles only);
+//     panel = A21 * L11^-T by forward substitution (a GEMM with inv(L11) loses cond(L11) digits),
+//     trailing A22 -= P P^T (DMMA GEMM, lower tiles only);
 //   * inv(L) by recursive doubling: X21 = -inv(C) (B inv(A)), two batched GEMMs per level;
 //   * alpha by blocked forward/back substitution in one CTA (n^2 work, bandwidth trivial).
 // inv(L) is then written in the tile-packed layout the score kernel streams with bulk copies.
 #include <math.h>
+#include <stdlib.h>
 
 #include "ob200_internal.cuh"
 
@@ -132,6 +134,7 @@ struct gemm_args {
   int m_last, k_eq_m;  // k_eq_m: K follows the batch entry's M (TRTRI second product)
   double alpha, beta;
   int lower_only;
+  int tri_k;  // both operands lower triangular: only k in [64*tn, 64*(tm+1)) contributes
 };
 
 template <bool TRANS_B>
@@ -158,7 +161,9 @@ __global__ void __launch_bounds__(128) gemm64_kernel(gemm_args g) {
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
 
-  for (int k0 = 0; k0 < K; k0 += GEMM_BK) {
+  const int k_begin = g.tri_k ? tn * 64 : 0;
+  if (g.tri_k) { const int k_end = (tm + 1) * 64; if (k_end < K) K = k_end; }
+  for (int k0 = k_begin; k0 < K; k0 += GEMM_BK) {
     {  // A tile 64 x 16: thread -> row tid/2, 8 contiguous doubles
       const int r = tid >> 1, c = (tid & 1) * 8;
       const double2* src = reinterpret_cast<const double2*>(A + (size_t)r * g.lda + k0 + c);
@@ -284,17 +289,60 @@ __global__ void trtri_init_kernel(double* __restrict__ X, int ld, const double* 
   for (int e = threadIdx.x; e < FB * FB; e += blockDim.x) blk[(size_t)(e >> 6) * ld + (e & 63)] = d[e];
 }
 
-// alpha = L^-T L^-1 y by blocked substitution with the inverted diagonal blocks; also
+// Panel of the blocked Cholesky: P = A21 * L11^-T by forward substitution, four lanes per row, 64 rows per
+// CTA.  (Multiplying by an explicitly inverted L11 loses cond(L11) digits: 7e-6 instead of 3e-8 in the
+// posterior variance at cond(K) = 1e12, see tools/illcond_probe.py.)
+__global__ void __launch_bounds__(256) chol_panel_trsm_kernel(double* __restrict__ A, int ld, int kb) {
+  extern __shared__ double psm[];
+  double (*Lk)[FB + 1] = reinterpret_cast<double (*)[FB + 1]>(psm);                 // L11[j][k]
+  double (*Xt)[FB + 1] = reinterpret_cast<double (*)[FB + 1]>(psm + FB * (FB + 1));  // row tile, transposed: Xt[k][row]
+  const int tid = threadIdx.x, row = tid >> 2, sub = tid & 3;  // 4 lanes per row split the inner sum
+  const size_t r0 = (size_t)(kb + 1 + blockIdx.x) * FB;
+  const double* Ld = A + (size_t)kb * FB * ld + (size_t)kb * FB;
+  double* At = A + r0 * ld + (size_t)kb * FB;
+  for (int e = tid; e < FB * FB; e += 256) {
+    const int r = e >> 6, c = e & 63;
+    Lk[r][c] = Ld[(size_t)r * ld + c];
+    Xt[c][r] = At[(size_t)r * ld + c];
+  }
+  __syncthreads();
+  for (int j = 0; j < FB; ++j) {
+    double acc = 0.0;
+    for (int k = sub; k < j; k += 4) acc = fma(Xt[k][row], Lk[j][k], acc);
+    acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+    acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+    if (sub == 0) Xt[j][row] = (Xt[j][row] - acc) / Lk[j][j];
+    __syncwarp();
+  }
+  __syncthreads();
+  for (int e = tid; e < FB * FB; e += 256) {
+    const int r = e >> 6, c = e & 63;
+    At[(size_t)r * ld + c] = Xt[c][r];
+  }
+}
+
+// R <- I - R on the lower triangle, 0 above it (32x32 tiles)
+__global__ void __launch_bounds__(256) eye_minus_lower_kernel(double* __restrict__ R, int n_pad) {
+  const int ti = blockIdx.y, tj = blockIdx.x;
+  for (int e = threadIdx.x; e < 1024; e += 256) {
+    const int i = ti * 32 + (e >> 5), j = tj * 32 + (e & 31);
+    double* p = R + (size_t)i * n_pad + j;
+    *p = (j > i) ? 0.0 : ((i == j ? 1.0 : 0.0) - *p);
+  }
+}
+
+// alpha = L^-T L^-1 y by blocked substitution (diagonal blocks by substitution too, like LAPACK potrs); also
 // lml = -0.5 y^T alpha - sum log L_ii - n/2 log(2 pi).  One CTA of 1024 threads.
 __global__ void __launch_bounds__(1024) chol_solve_kernel(const double* __restrict__ L, int ld, int n, int n_pad,
-                                                          const double* __restrict__ Dinv, const double* __restrict__ y,
-                                                          double* __restrict__ tvec, double* __restrict__ alpha_out,
-                                                          double* __restrict__ lml_out) {
+                                                          const double* __restrict__ y, double* __restrict__ tvec,
+                                                          double* __restrict__ alpha_out, double* __restrict__ lml_out) {
   __shared__ double part[16][FB + 1];
   __shared__ double r[FB];
-  const int tid = threadIdx.x;
+  __shared__ double shbuf[FB * (FB + 1)];  // diagonal block L_ii during the sweeps, reduction scratch at the end
+  double (*Ld)[FB + 1] = reinterpret_cast<double (*)[FB + 1]>(shbuf);
+  const int tid = threadIdx.x, lane = tid & 31;
   const int nb = n_pad / FB;
-  // forward: t_i = Dinv_i (y_i - L[i, :64 i] t[:64 i])
+  // forward: L_ii t_i = y_i - L[i, :64 i] t[:64 i], the diagonal system by substitution (warp 0)
   for (int ib = 0; ib < nb; ++ib) {
     {
       const int row = tid >> 4, g = tid & 15;  // 64 rows x 16 column lanes
@@ -303,6 +351,7 @@ __global__ void __launch_bounds__(1024) chol_solve_kernel(const double* __restri
       for (int j = g; j < ib * FB; j += 16) acc = fma(Lr[j], tvec[j], acc);
       part[g][row] = acc;
     }
+    for (int e = tid; e < FB * FB; e += 1024) Ld[e >> 6][e & 63] = L[(size_t)(ib * FB + (e >> 6)) * ld + ib * FB + (e & 63)];
     __syncthreads();
     if (tid < FB) {
       double s = 0.0;
@@ -310,16 +359,22 @@ __global__ void __launch_bounds__(1024) chol_solve_kernel(const double* __restri
       r[tid] = y[ib * FB + tid] - s;
     }
     __syncthreads();
-    if (tid < FB) {
-      const double* d = Dinv + (size_t)ib * FB * FB + (size_t)tid * FB;
-      double s = 0.0;
-      for (int k = 0; k <= tid; ++k) s = fma(d[k], r[k], s);
-      tvec[ib * FB + tid] = s;
+    if (tid < 32) {
+      for (int j = 0; j < FB; ++j) {
+        double p = 0.0;
+        if (lane < j) p = Ld[j][lane] * r[lane];
+        if (lane + 32 < j) p = fma(Ld[j][lane + 32], r[lane + 32], p);
+        for (int off = 16; off > 0; off >>= 1) p += __shfl_xor_sync(0xffffffffu, p, off);
+        if (lane == 0) r[j] = (r[j] - p) / Ld[j][j];
+        __syncwarp();
+      }
+      tvec[ib * FB + lane] = r[lane];
+      tvec[ib * FB + lane + 32] = r[lane + 32];
     }
     __threadfence_block();
     __syncthreads();
   }
-  // backward: alpha_i = Dinv_i^T (t_i - sum_{k >= 64(i+1)} L[k, i-block]^T alpha_k)
+  // backward: L_ii^T alpha_i = t_i - sum_{k >= 64(i+1)} L[k, i-block]^T alpha_k
   for (int ib = nb - 1; ib >= 0; --ib) {
     {
       const int c = tid & 63, g = tid >> 6;  // 64 columns x 16 row lanes
@@ -327,6 +382,7 @@ __global__ void __launch_bounds__(1024) chol_solve_kernel(const double* __restri
       for (int k = (ib + 1) * FB + g; k < n_pad; k += 16) acc = fma(L[(size_t)k * ld + ib * FB + c], alpha_out[k], acc);
       part[g][c] = acc;
     }
+    for (int e = tid; e < FB * FB; e += 1024) Ld[e >> 6][e & 63] = L[(size_t)(ib * FB + (e >> 6)) * ld + ib * FB + (e & 63)];
     __syncthreads();
     if (tid < FB) {
       double s = 0.0;
@@ -334,11 +390,17 @@ __global__ void __launch_bounds__(1024) chol_solve_kernel(const double* __restri
       r[tid] = tvec[ib * FB + tid] - s;
     }
     __syncthreads();
-    if (tid < FB) {
-      const double* d = Dinv + (size_t)ib * FB * FB;
-      double s = 0.0;
-      for (int m = tid; m < FB; ++m) s = fma(d[(size_t)m * FB + tid], r[m], s);
-      alpha_out[ib * FB + tid] = (ib * FB + tid < n) ? s : 0.0;
+    if (tid < 32) {
+      for (int j = FB - 1; j >= 0; --j) {
+        double p = 0.0;
+        if (lane > j) p = Ld[lane][j] * r[lane];
+        if (lane + 32 > j) p = fma(Ld[lane + 32][j], r[lane + 32], p);
+        for (int off = 16; off > 0; off >>= 1) p += __shfl_xor_sync(0xffffffffu, p, off);
+        if (lane == 0) r[j] = (r[j] - p) / Ld[j][j];
+        __syncwarp();
+      }
+      alpha_out[ib * FB + lane] = (ib * FB + lane < n) ? r[lane] : 0.0;
+      alpha_out[ib * FB + lane + 32] = (ib * FB + lane + 32 < n) ? r[lane + 32] : 0.0;
     }
     __threadfence_block();
     __syncthreads();
@@ -346,7 +408,8 @@ __global__ void __launch_bounds__(1024) chol_solve_kernel(const double* __restri
   // lml
   double a = 0.0, b = 0.0;
   for (int i = tid; i < n; i += 1024) { a = fma(y[i], alpha_out[i], a); b += log(L[(size_t)i * ld + i]); }
-  __shared__ double ra[1024], rb[1024];
+  double* ra = shbuf;
+  double* rb = shbuf + 1024;
   ra[tid] = a; rb[tid] = b;
   __syncthreads();
   for (int s = 512; s > 0; s >>= 1) { if (tid < s) { ra[tid] += ra[tid + s]; rb[tid] += rb[tid + s]; } __syncthreads(); }
@@ -562,12 +625,12 @@ int ob200_gp_fit(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n
   if ((rc = ob_reserve(ctx, &ctx->blob, &ctx->blob_cap, lay.total))) return rc;
   if ((rc = ob_reserve(ctx, &ctx->L_dev, &ctx->L_cap, (int64_t)n_pad * n_pad))) return rc;
   // workspace: X (n_pad^2) | T (n_pad^2 / 2) | Dinv (nb*64*64) | Xs (n_pad*D_pad) | y_norm | tvec | ls | stats(4) | info
-  const int64_t w_X = 0, w_T = w_X + (int64_t)n_pad * n_pad, w_Dinv = w_T + (int64_t)n_pad * n_pad / 2,
+  const int64_t w_X = 0, w_T = w_X + (int64_t)n_pad * n_pad, w_X2 = w_T + (int64_t)n_pad * n_pad, w_Dinv = w_X2 + (int64_t)n_pad * n_pad,
                 w_Xs = w_Dinv + (int64_t)nb * FB * FB, w_y = w_Xs + (int64_t)n_pad * D_pad, w_t = w_y + n_pad,
                 w_ls = w_t + n_pad, w_stats = w_ls + D_pad, w_end = w_stats + 8;
   if ((rc = ob_reserve(ctx, &ctx->work_dev, &ctx->work_cap, w_end))) return rc;
   double* W = ctx->work_dev;
-  double *Xinv = W + w_X, *T = W + w_T, *Dinv = W + w_Dinv, *Xs = W + w_Xs, *ynorm = W + w_y, *tvec = W + w_t,
+  double *Xinv = W + w_X, *T = W + w_T, *X2 = W + w_X2, *Dinv = W + w_Dinv, *Xs = W + w_Xs, *ynorm = W + w_y, *tvec = W + w_t,
          *ls_dev = W + w_ls, *stats = W + w_stats;
   int* info_dev = reinterpret_cast<int*>(stats + 6);
   double* lml_dev = stats + 4;
@@ -596,20 +659,19 @@ int ob200_gp_fit(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n
   // ---- right-looking blocked Cholesky ----------------------------------------------------
   double* Lm = ctx->L_dev;
   const size_t diag_smem = (size_t)2 * FB * (FB + 1) * sizeof(double);
+  const size_t panel_smem = diag_smem;
+  OB_CUDA(ctx, cudaFuncSetAttribute(chol_panel_trsm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)panel_smem));
   OB_CUDA(ctx, cudaFuncSetAttribute(chol_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)diag_smem));
   for (int kb = 0; kb < nb; ++kb) {
     chol_diag_kernel<<<1, 256, diag_smem, st>>>(Lm, n_pad, kb, Dinv, info_dev);
     OB_LAUNCH_CHECK(ctx);
     const int rem = n_pad - (kb + 1) * FB;
     if (rem <= 0) break;
-    gemm_args p{};
-    p.A = Lm + (size_t)(kb + 1) * FB * n_pad + (size_t)kb * FB; p.lda = n_pad;
-    p.B = Dinv + (size_t)kb * FB * FB; p.ldb = FB;
-    p.C = const_cast<double*>(p.A); p.ldc = n_pad;
-    p.M = rem; p.N = FB; p.K = FB; p.alpha = 1.0; p.beta = 0.0;
-    if ((rc = launch_gemm(ctx, true, p, 1))) return rc;
+    chol_panel_trsm_kernel<<<rem / FB, 256, panel_smem, st>>>(Lm, n_pad, kb);
+    OB_LAUNCH_CHECK(ctx);
+    const double* panel = Lm + (size_t)(kb + 1) * FB * n_pad + (size_t)kb * FB;
     gemm_args s{};
-    s.A = p.A; s.lda = n_pad; s.B = p.A; s.ldb = n_pad;
+    s.A = panel; s.lda = n_pad; s.B = panel; s.ldb = n_pad;
     s.C = Lm + (size_t)(kb + 1) * FB * n_pad + (size_t)(kb + 1) * FB; s.ldc = n_pad;
     s.M = rem; s.N = rem; s.K = FB; s.alpha = -1.0; s.beta = 1.0; s.lower_only = 1;
     if ((rc = launch_gemm(ctx, true, s, 1))) return rc;
@@ -623,7 +685,7 @@ int ob200_gp_fit(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n
             "parameter of your GaussianProcessRegressor estimator.", info, n);
 
   // ---- alpha, lml ----------------------------------------------------------------------------
-  chol_solve_kernel<<<1, 1024, 0, st>>>(Lm, n_pad, n, n_pad, Dinv, ynorm, tvec, b_alpha, lml_dev);
+  chol_solve_kernel<<<1, 1024, 0, st>>>(Lm, n_pad, n, n_pad, ynorm, tvec, b_alpha, lml_dev);
   OB_LAUNCH_CHECK(ctx);
 
   // ---- inv(L) by recursive doubling ----------------------------------------------------------
@@ -647,6 +709,23 @@ int ob200_gp_fit(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n
     g2.C = Xinv + (size_t)s * n_pad; g2.ldc = n_pad; g2.strideC = stride;
     g2.M = s; g2.N = s; g2.K = s; g2.m_last = c_last; g2.k_eq_m = 1; g2.alpha = -1.0; g2.beta = 0.0;
     if ((rc = launch_gemm(ctx, false, g2, pairs))) return rc;
+  }
+  // One Newton-Schulz step X <- X + X (I - L X): the recursive-doubling products compound rounding errors
+  // level by level (residual ~1e-6 at cond(K) = 1e12); the residual I - L X is computed to cond(L) eps, so one
+  // step brings inv(L) to the accuracy of a backward-stable triangular solve (tools/illcond_probe.py).
+  if (!getenv("OB200_NO_NS")) {  // (testing hook: measure what the refinement buys)
+    gemm_args r{};  // T = L X  (lower x lower -> lower tiles, triangular k range)
+    r.A = Lm; r.lda = n_pad; r.B = Xinv; r.ldb = n_pad; r.C = T; r.ldc = n_pad;
+    r.M = n_pad; r.N = n_pad; r.K = n_pad; r.alpha = 1.0; r.beta = 0.0; r.lower_only = 1; r.tri_k = 1;
+    if ((rc = launch_gemm(ctx, false, r, 1))) return rc;
+    eye_minus_lower_kernel<<<dim3(n_pad / 32, n_pad / 32), 256, 0, st>>>(T, n_pad);
+    OB_LAUNCH_CHECK(ctx);
+    OB_CUDA(ctx, cudaMemcpyAsync(X2, Xinv, (size_t)n_pad * n_pad * 8, cudaMemcpyDeviceToDevice, st));
+    gemm_args u{};  // X2 = X + X T
+    u.A = Xinv; u.lda = n_pad; u.B = T; u.ldb = n_pad; u.C = X2; u.ldc = n_pad;
+    u.M = n_pad; u.N = n_pad; u.K = n_pad; u.alpha = 1.0; u.beta = 1.0; u.lower_only = 1; u.tri_k = 1;
+    if ((rc = launch_gemm(ctx, false, u, 1))) return rc;
+    OB_CUDA(ctx, cudaMemcpyAsync(Xinv, X2, (size_t)n_pad * n_pad * 8, cudaMemcpyDeviceToDevice, st));
   }
   pack_linv_kernel<<<ctx->num_sms * 8, 256, 0, st>>>(Xinv, n, n_pad, b_linv);
   OB_LAUNCH_CHECK(ctx);
