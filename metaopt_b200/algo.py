@@ -97,7 +97,8 @@ class BayesianOptimizer(BaseAlgorithm):
     ('EI' | 'PI' | 'LCB' | 'gp_hedge'), `alpha`, `n_restarts_optimizer`, `noise`, `normalize_y`.
     Additive keys (defaults keep reference behaviour): `n_points` (candidates per suggest, skopt's
     default 10000), `xi`, `kappa`, `kernel` ('matern52' | 'rbf'), `length_scale`, `amplitude`,
-    `noise_level` (variance folded into the diagonal when `noise == 'gaussian'`), `device`, `prune`
+    `noise_level` (variance folded into the diagonal when `noise == 'gaussian'`), `device` (an index, or a
+    list of indices to shard the candidates of every suggest over several GPUs of this process), `prune`
     (exact mean-only pruning of hopeless candidates for single acquisitions; same winner, faster),
     `fit_hyperparameters` (maximise the log marginal likelihood over amplitude, per-dimension length
     scales and -- when `noise == 'gaussian'` -- the noise level, like the reference's scikit-learn
@@ -217,8 +218,16 @@ class BayesianOptimizer(BaseAlgorithm):
 
     # ---- internals -------------------------------------------------------------------------
     def _engine(self):
+        """Process-wide engine: one device (`device: 0`) or several in this process (`device: [0, 1, ...]`)."""
+        if isinstance(self.device, (list, tuple)):
+            if len(self.device) > 1:
+                from .multi import get_multi_engine
+                return get_multi_engine(self.device)
+            device = self.device[0]
+        else:
+            device = self.device
         from .engine import get_engine
-        return get_engine(int(self.device))
+        return get_engine(int(device))
 
     def _get_compiled(self):
         if self._compiled is None:
