@@ -135,6 +135,14 @@ int ob200_gp_lml(ob200_ctx* ctx, double* lml_host);
  * d/d(diagonal term) (multiply by the noise level for d/dlog(noise)).  n_grad must be D+2.  Needs a
  * fit made on this context (not an imported one).  Synchronous. */
 int ob200_gp_lml_grad(ob200_ctx* ctx, double* lml_host, double* grad_host, int n_grad);
+/* Posterior mean / standard deviation and their gradients with respect to the (normalised) input at m <= 64
+ * points: what skopt's acquisition optimiser "lbfgs" evaluates per step through its GaussianProcessRegressor
+ * subclass, predict(X, return_std=True, return_mean_grad=True, return_std_grad=True) (scikit-optimize, no version pinned
+ * by the reference -- SURVEY.md row 19; skopt/learning/gaussian_process/gpr.py, third-party and absent from the
+ * reference tree; reached from the fmin_l_bfgs_b loop of Optimizer._tell, skopt/optimizer/optimizer.py).  x_host [m x ldx] row-major,
+ * out_host [m x (2 + 2 D)]: mu, sigma, dmu/dx[D], dsigma/dx[D] per point, same units as ob200_score.
+ * sigma == 0 gives a zero dsigma.  Needs a fit made on this context (not an imported one).  Synchronous. */
+int ob200_gp_predict_grad_host(ob200_ctx* ctx, const double* x_host, int64_t ldx, int m, double* out_host);
 /* Parity/debug read-back of L [n x n] (lower, row-major, upper = 0) and alpha_ [n] (either may be NULL). */
 int ob200_gp_get_factor(ob200_ctx* ctx, double* L_host, double* alpha_host);
 /* y statistics used by the fit: y_mean, y_std (after _handle_zeros_in_scale), min(y). */

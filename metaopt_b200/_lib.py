@@ -61,6 +61,7 @@ SIGNATURES = {
     "ob200_gp_fit_host": (_i, [_vp, _vp, _vp, _i, _i, C.POINTER(Kernel), _d, _i]),
     "ob200_gp_lml": (_i, [_vp, _pd]),
     "ob200_gp_lml_grad": (_i, [_vp, _pd, _pd, _i]),
+    "ob200_gp_predict_grad_host": (_i, [_vp, _vp, _i64, _i, _vp]),
     "ob200_gp_get_factor": (_i, [_vp, _vp, _vp]),
     "ob200_gp_get_ystats": (_i, [_vp, _pd, _pd, _pd]),
     "ob200_gp_state_bytes": (_i, [_vp, _i, _i, C.POINTER(_i64)]),

@@ -103,7 +103,10 @@ class BayesianOptimizer(BaseAlgorithm):
     `fit_hyperparameters` (maximise the log marginal likelihood over amplitude, per-dimension length
     scales and -- when `noise == 'gaussian'` -- the noise level, like the reference's scikit-learn
     estimator does, with `n_restarts_optimizer` extra starts; `length_scale`/`amplitude`/`noise_level`
-    are then the starting point).
+    are then the starting point), `acq_optimizer` ('sampling': the proposal is the best of the `n_points`
+    candidates; 'lbfgs': skopt's default for this space -- the best candidate of each of `acq_n_restarts`
+    (5) slices of the candidate stream starts an L-BFGS-B ascent of the acquisition inside the unit box,
+    `metaopt_b200/acq_opt.py`, and the best end point is proposed).
     """
 
     requires = "real"
@@ -112,7 +115,7 @@ class BayesianOptimizer(BaseAlgorithm):
     def __init__(self, space, seed=None, n_initial_points=10, acq_func="gp_hedge", alpha=1e-10,
                  n_restarts_optimizer=0, noise="gaussian", normalize_y=False, n_points=10000, xi=0.01,
                  kappa=1.96, kernel="matern52", length_scale=1.0, amplitude=1.0, noise_level=1e-4, device=0,
-                 prune=True, fit_hyperparameters=True):
+                 prune=True, fit_hyperparameters=True, acq_optimizer="sampling", acq_n_restarts=5):
         self._seed = None
         self._offset = 0          # next unused global candidate index of the Philox stream
         self._X = []              # observed points, flat + normalised
@@ -125,7 +128,10 @@ class BayesianOptimizer(BaseAlgorithm):
                          n_restarts_optimizer=n_restarts_optimizer, noise=noise, normalize_y=normalize_y,
                          n_points=n_points, xi=xi, kappa=kappa, kernel=kernel, length_scale=length_scale,
                          amplitude=amplitude, noise_level=noise_level, device=device, prune=prune,
-                         fit_hyperparameters=fit_hyperparameters)
+                         fit_hyperparameters=fit_hyperparameters, acq_optimizer=acq_optimizer,
+                         acq_n_restarts=acq_n_restarts)
+        if str(acq_optimizer) not in ("sampling", "lbfgs"):
+            raise ValueError("acq_optimizer must be 'sampling' or 'lbfgs'; got %r" % (acq_optimizer,))
         if str(acq_func) not in ("EI", "PI", "LCB", "gp_hedge"):
             raise ValueError("acq_func must be one of 'EI', 'PI', 'LCB', 'gp_hedge' (EIps/PIps need timings "
                              "that Orion does not pass); got %r" % (acq_func,))
@@ -282,21 +288,48 @@ class BayesianOptimizer(BaseAlgorithm):
             self._theta = copy.deepcopy(eng._fit_theta)
         return float(y.min())
 
-    def _suggest_gp(self, eng, comp):
-        y_opt = self._ensure_fit(eng)
-        M = int(self.n_points)
+    def _score_range(self, eng, first, count, y_opt):
+        """Winner(s) {acq name: record} of the candidates [first, first + count) of the stream."""
         hedge = self.acq_func == "gp_hedge"
-        mask = 7 if hedge else (1 << _ACQ[self.acq_func])
         if self.prune:
             res = {}
             for name in (("EI", "LCB", "PI") if hedge else (self.acq_func,)):  # same winners as one dense pass
-                one, _ = eng.score_pruned(None, M=M, seed=self._seed, first_index=self._offset, acq=name,
+                one, _ = eng.score_pruned(None, M=count, seed=self._seed, first_index=first, acq=name,
                                           y_opt=y_opt, xi=float(self.xi), kappa=float(self.kappa))
                 res.update(one)
+            return res
+        mask = 7 if hedge else (1 << _ACQ[self.acq_func])
+        return eng.score(None, M=count, seed=self._seed, first_index=first, acq_mask=mask, y_opt=y_opt,
+                         xi=float(self.xi), kappa=float(self.kappa))
+
+    def _suggest_gp(self, eng, comp):
+        from . import dist as obdist
+        y_opt = self._ensure_fit(eng)
+        M = int(self.n_points)
+        hedge = self.acq_func == "gp_hedge"
+        refine = self.acq_optimizer == "lbfgs"
+        parts = []
+        if refine:  # one start per slice of the stream; the global winner is the best of them
+            n_parts = max(1, min(int(self.acq_n_restarts), M))
+            for r in range(n_parts):
+                start, count = obdist.shard_range(M, r, n_parts)
+                parts.append(self._score_range(eng, self._offset + start, count, y_opt))
+            res = obdist.merge_best(parts)
         else:
-            res = eng.score(None, M=M, seed=self._seed, first_index=self._offset, acq_mask=mask, y_opt=y_opt,
-                            xi=float(self.xi), kappa=float(self.kappa))
+            res = self._score_range(eng, self._offset, M, y_opt)
         self._offset += M
+        rows = {}
+        if refine:
+            from . import acq_opt
+            for name in res:
+                idx = sorted({int(p[name]["index"]) for p in parts if p and name in p},
+                             key=lambda i: (i != int(res[name]["index"]), i))  # global winner first
+                starts = np.stack([eng.sample(self._seed, i, 1, normalise=True).cpu().numpy()[0] for i in idx])
+                best = acq_opt.refine(eng, name, starts, y_opt, xi=float(self.xi), kappa=float(self.kappa))
+                # Orion's intervals are half-open (`space.py:356`: low <= x < high): an ascent that stops on the
+                # upper face is moved one ulp inside.
+                rows[name] = np.clip(comp.denormalise(best.x), comp.nlo, np.nextafter(comp.nhi, comp.nlo))
+                res[name] = dict(res[name], value=best.value, mu=best.mu, sigma=best.sigma, index=idx[best.start])
         if hedge:
             # skopt's gp_hedge: draw one of the three proposals with probability softmax(eta * gains);
             # the draw itself uses the Philox stream so that it follows state_dict/set_state.
@@ -305,12 +338,13 @@ class BayesianOptimizer(BaseAlgorithm):
             logits = gains - gains.max()
             probs = np.exp(logits) / np.exp(logits).sum()
             u = float(self._uniform())
-            pick = int(min(np.searchsorted(np.cumsum(probs), u, side="right"), 2))
+            pick = names[int(min(np.searchsorted(np.cumsum(probs), u, side="right"), 2))]
             self._hedge_pending = [(res[n]["index"], res[n]["mu"]) for n in names]
-            winner = res[names[pick]]
         else:
-            winner = res[self.acq_func]
-        return eng.sample(self._seed, winner["index"], 1, normalise=False).cpu().numpy()[0]
+            pick = self.acq_func
+        if refine:
+            return rows[pick]
+        return eng.sample(self._seed, res[pick]["index"], 1, normalise=False).cpu().numpy()[0]
 
     def _uniform(self):
         """One host-side uniform from the same counter-based stream (stream position = offset)."""

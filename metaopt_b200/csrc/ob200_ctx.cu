@@ -61,6 +61,7 @@ void ob200_ctx_destroy(ob200_ctx* ctx) {
   cudaFree(ctx->L_dev);
   cudaFree(ctx->work_dev);
   cudaFree(ctx->grad_dev);
+  cudaFree(ctx->pg_dev);
   cudaFree(ctx->kstar_dev);
   cudaFree(ctx->cand_tmp);
   cudaFree(ctx->dense_tmp);

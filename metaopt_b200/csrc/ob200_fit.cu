@@ -581,6 +581,118 @@ __global__ void __launch_bounds__(256) lml_final_kernel(const double* __restrict
   if (threadIdx.x == 0) out[which] = red[0];
 }
 
+// ---- posterior mean / std-dev gradients at a few points (acquisition refinement) ------------------------------
+// k_j = amp f(r_j), dk_j/dx_d = -g_j u_jd / ls_d with u_jd = (x_d - X_jd) / ls_d;
+// Matern 5/2: g = amp (5/3)(1 + sqrt5 r) exp(-sqrt5 r) (no 1/r singularity);  RBF: g = k.
+__global__ void __launch_bounds__(256) pg_k_kernel(const double* __restrict__ x, int ldx, const double* __restrict__ ls,
+                                                   const double* __restrict__ Xs, int n, int n_pad, int D, int D_pad, int kind,
+                                                   double amplitude, double* __restrict__ xs_out, double* __restrict__ Kv,
+                                                   double* __restrict__ Gv) {
+  extern __shared__ double pg_xs[];
+  const int p = blockIdx.y;
+  for (int d = threadIdx.x; d < D_pad; d += blockDim.x) {
+    const double v = d < D ? x[(size_t)p * ldx + d] / ls[d] : 0.0;  // the same quotient as scale_x_kernel
+    pg_xs[d] = v;
+    if (blockIdx.x == 0) xs_out[(size_t)p * D_pad + d] = v;
+  }
+  __syncthreads();
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n_pad) return;
+  double k = 0.0, g = 0.0;
+  if (j < n) {
+    double r2 = 0.0;
+    for (int d = 0; d < D_pad; ++d) { const double u = pg_xs[d] - Xs[(size_t)j * D_pad + d]; r2 = fma(u, u, r2); }
+    if (kind == OB200_KERNEL_MATERN52) {
+      const double t = sqrt(r2) * 2.23606797749979, e = exp(-t);
+      k = amplitude * ((1.0 + t + t * t / 3.0) * e);
+      g = amplitude * (5.0 / 3.0) * (1.0 + t) * e;
+    } else {
+      k = amplitude * exp(-0.5 * r2);
+      g = k;
+    }
+  }
+  Kv[(size_t)p * n_pad + j] = k;
+  Gv[(size_t)p * n_pad + j] = g;
+}
+
+// v = inv(L) k: one warp per row, lanes stride the columns (coalesced), fixed shuffle tree.
+__global__ void __launch_bounds__(256) pg_v_kernel(const double* __restrict__ Xinv, const double* __restrict__ Kv, int n_pad,
+                                                   double* __restrict__ V) {
+  const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31, p = blockIdx.y;
+  if (i >= n_pad) return;
+  const double* row = Xinv + (size_t)i * n_pad;
+  const double* kv = Kv + (size_t)p * n_pad;
+  double acc = 0.0;
+  for (int j = lane; j <= i; j += 32) acc = fma(row[j], kv[j], acc);
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if (lane == 0) V[(size_t)p * n_pad + i] = acc;
+}
+
+// w = inv(L)^T v = K^-1 k: 32 columns per CTA, 8 row groups walking down the rows (each row segment is one
+// coalesced 256 B read), fixed-order reduction over the groups.
+__global__ void __launch_bounds__(256) pg_w_kernel(const double* __restrict__ Xinv, const double* __restrict__ V, int n_pad,
+                                                   double* __restrict__ Wv) {
+  __shared__ double part[8][33];
+  const int c = threadIdx.x & 31, g = threadIdx.x >> 5, j0 = blockIdx.x * 32, j = j0 + c, p = blockIdx.y;
+  const double* v = V + (size_t)p * n_pad;
+  double acc = 0.0;
+  if (j < n_pad)
+    for (int i = j0 + g; i < n_pad; i += 8)
+      if (i >= j) acc = fma(Xinv[(size_t)i * n_pad + j], v[i], acc);
+  part[g][c] = acc;
+  __syncthreads();
+  if (g == 0 && j < n_pad) {
+    double t = 0.0;
+    for (int k = 0; k < 8; ++k) t += part[k][c];
+    Wv[(size_t)p * n_pad + j] = t;
+  }
+}
+
+__device__ __forceinline__ double pg_block_sum(double v, double* red) {
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  double t = 0.0;
+  for (int w = 0; w < 8; ++w) t += red[w];
+  return t;
+}
+
+// out[p] = (mu, sigma, dmu/dx[D], dsigma/dx[D]) in the units of ob200_score's mu / sigma.
+__global__ void __launch_bounds__(256) pg_final_kernel(const double* __restrict__ xs, const double* __restrict__ ls,
+                                                       const double* __restrict__ Xs, const double* __restrict__ alpha,
+                                                       const double* __restrict__ Kv, const double* __restrict__ Gv,
+                                                       const double* __restrict__ V, const double* __restrict__ Wv, int n, int n_pad,
+                                                       int D, int D_pad, double amplitude, double y_mean, double y_std,
+                                                       double* __restrict__ out) {
+  __shared__ double red[8];
+  const int p = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const double *kv = Kv + (size_t)p * n_pad, *gv = Gv + (size_t)p * n_pad, *v = V + (size_t)p * n_pad, *wv = Wv + (size_t)p * n_pad;
+  double m = 0.0, s2 = 0.0;
+  for (int j = threadIdx.x; j < n_pad; j += 256) { m = fma(kv[j], alpha[j], m); s2 = fma(v[j], v[j], s2); }
+  m = pg_block_sum(m, red);
+  s2 = pg_block_sum(s2, red);
+  double var = amplitude - s2;
+  if (var < 0.0) var = 0.0;
+  const double sd = sqrt(var);
+  double* o = out + (size_t)p * (2 + 2 * D);
+  if (threadIdx.x == 0) { o[0] = y_std * m + y_mean; o[1] = y_std * sd; }
+  for (int d = warp; d < D; d += 8) {
+    const double xd = xs[(size_t)p * D_pad + d];
+    double a1 = 0.0, a2 = 0.0;
+    for (int j = lane; j < n; j += 32) {
+      const double gu = gv[j] * (xd - Xs[(size_t)j * D_pad + d]);
+      a1 = fma(alpha[j], gu, a1);
+      a2 = fma(wv[j], gu, a2);
+    }
+    for (int s = 16; s > 0; s >>= 1) { a1 += __shfl_xor_sync(0xffffffffu, a1, s); a2 += __shfl_xor_sync(0xffffffffu, a2, s); }
+    if (lane == 0) {
+      o[2 + d] = -y_std * a1 / ls[d];
+      o[2 + D + d] = var > 0.0 ? y_std * (a2 / ls[d]) / sd : 0.0;  // d sqrt(var) = dvar / (2 sd), dvar = 2 a2 / ls
+    }
+  }
+}
+
 int launch_gemm(ob200_ctx* ctx, bool trans_b, const gemm_args& g, int batch) {
   dim3 grid(g.N / 64, g.M / 64, batch);
   if (grid.x == 0 || grid.y == 0 || batch == 0) return OB200_OK;
@@ -806,6 +918,48 @@ int ob200_gp_lml_grad(ob200_ctx* ctx, double* lml_host, double* grad_host, int n
   for (int d = 0; d < D; ++d) grad_host[1 + d] = h[1 + d];
   grad_host[1 + D] = h[1 + D_pad];
   if (lml_host) *lml_host = ctx->hdr.lml;
+  return OB200_OK;
+}
+
+int ob200_gp_predict_grad_host(ob200_ctx* ctx, const double* x_host, int64_t ldx, int m, double* out_host) {
+  if (!ctx) return OB200_EINVAL;
+  if (!x_host || !out_host) OB_FAIL(ctx, OB200_EINVAL, "null argument");
+  if (!ctx->fitted || !ctx->have_local_fit) OB_FAIL(ctx, OB200_ESTATE, "the posterior gradient needs a fit made on this context");
+  const int n = ctx->hdr.n, n_pad = ctx->hdr.n_pad, D = ctx->hdr.D, D_pad = ctx->hdr.D_pad;
+  if (m < 1 || m > 64) OB_FAIL(ctx, OB200_EINVAL, "m=%d outside [1, 64]", m);
+  if (ldx < D) OB_FAIL(ctx, OB200_EINVAL, "ldx=%lld < D=%d", (long long)ldx, D);
+  OB_CUDA(ctx, cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
+  const ob200_blob_layout lay = ob_blob_layout(n_pad, D_pad);
+  const double* alpha = reinterpret_cast<const double*>(ctx->blob + lay.off_alpha);
+  const double* invls = reinterpret_cast<const double*>(ctx->blob + lay.off_invls);  // holds ls_d (the blob's divisor table)
+  const double* Xinv = ctx->work_dev;                 // dense inv(L), row-major (fit workspace, offset 0)
+  const double* Xs = ctx->work_dev + ctx->w_Xs_off;   // X / ls, row-major [n_pad x D_pad]
+  const int W = 2 + 2 * D;
+  const int64_t p_x = 0, p_xs = p_x + (int64_t)m * D, p_K = p_xs + (int64_t)m * D_pad, p_G = p_K + (int64_t)m * n_pad,
+                p_V = p_G + (int64_t)m * n_pad, p_W = p_V + (int64_t)m * n_pad, p_out = p_W + (int64_t)m * n_pad,
+                p_end = p_out + (int64_t)m * W;
+  int rc = ob_reserve(ctx, &ctx->pg_dev, &ctx->pg_cap, p_end);
+  if (rc) return rc;
+  double* P = ctx->pg_dev;
+  if (ldx == D) {
+    OB_CUDA(ctx, cudaMemcpyAsync(P + p_x, x_host, (size_t)m * D * 8, cudaMemcpyHostToDevice, st));
+  } else {
+    for (int p = 0; p < m; ++p)
+      OB_CUDA(ctx, cudaMemcpyAsync(P + p_x + (size_t)p * D, x_host + (size_t)p * ldx, (size_t)D * 8, cudaMemcpyHostToDevice, st));
+  }
+  pg_k_kernel<<<dim3((n_pad + 255) / 256, m), 256, (size_t)D_pad * 8, st>>>(P + p_x, D, invls, Xs, n, n_pad, D, D_pad, ctx->hdr.kernel_kind,
+                                                                          ctx->hdr.amplitude, P + p_xs, P + p_K, P + p_G);
+  OB_LAUNCH_CHECK(ctx);
+  pg_v_kernel<<<dim3((n_pad * 32 + 255) / 256, m), 256, 0, st>>>(Xinv, P + p_K, n_pad, P + p_V);
+  OB_LAUNCH_CHECK(ctx);
+  pg_w_kernel<<<dim3((n_pad + 31) / 32, m), 256, 0, st>>>(Xinv, P + p_V, n_pad, P + p_W);
+  OB_LAUNCH_CHECK(ctx);
+  pg_final_kernel<<<m, 256, 0, st>>>(P + p_xs, invls, Xs, alpha, P + p_K, P + p_G, P + p_V, P + p_W, n, n_pad, D, D_pad,
+                                     ctx->hdr.amplitude, ctx->hdr.y_mean, ctx->hdr.y_std, P + p_out);
+  OB_LAUNCH_CHECK(ctx);
+  OB_CUDA(ctx, cudaMemcpyAsync(out_host, P + p_out, (size_t)m * W * 8, cudaMemcpyDeviceToHost, st));
+  OB_CUDA(ctx, cudaStreamSynchronize(st));
   return OB200_OK;
 }
 

@@ -84,6 +84,8 @@ struct ob200_ctx {
   int64_t w_Xs_off = 0, w_y_off = 0;  // offsets (doubles) of X/ls and normalised y inside work_dev
   double* grad_dev = nullptr;      // LML-gradient workspace
   int64_t grad_cap = 0;
+  double* pg_dev = nullptr;        // posterior-gradient workspace (ob200_gp_predict_grad_host)
+  int64_t pg_cap = 0;
 
   // score scratch
   double* kstar_dev = nullptr;     // per-CTA K* slices

@@ -153,6 +153,18 @@ class Engine:
         self._check(self.lib.ob200_gp_lml_grad(self.ctx, C.byref(v), g, self.D + 2))
         return v.value, np.asarray(list(g))
 
+    def predict_grad(self, x):
+        """(mu [m], sigma [m], dmu [m, D], dsigma [m, D]) at the normalised rows `x` [m, D] (host arrays)."""
+        x = np.ascontiguousarray(np.atleast_2d(np.asarray(x, dtype=np.float64)))
+        m, d = x.shape
+        if d != self.D:
+            raise ValueError("x has %d columns, the fit has D=%d" % (d, self.D))
+        self.use_torch_stream()
+        out = np.empty((m, 2 + 2 * d), dtype=np.float64)
+        self._check(self.lib.ob200_gp_predict_grad_host(self.ctx, x.ctypes.data_as(C.c_void_p), d, m,
+                                                        out.ctypes.data_as(C.c_void_p)))
+        return out[:, 0], out[:, 1], out[:, 2:2 + d], out[:, 2 + d:]
+
     def get_factor(self):
         L = np.empty((self.n, self.n), dtype=np.float64)
         al = np.empty(self.n, dtype=np.float64)

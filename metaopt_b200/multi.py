@@ -52,6 +52,9 @@ class MultiEngine:
     def lml_grad(self):
         return self.primary.lml_grad()
 
+    def predict_grad(self, x):
+        return self.primary.predict_grad(x)
+
     def ystats(self):
         return self.primary.ystats()
 

@@ -60,6 +60,36 @@ class NumpyGP:
         return mu, np.sqrt(var)
 
 
+    def predict_grad(self, Xc):
+        """(mu, sigma, dmu/dx, dsigma/dx) per row of Xc: the analytic derivatives of `predict` that skopt's
+        GaussianProcessRegressor subclass returns for return_mean_grad / return_std_grad (skopt
+        `learning/gaussian_process/gpr.py`, kernels' `gradient_x`; third-party, unpinned).  Checked against
+        central differences of `predict` in tests/test_oracle_golden.py."""
+        Xc = np.atleast_2d(np.asarray(Xc, float))
+        ls = np.broadcast_to(np.asarray(self.length_scale, float), (self.X.shape[1],))
+        mus, sds, dmus, dsds = [], [], [], []
+        for x in Xc:
+            u = (x - self.X) / ls                       # [n, D]
+            r2 = np.einsum('ij,ij->i', u, u)
+            if self.kind == KERNEL_MATERN52:
+                t = np.sqrt(5.0 * r2)
+                k = self.amplitude * (1.0 + t + t * t / 3.0) * np.exp(-t)
+                g = self.amplitude * (5.0 / 3.0) * (1.0 + t) * np.exp(-t)
+            else:
+                k = self.amplitude * np.exp(-0.5 * r2)
+                g = k
+            dk = -(g[:, None] * u) / ls                 # dk_j / dx_d
+            v = solve_triangular(self.L, k, lower=True)
+            w = solve_triangular(self.L.T, v, lower=False)
+            var = max(self.amplitude - v @ v, 0.0)
+            sd = np.sqrt(var)
+            mus.append(self.y_std * (k @ self.alpha_) + self.y_mean)
+            sds.append(self.y_std * sd)
+            dmus.append(self.y_std * (dk.T @ self.alpha_))
+            dsds.append(self.y_std * (-(dk.T @ w)) / sd if var > 0 else np.zeros(len(ls)))
+        return np.array(mus), np.array(sds), np.array(dmus), np.array(dsds)
+
+
 class SklearnGP:
     """The on-box scikit-learn estimator with fixed hyper-parameters (optimizer=None)."""
 

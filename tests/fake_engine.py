@@ -76,6 +76,9 @@ class OracleEngine:
         d_diag = 0.5 * (a @ a - np.trace(Kinv))
         return float(lml), np.concatenate([grad, [d_diag]])
 
+    def predict_grad(self, x):
+        return self.model.predict_grad(x)
+
     def score(self, cand=None, M=None, seed=0, first_index=0, acq_mask=1, y_opt=0.0, xi=0.01, kappa=1.96, dense=False):
         self.calls["score"] += 1
         assert cand is None

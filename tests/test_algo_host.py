@@ -142,3 +142,58 @@ def test_batch_suggest_uses_constant_liar_and_leaves_no_lies(fake):
     assert len({repr(p) for p in batch}) == 4          # the lies push the picks apart
     assert len(a._y) == 6 and len(a._X) == 6           # lies are gone
     assert a._theta[0] == theta[0] and a.fit_hyperparameters is True  # hyper-parameters untouched by lies
+
+
+@pytest.mark.parametrize("name", ["EI", "PI", "LCB"])
+def test_utility_gradients_match_central_differences(name):
+    from metaopt_b200 import acq_opt
+    from oracle import acquisition as oacq
+    from oracle import gp as ogp
+    rng = np.random.RandomState(2)
+    gp = ogp.NumpyGP(0, 1.3, np.array([0.5, 0.8, 0.6]), 1e-6, False).fit(rng.rand(30, 3), rng.randn(30))
+    k = {"EI": 0, "PI": 1, "LCB": 2}[name]
+    x = rng.rand(3)
+
+    def util(p):
+        mu, sd = gp.predict(p[None])
+        return float(oacq.utility(k, mu, sd, -0.3, 0.01, 1.96)[0])
+    mu, sd, dmu, dsd = gp.predict_grad(x[None])
+    val, grad = acq_opt.utility_and_grad(name, mu[0], sd[0], dmu[0], dsd[0], -0.3, 0.01, 1.96)
+    assert val == pytest.approx(util(x), rel=1e-10)
+    for d in range(3):
+        e = np.zeros(3)
+        e[d] = 1e-6
+        assert grad[d] == pytest.approx((util(x + e) - util(x - e)) / 2e-6, rel=1e-4, abs=1e-8)
+    assert acq_opt.utility_and_grad("EI", 0.0, 0.0, dmu[0], dsd[0], 0.0)[0] == 0.0  # sigma == 0 is masked
+
+
+@pytest.mark.parametrize("acq", ["EI", "gp_hedge"])
+def test_lbfgs_refinement_never_loses_to_the_best_sample(fake, acq):
+    s = Space()
+    s.register(Real("x", "uniform", -2, 4))
+    s.register(Real("z", "uniform", 0, 1))
+    t = build_required_space("real", s)
+
+    def run(opt):
+        a = BayesianOptimizer(t, seed=5, n_initial_points=6, acq_func=acq, n_points=300, fit_hyperparameters=False,
+                              acq_optimizer=opt, acq_n_restarts=3)
+        for _ in range(6):
+            (p,) = a.suggest(1)
+            a.observe([p], [{"objective": (p[0] - 0.5) ** 2 + (p[1] - 0.2) ** 2}])
+        return a, a.suggest(1)[0]
+    a_s, p_s = run("sampling")
+    a_l, p_l = run("lbfgs")
+    assert p_l in t and p_s in t
+    assert a_s._offset == a_l._offset            # the refinement consumes no stream positions
+    if acq == "EI":
+        comp = a_l._get_compiled()
+        gp = fake.model
+
+        def ei(p):
+            mu, sd = gp.predict(comp.normalise(np.asarray(p, float))[None])
+            from oracle import acquisition as oacq
+            return float(oacq.gaussian_ei(mu, sd, min(a_l._y))[0])
+        assert ei(p_l) >= ei(p_s) - 1e-15
+        assert ei(p_l) > ei(p_s)                  # 300 samples in 2-D leave room for the ascent
+    with pytest.raises(ValueError):
+        BayesianOptimizer(t, acq_optimizer="newton")

@@ -117,3 +117,24 @@ def test_acquisition_formulas():
     assert ei[0] == pytest.approx(0.49 * norm.cdf(z) + norm.pdf(z))
     assert oacq.gaussian_lcb(mu, sd, 1.96)[2] == pytest.approx(-1 - 3.92)
     assert oacq.pick(oacq.ACQ_LCB, mu, sd, 0.5) == 2
+
+
+@pytest.mark.parametrize("kind", [ogp.KERNEL_MATERN52, ogp.KERNEL_RBF])
+def test_posterior_gradients_match_central_differences_of_predict(kind):
+    rng = np.random.RandomState(5)
+    X, y = rng.rand(40, 4), rng.randn(40) * 3 + 2
+    ls = np.array([0.4, 0.7, 1.1, 0.3])
+    gp = ogp.NumpyGP(kind, 1.7, ls, 1e-6, True).fit(X, y)
+    P = rng.rand(5, 4)
+    mu, sd, dmu, dsd = gp.predict_grad(P)
+    mu0, sd0 = gp.predict(P)
+    np.testing.assert_allclose(mu, mu0, rtol=1e-12)
+    np.testing.assert_allclose(sd, sd0, rtol=1e-10)
+    h = 1e-6
+    for d in range(4):
+        e = np.zeros(4)
+        e[d] = h
+        mp, sp = gp.predict(P + e)
+        mm, sm = gp.predict(P - e)
+        np.testing.assert_allclose(dmu[:, d], (mp - mm) / (2 * h), rtol=2e-6, atol=1e-7)
+        np.testing.assert_allclose(dsd[:, d], (sp - sm) / (2 * h), rtol=2e-5, atol=1e-7)
