@@ -455,12 +455,12 @@ __global__ void pack_xs_kernel(const double* __restrict__ Xs, int n_pad, int D_p
 }
 
 __global__ void write_header_kernel(ob200_fit_header* hdr_dev, ob200_fit_header h, const double* stats, const double* lml,
-                                    double* inv_ls_out, const double* ls, int n_ls, int D, int D_pad) {
+                                    double* ls_out, const double* ls, int n_ls, int D, int D_pad) {
   if (threadIdx.x == 0 && blockIdx.x == 0) {
     h.y_mean = stats[0]; h.y_std = stats[1]; h.y_min = stats[2]; h.lml = *lml;
     *hdr_dev = h;
   }
-  for (int d = threadIdx.x; d < D_pad; d += blockDim.x) inv_ls_out[d] = d < D ? ls[n_ls == 1 ? 0 : d] : 1.0;
+  for (int d = threadIdx.x; d < D_pad; d += blockDim.x) ls_out[d] = d < D ? ls[n_ls == 1 ? 0 : d] : 1.0;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -748,7 +748,7 @@ int ob200_gp_fit(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n
   double* lml_dev = stats + 4;
   cudaStream_t st = ctx->stream;
   char* blob = ctx->blob;
-  double* b_invls = reinterpret_cast<double*>(blob + lay.off_invls);
+  double* b_ls = reinterpret_cast<double*>(blob + lay.off_ls);
   double* b_xs = reinterpret_cast<double*>(blob + lay.off_xs);
   double* b_xx = reinterpret_cast<double*>(blob + lay.off_xx);
   double* b_alpha = reinterpret_cast<double*>(blob + lay.off_alpha);
@@ -846,7 +846,7 @@ int ob200_gp_fit(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n
   ob200_fit_header h{};
   h.magic = OB200_FIT_MAGIC; h.n = n; h.D = D; h.n_pad = n_pad; h.D_pad = D_pad; h.kernel_kind = kernel->kind;
   h.amplitude = kernel->amplitude;
-  write_header_kernel<<<1, 128, 0, st>>>(reinterpret_cast<ob200_fit_header*>(blob), h, stats, lml_dev, b_invls, ls_dev,
+  write_header_kernel<<<1, 128, 0, st>>>(reinterpret_cast<ob200_fit_header*>(blob), h, stats, lml_dev, b_ls, ls_dev,
                                          kernel->n_length_scale, D, D_pad);
   OB_LAUNCH_CHECK(ctx);
   OB_CUDA(ctx, cudaMemcpyAsync(&ctx->hdr, blob, sizeof(ob200_fit_header), cudaMemcpyDeviceToHost, st));
@@ -932,7 +932,7 @@ int ob200_gp_predict_grad_host(ob200_ctx* ctx, const double* x_host, int64_t ldx
   cudaStream_t st = ctx->stream;
   const ob200_blob_layout lay = ob_blob_layout(n_pad, D_pad);
   const double* alpha = reinterpret_cast<const double*>(ctx->blob + lay.off_alpha);
-  const double* invls = reinterpret_cast<const double*>(ctx->blob + lay.off_invls);  // holds ls_d (the blob's divisor table)
+  const double* ls = reinterpret_cast<const double*>(ctx->blob + lay.off_ls);
   const double* Xinv = ctx->work_dev;                 // dense inv(L), row-major (fit workspace, offset 0)
   const double* Xs = ctx->work_dev + ctx->w_Xs_off;   // X / ls, row-major [n_pad x D_pad]
   const int W = 2 + 2 * D;
@@ -948,14 +948,14 @@ int ob200_gp_predict_grad_host(ob200_ctx* ctx, const double* x_host, int64_t ldx
     for (int p = 0; p < m; ++p)
       OB_CUDA(ctx, cudaMemcpyAsync(P + p_x + (size_t)p * D, x_host + (size_t)p * ldx, (size_t)D * 8, cudaMemcpyHostToDevice, st));
   }
-  pg_k_kernel<<<dim3((n_pad + 255) / 256, m), 256, (size_t)D_pad * 8, st>>>(P + p_x, D, invls, Xs, n, n_pad, D, D_pad, ctx->hdr.kernel_kind,
+  pg_k_kernel<<<dim3((n_pad + 255) / 256, m), 256, (size_t)D_pad * 8, st>>>(P + p_x, D, ls, Xs, n, n_pad, D, D_pad, ctx->hdr.kernel_kind,
                                                                           ctx->hdr.amplitude, P + p_xs, P + p_K, P + p_G);
   OB_LAUNCH_CHECK(ctx);
   pg_v_kernel<<<dim3((n_pad * 32 + 255) / 256, m), 256, 0, st>>>(Xinv, P + p_K, n_pad, P + p_V);
   OB_LAUNCH_CHECK(ctx);
   pg_w_kernel<<<dim3((n_pad + 31) / 32, m), 256, 0, st>>>(Xinv, P + p_V, n_pad, P + p_W);
   OB_LAUNCH_CHECK(ctx);
-  pg_final_kernel<<<m, 256, 0, st>>>(P + p_xs, invls, Xs, alpha, P + p_K, P + p_G, P + p_V, P + p_W, n, n_pad, D, D_pad,
+  pg_final_kernel<<<m, 256, 0, st>>>(P + p_xs, ls, Xs, alpha, P + p_K, P + p_G, P + p_V, P + p_W, n, n_pad, D, D_pad,
                                      ctx->hdr.amplitude, ctx->hdr.y_mean, ctx->hdr.y_std, P + p_out);
   OB_LAUNCH_CHECK(ctx);
   OB_CUDA(ctx, cudaMemcpyAsync(out_host, P + p_out, (size_t)m * W * 8, cudaMemcpyDeviceToHost, st));

@@ -71,7 +71,7 @@ struct ob200_ctx {
   double* col_nhi_dev = nullptr;
   int* status_dev = nullptr;       // latched sampler status
 
-  // fit state: one device blob [header | inv_ls[D_pad] | Xs packed | xx | alpha | Linv packed]
+  // fit state: one device blob [header | ls[D_pad] | Xs packed | xx | alpha | Linv packed]
   bool fitted = false;
   ob200_fit_header hdr{};
   char* blob = nullptr;
@@ -153,12 +153,12 @@ static inline int64_t ob_round_up(int64_t x, int64_t m) { return (x + m - 1) / m
 
 // blob layout (all offsets in bytes, 256-aligned)
 struct ob200_blob_layout {
-  int64_t off_invls, off_xs, off_xx, off_alpha, off_linv, total;
+  int64_t off_ls, off_xs, off_xx, off_alpha, off_linv, total;
 };
 static inline ob200_blob_layout ob_blob_layout(int n_pad, int D_pad) {
   ob200_blob_layout l;
   int64_t o = 256;  // header
-  l.off_invls = o; o += ob_round_up((int64_t)D_pad * 8, 256);
+  l.off_ls = o; o += ob_round_up((int64_t)D_pad * 8, 256);
   l.off_xs = o;    o += ob_round_up((int64_t)n_pad * D_pad * 8, 256);
   l.off_xx = o;    o += ob_round_up((int64_t)n_pad * 8, 256);
   l.off_alpha = o; o += ob_round_up((int64_t)n_pad * 8, 256);

@@ -592,7 +592,7 @@ int score_launch(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M,
   if ((rc = ob_reserve(ctx, &ctx->partial_dev, &ctx->partial_cap, (int64_t)4096 * 3 * (int64_t)sizeof(best_t)))) return rc;
   score_args a{};
   a.cand = cand_dev; a.ldc = ldc; a.M = M; a.first_index = first_index;
-  a.ls = reinterpret_cast<const double*>(ctx->blob + lay.off_invls);
+  a.ls = reinterpret_cast<const double*>(ctx->blob + lay.off_ls);
   a.xs = reinterpret_cast<const double*>(ctx->blob + lay.off_xs);
   a.xx = reinterpret_cast<const double*>(ctx->blob + lay.off_xx);
   a.alpha = reinterpret_cast<const double*>(ctx->blob + lay.off_alpha);

@@ -18,7 +18,8 @@ RTOL = 1e-6
 
 
 def _compare(engine, X, y, C, kind=0, amp=1.0, ls=1.0, alpha=1e-10 + 1e-4, normalize_y=True, xi=0.01, kappa=1.96,
-             host=False):
+             host=False, acq_rtol=None):
+    acq_rtol = RTOL if acq_rtol is None else acq_rtol  # (tools/fuzz_parity.py loosens this for EI's far tail)
     d = X.shape[1]
     ls_vec = np.broadcast_to(np.asarray(ls, dtype=float), (d,)).copy()
     engine.fit(X, y, kind=kind, amplitude=amp, length_scale=ls, alpha=alpha, normalize_y=normalize_y)
@@ -37,7 +38,7 @@ def _compare(engine, X, y, C, kind=0, amp=1.0, ls=1.0, alpha=1e-10 + 1e-4, norma
     np.testing.assert_allclose(sd, sd_r, rtol=RTOL, atol=floor)
     for k, name in ((0, "EI"), (1, "PI"), (2, "LCB")):
         util = oacq.utility(k, mu_r, sd_r, y_opt, xi, kappa)
-        np.testing.assert_allclose(acq[k], util, rtol=RTOL, atol=RTOL * np.abs(util).max())
+        np.testing.assert_allclose(acq[k], util, rtol=acq_rtol, atol=acq_rtol * np.abs(util).max())
         pick = oacq.pick(k, mu_r, sd_r, y_opt, xi, kappa)
         got = out[name]
         srt = np.sort(util)
@@ -46,7 +47,7 @@ def _compare(engine, X, y, C, kind=0, amp=1.0, ls=1.0, alpha=1e-10 + 1e-4, norma
             assert got["index"] == pick, (name, got, pick, gap)
         else:  # a genuine near-tie: the values must agree
             np.testing.assert_allclose(util[got["index"]], util[pick], rtol=RTOL)
-        np.testing.assert_allclose(got["value"], util[got["index"]], rtol=RTOL, atol=RTOL * np.abs(util).max())
+        np.testing.assert_allclose(got["value"], util[got["index"]], rtol=acq_rtol, atol=acq_rtol * np.abs(util).max())
         np.testing.assert_allclose(got["mu"], mu_r[got["index"]], rtol=RTOL, atol=RTOL * np.abs(mu_r).max())
         # the reported winner is exactly the argmax of the dense device values (first occurrence)
         assert got["index"] == int(np.argmax(acq[k]))
