@@ -144,6 +144,14 @@ __host__ __device__ inline size_t score_union_elems(int D_pad, int p1_stages) {
   return p1 > un ? p1 : un;
 }
 
+#ifdef SC_PROFILE_CYCLES
+// timing experiment only (tools/prof_phases.py): cycles spent by consumer thread 0 of every CTA in each part of a tile
+__device__ unsigned long long g_sc_prof[1024 * 8];
+#define SC_PROF_MARK(K) if (tid == 0) { const long long now_ = clock64(); prof_acc[K] += now_ - prof_t; prof_t = now_; }
+#else
+#define SC_PROF_MARK(K)
+#endif
+
 __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int D_pad = a.D_pad, nd4 = D_pad >> 2;
@@ -249,8 +257,13 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
     for (int k = 0; k < 3; ++k) best[k] = a.partials[(size_t)blockIdx.x * 3 + k];
   }
 
+#ifdef SC_PROFILE_CYCLES
+  long long prof_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  long long prof_t = clock64();
+#endif
   for (long long tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
     const long long row0 = tile * SC_BN;
+    SC_PROF_MARK(7)  // (loop overhead / before the first tile)
     // ---- stage the candidate tile: Cs = cand / ls in A-fragment order, cc = ||Cs||^2
     for (int e = tid; e < SC_BN * D_pad; e += SC_CONSUMER_WARPS * 32) {
       const int r = e / D_pad, d = e - r * D_pad;
@@ -270,6 +283,7 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
     }
     consumer_bar();
 
+    SC_PROF_MARK(0)  // candidate staging
     // ---- phase 1: k* = kernel(cand, X) and mu partials; warp w owns obs8 block w of each chunk
     {
       double ccr[SC_NCF], mup[SC_NCF];
@@ -317,8 +331,10 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
         if (q == 0) mured[warp * SC_BN + cf * 8 + g] = v;
       }
     }
+    SC_PROF_MARK(1)       // phase 1 loop of this warp
     fence_proxy_async();  // k* global writes (generic proxy) -> bulk reads (async proxy)
     __syncthreads();      // (A)
+    SC_PROF_MARK(2)       // wait for the other warps at (A)
 
     // ---- phase 2: sum v^2 with v = inv(L) k*
     const int wm = warp / SC_WN, wn = warp % SC_WN;
@@ -420,6 +436,7 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
           ss[j][1] = fma(acc[t][j][1], acc[t][j][1], ss[j][1]);
         }
     }
+    SC_PROF_MARK(3)  // phase 2 (incl. pipeline fill)
     // reduce over the 8 row lanes (g), then across the SC_WM row warps via shared memory
 #pragma unroll
     for (int j = 0; j < SC_FN; ++j)
@@ -463,9 +480,15 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
         }
       }
     }
+    SC_PROF_MARK(4)  // reductions + phase 3
     fence_proxy_async();
     __syncthreads();  // (B) end of tile: smem union and the k* slice may be reused
+    SC_PROF_MARK(5)  // wait at (B)
   }
+#ifdef SC_PROFILE_CYCLES
+  if (tid == 0 && blockIdx.x < 1024)
+    for (int k = 0; k < 8; ++k) g_sc_prof[blockIdx.x * 8 + k] = (unsigned long long)prof_acc[k];
+#endif
 
   // ---- per-CTA winner: warp-shuffle argmax inside the SC_BN/32 owner warps, then through smem
   if (warp < SC_BN / 32) {
@@ -644,6 +667,12 @@ int check_score_args(ob200_ctx* ctx, int64_t M, int acq_mask, const void* best) 
 }  // namespace
 
 extern "C" {
+
+#ifdef SC_PROFILE_CYCLES
+int ob200_debug_score_cycles(unsigned long long* host, int n_cta) {
+  return cudaMemcpyFromSymbol(host, g_sc_prof, (size_t)n_cta * 8 * sizeof(unsigned long long)) == cudaSuccess ? 0 : -2;
+}
+#endif
 
 int ob200_score_async(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M, uint64_t seed, uint64_t first_index,
                       int acq_mask, double y_opt, double xi, double kappa, ob200_best* best_dev, double* mu_dev,

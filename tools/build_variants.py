@@ -14,6 +14,8 @@ VARIANTS = {
     # timing experiments only (wrong results): isolate the phases of the score kernel
     "skip2": ["SC_DEBUG_SKIP_PHASE2"],
     "skip1": ["SC_DEBUG_SKIP_PHASE1"],
+    # clock64 marks around the parts of a tile (tools/prof_phases.py reads them back)
+    "prof": ["SC_PROFILE_CYCLES"],
 }
 if __name__ == "__main__":
     names = sys.argv[1:] or list(VARIANTS)
