@@ -25,15 +25,13 @@ int ob200_ctx_create(int device, ob200_ctx** out) {
   }
   ctx->num_sms = prop.multiProcessorCount;
   {
-    // The score kernel's k* slices are written once and re-read several times per tile: keep them in a
-    // persisting L2 set-aside so they never travel to HBM (OB200_L2_PERSIST=0 disables).
+    // The score kernel's k* slices are written once and re-read several times per tile: a persisting L2
+    // set-aside keeps them out of HBM.  Only the capability is recorded here; the carve-out itself is switched on
+    // around score launches (ob_l2_acquire / ob_l2_release), OB200_L2_PERSIST=0 disables it.
     const char* env = getenv("OB200_L2_PERSIST");
-    if (!(env && env[0] == '0') && prop.persistingL2CacheMaxSize > 0 &&
-        cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t)prop.persistingL2CacheMaxSize) == cudaSuccess) {
+    if (!(env && env[0] == '0') && prop.persistingL2CacheMaxSize > 0) {
       ctx->l2_persist_max = (size_t)prop.persistingL2CacheMaxSize;
       ctx->l2_window_max = (size_t)prop.accessPolicyMaxWindowSize;
-    } else {
-      cudaGetLastError();
     }
   }
   if (cudaMalloc((void**)&ctx->status_dev, sizeof(int)) != cudaSuccess ||
@@ -51,6 +49,7 @@ void ob200_ctx_destroy(ob200_ctx* ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   cudaDeviceSynchronize();
+  ob_l2_release(ctx);
   cudaFree(ctx->slots_dev);
   cudaFree(ctx->dslots_dev);
   cudaFree(ctx->cdf_dev);
@@ -91,6 +90,7 @@ int ob200_sync(ob200_ctx* ctx) {
   if (!ctx) return OB200_EINVAL;
   OB_CUDA(ctx, cudaSetDevice(ctx->device));
   OB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  ob_l2_release(ctx);
   return OB200_OK;
 }
 

@@ -57,6 +57,7 @@ struct ob200_ctx {
   int device = 0;
   int num_sms = OB200_NUM_SMS_FALLBACK;
   bool l2_dirty = false;   // persisting lines of a finished score launch have not been released yet
+  bool l2_limit_on = false;  // the device-wide persisting-L2 carve-out is currently set (only around score launches)
   size_t l2_persist_max = 0, l2_window_max = 0;  // persisting-L2 set-aside for the k* slices (0 = unavailable/disabled)
   cudaStream_t stream = 0;
   std::string err;
@@ -246,6 +247,19 @@ __device__ __forceinline__ double u53(uint32_t lo, uint32_t hi) {
   uint64_t x = ((uint64_t)hi << 32) | lo;
   return (double)(x >> 11) * 0x1.0p-53;
 }
+// The persisting-L2 carve-out is a DEVICE-WIDE setting: while it is on, streaming writes of every kernel on the
+// device drop from 7.4 to 2.8 TB/s (tools/l2_persist_probe.py).  It is therefore switched on for score launches
+// only and handed back as soon as a score call has been synchronised.
+inline void ob_l2_acquire(ob200_ctx* ctx) {
+  if (ctx->l2_persist_max > 0 && !ctx->l2_limit_on &&
+      cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, ctx->l2_persist_max) == cudaSuccess)
+    ctx->l2_limit_on = true;
+}
+inline void ob_l2_release(ob200_ctx* ctx) {
+  if (ctx->l2_dirty) { cudaCtxResetPersistingL2Cache(); ctx->l2_dirty = false; }
+  if (ctx->l2_limit_on) { cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, 0); ctx->l2_limit_on = false; }
+}
+
 #endif  // __CUDACC__
 
 // internal cross-TU entry points

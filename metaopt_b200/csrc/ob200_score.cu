@@ -35,11 +35,6 @@ struct best_t {
   double mu, sigma;
 };
 
-// after a synchronised score call: hand the persisting L2 lines back to everybody else
-inline void ob_release_l2(ob200_ctx* ctx) {
-  if (ctx->l2_dirty) { cudaCtxResetPersistingL2Cache(); ctx->l2_dirty = false; }
-}
-
 __device__ __forceinline__ bool better(double v, long long i, double bv, long long bi) {
   return (v > bv) || (v == bv && i < bi);
 }
@@ -636,6 +631,7 @@ int score_launch(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M,
   const size_t slices = (size_t)grid * h.n_pad * SC_BN * sizeof(double);
   const bool persist = ctx->l2_persist_max > 0 && !mean_only;
   if (persist) {
+    ob_l2_acquire(ctx);
     cudaStreamAttrValue attr{};
     attr.accessPolicyWindow.base_ptr = ctx->kstar_dev;
     attr.accessPolicyWindow.num_bytes = slices < ctx->l2_window_max ? slices : ctx->l2_window_max;
@@ -727,7 +723,7 @@ int ob200_score(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M, 
   OB_CUDA(ctx, cudaMemcpyAsync(ctx->best_pinned, ctx->best_dev, 3 * sizeof(ob200_best), cudaMemcpyDeviceToHost, ctx->stream));
   OB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   memcpy(best_host, ctx->best_pinned, 3 * sizeof(ob200_best));
-  ob_release_l2(ctx);
+  ob_l2_release(ctx);
   if (!cand_dev) return ob200_sample_status(ctx);
   return OB200_OK;
 }
@@ -786,7 +782,7 @@ int ob200_score_host(ob200_ctx* ctx, const double* cand_host, int64_t ldc, int64
   if (acq_host) OB_CUDA(ctx, cudaMemcpyAsync(acq_host, aq_dev, (size_t)3 * M * 8, cudaMemcpyDeviceToHost, ctx->stream));
   OB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   memcpy(best_host, ctx->best_pinned, 3 * sizeof(ob200_best));
-  ob_release_l2(ctx);
+  ob_l2_release(ctx);
   return OB200_OK;
 }
 
@@ -1020,7 +1016,7 @@ extern "C" int ob200_score_pruned(ob200_ctx* ctx, const double* cand_dev, int64_
   }
   best_host[0] = incumbent;
   if (n_scored_host) *n_scored_host = n_scored;
-  ob_release_l2(ctx);
+  ob_l2_release(ctx);
   if (cand_dev == ctx->cand_tmp) return ob200_sample_status(ctx);
   return OB200_OK;
 }
