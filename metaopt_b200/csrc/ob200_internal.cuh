@@ -247,6 +247,31 @@ __device__ __forceinline__ double u53(uint32_t lo, uint32_t hi) {
   uint64_t x = ((uint64_t)hi << 32) | lo;
   return (double)(x >> 11) * 0x1.0p-53;
 }
+// exp(t) with a 32-entry table (any t whose result is a normal double; used with t <= 0 by the score kernel and
+// with log-uniform exponents by the sampler): t = (32 n + j) ln2/32 + r, |r| <= ln2/64, so
+// exp(t) = 2^n * 2^(j/32) * exp(r) and a degree-6 Taylor polynomial suffices (truncation 3.5e-18);
+// Cody-Waite two-constant reduction, scaling by exponent-field addition.  ~2 ulp; below 2^-1021 -> 0.
+// `tab` = 2^(j/32), j = 0..31, in shared memory.
+__device__ __forceinline__ double ob_exp_tab(double t, const double* __restrict__ tab) {
+  const double magic = 6755399441055744.0;         // 1.5 * 2^52: round-to-nearest-integer trick
+  const double mb = fma(t, 46.16624130844683, magic);  // t * 32 / ln2
+  const int m = __double2loint(mb);
+  const double md = mb - magic;
+  double r = fma(md, -2.16608493865351192653e-02, t);   // ln2/32, high part
+  r = fma(md, -5.96317165397058692146e-12, r);          // ln2/32, low part
+  double p = 1.0 / 720.0;
+  p = fma(p, r, 1.0 / 120.0);
+  p = fma(p, r, 1.0 / 24.0);
+  p = fma(p, r, 1.0 / 6.0);
+  p = fma(p, r, 0.5);
+  p = fma(p, r, 1.0);
+  p = fma(p, r, 1.0);
+  const double v = tab[m & 31] * p;
+  const int n = m >> 5;
+  const double scaled = __hiloint2double(__double2hiint(v) + (n << 20), __double2loint(v));
+  return (n >= -1021) ? scaled : 0.0;
+}
+
 // The persisting-L2 carve-out is a DEVICE-WIDE setting: while it is on, streaming writes of every kernel on the
 // device drop from 7.4 to 2.8 TB/s (tools/l2_persist_probe.py).  It is therefore switched on for score launches
 // only and handed back as soon as a score call has been synchronised.

@@ -91,17 +91,17 @@ __device__ __forceinline__ double div_const(double a, double b, double rb) {
 
 // value of a real / integer slot; products and sums rounded separately like scipy (loc + scale * U)
 template <int OP>
-__device__ __forceinline__ double draw_op(const dslot& s, double u, double z) {
+__device__ __forceinline__ double draw_op(const dslot& s, double u, double z, const double* __restrict__ exp_tab) {
   double x;
   if (OP == OP_UNIFORM || OP == OP_UNIFORM_INT) x = __dadd_rn(s.p0, __dmul_rn(s.p1, u));
-  else if (OP == OP_LOGUNIFORM || OP == OP_LOGUNIFORM_INT) x = exp(__dadd_rn(s.p0, __dmul_rn(u, s.p1)));
+  else if (OP == OP_LOGUNIFORM || OP == OP_LOGUNIFORM_INT) x = ob_exp_tab(__dadd_rn(s.p0, __dmul_rn(u, s.p1)), exp_tab);  // ~2 ulp, branch-free
   else x = __dadd_rn(s.p0, __dmul_rn(s.p1, z));
   if (OP & 1) x = floor(x);
   return x;
 }
 
 // Real.sample's retries (space.py:379-389), tries 1..3.  Rare: out of line.  NaN = all rejected.
-__device__ __noinline__ double retry_slot(const dslot* s, int q, uint64_t index, const philox_keys* rk) {
+__device__ __noinline__ double retry_slot(const dslot* s, int q, uint64_t index, const philox_keys* rk, const double* exp_tab) {
   for (int t = 1; t < 4; ++t) {
     double u = 0.0, z = 0.0;
     if (s->op == OP_NORMAL || s->op == OP_NORMAL_INT) {
@@ -112,12 +112,12 @@ __device__ __noinline__ double retry_slot(const dslot* s, int q, uint64_t index,
     }
     double xt;
     switch (s->op) {
-      case OP_UNIFORM: xt = draw_op<OP_UNIFORM>(*s, u, z); break;
-      case OP_UNIFORM_INT: xt = draw_op<OP_UNIFORM_INT>(*s, u, z); break;
-      case OP_LOGUNIFORM: xt = draw_op<OP_LOGUNIFORM>(*s, u, z); break;
-      case OP_LOGUNIFORM_INT: xt = draw_op<OP_LOGUNIFORM_INT>(*s, u, z); break;
-      case OP_NORMAL: xt = draw_op<OP_NORMAL>(*s, u, z); break;
-      default: xt = draw_op<OP_NORMAL_INT>(*s, u, z); break;
+      case OP_UNIFORM: xt = draw_op<OP_UNIFORM>(*s, u, z, exp_tab); break;
+      case OP_UNIFORM_INT: xt = draw_op<OP_UNIFORM_INT>(*s, u, z, exp_tab); break;
+      case OP_LOGUNIFORM: xt = draw_op<OP_LOGUNIFORM>(*s, u, z, exp_tab); break;
+      case OP_LOGUNIFORM_INT: xt = draw_op<OP_LOGUNIFORM_INT>(*s, u, z, exp_tab); break;
+      case OP_NORMAL: xt = draw_op<OP_NORMAL>(*s, u, z, exp_tab); break;
+      default: xt = draw_op<OP_NORMAL_INT>(*s, u, z, exp_tab); break;
     }
     if ((xt >= s->low) && (xt < s->high)) return xt;
   }
@@ -127,22 +127,22 @@ __device__ __noinline__ double retry_slot(const dslot* s, int q, uint64_t index,
 template <int OP>
 __device__ __forceinline__ void real_slot(const dslot* __restrict__ sp, int q, uint64_t index, const philox_keys& rk, double u0,
                                           const double* __restrict__ var_row, bool active, int normalise,
-                                          double* __restrict__ row_out, int* __restrict__ status) {
+                                          double* __restrict__ row_out, int* __restrict__ status, const double* __restrict__ exp_tab) {
   const dslot s = *sp;  // four LDS.128, broadcast
   double x;
   bool ok;
   if (var_row) {  // parity mode: one host-supplied variate, no resampling
     const double v = active ? var_row[s.col_src >> 16] : 0.5;
-    x = draw_op<OP>(s, v, v);
+    x = draw_op<OP>(s, v, v, exp_tab);
     ok = (x >= s.low) && (x < s.high);
   } else {
     double z = 0.0;
     if (OP == OP_NORMAL || OP == OP_NORMAL_INT)
       z = box_muller(philox_rk((uint32_t)index, (uint32_t)(index >> 32), 0x80000000u | (uint32_t)q, 0u, rk));
-    x = draw_op<OP>(s, u0, z);
+    x = draw_op<OP>(s, u0, z, exp_tab);
     ok = (x >= s.low) && (x < s.high);
     if (__any_sync(0xffffffffu, active && !ok)) {
-      if (active && !ok) { x = retry_slot(sp, q, index, &rk); ok = (x == x); }
+      if (active && !ok) { x = retry_slot(sp, q, index, &rk, exp_tab); ok = (x == x); }
     }
   }
   if (active && !ok) { atomicOr(status, 1); x = 0.0; }
@@ -164,6 +164,16 @@ __device__ __forceinline__ int cdf_count(const double* __restrict__ cdf, int k, 
   return n < k - 1 ? n : k - 1;
 }
 
+// one-hot group of a compile-time width: K - 1 compares (the clamp of cdf_count absorbs the last one), K selects
+template <int K>
+__device__ __forceinline__ void onehot_fixed(const double* __restrict__ cdf, double u, double v0, double v1, double* __restrict__ dst) {
+  int hot = 0;
+#pragma unroll
+  for (int j = 0; j < K - 1; ++j) hot += (cdf[j] <= u) ? 1 : 0;
+#pragma unroll
+  for (int j = 0; j < K; ++j) dst[j] = (j == hot) ? v1 : v0;
+}
+
 template <bool ONEHOT>
 __device__ __forceinline__ void cat_slot(const dslot* __restrict__ sp, const double* __restrict__ cdf, double u0,
                                          const double* __restrict__ var_row, bool active, int normalise,
@@ -171,9 +181,16 @@ __device__ __forceinline__ void cat_slot(const dslot* __restrict__ sp, const dou
   const dslot s = *sp;
   const dslot_cat c = *reinterpret_cast<const dslot_cat*>(&sp->low);
   const double u = var_row ? (active ? var_row[s.col_src >> 16] : 0.0) : u0;
-  const int hot = cdf_count(cdf + c.cdf_off, c.ncat, u);
   const double v0 = normalise ? s.p0 : 0.0, v1 = normalise ? s.p1 : 1.0;
   const int col = s.col_src & 0xffff;
+  if (ONEHOT && c.ncat <= 4) {  // (one-hot means ncat >= 3) straight-line code for the common widths
+    if (active) {
+      if (c.ncat == 4) onehot_fixed<4>(cdf + c.cdf_off, u, v0, v1, row_out + col);
+      else onehot_fixed<3>(cdf + c.cdf_off, u, v0, v1, row_out + col);
+    }
+    return;
+  }
+  const int hot = cdf_count(cdf + c.cdf_off, c.ncat, u);
   if (active) {
     if (ONEHOT) {
       for (int j = 0; j < c.ncat; ++j) row_out[col + j] = (j == hot) ? v1 : v0;
@@ -188,13 +205,14 @@ __device__ __forceinline__ void cat_slot(const dslot* __restrict__ sp, const dou
 template <int OP>
 __device__ __forceinline__ void pair_op(const dslot* __restrict__ sp, const double* __restrict__ cdf, int q, uint64_t index,
                                         const philox_keys& rk, double ua, double ub, const double* __restrict__ var_row,
-                                        bool active, int normalise, double* __restrict__ row_out, int* __restrict__ status) {
+                                        bool active, int normalise, double* __restrict__ row_out, int* __restrict__ status,
+                                        const double* __restrict__ exp_tab) {
   if (OP == OP_ONEHOT || OP == OP_CAT_SMALL) {
     cat_slot<OP == OP_ONEHOT>(sp, cdf, ua, var_row, active, normalise, row_out);
     if (sp[1].op != OP_NONE) cat_slot<OP == OP_ONEHOT>(sp + 1, cdf, ub, var_row, active, normalise, row_out);
   } else {
-    real_slot<OP>(sp, q, index, rk, ua, var_row, active, normalise, row_out, status);
-    if (sp[1].op != OP_NONE) real_slot<OP>(sp + 1, q + 1, index, rk, ub, var_row, active, normalise, row_out, status);
+    real_slot<OP>(sp, q, index, rk, ua, var_row, active, normalise, row_out, status, exp_tab);
+    if (sp[1].op != OP_NONE) real_slot<OP>(sp + 1, q + 1, index, rk, ub, var_row, active, normalise, row_out, status, exp_tab);
   }
 }
 
@@ -207,6 +225,8 @@ sample_transform_kernel(const dslot* __restrict__ slots_g, int n_dslots, int n_s
   double* tile = reinterpret_cast<double*>(smem_raw);                                   // [ST_ROWS][stride]
   dslot* slots = reinterpret_cast<dslot*>(tile + (((size_t)ST_ROWS * stride + 1) & ~(size_t)1));  // 16-byte aligned
   double* cdf = reinterpret_cast<double*>(slots + n_dslots);
+  double* exp_tab = cdf + n_cdf;                                                        // 2^(j/32), j = 0..31
+  if (threadIdx.x < 32) exp_tab[threadIdx.x] = exp2((double)threadIdx.x * 0.03125);
   for (int i = threadIdx.x; i < n_dslots * (int)(sizeof(dslot) / 8); i += ST_THREADS)
     reinterpret_cast<double*>(slots)[i] = reinterpret_cast<const double*>(slots_g)[i];
   for (int i = threadIdx.x; i < n_cdf; i += ST_THREADS) cdf[i] = cdf_g[i];
@@ -220,42 +240,49 @@ sample_transform_kernel(const dslot* __restrict__ slots_g, int n_dslots, int n_s
   for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
     const int64_t row0 = t * ST_ROWS;
     const int rows = (int)min((int64_t)ST_ROWS, count - row0);
+#ifdef ST_DEBUG_NO_COMPUTE  // timing experiment only: copy-out without generation
+    const int n_rg = 0;
+#else
     const int n_rg = (rows + 31) >> 5;
-    // items = (row group, pair), dealt round-robin to the warps without an integer division
-    int rg = 0, p = warp;
-    while (p >= n_pairs) { p -= n_pairs; ++rg; }
-    while (rg < n_rg) {
+#endif
+    // items = (row group, pair), dealt round-robin to the warps: item rg * n_pairs + p goes to warp (item mod W)
+    int p0 = warp;
+    for (int rg = 0; rg < n_rg; ++rg) {
       const int r = rg * 32 + lane;
       const bool active = r < rows;
       const uint64_t index = first_index + (uint64_t)(row0 + r);
       double* row_out = tile + (size_t)r * stride;
-      const dslot* sp = slots + 2 * p;
       const double* var_row = variates ? variates + (size_t)(row0 + (active ? r : 0)) * n_slots : nullptr;
-      double ua = 0.0, ub = 0.0;
-      if (!variates) {
-        const philox_out pr = philox_rk((uint32_t)index, (uint32_t)(index >> 32), (uint32_t)p, 0u, rk);
-        ua = u53_fast(pr.r0, pr.r1);
-        ub = u53_fast(pr.r2, pr.r3);
+      int p = p0;
+      for (; p < n_pairs; p += ST_THREADS / 32) {
+        const dslot* sp = slots + 2 * p;
+        double ua = 0.0, ub = 0.0;
+        if (!variates) {
+          const philox_out pr = philox_rk((uint32_t)index, (uint32_t)(index >> 32), (uint32_t)p, 0u, rk);
+          ua = u53_fast(pr.r0, pr.r1);
+          ub = u53_fast(pr.r2, pr.r3);
+        }
+        switch (sp->op) {
+          case OP_UNIFORM: pair_op<OP_UNIFORM>(sp, cdf, 2 * p, index, rk, ua, ub, var_row, active, normalise, row_out, status, exp_tab); break;
+          case OP_UNIFORM_INT: pair_op<OP_UNIFORM_INT>(sp, cdf, 2 * p, index, rk, ua, ub, var_row, active, normalise, row_out, status, exp_tab); break;
+          case OP_LOGUNIFORM: pair_op<OP_LOGUNIFORM>(sp, cdf, 2 * p, index, rk, ua, ub, var_row, active, normalise, row_out, status, exp_tab); break;
+          case OP_LOGUNIFORM_INT: pair_op<OP_LOGUNIFORM_INT>(sp, cdf, 2 * p, index, rk, ua, ub, var_row, active, normalise, row_out, status, exp_tab); break;
+          case OP_NORMAL: pair_op<OP_NORMAL>(sp, cdf, 2 * p, index, rk, ua, ub, var_row, active, normalise, row_out, status, exp_tab); break;
+          case OP_NORMAL_INT: pair_op<OP_NORMAL_INT>(sp, cdf, 2 * p, index, rk, ua, ub, var_row, active, normalise, row_out, status, exp_tab); break;
+          case OP_ONEHOT: pair_op<OP_ONEHOT>(sp, cdf, 2 * p, index, rk, ua, ub, var_row, active, normalise, row_out, status, exp_tab); break;
+          default: pair_op<OP_CAT_SMALL>(sp, cdf, 2 * p, index, rk, ua, ub, var_row, active, normalise, row_out, status, exp_tab); break;
+        }
       }
-      switch (sp->op) {
-        case OP_UNIFORM: pair_op<OP_UNIFORM>(sp, cdf, 2 * p, index, rk, ua, ub, var_row, active, normalise, row_out, status); break;
-        case OP_UNIFORM_INT: pair_op<OP_UNIFORM_INT>(sp, cdf, 2 * p, index, rk, ua, ub, var_row, active, normalise, row_out, status); break;
-        case OP_LOGUNIFORM: pair_op<OP_LOGUNIFORM>(sp, cdf, 2 * p, index, rk, ua, ub, var_row, active, normalise, row_out, status); break;
-        case OP_LOGUNIFORM_INT: pair_op<OP_LOGUNIFORM_INT>(sp, cdf, 2 * p, index, rk, ua, ub, var_row, active, normalise, row_out, status); break;
-        case OP_NORMAL: pair_op<OP_NORMAL>(sp, cdf, 2 * p, index, rk, ua, ub, var_row, active, normalise, row_out, status); break;
-        case OP_NORMAL_INT: pair_op<OP_NORMAL_INT>(sp, cdf, 2 * p, index, rk, ua, ub, var_row, active, normalise, row_out, status); break;
-        case OP_ONEHOT: pair_op<OP_ONEHOT>(sp, cdf, 2 * p, index, rk, ua, ub, var_row, active, normalise, row_out, status); break;
-        default: pair_op<OP_CAT_SMALL>(sp, cdf, 2 * p, index, rk, ua, ub, var_row, active, normalise, row_out, status); break;
-      }
-      p += ST_THREADS / 32;
-      while (p >= n_pairs) { p -= n_pairs; ++rg; }
+      p0 = p - n_pairs;  // the round-robin continues into the next row group
     }
     if (bulk_ok) {
       fence_proxy_async();  // generic-proxy smem writes -> async-proxy (TMA) reads
       __syncthreads();
       if (warp == 0) {
         if (bulk_ok == 2) {
+#ifndef ST_DEBUG_NO_STORE  // timing experiment only: generation without copy-out
           if (lane == 0) bulk_s2g(out + row0 * ld, tile, (uint32_t)rows * row_bytes);
+#endif
         } else {
           for (int r = lane; r < rows; r += 32) bulk_s2g(out + (row0 + r) * ld, tile + (size_t)r * stride, row_bytes);
         }
@@ -325,7 +352,7 @@ int ob200_sample_launch(ob200_ctx* ctx, uint64_t seed, uint64_t first_index, int
   if (aligned && stride == d_out && ld == d_out) bulk_ok = 2;
   else if (aligned && d_out * 8 >= 512) bulk_ok = 1;
   else if (aligned) { vec_lanes = 1; while (vec_lanes < 32 && vec_lanes < d_out / 2) vec_lanes <<= 1; }
-  const size_t smem = ((((size_t)ST_ROWS * stride + 1) & ~(size_t)1) + (size_t)ctx->n_cdf) * sizeof(double) + (size_t)ctx->n_dslots * sizeof(dslot);
+  const size_t smem = ((((size_t)ST_ROWS * stride + 1) & ~(size_t)1) + (size_t)ctx->n_cdf + 32) * sizeof(double) + (size_t)ctx->n_dslots * sizeof(dslot);
   if (smem > 227 * 1024) OB_FAIL(ctx, OB200_EINVAL, "D_out=%d too wide for the sampler tile", d_out);
   const int64_t n_tiles = (count + ST_ROWS - 1) / ST_ROWS;
   int per_sm = (int)((227 * 1024) / (smem + 1024));

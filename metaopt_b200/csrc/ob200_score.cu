@@ -74,36 +74,12 @@ __device__ __forceinline__ double sqrt_pos(double x) {
   return s;
 }
 
-// exp(t) for t <= 0 with a 32-entry table: t = (32 n + j) ln2/32 + r, |r| <= ln2/64, so
-// exp(t) = 2^n * 2^(j/32) * exp(r) and a degree-6 Taylor polynomial suffices (truncation 3.5e-18);
-// Cody-Waite two-constant reduction, scaling by exponent-field addition.  ~2 ulp; below 2^-1021 -> 0.
-// `tab` = 2^(j/32), j = 0..31, in shared memory.
-__device__ __forceinline__ double exp_neg(double t, const double* __restrict__ tab) {
-  const double magic = 6755399441055744.0;         // 1.5 * 2^52: round-to-nearest-integer trick
-  const double mb = fma(t, 46.16624130844683, magic);  // t * 32 / ln2
-  const int m = __double2loint(mb);
-  const double md = mb - magic;
-  double r = fma(md, -2.16608493865351192653e-02, t);   // ln2/32, high part
-  r = fma(md, -5.96317165397058692146e-12, r);          // ln2/32, low part
-  double p = 1.0 / 720.0;
-  p = fma(p, r, 1.0 / 120.0);
-  p = fma(p, r, 1.0 / 24.0);
-  p = fma(p, r, 1.0 / 6.0);
-  p = fma(p, r, 0.5);
-  p = fma(p, r, 1.0);
-  p = fma(p, r, 1.0);
-  const double v = tab[m & 31] * p;
-  const int n = m >> 5;
-  const double scaled = __hiloint2double(__double2hiint(v) + (n << 20), __double2loint(v));
-  return (n >= -1021) ? scaled : 0.0;
-}
-
 __device__ __forceinline__ double kernel_from_d2(int kind, double d2, double amplitude, const double* __restrict__ tab) {
   if (kind == OB200_KERNEL_MATERN52) {
     const double k = sqrt_pos(d2) * 2.23606797749979;  // sqrt(5) * dist
-    return amplitude * (fma(k, fma(k, 0.3333333333333333, 1.0), 1.0) * exp_neg(-k, tab));
+    return amplitude * (fma(k, fma(k, 0.3333333333333333, 1.0), 1.0) * ob_exp_tab(-k, tab));
   }
-  return amplitude * exp_neg(-0.5 * d2, tab);
+  return amplitude * ob_exp_tab(-0.5 * d2, tab);
 }
 
 __device__ __forceinline__ void acquisition(double mu, double sigma, double y_opt, double xi, double kappa, double out[3]) {

@@ -16,6 +16,9 @@ VARIANTS = {
     "skip1": ["SC_DEBUG_SKIP_PHASE1"],
     # clock64 marks around the parts of a tile (tools/prof_phases.py reads them back)
     "prof": ["SC_PROFILE_CYCLES"],
+    # sampler with one half switched off (wrong output): which half bounds it?
+    "st_nostore": ["ST_DEBUG_NO_STORE"],
+    "st_nocompute": ["ST_DEBUG_NO_COMPUTE"],
 }
 if __name__ == "__main__":
     names = sys.argv[1:] or list(VARIANTS)
