@@ -124,30 +124,47 @@ __device__ __noinline__ double retry_slot(const dslot* s, int q, uint64_t index,
   return __longlong_as_double(0x7ff8000000000000LL);
 }
 
-template <int OP>
-__device__ __forceinline__ void real_slot(const dslot* __restrict__ sp, int q, uint64_t index, const philox_keys& rk, double u0,
-                                          const double* __restrict__ var_row, bool active, int normalise,
-                                          double* __restrict__ row_out, int* __restrict__ status, const double* __restrict__ exp_tab) {
+// Kernel modes (template parameter): the hot generation paths know `normalise` at compile time and carry no
+// per-row predicates; the parity mode (host-supplied variates) keeps the runtime flags.
+enum { MODE_RAW = 0, MODE_NORM = 1, MODE_VARIATES = 2 };
+
+// shared-memory store through a 32-bit shared address (the generic-pointer form re-derives the window base per store)
+__device__ __forceinline__ void sts_f64(uint32_t addr, double v) {
+  asm volatile("st.shared.f64 [%0], %1;" ::"r"(addr), "d"(v) : "memory");
+}
+
+// Per-row context of one lane.  Rows past the end of a ragged last tile still generate (their smem rows exist and
+// are never copied out); `active` only gates the status latch and the parity-mode loads.
+struct row_ctx {
+  uint64_t index;
+  uint32_t row_sa;          // shared address of the row in the tile
+  const double* var_row;    // parity mode only
+  bool active;
+};
+
+template <int OP, int MODE>
+__device__ __forceinline__ void real_slot(const dslot* __restrict__ sp, int q, const row_ctx& rc, const philox_keys& rk, double u0,
+                                          int normalise, int* __restrict__ status, const double* __restrict__ exp_tab) {
   const dslot s = *sp;  // four LDS.128, broadcast
   double x;
   bool ok;
-  if (var_row) {  // parity mode: one host-supplied variate, no resampling
-    const double v = active ? var_row[s.col_src >> 16] : 0.5;
+  if (MODE == MODE_VARIATES) {  // parity mode: one host-supplied variate, no resampling
+    const double v = rc.active ? rc.var_row[s.col_src >> 16] : 0.5;
     x = draw_op<OP>(s, v, v, exp_tab);
     ok = (x >= s.low) && (x < s.high);
   } else {
     double z = 0.0;
     if (OP == OP_NORMAL || OP == OP_NORMAL_INT)
-      z = box_muller(philox_rk((uint32_t)index, (uint32_t)(index >> 32), 0x80000000u | (uint32_t)q, 0u, rk));
+      z = box_muller(philox_rk((uint32_t)rc.index, (uint32_t)(rc.index >> 32), 0x80000000u | (uint32_t)q, 0u, rk));
     x = draw_op<OP>(s, u0, z, exp_tab);
     ok = (x >= s.low) && (x < s.high);
-    if (__any_sync(0xffffffffu, active && !ok)) {
-      if (active && !ok) { x = retry_slot(sp, q, index, &rk, exp_tab); ok = (x == x); }
+    if (__any_sync(0xffffffffu, !ok)) {
+      if (!ok) { x = retry_slot(sp, q, rc.index, &rk, exp_tab); ok = (x == x); }
     }
   }
-  if (active && !ok) { atomicOr(status, 1); x = 0.0; }
-  if (normalise) x = div_const(__dsub_rn(x, s.nlo), s.span, s.rspan);
-  if (active) row_out[s.col_src & 0xffff] = x;
+  if (!ok) { if (rc.active) atomicOr(status, 1); x = 0.0; }
+  if (MODE == MODE_NORM || (MODE == MODE_VARIATES && normalise)) x = div_const(__dsub_rn(x, s.nlo), s.span, s.rspan);
+  sts_f64(rc.row_sa + (uint32_t)(s.col_src & 0xffff) * 8u, x);
 }
 
 // numpy searchsorted(cdf, u, side='right') clamped to k-1: number of entries <= u
@@ -166,56 +183,52 @@ __device__ __forceinline__ int cdf_count(const double* __restrict__ cdf, int k, 
 
 // one-hot group of a compile-time width: K - 1 compares (the clamp of cdf_count absorbs the last one), K selects
 template <int K>
-__device__ __forceinline__ void onehot_fixed(const double* __restrict__ cdf, double u, double v0, double v1, double* __restrict__ dst) {
+__device__ __forceinline__ void onehot_fixed(const double* __restrict__ cdf, double u, double v0, double v1, uint32_t dst_sa) {
   int hot = 0;
 #pragma unroll
   for (int j = 0; j < K - 1; ++j) hot += (cdf[j] <= u) ? 1 : 0;
 #pragma unroll
-  for (int j = 0; j < K; ++j) dst[j] = (j == hot) ? v1 : v0;
+  for (int j = 0; j < K; ++j) sts_f64(dst_sa + 8u * j, (j == hot) ? v1 : v0);
 }
 
-template <bool ONEHOT>
-__device__ __forceinline__ void cat_slot(const dslot* __restrict__ sp, const double* __restrict__ cdf, double u0,
-                                         const double* __restrict__ var_row, bool active, int normalise,
-                                         double* __restrict__ row_out) {
+template <bool ONEHOT, int MODE>
+__device__ __forceinline__ void cat_slot(const dslot* __restrict__ sp, const double* __restrict__ cdf, double u0, const row_ctx& rc,
+                                         int normalise) {
   const dslot s = *sp;
   const dslot_cat c = *reinterpret_cast<const dslot_cat*>(&sp->low);
-  const double u = var_row ? (active ? var_row[s.col_src >> 16] : 0.0) : u0;
-  const double v0 = normalise ? s.p0 : 0.0, v1 = normalise ? s.p1 : 1.0;
-  const int col = s.col_src & 0xffff;
+  const double u = (MODE == MODE_VARIATES) ? (rc.active ? rc.var_row[s.col_src >> 16] : 0.0) : u0;
+  const bool norm = MODE == MODE_NORM || (MODE == MODE_VARIATES && normalise);
+  const double v0 = norm ? s.p0 : 0.0, v1 = norm ? s.p1 : 1.0;
+  const uint32_t dst = rc.row_sa + (uint32_t)(s.col_src & 0xffff) * 8u;
   if (ONEHOT && c.ncat <= 4) {  // (one-hot means ncat >= 3) straight-line code for the common widths
-    if (active) {
-      if (c.ncat == 4) onehot_fixed<4>(cdf + c.cdf_off, u, v0, v1, row_out + col);
-      else onehot_fixed<3>(cdf + c.cdf_off, u, v0, v1, row_out + col);
-    }
+    if (c.ncat == 4) onehot_fixed<4>(cdf + c.cdf_off, u, v0, v1, dst);
+    else onehot_fixed<3>(cdf + c.cdf_off, u, v0, v1, dst);
     return;
   }
   const int hot = cdf_count(cdf + c.cdf_off, c.ncat, u);
-  if (active) {
-    if (ONEHOT) {
-      for (int j = 0; j < c.ncat; ++j) row_out[col + j] = (j == hot) ? v1 : v0;
-    } else {
-      row_out[col] = hot ? v1 : v0;  // k == 2: float(index); k == 1: 0.0
-    }
+  if (ONEHOT) {
+    for (int j = 0; j < c.ncat; ++j) sts_f64(dst + 8u * j, (j == hot) ? v1 : v0);
+  } else {
+    sts_f64(dst, hot ? v1 : v0);  // k == 2: float(index); k == 1: 0.0
   }
 }
 
 // Both slots of a pair share the operation (groups are padded to even size), so one warp-uniform
 // switch per pair selects straight-line code for the two of them.
-template <int OP>
-__device__ __forceinline__ void pair_op(const dslot* __restrict__ sp, const double* __restrict__ cdf, int q, uint64_t index,
-                                        const philox_keys& rk, double ua, double ub, const double* __restrict__ var_row,
-                                        bool active, int normalise, double* __restrict__ row_out, int* __restrict__ status,
+template <int OP, int MODE>
+__device__ __forceinline__ void pair_op(const dslot* __restrict__ sp, const double* __restrict__ cdf, int q, const row_ctx& rc,
+                                        const philox_keys& rk, double ua, double ub, int normalise, int* __restrict__ status,
                                         const double* __restrict__ exp_tab) {
   if (OP == OP_ONEHOT || OP == OP_CAT_SMALL) {
-    cat_slot<OP == OP_ONEHOT>(sp, cdf, ua, var_row, active, normalise, row_out);
-    if (sp[1].op != OP_NONE) cat_slot<OP == OP_ONEHOT>(sp + 1, cdf, ub, var_row, active, normalise, row_out);
+    cat_slot<OP == OP_ONEHOT, MODE>(sp, cdf, ua, rc, normalise);
+    if (sp[1].op != OP_NONE) cat_slot<OP == OP_ONEHOT, MODE>(sp + 1, cdf, ub, rc, normalise);
   } else {
-    real_slot<OP>(sp, q, index, rk, ua, var_row, active, normalise, row_out, status, exp_tab);
-    if (sp[1].op != OP_NONE) real_slot<OP>(sp + 1, q + 1, index, rk, ub, var_row, active, normalise, row_out, status, exp_tab);
+    real_slot<OP, MODE>(sp, q, rc, rk, ua, normalise, status, exp_tab);
+    if (sp[1].op != OP_NONE) real_slot<OP, MODE>(sp + 1, q + 1, rc, rk, ub, normalise, status, exp_tab);
   }
 }
 
+template <int MODE>
 __global__ void __launch_bounds__(ST_THREADS, ST_MIN_CTAS)
 sample_transform_kernel(const dslot* __restrict__ slots_g, int n_dslots, int n_slots, const double* __restrict__ cdf_g, int n_cdf,
                         int d_out, int stride, const __grid_constant__ philox_keys rk, uint64_t first_index, int64_t count,
@@ -236,6 +249,7 @@ sample_transform_kernel(const dslot* __restrict__ slots_g, int n_dslots, int n_s
   const int n_pairs = n_dslots >> 1;
   const int64_t n_tiles = (count + ST_ROWS - 1) / ST_ROWS;
   const uint32_t row_bytes = (uint32_t)d_out * 8u;
+  const uint32_t tile_sa = (uint32_t)__cvta_generic_to_shared(tile);
 
   for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
     const int64_t row0 = t * ST_ROWS;
@@ -249,28 +263,29 @@ sample_transform_kernel(const dslot* __restrict__ slots_g, int n_dslots, int n_s
     int p0 = warp;
     for (int rg = 0; rg < n_rg; ++rg) {
       const int r = rg * 32 + lane;
-      const bool active = r < rows;
-      const uint64_t index = first_index + (uint64_t)(row0 + r);
-      double* row_out = tile + (size_t)r * stride;
-      const double* var_row = variates ? variates + (size_t)(row0 + (active ? r : 0)) * n_slots : nullptr;
+      row_ctx rc;
+      rc.active = r < rows;
+      rc.index = first_index + (uint64_t)(row0 + r);
+      rc.row_sa = tile_sa + (uint32_t)r * (uint32_t)stride * 8u;
+      rc.var_row = (MODE == MODE_VARIATES) ? variates + (size_t)(row0 + (rc.active ? r : 0)) * n_slots : nullptr;
       int p = p0;
       for (; p < n_pairs; p += ST_THREADS / 32) {
         const dslot* sp = slots + 2 * p;
         double ua = 0.0, ub = 0.0;
-        if (!variates) {
-          const philox_out pr = philox_rk((uint32_t)index, (uint32_t)(index >> 32), (uint32_t)p, 0u, rk);
+        if (MODE != MODE_VARIATES) {
+          const philox_out pr = philox_rk((uint32_t)rc.index, (uint32_t)(rc.index >> 32), (uint32_t)p, 0u, rk);
           ua = u53_fast(pr.r0, pr.r1);
           ub = u53_fast(pr.r2, pr.r3);
         }
         switch (sp->op) {
-          case OP_UNIFORM: pair_op<OP_UNIFORM>(sp, cdf, 2 * p, index, rk, ua, ub, var_row, active, normalise, row_out, status, exp_tab); break;
-          case OP_UNIFORM_INT: pair_op<OP_UNIFORM_INT>(sp, cdf, 2 * p, index, rk, ua, ub, var_row, active, normalise, row_out, status, exp_tab); break;
-          case OP_LOGUNIFORM: pair_op<OP_LOGUNIFORM>(sp, cdf, 2 * p, index, rk, ua, ub, var_row, active, normalise, row_out, status, exp_tab); break;
-          case OP_LOGUNIFORM_INT: pair_op<OP_LOGUNIFORM_INT>(sp, cdf, 2 * p, index, rk, ua, ub, var_row, active, normalise, row_out, status, exp_tab); break;
-          case OP_NORMAL: pair_op<OP_NORMAL>(sp, cdf, 2 * p, index, rk, ua, ub, var_row, active, normalise, row_out, status, exp_tab); break;
-          case OP_NORMAL_INT: pair_op<OP_NORMAL_INT>(sp, cdf, 2 * p, index, rk, ua, ub, var_row, active, normalise, row_out, status, exp_tab); break;
-          case OP_ONEHOT: pair_op<OP_ONEHOT>(sp, cdf, 2 * p, index, rk, ua, ub, var_row, active, normalise, row_out, status, exp_tab); break;
-          default: pair_op<OP_CAT_SMALL>(sp, cdf, 2 * p, index, rk, ua, ub, var_row, active, normalise, row_out, status, exp_tab); break;
+          case OP_UNIFORM: pair_op<OP_UNIFORM, MODE>(sp, cdf, 2 * p, rc, rk, ua, ub, normalise, status, exp_tab); break;
+          case OP_UNIFORM_INT: pair_op<OP_UNIFORM_INT, MODE>(sp, cdf, 2 * p, rc, rk, ua, ub, normalise, status, exp_tab); break;
+          case OP_LOGUNIFORM: pair_op<OP_LOGUNIFORM, MODE>(sp, cdf, 2 * p, rc, rk, ua, ub, normalise, status, exp_tab); break;
+          case OP_LOGUNIFORM_INT: pair_op<OP_LOGUNIFORM_INT, MODE>(sp, cdf, 2 * p, rc, rk, ua, ub, normalise, status, exp_tab); break;
+          case OP_NORMAL: pair_op<OP_NORMAL, MODE>(sp, cdf, 2 * p, rc, rk, ua, ub, normalise, status, exp_tab); break;
+          case OP_NORMAL_INT: pair_op<OP_NORMAL_INT, MODE>(sp, cdf, 2 * p, rc, rk, ua, ub, normalise, status, exp_tab); break;
+          case OP_ONEHOT: pair_op<OP_ONEHOT, MODE>(sp, cdf, 2 * p, rc, rk, ua, ub, normalise, status, exp_tab); break;
+          default: pair_op<OP_CAT_SMALL, MODE>(sp, cdf, 2 * p, rc, rk, ua, ub, normalise, status, exp_tab); break;
         }
       }
       p0 = p - n_pairs;  // the round-robin continues into the next row group
@@ -365,10 +380,12 @@ int ob200_sample_launch(ob200_ctx* ctx, uint64_t seed, uint64_t first_index, int
     uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
     for (int r = 0; r < 10; ++r) { rk.k0[r] = k0; rk.k1[r] = k1; k0 += 0x9E3779B9u; k1 += 0xBB67AE85u; }
   }
-  OB_CUDA(ctx, cudaFuncSetAttribute(sample_transform_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  sample_transform_kernel<<<grid, ST_THREADS, smem, ctx->stream>>>(reinterpret_cast<const dslot*>(ctx->dslots_dev), ctx->n_dslots, ctx->n_slots, ctx->cdf_dev, ctx->n_cdf, d_out,
-                                                                   stride, rk, first_index, count, normalise, out_dev, ld,
-                                                                   variates_dev, bulk_ok, vec_lanes, ctx->status_dev);
+  auto kernel = variates_dev ? sample_transform_kernel<MODE_VARIATES>
+                             : (normalise ? sample_transform_kernel<MODE_NORM> : sample_transform_kernel<MODE_RAW>);
+  OB_CUDA(ctx, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  kernel<<<grid, ST_THREADS, smem, ctx->stream>>>(reinterpret_cast<const dslot*>(ctx->dslots_dev), ctx->n_dslots, ctx->n_slots, ctx->cdf_dev, ctx->n_cdf, d_out,
+                                                  stride, rk, first_index, count, normalise, out_dev, ld, variates_dev, bulk_ok, vec_lanes,
+                                                  ctx->status_dev);
   OB_LAUNCH_CHECK(ctx);
   return OB200_OK;
 }
