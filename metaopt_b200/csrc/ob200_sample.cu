@@ -53,6 +53,18 @@ struct dslot_cat { int ncat, cdf_off; };  // categorical slots reinterpret (low)
 enum { OP_UNIFORM = 0, OP_UNIFORM_INT = 1, OP_LOGUNIFORM = 2, OP_LOGUNIFORM_INT = 3, OP_NORMAL = 4, OP_NORMAL_INT = 5,
        OP_ONEHOT = 6, OP_CAT_SMALL = 7, OP_NONE = 8 };
 
+// 2^(j/32), j = 0..31, correctly rounded (numpy.exp2): read through L1 (__ldg) so that the tile keeps all of the
+// CTA's shared memory budget (8 CTAs per SM)
+__device__ const double g_exp2_tab[32] = {
+    0x1.0000000000000p+0, 0x1.059b0d3158574p+0, 0x1.0b5586cf9890fp+0, 0x1.11301d0125b51p+0,
+    0x1.172b83c7d517bp+0, 0x1.1d4873168b9aap+0, 0x1.2387a6e756238p+0, 0x1.29e9df51fdee1p+0,
+    0x1.306fe0a31b715p+0, 0x1.371a7373aa9cbp+0, 0x1.3dea64c123422p+0, 0x1.44e086061892dp+0,
+    0x1.4bfdad5362a27p+0, 0x1.5342b569d4f82p+0, 0x1.5ab07dd485429p+0, 0x1.6247eb03a5585p+0,
+    0x1.6a09e667f3bcdp+0, 0x1.71f75e8ec5f74p+0, 0x1.7a11473eb0187p+0, 0x1.82589994cce12p+0,
+    0x1.8ace5422aa0dbp+0, 0x1.93737b0cdc5e5p+0, 0x1.9c49182a3f090p+0, 0x1.a5503b23e255cp+0,
+    0x1.ae89f995ad3adp+0, 0x1.b7f76f2fb5e47p+0, 0x1.c199bdd85529cp+0, 0x1.cb720dcef9069p+0,
+    0x1.d5818dcfba487p+0, 0x1.dfc97337b9b5fp+0, 0x1.ea4afa2a490dap+0, 0x1.f50765b6e4540p+0};
+
 struct philox_keys { uint32_t k0[10], k1[10]; };  // round keys, precomputed on the host (constant bank operands)
 
 __device__ __forceinline__ philox_out philox_rk(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, const philox_keys& rk) {
@@ -238,8 +250,7 @@ sample_transform_kernel(const dslot* __restrict__ slots_g, int n_dslots, int n_s
   double* tile = reinterpret_cast<double*>(smem_raw);                                   // [ST_ROWS][stride]
   dslot* slots = reinterpret_cast<dslot*>(tile + (((size_t)ST_ROWS * stride + 1) & ~(size_t)1));  // 16-byte aligned
   double* cdf = reinterpret_cast<double*>(slots + n_dslots);
-  double* exp_tab = cdf + n_cdf;                                                        // 2^(j/32), j = 0..31
-  if (threadIdx.x < 32) exp_tab[threadIdx.x] = exp2((double)threadIdx.x * 0.03125);
+  const double* exp_tab = g_exp2_tab;
   for (int i = threadIdx.x; i < n_dslots * (int)(sizeof(dslot) / 8); i += ST_THREADS)
     reinterpret_cast<double*>(slots)[i] = reinterpret_cast<const double*>(slots_g)[i];
   for (int i = threadIdx.x; i < n_cdf; i += ST_THREADS) cdf[i] = cdf_g[i];
@@ -367,7 +378,7 @@ int ob200_sample_launch(ob200_ctx* ctx, uint64_t seed, uint64_t first_index, int
   if (aligned && stride == d_out && ld == d_out) bulk_ok = 2;
   else if (aligned && d_out * 8 >= 512) bulk_ok = 1;
   else if (aligned) { vec_lanes = 1; while (vec_lanes < 32 && vec_lanes < d_out / 2) vec_lanes <<= 1; }
-  const size_t smem = ((((size_t)ST_ROWS * stride + 1) & ~(size_t)1) + (size_t)ctx->n_cdf + 32) * sizeof(double) + (size_t)ctx->n_dslots * sizeof(dslot);
+  const size_t smem = ((((size_t)ST_ROWS * stride + 1) & ~(size_t)1) + (size_t)ctx->n_cdf) * sizeof(double) + (size_t)ctx->n_dslots * sizeof(dslot);
   if (smem > 227 * 1024) OB_FAIL(ctx, OB200_EINVAL, "D_out=%d too wide for the sampler tile", d_out);
   const int64_t n_tiles = (count + ST_ROWS - 1) / ST_ROWS;
   int per_sm = (int)((227 * 1024) / (smem + 1024));
