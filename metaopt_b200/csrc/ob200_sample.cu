@@ -34,7 +34,7 @@ namespace {
 #define ST_THREADS 128   // 4 warps share the slot pairs of the tile; many small independent CTAs per SM
 #endif
 #ifndef ST_MIN_CTAS
-#define ST_MIN_CTAS 8
+#define ST_MIN_CTAS 7   // 72 registers: the paired slot code spills at 64, and one CTA less per SM costs nothing
 #endif
 
 // Slot as the kernel reads it: 64 bytes = four 16-byte shared-memory loads, everything that only
@@ -225,6 +225,59 @@ __device__ __forceinline__ void cat_slot(const dslot* __restrict__ sp, const dou
   }
 }
 
+// Two real / integer slots of one pair side by side: their dependency chains (draw, range test, exact division)
+// are independent, so keeping them in one basic block lets the scheduler overlap them.  A padding second slot
+// (all-zero parameters) is computed too and just not stored.
+template <int OP, int MODE>
+__device__ __forceinline__ void real_pair(const dslot* __restrict__ sp, int q, const row_ctx& rc, const philox_keys& rk, double ua,
+                                          double ub, int normalise, int* __restrict__ status, const double* __restrict__ exp_tab) {
+  const dslot s0 = sp[0], s1 = sp[1];
+  const bool two = s1.op != OP_NONE;
+  double z0 = 0.0, z1 = 0.0;
+  if (OP == OP_NORMAL || OP == OP_NORMAL_INT) {
+    z0 = box_muller(philox_rk((uint32_t)rc.index, (uint32_t)(rc.index >> 32), 0x80000000u | (uint32_t)q, 0u, rk));
+    z1 = box_muller(philox_rk((uint32_t)rc.index, (uint32_t)(rc.index >> 32), 0x80000000u | (uint32_t)(q + 1), 0u, rk));
+  }
+  double x0 = draw_op<OP>(s0, ua, z0, exp_tab), x1 = draw_op<OP>(s1, ub, z1, exp_tab);
+  bool ok0 = (x0 >= s0.low) && (x0 < s0.high), ok1 = !two || ((x1 >= s1.low) && (x1 < s1.high));
+  if (__any_sync(0xffffffffu, !(ok0 && ok1))) {
+    if (!ok0) { x0 = retry_slot(sp, q, rc.index, &rk, exp_tab); ok0 = (x0 == x0); }
+    if (!ok1) { x1 = retry_slot(sp + 1, q + 1, rc.index, &rk, exp_tab); ok1 = (x1 == x1); }
+    if (!(ok0 && ok1)) {
+      if (rc.active) atomicOr(status, 1);
+      if (!ok0) x0 = 0.0;
+      if (!ok1) x1 = 0.0;
+    }
+  }
+  if (MODE == MODE_NORM) {
+    x0 = div_const(__dsub_rn(x0, s0.nlo), s0.span, s0.rspan);
+    x1 = div_const(__dsub_rn(x1, s1.nlo), s1.span, s1.rspan);
+  }
+  sts_f64(rc.row_sa + (uint32_t)(s0.col_src & 0xffff) * 8u, x0);
+  if (two) sts_f64(rc.row_sa + (uint32_t)(s1.col_src & 0xffff) * 8u, x1);
+}
+
+// Two one-hot groups of width 4 side by side (the common case); anything else goes slot by slot.
+template <int MODE>
+__device__ __forceinline__ bool onehot4_pair(const dslot* __restrict__ sp, const double* __restrict__ cdf, double ua, double ub,
+                                             const row_ctx& rc) {
+  const dslot_cat c0 = *reinterpret_cast<const dslot_cat*>(&sp[0].low), c1 = *reinterpret_cast<const dslot_cat*>(&sp[1].low);
+  if (c0.ncat != 4 || c1.ncat != 4 || sp[1].op == OP_NONE) return false;
+  const double2 p0 = *reinterpret_cast<const double2*>(&sp[0].p0), p1 = *reinterpret_cast<const double2*>(&sp[1].p0);
+  const double a0 = MODE == MODE_NORM ? p0.x : 0.0, a1 = MODE == MODE_NORM ? p0.y : 1.0;
+  const double b0 = MODE == MODE_NORM ? p1.x : 0.0, b1 = MODE == MODE_NORM ? p1.y : 1.0;
+  const double *ca = cdf + c0.cdf_off, *cb = cdf + c1.cdf_off;
+  const int ha = (ca[0] <= ua ? 1 : 0) + (ca[1] <= ua ? 1 : 0) + (ca[2] <= ua ? 1 : 0);
+  const int hb = (cb[0] <= ub ? 1 : 0) + (cb[1] <= ub ? 1 : 0) + (cb[2] <= ub ? 1 : 0);
+  const uint32_t da = rc.row_sa + (uint32_t)(sp[0].col_src & 0xffff) * 8u, db = rc.row_sa + (uint32_t)(sp[1].col_src & 0xffff) * 8u;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    sts_f64(da + 8u * j, (j == ha) ? a1 : a0);
+    sts_f64(db + 8u * j, (j == hb) ? b1 : b0);
+  }
+  return true;
+}
+
 // Both slots of a pair share the operation (groups are padded to even size), so one warp-uniform
 // switch per pair selects straight-line code for the two of them.
 template <int OP, int MODE>
@@ -232,8 +285,11 @@ __device__ __forceinline__ void pair_op(const dslot* __restrict__ sp, const doub
                                         const philox_keys& rk, double ua, double ub, int normalise, int* __restrict__ status,
                                         const double* __restrict__ exp_tab) {
   if (OP == OP_ONEHOT || OP == OP_CAT_SMALL) {
+    if (OP == OP_ONEHOT && MODE != MODE_VARIATES && onehot4_pair<MODE>(sp, cdf, ua, ub, rc)) return;
     cat_slot<OP == OP_ONEHOT, MODE>(sp, cdf, ua, rc, normalise);
     if (sp[1].op != OP_NONE) cat_slot<OP == OP_ONEHOT, MODE>(sp + 1, cdf, ub, rc, normalise);
+  } else if (MODE != MODE_VARIATES) {
+    real_pair<OP, MODE>(sp, q, rc, rk, ua, ub, normalise, status, exp_tab);
   } else {
     real_slot<OP, MODE>(sp, q, rc, rk, ua, normalise, status, exp_tab);
     if (sp[1].op != OP_NONE) real_slot<OP, MODE>(sp + 1, q + 1, rc, rk, ub, normalise, status, exp_tab);
@@ -381,8 +437,11 @@ int ob200_sample_launch(ob200_ctx* ctx, uint64_t seed, uint64_t first_index, int
   const size_t smem = ((((size_t)ST_ROWS * stride + 1) & ~(size_t)1) + (size_t)ctx->n_cdf) * sizeof(double) + (size_t)ctx->n_dslots * sizeof(dslot);
   if (smem > 227 * 1024) OB_FAIL(ctx, OB200_EINVAL, "D_out=%d too wide for the sampler tile", d_out);
   const int64_t n_tiles = (count + ST_ROWS - 1) / ST_ROWS;
-  int per_sm = (int)((227 * 1024) / (smem + 1024));
-  if (per_sm > 2048 / ST_THREADS) per_sm = 2048 / ST_THREADS;
+  auto kernel = variates_dev ? sample_transform_kernel<MODE_VARIATES>
+                             : (normalise ? sample_transform_kernel<MODE_NORM> : sample_transform_kernel<MODE_RAW>);
+  OB_CUDA(ctx, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int per_sm = 0;  // resident CTAs per SM for this instantiation (registers and shared memory): one wave, grid-stride
+  OB_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, ST_THREADS, smem));
   if (per_sm < 1) per_sm = 1;
   const int64_t max_grid = (int64_t)ctx->num_sms * per_sm;
   const int grid = (int)(n_tiles < max_grid ? n_tiles : max_grid);
@@ -391,9 +450,6 @@ int ob200_sample_launch(ob200_ctx* ctx, uint64_t seed, uint64_t first_index, int
     uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
     for (int r = 0; r < 10; ++r) { rk.k0[r] = k0; rk.k1[r] = k1; k0 += 0x9E3779B9u; k1 += 0xBB67AE85u; }
   }
-  auto kernel = variates_dev ? sample_transform_kernel<MODE_VARIATES>
-                             : (normalise ? sample_transform_kernel<MODE_NORM> : sample_transform_kernel<MODE_RAW>);
-  OB_CUDA(ctx, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   kernel<<<grid, ST_THREADS, smem, ctx->stream>>>(reinterpret_cast<const dslot*>(ctx->dslots_dev), ctx->n_dslots, ctx->n_slots, ctx->cdf_dev, ctx->n_cdf, d_out,
                                                   stride, rk, first_index, count, normalise, out_dev, ld, variates_dev, bulk_ok, vec_lanes,
                                                   ctx->status_dev);

@@ -17,6 +17,9 @@ VARIANTS = {
     # clock64 marks around the parts of a tile (tools/prof_phases.py reads them back)
     "prof": ["SC_PROFILE_CYCLES"],
     # sampler with one half switched off (wrong output): which half bounds it?
+    "st7": ["ST_MIN_CTAS=7"],
+    "st6": ["ST_MIN_CTAS=6"],
+    "st5": ["ST_MIN_CTAS=5"],
     "st_nostore": ["ST_DEBUG_NO_STORE"],
     "st_nocompute": ["ST_DEBUG_NO_COMPUTE"],
 }
