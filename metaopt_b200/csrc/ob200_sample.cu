@@ -33,6 +33,9 @@ namespace {
 #ifndef ST_THREADS
 #define ST_THREADS 128   // 4 warps share the slot pairs of the tile; many small independent CTAs per SM
 #endif
+#ifndef ST_NBUF
+#define ST_NBUF 1        // tile buffers per CTA: with 2, a tile drains through the TMA engine while the next one is generated
+#endif
 #ifndef ST_MIN_CTAS
 #define ST_MIN_CTAS 7   // 72 registers: the paired slot code spills at 64, and one CTA less per SM costs nothing
 #endif
@@ -303,8 +306,9 @@ sample_transform_kernel(const dslot* __restrict__ slots_g, int n_dslots, int n_s
                         int normalise, double* __restrict__ out, int64_t ld, const double* __restrict__ variates,
                         int bulk_ok, int vec_lanes, int* __restrict__ status) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  double* tile = reinterpret_cast<double*>(smem_raw);                                   // [ST_ROWS][stride]
-  dslot* slots = reinterpret_cast<dslot*>(tile + (((size_t)ST_ROWS * stride + 1) & ~(size_t)1));  // 16-byte aligned
+  const size_t tile_elems = ((size_t)ST_ROWS * stride + 1) & ~(size_t)1;                 // 16-byte aligned
+  double* tile0 = reinterpret_cast<double*>(smem_raw);                                  // ST_NBUF x [ST_ROWS][stride]
+  dslot* slots = reinterpret_cast<dslot*>(tile0 + ST_NBUF * tile_elems);
   double* cdf = reinterpret_cast<double*>(slots + n_dslots);
   const double* exp_tab = g_exp2_tab;
   for (int i = threadIdx.x; i < n_dslots * (int)(sizeof(dslot) / 8); i += ST_THREADS)
@@ -316,9 +320,11 @@ sample_transform_kernel(const dslot* __restrict__ slots_g, int n_dslots, int n_s
   const int n_pairs = n_dslots >> 1;
   const int64_t n_tiles = (count + ST_ROWS - 1) / ST_ROWS;
   const uint32_t row_bytes = (uint32_t)d_out * 8u;
-  const uint32_t tile_sa = (uint32_t)__cvta_generic_to_shared(tile);
 
-  for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+  int buf = 0;
+  for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x, buf ^= (ST_NBUF - 1)) {
+    double* tile = tile0 + (size_t)buf * tile_elems;
+    const uint32_t tile_sa = (uint32_t)__cvta_generic_to_shared(tile);
     const int64_t row0 = t * ST_ROWS;
     const int rows = (int)min((int64_t)ST_ROWS, count - row0);
 #ifdef ST_DEBUG_NO_COMPUTE  // timing experiment only: copy-out without generation
@@ -359,6 +365,9 @@ sample_transform_kernel(const dslot* __restrict__ slots_g, int n_dslots, int n_s
     }
     if (bulk_ok) {
       fence_proxy_async();  // generic-proxy smem writes -> async-proxy (TMA) reads
+#if ST_NBUF == 2
+      if (threadIdx.x == 0) bulk_wait_read0();  // the previous tile has left the other buffer (it had a whole tile's time)
+#endif
       __syncthreads();
       if (warp == 0) {
         if (bulk_ok == 2) {
@@ -369,9 +378,13 @@ sample_transform_kernel(const dslot* __restrict__ slots_g, int n_dslots, int n_s
           for (int r = lane; r < rows; r += 32) bulk_s2g(out + (row0 + r) * ld, tile + (size_t)r * stride, row_bytes);
         }
         bulk_commit();
+#if ST_NBUF == 1
         bulk_wait_read0();  // the tile is rewritten next iteration
+#endif
       }
+#if ST_NBUF == 1
       __syncthreads();
+#endif
     } else if (vec_lanes) {
       __syncthreads();
       // 16-byte coalesced stores: a power-of-two group of lanes per row
@@ -381,7 +394,9 @@ sample_transform_kernel(const dslot* __restrict__ slots_g, int n_dslots, int n_s
         double2* dst = reinterpret_cast<double2*>(out + (row0 + r) * ld);
         for (int c = l; c < (d_out >> 1); c += vec_lanes) dst[c] = src[c];
       }
+#if ST_NBUF == 1
       __syncthreads();
+#endif
     } else {
       __syncthreads();
       for (int r = warp; r < rows; r += ST_THREADS / 32) {
@@ -389,7 +404,9 @@ sample_transform_kernel(const dslot* __restrict__ slots_g, int n_dslots, int n_s
         double* dst = out + (row0 + r) * ld;
         for (int c = lane; c < d_out; c += 32) dst[c] = src[c];
       }
+#if ST_NBUF == 1
       __syncthreads();
+#endif
     }
   }
   if (bulk_ok && warp == 0) bulk_wait0();
@@ -434,7 +451,7 @@ int ob200_sample_launch(ob200_ctx* ctx, uint64_t seed, uint64_t first_index, int
   if (aligned && stride == d_out && ld == d_out) bulk_ok = 2;
   else if (aligned && d_out * 8 >= 512) bulk_ok = 1;
   else if (aligned) { vec_lanes = 1; while (vec_lanes < 32 && vec_lanes < d_out / 2) vec_lanes <<= 1; }
-  const size_t smem = ((((size_t)ST_ROWS * stride + 1) & ~(size_t)1) + (size_t)ctx->n_cdf) * sizeof(double) + (size_t)ctx->n_dslots * sizeof(dslot);
+  const size_t smem = (ST_NBUF * (((size_t)ST_ROWS * stride + 1) & ~(size_t)1) + (size_t)ctx->n_cdf) * sizeof(double) + (size_t)ctx->n_dslots * sizeof(dslot);
   if (smem > 227 * 1024) OB_FAIL(ctx, OB200_EINVAL, "D_out=%d too wide for the sampler tile", d_out);
   const int64_t n_tiles = (count + ST_ROWS - 1) / ST_ROWS;
   auto kernel = variates_dev ? sample_transform_kernel<MODE_VARIATES>

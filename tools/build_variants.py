@@ -17,6 +17,8 @@ VARIANTS = {
     # clock64 marks around the parts of a tile (tools/prof_phases.py reads them back)
     "prof": ["SC_PROFILE_CYCLES"],
     # sampler with one half switched off (wrong output): which half bounds it?
+    "st_db4": ["ST_NBUF=2", "ST_MIN_CTAS=4"],
+    "st_db4w8": ["ST_NBUF=2", "ST_MIN_CTAS=2", "ST_THREADS=256", "ST_ROWS=64"],
     "st7": ["ST_MIN_CTAS=7"],
     "st6": ["ST_MIN_CTAS=6"],
     "st5": ["ST_MIN_CTAS=5"],
