@@ -127,6 +127,14 @@ int ob200_gp_fit(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n
                  const ob200_kernel* kernel, double alpha, int normalize_y);
 int ob200_gp_fit_host(ob200_ctx* ctx, const double* X_host, const double* y_host, int n, int D,
                       const ob200_kernel* kernel, double alpha, int normalize_y);
+/* Append ONE observation to the current fit in O(n^2) instead of refitting in O(n^3): new row of L from
+ * inv(L) k, new row of inv(L), alpha_ recomputed in full from inv(L) (the y statistics move with every observation
+ * when normalize_y is on), same hyper-parameters and diagonal term as the fit.  Counterpart of what
+ * GaussianProcessRegressor.fit (sklearn _gpr.py:233-368) recomputes from scratch after every skopt tell(); used for
+ * constant-liar batches and fixed-hyper-parameter runs.  x_new_dev [D], y_dev [n_total] = ALL
+ * targets, n_total = current n + 1.  OB200_ESTATE when the padded factor has no free row (caller refits) or the fit
+ * was imported; OB200_ENOTSPD like the fit.  Synchronous. */
+int ob200_gp_append(ob200_ctx* ctx, const double* x_new_dev, const double* y_dev, int n_total, int normalize_y);
 /* log marginal likelihood of the current fit (sklearn:_gpr.py:541-656, value only). */
 int ob200_gp_lml(ob200_ctx* ctx, double* lml_host);
 /* Gradient of the log marginal likelihood of the current fit (sklearn:_gpr.py:541-656,

@@ -59,6 +59,7 @@ SIGNATURES = {
     "ob200_sample_transform_host": (_i, [_vp, _u64, _u64, _i64, _i, _vp, _i64, _vp]),
     "ob200_gp_fit": (_i, [_vp, _vp, _vp, _i, _i, C.POINTER(Kernel), _d, _i]),
     "ob200_gp_fit_host": (_i, [_vp, _vp, _vp, _i, _i, C.POINTER(Kernel), _d, _i]),
+    "ob200_gp_append": (_i, [_vp, _vp, _vp, _i, _i]),
     "ob200_gp_lml": (_i, [_vp, _pd]),
     "ob200_gp_lml_grad": (_i, [_vp, _pd, _pd, _i]),
     "ob200_gp_predict_grad_host": (_i, [_vp, _vp, _i64, _i, _vp]),

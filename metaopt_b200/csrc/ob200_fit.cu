@@ -693,6 +693,70 @@ __global__ void __launch_bounds__(256) pg_final_kernel(const double* __restrict_
   }
 }
 
+// ---- rank-1 append of one observation to the current fit (ob200_gp_append) --------------------------------------
+// new row of K against the n old points (direct differences, like gram_kernel), X/ls row and its squared norm
+__global__ void __launch_bounds__(256) append_k_kernel(const double* __restrict__ x_new, const double* __restrict__ ls, int D,
+                                                       int D_pad, int n, int n_pad, int kind, double amplitude,
+                                                       double* __restrict__ Xs, double* __restrict__ xx, double* __restrict__ kvec) {
+  extern __shared__ double ap_xs[];
+  for (int d = threadIdx.x; d < D_pad; d += blockDim.x) ap_xs[d] = d < D ? x_new[d] / ls[d] : 0.0;
+  __syncthreads();
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < n_pad) {
+    double k = 0.0;
+    if (j < n) {
+      double d2 = 0.0;
+      for (int d = 0; d < D_pad; ++d) { const double df = ap_xs[d] - Xs[(size_t)j * D_pad + d]; d2 = fma(df, df, d2); }
+      k = kernel_from_d2(kind, d2, amplitude);
+    }
+    kvec[j] = k;
+  }
+  if (blockIdx.x == 0) {
+    __syncthreads();
+    double acc = 0.0;
+    for (int d = threadIdx.x; d < D_pad; d += blockDim.x) Xs[(size_t)n * D_pad + d] = ap_xs[d];
+    if (threadIdx.x == 0) {
+      for (int d = 0; d < D_pad; ++d) acc = fma(ap_xs[d], ap_xs[d], acc);
+      xx[n] = acc;
+    }
+  }
+}
+
+// pivot d = sqrt(k_nn + alpha - |l|^2), new row of L; scal[0] = d, scal[1] = 1/d
+__global__ void __launch_bounds__(1024) append_diag_kernel(const double* __restrict__ lvec, int n, int n_pad, double knn,
+                                                           double* __restrict__ L, double* __restrict__ scal, int* __restrict__ info) {
+  __shared__ double red[1024];
+  double acc = 0.0;
+  for (int i = threadIdx.x; i < n; i += 1024) { const double v = lvec[i]; acc = fma(v, v, acc); L[(size_t)n * n_pad + i] = v; }
+  red[threadIdx.x] = acc;
+  __syncthreads();
+  for (int s = 512; s > 0; s >>= 1) { if (threadIdx.x < s) red[threadIdx.x] += red[threadIdx.x + s]; __syncthreads(); }
+  if (threadIdx.x == 0) {
+    const double d2 = knn - red[0];
+    if (!(d2 > 0.0)) { *info = n + 1; scal[0] = 1.0; scal[1] = 1.0; }
+    else { const double d = sqrt(d2); scal[0] = d; scal[1] = 1.0 / d; L[(size_t)n * n_pad + n] = d; }
+  }
+}
+
+// new row of inv(L): -(l^T inv(L)) / d, 1 / d on the diagonal
+__global__ void __launch_bounds__(256) append_row_kernel(const double* __restrict__ wvec, const double* __restrict__ scal, int n,
+                                                         int n_pad, double* __restrict__ Xinv) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j > n) return;
+  Xinv[(size_t)n * n_pad + j] = j < n ? -wvec[j] * scal[1] : scal[1];
+}
+
+__global__ void __launch_bounds__(1024) append_lml_kernel(const double* __restrict__ L, int ld, int n, const double* __restrict__ y,
+                                                          const double* __restrict__ alpha, double* __restrict__ lml_out) {
+  __shared__ double ra[1024], rb[1024];
+  double a = 0.0, b = 0.0;
+  for (int i = threadIdx.x; i < n; i += 1024) { a = fma(y[i], alpha[i], a); b += log(L[(size_t)i * ld + i]); }
+  ra[threadIdx.x] = a; rb[threadIdx.x] = b;
+  __syncthreads();
+  for (int s = 512; s > 0; s >>= 1) { if (threadIdx.x < s) { ra[threadIdx.x] += ra[threadIdx.x + s]; rb[threadIdx.x] += rb[threadIdx.x + s]; } __syncthreads(); }
+  if (threadIdx.x == 0) *lml_out = -0.5 * ra[0] - rb[0] - 0.5 * (double)n * 1.8378770664093453;  // log(2 pi)
+}
+
 int launch_gemm(ob200_ctx* ctx, bool trans_b, const gemm_args& g, int batch) {
   dim3 grid(g.N / 64, g.M / 64, batch);
   if (grid.x == 0 || grid.y == 0 || batch == 0) return OB200_OK;
@@ -856,6 +920,9 @@ int ob200_gp_fit(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n
   ctx->have_local_fit = true;
   ctx->w_Xs_off = w_Xs;
   ctx->w_y_off = w_y;
+  ctx->w_t_off = w_t;
+  ctx->w_stats_off = w_stats;
+  ctx->fit_alpha = alpha;
   return OB200_OK;
 }
 
@@ -960,6 +1027,74 @@ int ob200_gp_predict_grad_host(ob200_ctx* ctx, const double* x_host, int64_t ldx
   OB_LAUNCH_CHECK(ctx);
   OB_CUDA(ctx, cudaMemcpyAsync(out_host, P + p_out, (size_t)m * W * 8, cudaMemcpyDeviceToHost, st));
   OB_CUDA(ctx, cudaStreamSynchronize(st));
+  return OB200_OK;
+}
+
+int ob200_gp_append(ob200_ctx* ctx, const double* x_new_dev, const double* y_dev, int n_total, int normalize_y) {
+  if (!ctx) return OB200_EINVAL;
+  if (!x_new_dev || !y_dev) OB_FAIL(ctx, OB200_EINVAL, "null argument");
+  if (!ctx->fitted || !ctx->have_local_fit) OB_FAIL(ctx, OB200_ESTATE, "append needs a fit made on this context");
+  const int n = ctx->hdr.n, n_pad = ctx->hdr.n_pad, D = ctx->hdr.D, D_pad = ctx->hdr.D_pad;
+  if (n_total != n + 1) OB_FAIL(ctx, OB200_EINVAL, "n_total=%d, the current fit has %d observations", n_total, n);
+  if (n + 1 > n_pad || n + 1 > OB200_MAX_N) OB_FAIL(ctx, OB200_ESTATE, "no room in the padded factor (n=%d, n_pad=%d): refit", n, n_pad);
+  OB_CUDA(ctx, cudaSetDevice(ctx->device));
+  cudaStream_t st = ctx->stream;
+  const ob200_blob_layout lay = ob_blob_layout(n_pad, D_pad);
+  char* blob = ctx->blob;
+  double* b_ls = reinterpret_cast<double*>(blob + lay.off_ls);
+  double* b_xs = reinterpret_cast<double*>(blob + lay.off_xs);
+  double* b_xx = reinterpret_cast<double*>(blob + lay.off_xx);
+  double* b_alpha = reinterpret_cast<double*>(blob + lay.off_alpha);
+  double* b_linv = reinterpret_cast<double*>(blob + lay.off_linv);
+  double* W = ctx->work_dev;
+  double *Xinv = W, *Xs = W + ctx->w_Xs_off, *ynorm = W + ctx->w_y_off, *tvec = W + ctx->w_t_off, *stats = W + ctx->w_stats_off;
+  int* info_dev = reinterpret_cast<int*>(stats + 6);
+  double* lml_dev = stats + 4;
+  // scratch: k | l | w | (d, 1/d)
+  int rc = ob_reserve(ctx, &ctx->pg_dev, &ctx->pg_cap, (int64_t)3 * n_pad + 8);
+  if (rc) return rc;
+  double *kvec = ctx->pg_dev, *lvec = kvec + n_pad, *wvec = lvec + n_pad, *scal = wvec + n_pad;
+  ctx->fitted = false;  // a failure below leaves no usable fit
+  ctx->have_local_fit = false;
+  OB_CUDA(ctx, cudaMemsetAsync(info_dev, 0, sizeof(int), st));
+  append_k_kernel<<<(n_pad + 255) / 256, 256, (size_t)D_pad * 8, st>>>(x_new_dev, b_ls, D, D_pad, n, n_pad, ctx->hdr.kernel_kind,
+                                                                     ctx->hdr.amplitude, Xs, b_xx, kvec);
+  OB_LAUNCH_CHECK(ctx);
+  pg_v_kernel<<<dim3((n_pad * 32 + 255) / 256, 1), 256, 0, st>>>(Xinv, kvec, n_pad, lvec);  // l = inv(L) k
+  OB_LAUNCH_CHECK(ctx);
+  append_diag_kernel<<<1, 1024, 0, st>>>(lvec, n, n_pad, ctx->hdr.amplitude + ctx->fit_alpha, ctx->L_dev, scal, info_dev);
+  OB_LAUNCH_CHECK(ctx);
+  pg_w_kernel<<<dim3((n_pad + 31) / 32, 1), 256, 0, st>>>(Xinv, lvec, n_pad, wvec);         // w = inv(L)^T l
+  OB_LAUNCH_CHECK(ctx);
+  append_row_kernel<<<(n + 256) / 256, 256, 0, st>>>(wvec, scal, n, n_pad, Xinv);
+  OB_LAUNCH_CHECK(ctx);
+  // y statistics change with every observation when normalize_y is on: alpha = inv(L)^T inv(L) y_norm in full
+  ystats_kernel<<<1, 1024, 0, st>>>(y_dev, n + 1, n_pad, normalize_y, ynorm, stats);
+  OB_LAUNCH_CHECK(ctx);
+  pg_v_kernel<<<dim3((n_pad * 32 + 255) / 256, 1), 256, 0, st>>>(Xinv, ynorm, n_pad, tvec);
+  OB_LAUNCH_CHECK(ctx);
+  pg_w_kernel<<<dim3((n_pad + 31) / 32, 1), 256, 0, st>>>(Xinv, tvec, n_pad, b_alpha);
+  OB_LAUNCH_CHECK(ctx);
+  append_lml_kernel<<<1, 1024, 0, st>>>(ctx->L_dev, n_pad, n + 1, ynorm, b_alpha, lml_dev);
+  OB_LAUNCH_CHECK(ctx);
+  pack_linv_kernel<<<ctx->num_sms * 8, 256, 0, st>>>(Xinv, n + 1, n_pad, b_linv);
+  OB_LAUNCH_CHECK(ctx);
+  pack_xs_kernel<<<ctx->num_sms * 2, 256, 0, st>>>(Xs, n_pad, D_pad, b_xs);
+  OB_LAUNCH_CHECK(ctx);
+  ob200_fit_header h = ctx->hdr;
+  h.n = n + 1;
+  write_header_kernel<<<1, 128, 0, st>>>(reinterpret_cast<ob200_fit_header*>(blob), h, stats, lml_dev, b_ls, b_ls, D_pad, D_pad, D_pad);
+  OB_LAUNCH_CHECK(ctx);
+  int info = 0;
+  OB_CUDA(ctx, cudaMemcpyAsync(&info, info_dev, sizeof(int), cudaMemcpyDeviceToHost, st));
+  OB_CUDA(ctx, cudaMemcpyAsync(&ctx->hdr, blob, sizeof(ob200_fit_header), cudaMemcpyDeviceToHost, st));
+  OB_CUDA(ctx, cudaStreamSynchronize(st));
+  if (info != 0)
+    OB_FAIL(ctx, OB200_ENOTSPD,
+            "The kernel is not returning a positive definite matrix (pivot %d of %d). Try gradually increasing the 'alpha' "
+            "parameter of your GaussianProcessRegressor estimator.", info, n + 1);
+  ctx->fitted = true;
+  ctx->have_local_fit = true;
   return OB200_OK;
 }
 

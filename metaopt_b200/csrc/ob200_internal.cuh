@@ -83,6 +83,8 @@ struct ob200_ctx {
   int64_t work_cap = 0;
   bool have_local_fit = false;     // work_dev / L_dev hold the factors of the current fit (not an imported one)
   int64_t w_Xs_off = 0, w_y_off = 0;  // offsets (doubles) of X/ls and normalised y inside work_dev
+  int64_t w_t_off = 0, w_stats_off = 0;  // ... of the scratch vector and the statistics block
+  double fit_alpha = 0.0;             // diagonal term of the current local fit (ob200_gp_append re-uses it)
   double* grad_dev = nullptr;      // LML-gradient workspace
   int64_t grad_cap = 0;
   double* pg_dev = nullptr;        // posterior-gradient workspace (ob200_gp_predict_grad_host)

@@ -50,6 +50,8 @@ class Engine:
         self.d_out = 0
         self.n_slots = 0
         self.n = self.D = 0
+        self._fit_host = None   # (kernel key, X) of the last fit from host arrays: lets fit() append one row
+        self.n_appends = 0
         self.use_torch_stream()
 
     def close(self):
@@ -117,10 +119,15 @@ class Engine:
         return out
 
     # ---- fit -------------------------------------------------------------------------------
-    def fit(self, X, y, kind=_lib.KERNEL_MATERN52, amplitude=1.0, length_scale=1.0, alpha=1e-10, normalize_y=False):
+    def fit(self, X, y, kind=_lib.KERNEL_MATERN52, amplitude=1.0, length_scale=1.0, alpha=1e-10, normalize_y=False,
+            incremental=True):
+        """Fit the GP.  With host arrays and `incremental`, a call whose X is the previous call's X plus ONE row, with
+        the same kernel / diagonal term, is served by the O(n^2) append (`ob200_gp_append`) instead of a refit."""
         self.use_torch_stream()
         ls = np.atleast_1d(np.asarray(length_scale, dtype=np.float64)).copy()
         k = Kernel(kind, len(ls), float(amplitude), ls.ctypes.data_as(C.POINTER(C.c_double)))
+        key = None
+        prev, self._fit_host = self._fit_host, None
         if isinstance(X, torch.Tensor):
             X = X.to(self.tdev, torch.float64).contiguous()
             y = torch.as_tensor(y).to(self.tdev, torch.float64).contiguous()
@@ -130,10 +137,24 @@ class Engine:
             X = np.ascontiguousarray(X, dtype=np.float64)
             y = np.ascontiguousarray(y, dtype=np.float64)
             n, D = X.shape
-            rc = self.lib.ob200_gp_fit_host(self.ctx, X.ctypes.data_as(C.c_void_p), y.ctypes.data_as(C.c_void_p), n, D,
-                                            C.byref(k), float(alpha), int(bool(normalize_y)))
+            key = (int(kind), float(amplitude), ls.tobytes(), float(alpha), D)
+            if (incremental and prev is not None and prev[0] == key and prev[1].shape[0] == n - 1
+                    and np.array_equal(prev[1], X[:n - 1])):
+                xy = self.to_device(np.concatenate([X[n - 1], y]))
+                rc = self.lib.ob200_gp_append(self.ctx, _ptr(xy), _ptr(xy[D:]), n, int(bool(normalize_y)))
+                if rc == _lib.ESTATE:  # no free row in the padded factor: refit
+                    rc = None
+                else:
+                    self.n_appends += 1
+            else:
+                rc = None
+            if rc is None:
+                rc = self.lib.ob200_gp_fit_host(self.ctx, X.ctypes.data_as(C.c_void_p), y.ctypes.data_as(C.c_void_p), n, D,
+                                                C.byref(k), float(alpha), int(bool(normalize_y)))
         self._check(rc)
         self.n, self.D = n, D
+        if key is not None:
+            self._fit_host = (key, X.copy())
 
     def ystats(self):
         a, b, c = C.c_double(), C.c_double(), C.c_double()
@@ -190,6 +211,7 @@ class Engine:
         assert blob.dtype == torch.uint8 and blob.is_cuda and blob.is_contiguous()
         self._check(self.lib.ob200_gp_import(self.ctx, _ptr(blob), blob.numel()))
         self.n, self.D = n, D
+        self._fit_host = None
 
     # ---- score -----------------------------------------------------------------------------
     @staticmethod

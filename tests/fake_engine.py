@@ -43,7 +43,7 @@ class OracleEngine:
             raise ValueError("Improbable bounds: a draw was rejected 4 times. Please make interval larger.")
         return _Host(mat)
 
-    def fit(self, X, y, kind=0, amplitude=1.0, length_scale=1.0, alpha=1e-10, normalize_y=False):
+    def fit(self, X, y, kind=0, amplitude=1.0, length_scale=1.0, alpha=1e-10, normalize_y=False, incremental=True):
         self.calls["fit"] += 1
         X = np.asarray(X, float)
         ls = np.broadcast_to(np.asarray(length_scale, float), (X.shape[1],)).copy()

@@ -108,3 +108,78 @@ def test_hyperparameter_optimisation_reaches_sklearn_optimum(engine):
     assert res.n_evals < 200 and 1e-5 <= res.noise <= 1e5
     # the engine is left fitted at the optimum
     np.testing.assert_allclose(engine.lml(), res.lml, rtol=1e-12)
+
+
+@pytest.mark.parametrize("n0,steps,d,kind,normalize_y", [(1, 40, 2, 0, True), (150, 60, 5, 1, False), (500, 30, 20, 0, True)])
+def test_appending_observations_equals_refitting(engine, n0, steps, d, kind, normalize_y):
+    """`ob200_gp_append` (one row of L / inv(L) per new observation) against a from-scratch fit and against sklearn,
+    across a padded-factor boundary (n_pad grows in steps of 192 -> the engine falls back to a refit there)."""
+    X, y = gp_problem(n0 + steps, d, seed=7)
+    ls = np.linspace(0.8, 1.3, d)
+    kw = dict(kind=kind, amplitude=1.2, length_scale=ls, alpha=1e-6, normalize_y=normalize_y)
+    engine.fit(X[:n0], y[:n0], **kw)
+    before = engine.n_appends
+    C = np.random.RandomState(1).rand(300, d)
+    for n in range(n0 + 1, n0 + steps + 1):
+        engine.fit(X[:n], y[:n], **kw)
+    crossed = (n0 + steps - 1) // 192 - (n0 - 1) // 192      # refits forced by a full padded factor
+    assert engine.n_appends - before == steps - crossed
+    L1, a1 = engine.get_factor()
+    out1 = engine.score(torch.as_tensor(C).cuda(), acq_mask=7, y_opt=float(y.min()), dense=True)
+    lml1 = engine.lml()
+    engine.fit(X, y, incremental=False, **kw)
+    L2, a2 = engine.get_factor()
+    out2 = engine.score(torch.as_tensor(C).cuda(), acq_mask=7, y_opt=float(y.min()), dense=True)
+    # the appended rows come from inv(L) k (error ~ cond(L) eps) instead of a substitution: absolute 1e-10 on entries of O(1)
+    np.testing.assert_allclose(L1, L2, rtol=1e-7, atol=1e-10)
+    np.testing.assert_allclose(a1, a2, rtol=1e-6, atol=1e-6 * np.abs(a2).max())
+    np.testing.assert_allclose(lml1, engine.lml(), rtol=1e-9)
+    np.testing.assert_allclose(out1["mu"].cpu().numpy(), out2["mu"].cpu().numpy(), rtol=1e-8, atol=1e-9)
+    np.testing.assert_allclose(out1["sigma"].cpu().numpy(), out2["sigma"].cpu().numpy(), rtol=1e-6, atol=1e-8)
+    ref = ogp.SklearnGP(kind, 1.2, ls, 1e-6, normalize_y).fit(X, y)
+    mu_r, sd_r = ref.predict(C)
+    np.testing.assert_allclose(out1["mu"].cpu().numpy(), mu_r, rtol=1e-6, atol=1e-6 * np.abs(mu_r).max())
+    np.testing.assert_allclose(out1["sigma"].cpu().numpy(), sd_r, rtol=1e-6, atol=1e-6)
+    assert out1["EI"]["index"] == out2["EI"]["index"]
+
+
+def test_append_is_not_used_when_history_or_kernel_changes(engine):
+    X, y = gp_problem(40, 3, seed=2)
+    engine.fit(X[:30], y[:30], alpha=1e-6)
+    k = engine.n_appends
+    engine.fit(X[:31], y[:31], alpha=1e-6)
+    assert engine.n_appends == k + 1
+    engine.fit(X[:32], y[:32], alpha=1e-5)                 # different diagonal term -> refit
+    assert engine.n_appends == k + 1
+    X2 = X.copy()
+    X2[3, 0] += 0.25
+    engine.fit(X2[:33], y[:33], alpha=1e-5)                # an old row changed -> refit
+    assert engine.n_appends == k + 1
+    engine.fit(X2[:34], y[:34], alpha=1e-5)
+    assert engine.n_appends == k + 2
+    engine.fit(X2[:36], y[:36], alpha=1e-5)                # two new rows -> refit
+    assert engine.n_appends == k + 2
+    ref = ogp.SklearnGP(0, 1.0, np.ones(3), 1e-5, False).fit(X2[:36], y[:36])
+    L, al = engine.get_factor()
+    np.testing.assert_allclose(L, ref.L, rtol=1e-9, atol=1e-12)
+
+
+def test_append_reports_a_duplicate_point(engine):
+    """alpha = 0 and a repeated point: the new pivot is 0 up to rounding, so (deterministically per data set) it comes
+    out <= 0 and is reported like numpy.linalg.LinAlgError, or as a tiny positive number; never as NaN."""
+    raised = 0
+    for seed in range(8):
+        X, y = gp_problem(20, 3, seed=seed)
+        engine.fit(X, y, alpha=0.0)
+        k = engine.n_appends
+        try:
+            engine.fit(np.vstack([X, X[4]]), np.append(y, y[4]), alpha=0.0)
+        except _lib.NotPositiveDefinite as exc:
+            assert "positive definite" in str(exc)
+            raised += 1
+        else:
+            assert engine.n_appends == k + 1
+            L, _ = engine.get_factor()
+            assert np.all(np.isfinite(L)) and 0.0 < L[20, 20] < 1e-6
+    assert raised >= 1
+    engine.fit(X, y, alpha=1e-8)
