@@ -757,6 +757,48 @@ __global__ void __launch_bounds__(1024) append_lml_kernel(const double* __restri
   if (threadIdx.x == 0) *lml_out = -0.5 * ra[0] - rb[0] - 0.5 * (double)n * 1.8378770664093453;  // log(2 pi)
 }
 
+// r = y - q ;  a += d   (vectors of n_pad entries)
+__global__ void vec_sub_kernel(const double* __restrict__ y, const double* __restrict__ q, int n, double* __restrict__ r) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) r[i] = y[i] - q[i];
+}
+__global__ void vec_add_kernel(double* __restrict__ a, const double* __restrict__ d, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) a[i] += d[i];
+}
+
+// alpha = K^-1 y from the explicit inverse factor, a = inv(L)^T (inv(L) y), followed by `refine` steps of iterative
+// refinement with the residual taken through the Cholesky factor itself, r = y - L (L^T a), a += inv(L)^T (inv(L) r).
+// The products with inv(L) carry an error ~cond(L) eps; each refinement step multiplies it by that factor again, so
+// two steps reach the accuracy of the substitution-based solve (cho_solve) at a fraction of its serial latency.
+// Scratch: 3 vectors of n_pad doubles.  All reductions have a fixed order.
+int solve_alpha(ob200_ctx* ctx, const double* Xinv, const double* L, const double* y, int n_pad, double* alpha, double* scratch,
+                int refine) {
+  cudaStream_t st = ctx->stream;
+  double *t = scratch, *r = scratch + n_pad, *d = scratch + 2 * (size_t)n_pad;
+  const dim3 gv((n_pad * 32 + 255) / 256, 1), gw((n_pad + 31) / 32, 1);
+  const int gb = (n_pad + 255) / 256;
+  pg_v_kernel<<<gv, 256, 0, st>>>(Xinv, y, n_pad, t);
+  OB_LAUNCH_CHECK(ctx);
+  pg_w_kernel<<<gw, 256, 0, st>>>(Xinv, t, n_pad, alpha);
+  OB_LAUNCH_CHECK(ctx);
+  for (int it = 0; it < refine; ++it) {
+    pg_w_kernel<<<gw, 256, 0, st>>>(L, alpha, n_pad, t);   // t = L^T a
+    OB_LAUNCH_CHECK(ctx);
+    pg_v_kernel<<<gv, 256, 0, st>>>(L, t, n_pad, d);       // d = L t = K a
+    OB_LAUNCH_CHECK(ctx);
+    vec_sub_kernel<<<gb, 256, 0, st>>>(y, d, n_pad, r);
+    OB_LAUNCH_CHECK(ctx);
+    pg_v_kernel<<<gv, 256, 0, st>>>(Xinv, r, n_pad, t);
+    OB_LAUNCH_CHECK(ctx);
+    pg_w_kernel<<<gw, 256, 0, st>>>(Xinv, t, n_pad, d);
+    OB_LAUNCH_CHECK(ctx);
+    vec_add_kernel<<<gb, 256, 0, st>>>(alpha, d, n_pad);
+    OB_LAUNCH_CHECK(ctx);
+  }
+  return OB200_OK;
+}
+
 int launch_gemm(ob200_ctx* ctx, bool trans_b, const gemm_args& g, int batch) {
   dim3 grid(g.N / 64, g.M / 64, batch);
   if (grid.x == 0 || grid.y == 0 || batch == 0) return OB200_OK;
@@ -860,9 +902,11 @@ int ob200_gp_fit(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n
             "The kernel is not returning a positive definite matrix (pivot %d of %d). Try gradually increasing the 'alpha' "
             "parameter of your GaussianProcessRegressor estimator.", info, n);
 
-  // ---- alpha, lml ----------------------------------------------------------------------------
-  chol_solve_kernel<<<1, 1024, 0, st>>>(Lm, n_pad, n, n_pad, ynorm, tvec, b_alpha, lml_dev);
-  OB_LAUNCH_CHECK(ctx);
+  const bool serial_solve = getenv("OB200_SERIAL_SOLVE") != nullptr;  // (testing hook: the substitution-based solve)
+  if (serial_solve) {
+    chol_solve_kernel<<<1, 1024, 0, st>>>(Lm, n_pad, n, n_pad, ynorm, tvec, b_alpha, lml_dev);
+    OB_LAUNCH_CHECK(ctx);
+  }
 
   // ---- inv(L) by recursive doubling ----------------------------------------------------------
   OB_CUDA(ctx, cudaMemsetAsync(Xinv, 0, (size_t)n_pad * n_pad * 8, st));
@@ -902,6 +946,12 @@ int ob200_gp_fit(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n
     u.M = n_pad; u.N = n_pad; u.K = n_pad; u.alpha = 1.0; u.beta = 1.0; u.lower_only = 1; u.tri_k = 1;
     if ((rc = launch_gemm(ctx, false, u, 1))) return rc;
     OB_CUDA(ctx, cudaMemcpyAsync(Xinv, X2, (size_t)n_pad * n_pad * 8, cudaMemcpyDeviceToDevice, st));
+  }
+  // ---- alpha, lml (from the refined inverse factor; T is free again and serves as scratch) -----------------------
+  if (!serial_solve) {
+    if ((rc = solve_alpha(ctx, Xinv, Lm, ynorm, n_pad, b_alpha, T, 2))) return rc;
+    append_lml_kernel<<<1, 1024, 0, st>>>(Lm, n_pad, n, ynorm, b_alpha, lml_dev);
+    OB_LAUNCH_CHECK(ctx);
   }
   pack_linv_kernel<<<ctx->num_sms * 8, 256, 0, st>>>(Xinv, n, n_pad, b_linv);
   OB_LAUNCH_CHECK(ctx);
@@ -1047,13 +1097,13 @@ int ob200_gp_append(ob200_ctx* ctx, const double* x_new_dev, const double* y_dev
   double* b_alpha = reinterpret_cast<double*>(blob + lay.off_alpha);
   double* b_linv = reinterpret_cast<double*>(blob + lay.off_linv);
   double* W = ctx->work_dev;
-  double *Xinv = W, *Xs = W + ctx->w_Xs_off, *ynorm = W + ctx->w_y_off, *tvec = W + ctx->w_t_off, *stats = W + ctx->w_stats_off;
+  double *Xinv = W, *Xs = W + ctx->w_Xs_off, *ynorm = W + ctx->w_y_off, *stats = W + ctx->w_stats_off;
   int* info_dev = reinterpret_cast<int*>(stats + 6);
   double* lml_dev = stats + 4;
   // scratch: k | l | w | (d, 1/d)
-  int rc = ob_reserve(ctx, &ctx->pg_dev, &ctx->pg_cap, (int64_t)3 * n_pad + 8);
+  int rc = ob_reserve(ctx, &ctx->pg_dev, &ctx->pg_cap, (int64_t)6 * n_pad + 8);
   if (rc) return rc;
-  double *kvec = ctx->pg_dev, *lvec = kvec + n_pad, *wvec = lvec + n_pad, *scal = wvec + n_pad;
+  double *kvec = ctx->pg_dev, *lvec = kvec + n_pad, *wvec = lvec + n_pad, *sol = wvec + n_pad, *scal = sol + 3 * (size_t)n_pad;
   ctx->fitted = false;  // a failure below leaves no usable fit
   ctx->have_local_fit = false;
   OB_CUDA(ctx, cudaMemsetAsync(info_dev, 0, sizeof(int), st));
@@ -1071,10 +1121,7 @@ int ob200_gp_append(ob200_ctx* ctx, const double* x_new_dev, const double* y_dev
   // y statistics change with every observation when normalize_y is on: alpha = inv(L)^T inv(L) y_norm in full
   ystats_kernel<<<1, 1024, 0, st>>>(y_dev, n + 1, n_pad, normalize_y, ynorm, stats);
   OB_LAUNCH_CHECK(ctx);
-  pg_v_kernel<<<dim3((n_pad * 32 + 255) / 256, 1), 256, 0, st>>>(Xinv, ynorm, n_pad, tvec);
-  OB_LAUNCH_CHECK(ctx);
-  pg_w_kernel<<<dim3((n_pad + 31) / 32, 1), 256, 0, st>>>(Xinv, tvec, n_pad, b_alpha);
-  OB_LAUNCH_CHECK(ctx);
+  if ((rc = solve_alpha(ctx, Xinv, ctx->L_dev, ynorm, n_pad, b_alpha, sol, 1))) return rc;
   append_lml_kernel<<<1, 1024, 0, st>>>(ctx->L_dev, n_pad, n + 1, ynorm, b_alpha, lml_dev);
   OB_LAUNCH_CHECK(ctx);
   pack_linv_kernel<<<ctx->num_sms * 8, 256, 0, st>>>(Xinv, n + 1, n_pad, b_linv);
