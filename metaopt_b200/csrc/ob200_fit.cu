@@ -217,67 +217,96 @@ __global__ void __launch_bounds__(128) gemm64_kernel(gemm_args g) {
 // ------------------------------------------------------------------------------------------
 // Diagonal block: factor A[kb,kb] (64x64) in shared memory, write L back (upper zeroed), and
 // write inv(L_kk) to Dinv[kb].  info: 0 ok, else 1-based index of the failing pivot.
+// Forward substitution L x = b for ONE right-hand side per thread, L (64 x 64, lower) broadcast from shared memory,
+// x in registers, both loops fully unrolled: the only serial chain is the 4-way split dot product (<= 16 FMAs)
+// plus one multiply by the stored reciprocal of the pivot; no barrier, no division, no shared-memory round trip.
+// LS = row stride of L in doubles (even: the compiler can pair the broadcast loads).
+template <int LS>
+__device__ __forceinline__ void fwd_subst64(const double* __restrict__ L, const double* __restrict__ rdiag, double (&x)[FB]) {
+#pragma unroll
+  for (int j = 0; j < FB; ++j) {
+    double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+#pragma unroll
+    for (int k = 0; k < j; ++k) {
+      const double l = L[j * LS + k];
+      if ((k & 3) == 0) a0 = fma(l, x[k], a0);
+      else if ((k & 3) == 1) a1 = fma(l, x[k], a1);
+      else if ((k & 3) == 2) a2 = fma(l, x[k], a2);
+      else a3 = fma(l, x[k], a3);
+    }
+    x[j] = (x[j] - ((a0 + a1) + (a2 + a3))) * rdiag[j];
+  }
+}
+
+#define FBS (FB + 2)  // shared-memory row stride of the 64 x 64 blocks (even: 16-byte aligned rows)
+
 __global__ void __launch_bounds__(256) chol_diag_kernel(double* __restrict__ A, int ld, int kb, double* __restrict__ Dinv,
                                                         int* __restrict__ info) {
   extern __shared__ double diag_sm[];
-  double (*S)[FB + 1] = reinterpret_cast<double (*)[FB + 1]>(diag_sm);
-  double (*Inv)[FB + 1] = reinterpret_cast<double (*)[FB + 1]>(diag_sm + FB * (FB + 1));
+  double* S = diag_sm;                 // [FB][FBS] the block, then its factor
+  double* Inv = diag_sm + FB * FBS;    // [FB][FBS] inverse of the factor
+  __shared__ double piv_s[FB], rdiag[FB];
   __shared__ int bad;
   double* blk = A + (size_t)kb * FB * ld + (size_t)kb * FB;
   const int tid = threadIdx.x;
-  const int ty = tid >> 4, tx = tid & 15;  // 16 x 16 thread grid over the trailing block
   if (tid == 0) bad = 0;
-  for (int e = tid; e < FB * FB; e += 256) { const int r = e >> 6, c = e & 63; S[r][c] = (c <= r) ? blk[(size_t)r * ld + c] : 0.0; }
+  for (int e = tid; e < FB * FB; e += 256) { const int r = e >> 6, c = e & 63; S[r * FBS + c] = (c <= r) ? blk[(size_t)r * ld + c] : 0.0; }
   __syncthreads();
   if (*info != 0) return;  // an earlier block already failed
-  for (int j = 0; j < FB; ++j) {
-    const double piv = S[j][j];
-    if (!(piv > 0.0)) {  // also catches NaN
-      if (tid == 0) { bad = 1; *info = kb * FB + j + 1; }
-      break;
+  // Left-looking factorisation, one thread per row (first two warps), the own row in registers, fully unrolled:
+  // column j of row i is (a_ij - sum_{k<j} l_ik l_jk) / l_jj with row j read from shared memory (broadcast).
+  // Per column: the split dot product, the pivot through shared memory, one rsqrt, two 64-thread barriers.
+  if (tid < FB) {
+    const int i = tid;
+    double l[FB];
+#pragma unroll
+    for (int k = 0; k < FB; ++k) l[k] = S[i * FBS + k];
+#pragma unroll
+    for (int j = 0; j < FB; ++j) {
+      double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+#pragma unroll
+      for (int k = 0; k < j; ++k) {
+        const double r = S[j * FBS + k];
+        if ((k & 3) == 0) a0 = fma(l[k], r, a0);
+        else if ((k & 3) == 1) a1 = fma(l[k], r, a1);
+        else if ((k & 3) == 2) a2 = fma(l[k], r, a2);
+        else a3 = fma(l[k], r, a3);
+      }
+      const double v = l[j] - ((a0 + a1) + (a2 + a3));
+      if (i == j) piv_s[j] = v;
+      asm volatile("bar.sync 1, 64;" ::: "memory");
+      const double piv = piv_s[j];
+      if (!(piv > 0.0)) {  // also catches NaN (uniform: everybody reads the same pivot)
+        if (tid == 0) { bad = 1; *info = kb * FB + j + 1; }
+        break;
+      }
+      const double d = sqrt(piv), rd = 1.0 / d;
+      l[j] = (i == j) ? d : v * rd;
+      if (i >= j) S[i * FBS + j] = l[j];
+      if (i == j) rdiag[j] = rd;
+      asm volatile("bar.sync 1, 64;" ::: "memory");  // column j is final before row j + 1 is read by everybody
     }
-    const double d = sqrt(piv);
-    __syncthreads();  // everybody has read the pivot
-    // scale column j (one division per row), then the rank-1 update of the trailing lower triangle
-    if (tid == 0) S[j][j] = d;
-    for (int i = j + 1 + tid; i < FB; i += 256) S[i][j] = S[i][j] / d;
-    __syncthreads();
-    for (int i = j + 1 + ty; i < FB; i += 16) {
-      const double li = S[i][j];
-      for (int c = j + 1 + tx; c <= i; c += 16) S[i][c] = fma(-li, S[c][j], S[i][c]);
-    }
-    __syncthreads();
   }
   __syncthreads();
   if (bad) return;
-  // inverse of the lower-triangular block: column c by forward substitution, 4 lanes per column
-  // splitting the inner sum (fixed split + shuffle tree: deterministic)
-  {
-    const int c = tid >> 2, sub = tid & 3;
-    const int c_first = (tid >> 5) * 8;  // first column of this warp: uniform trip count for the shuffles
-    if (sub == 0) {
-      for (int i = 0; i < c; ++i) Inv[i][c] = 0.0;
-      Inv[c][c] = 1.0 / S[c][c];
-    }
-    __syncwarp();
-    for (int i = c_first + 1; i < FB; ++i) {
-      double acc = 0.0;
-      if (i > c)
-        for (int k = c + sub; k < i; k += 4) acc = fma(S[i][k], Inv[k][c], acc);
-      acc += __shfl_xor_sync(0xffffffffu, acc, 1);
-      acc += __shfl_xor_sync(0xffffffffu, acc, 2);
-      if (sub == 0 && i > c) Inv[i][c] = -acc / S[i][i];
-      __syncwarp();
-    }
+  // inverse of the factor: thread c solves L x = e_c (rows < c come out as exact zeros)
+  if (tid < FB) {
+    double x[FB];
+#pragma unroll
+    for (int k = 0; k < FB; ++k) x[k] = (k == tid) ? 1.0 : 0.0;
+    fwd_subst64<FBS>(S, rdiag, x);
+#pragma unroll
+    for (int k = 0; k < FB; ++k) Inv[k * FBS + tid] = x[k];
   }
   __syncthreads();
   double* dinv = Dinv + (size_t)kb * FB * FB;
   for (int e = tid; e < FB * FB; e += 256) {
     const int r = e >> 6, c = e & 63;
-    blk[(size_t)r * ld + c] = S[r][c];
-    dinv[e] = Inv[r][c];
+    blk[(size_t)r * ld + c] = S[r * FBS + c];
+    dinv[e] = Inv[r * FBS + c];
   }
 }
+
 
 // zero the strict upper triangle tiles left over from the Gram/SYRK (they hold garbage-free zeros
 // already from gram_kernel; SYRK only touches lower tiles) -- nothing to do.  X (inverse) init:
@@ -292,36 +321,40 @@ __global__ void trtri_init_kernel(double* __restrict__ X, int ld, const double* 
 // Panel of the blocked Cholesky: P = A21 * L11^-T by forward substitution, four lanes per row, 64 rows per
 // CTA.  (Multiplying by an explicitly inverted L11 loses cond(L11) digits: 7e-6 instead of 3e-8 in the
 // posterior variance at cond(K) = 1e12, see tools/illcond_probe.py.)
-__global__ void __launch_bounds__(256) chol_panel_trsm_kernel(double* __restrict__ A, int ld, int kb) {
+__global__ void __launch_bounds__(256) chol_panel_trsm_kernel(double* __restrict__ A, int ld, int kb, const double* __restrict__ Dinv) {
   extern __shared__ double psm[];
-  double (*Lk)[FB + 1] = reinterpret_cast<double (*)[FB + 1]>(psm);                 // L11[j][k]
-  double (*Xt)[FB + 1] = reinterpret_cast<double (*)[FB + 1]>(psm + FB * (FB + 1));  // row tile, transposed: Xt[k][row]
-  const int tid = threadIdx.x, row = tid >> 2, sub = tid & 3;  // 4 lanes per row split the inner sum
+  double* Lk = psm;                    // [FB][FBS] L11
+  double* Xt = psm + FB * FBS;         // [FB][FB + 1] row tile, transposed: Xt[k][row]
+  __shared__ double rdiag[FB];
+  const int tid = threadIdx.x;
   const size_t r0 = (size_t)(kb + 1 + blockIdx.x) * FB;
   const double* Ld = A + (size_t)kb * FB * ld + (size_t)kb * FB;
   double* At = A + r0 * ld + (size_t)kb * FB;
   for (int e = tid; e < FB * FB; e += 256) {
     const int r = e >> 6, c = e & 63;
-    Lk[r][c] = Ld[(size_t)r * ld + c];
-    Xt[c][r] = At[(size_t)r * ld + c];
+    Lk[r * FBS + c] = Ld[(size_t)r * ld + c];
+    Xt[c * (FB + 1) + r] = At[(size_t)r * ld + c];
   }
+  if (tid < FB) rdiag[tid] = Dinv[(size_t)kb * FB * FB + tid * FB + tid];  // 1 / l_jj from the diagonal-block kernel
   __syncthreads();
-  for (int j = 0; j < FB; ++j) {
-    double acc = 0.0;
-    for (int k = sub; k < j; k += 4) acc = fma(Xt[k][row], Lk[j][k], acc);
-    acc += __shfl_xor_sync(0xffffffffu, acc, 1);
-    acc += __shfl_xor_sync(0xffffffffu, acc, 2);
-    if (sub == 0) Xt[j][row] = (Xt[j][row] - acc) / Lk[j][j];
-    __syncwarp();
+  // x L11^T = a, i.e. L11 x^T = a^T: one thread per row of the panel, true forward substitution (the explicit
+  // inverse of L11 would lose digits when K is ill-conditioned), see fwd_subst64
+  if (tid < FB) {
+    double x[FB];
+#pragma unroll
+    for (int k = 0; k < FB; ++k) x[k] = Xt[k * (FB + 1) + tid];
+    fwd_subst64<FBS>(Lk, rdiag, x);
+#pragma unroll
+    for (int k = 0; k < FB; ++k) Xt[k * (FB + 1) + tid] = x[k];
   }
   __syncthreads();
   for (int e = tid; e < FB * FB; e += 256) {
     const int r = e >> 6, c = e & 63;
-    At[(size_t)r * ld + c] = Xt[c][r];
+    At[(size_t)r * ld + c] = Xt[c * (FB + 1) + r];
   }
 }
 
-// R <- I - R on the lower triangle, 0 above it (32x32 tiles)
+
 __global__ void __launch_bounds__(256) eye_minus_lower_kernel(double* __restrict__ R, int n_pad) {
   const int ti = blockIdx.y, tj = blockIdx.x;
   for (int e = threadIdx.x; e < 1024; e += 256) {
@@ -863,6 +896,12 @@ int ob200_gp_fit(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n
   OB_CUDA(ctx, cudaMemcpyAsync(ls_dev, kernel->length_scale_host, (size_t)kernel->n_length_scale * 8, cudaMemcpyHostToDevice, st));
   OB_CUDA(ctx, cudaMemsetAsync(stats, 0, 8 * sizeof(double), st));
 
+  // OB200_FIT_TIMING=1: CUDA-event time of each phase on stderr (tuning aid)
+  const bool timing = getenv("OB200_FIT_TIMING") != nullptr;
+  cudaEvent_t tev[9];
+  int n_tev = 0;
+  auto mark = [&]() { if (timing && n_tev < 8) { cudaEventCreate(&tev[n_tev]); cudaEventRecord(tev[n_tev++], st); } };
+  mark();
   ystats_kernel<<<1, 1024, 0, st>>>(y_dev, n, n_pad, normalize_y, ynorm, stats);
   OB_LAUNCH_CHECK(ctx);
   scale_x_kernel<<<(n_pad + 127) / 128, 128, 0, st>>>(X_dev, n, D, n_pad, D_pad, ls_dev, kernel->n_length_scale, Xs, b_xx);
@@ -874,25 +913,32 @@ int ob200_gp_fit(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n
     gram_kernel<<<grid, 256, smem, st>>>(Xs, n, n_pad, D_pad, kernel->kind, kernel->amplitude, alpha, ctx->L_dev);
     OB_LAUNCH_CHECK(ctx);
   }
+  mark();
   // ---- right-looking blocked Cholesky ----------------------------------------------------
   double* Lm = ctx->L_dev;
-  const size_t diag_smem = (size_t)2 * FB * (FB + 1) * sizeof(double);
+  const size_t diag_smem = (size_t)2 * FB * (FB + 2) * sizeof(double);
   const size_t panel_smem = diag_smem;
   OB_CUDA(ctx, cudaFuncSetAttribute(chol_panel_trsm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)panel_smem));
   OB_CUDA(ctx, cudaFuncSetAttribute(chol_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)diag_smem));
   for (int kb = 0; kb < nb; ++kb) {
+#ifndef FIT_DEBUG_SKIP_DIAG
     chol_diag_kernel<<<1, 256, diag_smem, st>>>(Lm, n_pad, kb, Dinv, info_dev);
     OB_LAUNCH_CHECK(ctx);
+#endif
     const int rem = n_pad - (kb + 1) * FB;
     if (rem <= 0) break;
-    chol_panel_trsm_kernel<<<rem / FB, 256, panel_smem, st>>>(Lm, n_pad, kb);
+#ifndef FIT_DEBUG_SKIP_PANEL
+    chol_panel_trsm_kernel<<<rem / FB, 256, panel_smem, st>>>(Lm, n_pad, kb, Dinv);
     OB_LAUNCH_CHECK(ctx);
+#endif
     const double* panel = Lm + (size_t)(kb + 1) * FB * n_pad + (size_t)kb * FB;
     gemm_args s{};
     s.A = panel; s.lda = n_pad; s.B = panel; s.ldb = n_pad;
     s.C = Lm + (size_t)(kb + 1) * FB * n_pad + (size_t)(kb + 1) * FB; s.ldc = n_pad;
     s.M = rem; s.N = rem; s.K = FB; s.alpha = -1.0; s.beta = 1.0; s.lower_only = 1;
+#ifndef FIT_DEBUG_SKIP_SYRK
     if ((rc = launch_gemm(ctx, true, s, 1))) return rc;
+#endif
   }
   int info = 0;
   OB_CUDA(ctx, cudaMemcpyAsync(&info, info_dev, sizeof(int), cudaMemcpyDeviceToHost, st));
@@ -908,6 +954,7 @@ int ob200_gp_fit(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n
     OB_LAUNCH_CHECK(ctx);
   }
 
+  mark();
   // ---- inv(L) by recursive doubling ----------------------------------------------------------
   OB_CUDA(ctx, cudaMemsetAsync(Xinv, 0, (size_t)n_pad * n_pad * 8, st));
   trtri_init_kernel<<<nb, 256, 0, st>>>(Xinv, n_pad, Dinv);
@@ -930,6 +977,7 @@ int ob200_gp_fit(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n
     g2.M = s; g2.N = s; g2.K = s; g2.m_last = c_last; g2.k_eq_m = 1; g2.alpha = -1.0; g2.beta = 0.0;
     if ((rc = launch_gemm(ctx, false, g2, pairs))) return rc;
   }
+  mark();
   // One Newton-Schulz step X <- X + X (I - L X): the recursive-doubling products compound rounding errors
   // level by level (residual ~1e-6 at cond(K) = 1e12); the residual I - L X is computed to cond(L) eps, so one
   // step brings inv(L) to the accuracy of a backward-stable triangular solve (tools/illcond_probe.py).
@@ -947,6 +995,7 @@ int ob200_gp_fit(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n
     if ((rc = launch_gemm(ctx, false, u, 1))) return rc;
     OB_CUDA(ctx, cudaMemcpyAsync(Xinv, X2, (size_t)n_pad * n_pad * 8, cudaMemcpyDeviceToDevice, st));
   }
+  mark();
   // ---- alpha, lml (from the refined inverse factor; T is free again and serves as scratch) -----------------------
   if (!serial_solve) {
     if ((rc = solve_alpha(ctx, Xinv, Lm, ynorm, n_pad, b_alpha, T, 2))) return rc;
@@ -965,6 +1014,17 @@ int ob200_gp_fit(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n
   OB_LAUNCH_CHECK(ctx);
   OB_CUDA(ctx, cudaMemcpyAsync(&ctx->hdr, blob, sizeof(ob200_fit_header), cudaMemcpyDeviceToHost, st));
   OB_CUDA(ctx, cudaStreamSynchronize(st));
+  if (timing) {
+    static const char* names[] = {"gram", "cholesky", "trtri", "newton-schulz", "alpha+lml", "pack"};
+    float ms = 0.f;
+    fprintf(stderr, "ob200_gp_fit n=%d:", n);
+    cudaEventCreate(&tev[n_tev]);
+    cudaEventRecord(tev[n_tev], st);
+    cudaEventSynchronize(tev[n_tev]);
+    for (int i = 0; i < n_tev; ++i) { cudaEventElapsedTime(&ms, tev[i], tev[i + 1]); fprintf(stderr, " %s %.3f ms", names[i], ms); }
+    fprintf(stderr, "\n");
+    for (int i = 0; i <= n_tev; ++i) cudaEventDestroy(tev[i]);
+  }
   ctx->blob_bytes = lay.total;
   ctx->fitted = true;
   ctx->have_local_fit = true;

@@ -133,7 +133,7 @@ def test_appending_observations_equals_refitting(engine, n0, steps, d, kind, nor
     # the appended rows come from inv(L) k (error ~ cond(L) eps) instead of a substitution: absolute 1e-10 on entries of O(1)
     np.testing.assert_allclose(L1, L2, rtol=1e-7, atol=1e-10)
     np.testing.assert_allclose(a1, a2, rtol=1e-6, atol=1e-6 * np.abs(a2).max())
-    np.testing.assert_allclose(lml1, engine.lml(), rtol=1e-9)
+    np.testing.assert_allclose(lml1, engine.lml(), rtol=1e-7)  # y^T alpha inherits alpha's conditioning (RBF case: cond ~1e9)
     np.testing.assert_allclose(out1["mu"].cpu().numpy(), out2["mu"].cpu().numpy(), rtol=1e-8, atol=1e-9)
     np.testing.assert_allclose(out1["sigma"].cpu().numpy(), out2["sigma"].cpu().numpy(), rtol=1e-6, atol=1e-8)
     ref = ogp.SklearnGP(kind, 1.2, ls, 1e-6, normalize_y).fit(X, y)

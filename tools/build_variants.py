@@ -16,6 +16,10 @@ VARIANTS = {
     "skip1": ["SC_DEBUG_SKIP_PHASE1"],
     # clock64 marks around the parts of a tile (tools/prof_phases.py reads them back)
     "prof": ["SC_PROFILE_CYCLES"],
+    # fit: drop one of the three kernels of a Cholesky iteration (wrong results) to see what each costs in place
+    "fit_nodiag": ["FIT_DEBUG_SKIP_DIAG"],
+    "fit_nopanel": ["FIT_DEBUG_SKIP_PANEL"],
+    "fit_nosyrk": ["FIT_DEBUG_SKIP_SYRK"],
     # sampler with one half switched off (wrong output): which half bounds it?
     "st_db4": ["ST_NBUF=2", "ST_MIN_CTAS=4"],
     "st_db4w8": ["ST_NBUF=2", "ST_MIN_CTAS=2", "ST_THREADS=256", "ST_ROWS=64"],
