@@ -21,7 +21,7 @@
 
 #define FB 64            // block size of the fit algorithms
 #define GEMM_BK 16
-#define OB200_FIT_MAGIC 0x0b200f17
+#define OB200_FIT_MAGIC 0x0b200f18
 
 namespace {
 
@@ -1009,6 +1009,7 @@ int ob200_gp_fit(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n
   ob200_fit_header h{};
   h.magic = OB200_FIT_MAGIC; h.n = n; h.D = D; h.n_pad = n_pad; h.D_pad = D_pad; h.kernel_kind = kernel->kind;
   h.amplitude = kernel->amplitude;
+  h.diag = alpha;
   write_header_kernel<<<1, 128, 0, st>>>(reinterpret_cast<ob200_fit_header*>(blob), h, stats, lml_dev, b_ls, ls_dev,
                                          kernel->n_length_scale, D, D_pad);
   OB_LAUNCH_CHECK(ctx);

@@ -51,6 +51,7 @@
 struct ob200_fit_header {   // first bytes of the exported fit blob
   int32_t magic, n, D, n_pad, D_pad, kernel_kind;
   double amplitude, y_mean, y_std, y_min, lml;
+  double diag;   // alpha + noise: the term added to the diagonal of K (bounds the posterior variance from one observation)
 };
 
 struct ob200_ctx {

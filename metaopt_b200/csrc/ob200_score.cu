@@ -51,7 +51,8 @@ struct score_args {
   long long n_tiles;
   int accumulate;    // 1: fold the partials already stored (multi-chunk calls)
   int p1_stages;     // phase-1 ring depth (1..P1_STAGES, the deepest that fits in shared memory)
-  int mean_only;     // 1: phase 1 only, write mu_out (pruned scoring, pass 1)
+  int mean_only;     // 1: phase 1 only, write mu_out (pruned scoring, pass 1) and, if sigma_out is set, an upper bound of sigma
+  double diag;       // term added to the diagonal of K (alpha + noise)
   const long long* index_map;  // optional: global index of row r (gathered survivors); else first_index + r
 };
 
@@ -257,9 +258,9 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
     SC_PROF_MARK(0)  // candidate staging
     // ---- phase 1: k* = kernel(cand, X) and mu partials; warp w owns obs8 block w of each chunk
     {
-      double ccr[SC_NCF], mup[SC_NCF];
+      double ccr[SC_NCF], mup[SC_NCF], kmx[SC_NCF];  // kmx: largest kernel value against a real observation (mean-only pass)
 #pragma unroll
-      for (int cf = 0; cf < SC_NCF; ++cf) { ccr[cf] = cc[cf * 8 + g]; mup[cf] = 0.0; }
+      for (int cf = 0; cf < SC_NCF; ++cf) { ccr[cf] = cc[cf * 8 + g]; mup[cf] = 0.0; kmx[cf] = 0.0; }
       for (int c = 0; c < n_chunks1; ++c, ++it1) {
         const int s = it1 % P1S;
         const uint32_t ph = (it1 / P1S) & 1;
@@ -291,6 +292,7 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
           mup[cf] = fma(kv.x, al0, mup[cf]);
           mup[cf] = fma(kv.y, al1, mup[cf]);
           if (!a.mean_only) dst[cf * 32] = kv;
+          else kmx[cf] = fmax(kmx[cf], fmax(ob * 8 + 2 * q < a.n ? kv.x : 0.0, ob * 8 + 2 * q + 1 < a.n ? kv.y : 0.0));
         }
       }
       // mu: reduce over q (4 lanes) then across warps through shared memory
@@ -300,6 +302,14 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
         v += __shfl_xor_sync(0xffffffffu, v, 1);
         v += __shfl_xor_sync(0xffffffffu, v, 2);
         if (q == 0) mured[warp * SC_BN + cf * 8 + g] = v;
+#if SC_WN == 1
+        if (a.mean_only) {  // ssred is idle in this mode: it carries the per-warp maxima to phase 3
+          double kx = kmx[cf];
+          kx = fmax(kx, __shfl_xor_sync(0xffffffffu, kx, 1));
+          kx = fmax(kx, __shfl_xor_sync(0xffffffffu, kx, 2));
+          if (q == 0) ssred[warp * SC_BN + cf * 8 + g] = kx;
+        }
+#endif
       }
     }
     SC_PROF_MARK(1)       // phase 1 loop of this warp
@@ -409,6 +419,7 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
     }
     SC_PROF_MARK(3)  // phase 2 (incl. pipeline fill)
     // reduce over the 8 row lanes (g), then across the SC_WM row warps via shared memory
+    if (!a.mean_only)
 #pragma unroll
     for (int j = 0; j < SC_FN; ++j)
 #pragma unroll
@@ -433,6 +444,19 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
       const long long row = row0 + tid;
       if (a.mean_only) {
         a.mu_out[row] = mu;
+        if (a.sigma_out) {
+          // Conditioning on ONE observation j already gives var <= amp - k_j^2 / (amp + diag), and more observations
+          // only lower it: the nearest observation bounds sigma without any triangular product.  The slack covers the
+          // rounding of the full computation it is compared with (amp - sum v^2 cancels ~cond(K) eps).
+          double var_ub = a.amplitude;
+#if SC_WN == 1
+          double kx = 0.0;
+#pragma unroll
+          for (int w = 0; w < SC_WM; ++w) kx = fmax(kx, ssred[w * SC_BN + tid]);
+          var_ub = fmin(fmax(a.amplitude - kx * kx / (a.amplitude + a.diag), 0.0) + 1e-6 * a.amplitude, a.amplitude);
+#endif
+          a.sigma_out[row] = a.y_std * sqrt(var_ub);
+        }
       } else {
         double var = a.amplitude - s2;
         if (var < 0.0) var = 0.0;
@@ -601,6 +625,7 @@ int score_launch(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M,
   a.accumulate = accumulate;
   a.p1_stages = p1_stages;
   a.mean_only = mean_only;
+  a.diag = h.diag;
   a.index_map = index_map;
   OB_CUDA(ctx, cudaFuncSetAttribute(score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   // k* slices -> persisting L2 lines for this launch (the window is a launch-time stream attribute)
@@ -787,9 +812,10 @@ int ob200_acq_argmax(ob200_ctx* ctx, const double* mu_dev, const double* sigma_d
 
 // ---------------------------------------------------------------------------------------------
 // Exact pruned scoring.  EI, PI (for y_opt - xi - mu <= 0) and -LCB are increasing in
-// sigma, and sigma^2 <= amplitude * y_std^2 (the prior variance), so U(mu, sigma_max) is an upper
-// bound of the utility that needs only the O(nD) mean.  Pass 1 computes mu for every candidate
-// (phase 1 of the score kernel), a first batch with the largest bounds is scored in full to get an
+// sigma, and sigma^2 <= (amplitude - k_max^2 / (amplitude + diag)) * y_std^2, the variance left by the nearest
+// observation alone (k_max = largest kernel value of the candidate against the observations; at worst the prior
+// variance), so U(mu, sigma_ub) is an upper bound of the utility that needs only the O(nD) cross-kernel.  Pass 1
+// computes mu and sigma_ub for every candidate (phase 1 of the score kernel), a first batch with the largest bounds is scored in full to get an
 // incumbent, and only candidates whose bound reaches the incumbent are scored after that.  Every
 // candidate left out has utility <= bound < incumbent <= maximum, so the argmax (ties included) and
 // the winner's values are bit-identical to the dense call.
@@ -804,12 +830,13 @@ __device__ __forceinline__ double upper_bound_utility(int acq, double mu, double
   return u[acq];
 }
 
-__global__ void __launch_bounds__(256) ub_kernel(const double* __restrict__ mu, long long M, int acq, double sigma_max, double y_opt,
-                                                 double xi, double kappa, double* __restrict__ ub, double* __restrict__ blk_minmax) {
+// ub[i] holds the sigma bound of candidate i on entry and the utility bound on exit
+__global__ void __launch_bounds__(256) ub_kernel(const double* __restrict__ mu, long long M, int acq, double y_opt, double xi,
+                                                 double kappa, double* __restrict__ ub, double* __restrict__ blk_minmax) {
   __shared__ double smin[256], smax[256];
   double lo = INFINITY, hi = -INFINITY;
   for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < M; i += (long long)gridDim.x * 256) {
-    const double v = upper_bound_utility(acq, mu[i], sigma_max, y_opt, xi, kappa);
+    const double v = upper_bound_utility(acq, mu[i], ub[i], y_opt, xi, kappa);
     ub[i] = v;
     if (v == v) { lo = fmin(lo, v); hi = fmax(hi, v); }
   }
@@ -915,9 +942,9 @@ extern "C" int ob200_score_pruned(ob200_ctx* ctx, const double* cand_dev, int64_
 
   // pass 1: posterior mean of every candidate
   int grid = 0;
-  if ((rc = score_launch(ctx, cand_dev, ldc, M, first_index, mask, y_opt, xi, kappa, mu, nullptr, nullptr, 0, &grid, 1, nullptr))) return rc;
-  const double sigma_max = sqrt(ctx->hdr.amplitude) * ctx->hdr.y_std;
-  ub_kernel<<<nblk, 256, 0, st>>>(mu, M, acq, sigma_max, y_opt, xi, kappa, ub, blk);
+  // ... and an upper bound of its sigma from the nearest observation (written to `ub`, turned into the utility bound in place)
+  if ((rc = score_launch(ctx, cand_dev, ldc, M, first_index, mask, y_opt, xi, kappa, mu, ub, nullptr, 0, &grid, 1, nullptr))) return rc;
+  ub_kernel<<<nblk, 256, 0, st>>>(mu, M, acq, y_opt, xi, kappa, ub, blk);
   OB_LAUNCH_CHECK(ctx);
   std::vector<double> h_blk((size_t)nblk * 2);
   OB_CUDA(ctx, cudaMemcpyAsync(h_blk.data(), blk, (size_t)nblk * 16, cudaMemcpyDeviceToHost, st));
