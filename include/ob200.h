@@ -188,12 +188,18 @@ int ob200_score_async(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64
 /* Exact pruned form of ob200_score for ONE acquisition (acq = OB200_ACQ_*): same winner, bit for bit,
  * as the dense call (same reference functions: sklearn:_gpr.py:444-500 + skopt gaussian_ei/pi/lcb +
  * np.argmin), but the O(n^2) variance is computed only for candidates whose utility upper bound
- * U(mu, sigma_max) -- from the O(nD) mean alone, sigma_max^2 = amplitude*y_std^2 -- reaches the best
- * utility found so far.  best_host[0] receives the winner; n_scored_host (may be NULL) the number of
+ * U(mu, sigma_ub) -- from the O(nD) cross-kernel alone: the mean, and the variance the nearest observation
+ * leaves, sigma_ub^2 = (amplitude - k_max^2 / (amplitude + diag)) * y_std^2 -- reaches the best utility found so far.  best_host[0] receives the winner; n_scored_host (may be NULL) the number of
  * candidates that went through the full posterior.  Synchronous. */
 int ob200_score_pruned(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M, uint64_t seed,
                        uint64_t first_index, int acq, double y_opt, double xi, double kappa,
                        ob200_best* best_host, int64_t* n_scored_host);
+/* The same for several acquisitions at once (acq_mask bits 1 << OB200_ACQ_*; the gp_hedge portfolio): the mean-only
+ * pass is shared, the selection runs per acquisition.  best_host [3] and n_scored_host [3] (may be NULL) are indexed
+ * by OB200_ACQ_*; entries outside the mask are zeroed. */
+int ob200_score_pruned_multi(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M, uint64_t seed,
+                             uint64_t first_index, int acq_mask, double y_opt, double xi, double kappa,
+                             ob200_best* best_host, int64_t* n_scored_host);
 
 /* a16-a17 alone: acquisition + first-occurrence argmax over given posterior arrays
  * (skopt.acquisition.gaussian_ei/pi/lcb + numpy.argmin).  mu_dev, sigma_dev [M]. */

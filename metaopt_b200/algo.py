@@ -291,14 +291,11 @@ class BayesianOptimizer(BaseAlgorithm):
     def _score_range(self, eng, first, count, y_opt):
         """Winner(s) {acq name: record} of the candidates [first, first + count) of the stream."""
         hedge = self.acq_func == "gp_hedge"
-        if self.prune:
-            res = {}
-            for name in (("EI", "LCB", "PI") if hedge else (self.acq_func,)):  # same winners as one dense pass
-                one, _ = eng.score_pruned(None, M=count, seed=self._seed, first_index=first, acq=name,
-                                          y_opt=y_opt, xi=float(self.xi), kappa=float(self.kappa))
-                res.update(one)
-            return res
         mask = 7 if hedge else (1 << _ACQ[self.acq_func])
+        if self.prune:  # same winners as one dense pass; the portfolio shares the mean-only pass
+            res, _ = eng.score_pruned_multi(None, M=count, seed=self._seed, first_index=first, acq_mask=mask,
+                                            y_opt=y_opt, xi=float(self.xi), kappa=float(self.kappa))
+            return res
         return eng.score(None, M=count, seed=self._seed, first_index=first, acq_mask=mask, y_opt=y_opt,
                          xi=float(self.xi), kappa=float(self.kappa))
 

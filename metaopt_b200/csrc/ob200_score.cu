@@ -830,13 +830,13 @@ __device__ __forceinline__ double upper_bound_utility(int acq, double mu, double
   return u[acq];
 }
 
-// ub[i] holds the sigma bound of candidate i on entry and the utility bound on exit
-__global__ void __launch_bounds__(256) ub_kernel(const double* __restrict__ mu, long long M, int acq, double y_opt, double xi,
-                                                 double kappa, double* __restrict__ ub, double* __restrict__ blk_minmax) {
+__global__ void __launch_bounds__(256) ub_kernel(const double* __restrict__ mu, const double* __restrict__ sig, long long M, int acq,
+                                                 double y_opt, double xi, double kappa, double* __restrict__ ub,
+                                                 double* __restrict__ blk_minmax) {
   __shared__ double smin[256], smax[256];
   double lo = INFINITY, hi = -INFINITY;
   for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < M; i += (long long)gridDim.x * 256) {
-    const double v = upper_bound_utility(acq, mu[i], ub[i], y_opt, xi, kappa);
+    const double v = upper_bound_utility(acq, mu[i], sig[i], y_opt, xi, kappa);
     ub[i] = v;
     if (v == v) { lo = fmin(lo, v); hi = fmax(hi, v); }
   }
@@ -898,53 +898,22 @@ __global__ void __launch_bounds__(256) globalise_kernel(long long* __restrict__ 
 
 }  // namespace
 
-extern "C" int ob200_score_pruned(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M, uint64_t seed, uint64_t first_index,
-                                  int acq, double y_opt, double xi, double kappa, ob200_best* best_host, int64_t* n_scored_host) {
-  if (!ctx) return OB200_EINVAL;
-  if (acq < 0 || acq > 2) OB_FAIL(ctx, OB200_EINVAL, "acq must be OB200_ACQ_EI, _PI or _LCB");
-  const int mask = 1 << acq;
-  int rc = check_score_args(ctx, M, mask, best_host);
-  if (rc) return rc;
-  OB_CUDA(ctx, cudaSetDevice(ctx->device));
-  const int D = ctx->hdr.D;
+namespace {
+
+// Selection for ONE acquisition on top of the shared mean-only pass (mu, sigma bound per candidate): utility bounds,
+// batch A (largest bounds) -> incumbent, batch B (bounds that still reach it).
+int prune_select(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M, uint64_t first_index, int acq, double y_opt,
+                 double xi, double kappa, const double* mu, const double* sig, double* ub, ob200_best* best_out,
+                 int64_t* n_scored_out) {
+  const int mask = 1 << acq, D = ctx->hdr.D;
   const int64_t batch = (int64_t)ctx->num_sms * SC_BN;  // one tile per CTA
   cudaStream_t st = ctx->stream;
-  // small problems, or candidate sets that do not fit in one resident buffer: dense path
-  const bool too_big = !cand_dev && (M * (int64_t)D * 8 > ((int64_t)1 << 31));
-  if (M <= 4 * batch || too_big) {
-    ob200_best tmp[3];
-    rc = ob200_score(ctx, cand_dev, ldc, M, seed, first_index, mask, y_opt, xi, kappa, tmp, nullptr, nullptr, nullptr);
-    if (rc) return rc;
-    best_host[0] = tmp[acq];
-    if (n_scored_host) *n_scored_host = M;
-    return OB200_OK;
-  }
-  if (cand_dev) {
-    if (ldc < D) OB_FAIL(ctx, OB200_EINVAL, "ldc=%lld < D=%d", (long long)ldc, D);
-  } else {
-    if (ctx->n_slots <= 0) OB_FAIL(ctx, OB200_ESTATE, "cand_dev is NULL and no space was set");
-    if (ctx->d_out != D) OB_FAIL(ctx, OB200_EINVAL, "space width %d != fitted D %d", ctx->d_out, D);
-    if ((rc = ob_reserve(ctx, &ctx->cand_tmp, &ctx->cand_cap, M * D))) return rc;
-    if ((rc = ob200_sample_launch(ctx, seed, first_index, M, 1, ctx->cand_tmp, D, nullptr))) return rc;
-    cand_dev = ctx->cand_tmp;
-    ldc = D;
-  }
-  if ((rc = ob_reserve(ctx, &ctx->ub_dev, &ctx->ub_cap, 2 * M))) return rc;
-  if ((rc = ob_reserve(ctx, &ctx->idx_dev, &ctx->idx_cap, M))) return rc;
   const int nblk = ctx->num_sms * 8;
-  const int64_t small_bytes = (int64_t)nblk * 16 + PR_BINS * 4 + 64;
-  if ((rc = ob_reserve(ctx, &ctx->prune_small_dev, &ctx->prune_small_cap, small_bytes))) return rc;
-  double* mu = ctx->ub_dev;
-  double* ub = ctx->ub_dev + M;
   double* blk = reinterpret_cast<double*>(ctx->prune_small_dev);
   int* hist = reinterpret_cast<int*>(ctx->prune_small_dev + (size_t)nblk * 16);
   unsigned long long* counter = reinterpret_cast<unsigned long long*>(ctx->prune_small_dev + (size_t)nblk * 16 + PR_BINS * 4);
-
-  // pass 1: posterior mean of every candidate
-  int grid = 0;
-  // ... and an upper bound of its sigma from the nearest observation (written to `ub`, turned into the utility bound in place)
-  if ((rc = score_launch(ctx, cand_dev, ldc, M, first_index, mask, y_opt, xi, kappa, mu, ub, nullptr, 0, &grid, 1, nullptr))) return rc;
-  ub_kernel<<<nblk, 256, 0, st>>>(mu, M, acq, y_opt, xi, kappa, ub, blk);
+  int rc;
+  ub_kernel<<<nblk, 256, 0, st>>>(mu, sig, M, acq, y_opt, xi, kappa, ub, blk);
   OB_LAUNCH_CHECK(ctx);
   std::vector<double> h_blk((size_t)nblk * 2);
   OB_CUDA(ctx, cudaMemcpyAsync(h_blk.data(), blk, (size_t)nblk * 16, cudaMemcpyDeviceToHost, st));
@@ -968,6 +937,7 @@ extern "C" int ob200_score_pruned(ob200_ctx* ctx, const double* cand_dev, int64_
     tau = tau - 1e-9 * fabs(tau);  // bin edges are computed differently on the device: err on the inclusive side
   }
   // batch A: the candidates with the largest bounds
+  int grid = 0;
   int64_t n_scored = 0;
   unsigned long long h_count = 0;
   compact_kernel<<<nblk, 256, 0, st>>>(ub, M, tau, INFINITY, first_index, ctx->idx_dev, counter);
@@ -1017,10 +987,73 @@ extern "C" int ob200_score_pruned(ob200_ctx* ctx, const double* cand_dev, int64_
       n_scored += nB;
     }
   }
-  best_host[0] = incumbent;
-  if (n_scored_host) *n_scored_host = n_scored;
+  *best_out = incumbent;
+  *n_scored_out = n_scored;
+  return OB200_OK;
+}
+
+}  // namespace
+
+extern "C" int ob200_score_pruned_multi(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M, uint64_t seed,
+                                        uint64_t first_index, int acq_mask, double y_opt, double xi, double kappa,
+                                        ob200_best* best_host, int64_t* n_scored_host) {
+  if (!ctx) return OB200_EINVAL;
+  int rc = check_score_args(ctx, M, acq_mask, best_host);
+  if (rc) return rc;
+  OB_CUDA(ctx, cudaSetDevice(ctx->device));
+  const int D = ctx->hdr.D;
+  const int64_t batch = (int64_t)ctx->num_sms * SC_BN;
+  for (int k = 0; k < 3; ++k) { best_host[k] = ob200_best{}; if (n_scored_host) n_scored_host[k] = 0; }
+  // small problems, or candidate sets that do not fit in one resident buffer: dense path
+  const bool too_big = !cand_dev && (M * (int64_t)D * 8 > ((int64_t)1 << 31));
+  if (M <= 4 * batch || too_big) {
+    rc = ob200_score(ctx, cand_dev, ldc, M, seed, first_index, acq_mask, y_opt, xi, kappa, best_host, nullptr, nullptr, nullptr);
+    if (rc) return rc;
+    for (int k = 0; k < 3; ++k) if (n_scored_host && (acq_mask & (1 << k))) n_scored_host[k] = M;
+    return OB200_OK;
+  }
+  if (cand_dev) {
+    if (ldc < D) OB_FAIL(ctx, OB200_EINVAL, "ldc=%lld < D=%d", (long long)ldc, D);
+  } else {
+    if (ctx->n_slots <= 0) OB_FAIL(ctx, OB200_ESTATE, "cand_dev is NULL and no space was set");
+    if (ctx->d_out != D) OB_FAIL(ctx, OB200_EINVAL, "space width %d != fitted D %d", ctx->d_out, D);
+    if ((rc = ob_reserve(ctx, &ctx->cand_tmp, &ctx->cand_cap, M * D))) return rc;
+    if ((rc = ob200_sample_launch(ctx, seed, first_index, M, 1, ctx->cand_tmp, D, nullptr))) return rc;
+    cand_dev = ctx->cand_tmp;
+    ldc = D;
+  }
+  if ((rc = ob_reserve(ctx, &ctx->ub_dev, &ctx->ub_cap, 3 * M))) return rc;
+  if ((rc = ob_reserve(ctx, &ctx->idx_dev, &ctx->idx_cap, M))) return rc;
+  const int nblk = ctx->num_sms * 8;
+  const int64_t small_bytes = (int64_t)nblk * 16 + PR_BINS * 4 + 64;
+  if ((rc = ob_reserve(ctx, &ctx->prune_small_dev, &ctx->prune_small_cap, small_bytes))) return rc;
+  double *mu = ctx->ub_dev, *sig = ctx->ub_dev + M, *ub = ctx->ub_dev + 2 * M;
+  // pass 1 (shared by the acquisitions): posterior mean of every candidate and an upper bound of its sigma from the
+  // nearest observation
+  int grid = 0;
+  if ((rc = score_launch(ctx, cand_dev, ldc, M, first_index, acq_mask, y_opt, xi, kappa, mu, sig, nullptr, 0, &grid, 1, nullptr))) return rc;
+  for (int k = 0; k < 3; ++k) {
+    if (!(acq_mask & (1 << k))) continue;
+    int64_t ns = 0;
+    if ((rc = prune_select(ctx, cand_dev, ldc, M, first_index, k, y_opt, xi, kappa, mu, sig, ub, &best_host[k], &ns))) return rc;
+    if (n_scored_host) n_scored_host[k] = ns;
+  }
   ob_l2_release(ctx);
   if (cand_dev == ctx->cand_tmp) return ob200_sample_status(ctx);
+  return OB200_OK;
+}
+
+extern "C" int ob200_score_pruned(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M, uint64_t seed, uint64_t first_index,
+                                  int acq, double y_opt, double xi, double kappa, ob200_best* best_host, int64_t* n_scored_host) {
+  if (!ctx) return OB200_EINVAL;
+  if (acq < 0 || acq > 2) OB_FAIL(ctx, OB200_EINVAL, "acq must be OB200_ACQ_EI, _PI or _LCB");
+  if (!best_host) OB_FAIL(ctx, OB200_EINVAL, "best_host is null");
+  ob200_best best[3];
+  int64_t ns[3];
+  const int rc = ob200_score_pruned_multi(ctx, cand_dev, ldc, M, seed, first_index, 1 << acq, y_opt, xi, kappa, best, ns);
+  if (rc) return rc;
+  best_host[0] = best[acq];
+  if (n_scored_host) *n_scored_host = ns[acq];
   return OB200_OK;
 }
 

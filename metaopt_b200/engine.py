@@ -258,6 +258,21 @@ class Engine:
         rec = dict(value=best[0].value, index=int(best[0].index), mu=best[0].mu, sigma=best[0].sigma)
         return {acq: rec}, int(n_scored.value)
 
+    def score_pruned_multi(self, cand=None, M=None, seed=0, first_index=0, acq_mask=7, y_opt=0.0, xi=0.01, kappa=1.96):
+        """`score_pruned` for several acquisitions with ONE shared mean-only pass (the gp_hedge portfolio).
+        Returns ({acq: record}, {acq: n_scored})."""
+        self.use_torch_stream()
+        ldc = 0
+        if cand is not None:
+            assert cand.dtype == torch.float64 and cand.is_cuda and cand.stride(1) == 1
+            M, ldc = cand.shape[0], cand.stride(0)
+        best = (Best * 3)()
+        n_scored = (C.c_int64 * 3)()
+        self._check(self.lib.ob200_score_pruned_multi(self.ctx, _ptr(cand), ldc, M, seed, first_index, acq_mask, y_opt, xi,
+                                                      kappa, best, n_scored))
+        names = {0: "EI", 1: "PI", 2: "LCB"}
+        return self._bests(best, acq_mask), {names[k]: int(n_scored[k]) for k in range(3) if acq_mask & (1 << k)}
+
     def score_host(self, cand, acq_mask=1, y_opt=0.0, xi=0.01, kappa=1.96, dense=False):
         """Same through host buffers (numpy in, numpy out): H2D/D2H copies happen inside the call."""
         self.use_torch_stream()

@@ -116,6 +116,25 @@ class MultiEngine:
         results = list(self.pool.map(one, self._shards(M, first_index)))
         return obdist.merge_best([r[0] for r in results]), sum(r[1] for r in results)
 
+    def score_pruned_multi(self, cand=None, M=None, seed=0, first_index=0, acq_mask=7, y_opt=0.0, xi=0.01, kappa=1.96):
+        if cand is not None:
+            return self.primary.score_pruned_multi(cand, M=M, seed=seed, first_index=first_index, acq_mask=acq_mask,
+                                                   y_opt=y_opt, xi=xi, kappa=kappa)
+        self._replicate()
+
+        def one(job):
+            e, start, count = job
+            if count == 0:
+                return None, {}
+            return e.score_pruned_multi(None, M=count, seed=seed, first_index=start, acq_mask=acq_mask, y_opt=y_opt,
+                                        xi=xi, kappa=kappa)
+        results = list(self.pool.map(one, self._shards(M, first_index)))
+        scored = {}
+        for _, ns in results:
+            for name, v in ns.items():
+                scored[name] = scored.get(name, 0) + v
+        return obdist.merge_best([r[0] for r in results]), scored
+
 
 _MULTI = {}
 

@@ -92,6 +92,10 @@ class OracleEngine:
                                  mu=float(mu[i]), sigma=float(sd[i]))
         return out
 
+    def score_pruned_multi(self, cand=None, M=None, seed=0, first_index=0, acq_mask=7, y_opt=0.0, xi=0.01, kappa=1.96):
+        out = self.score(cand, M=M, seed=seed, first_index=first_index, acq_mask=acq_mask, y_opt=y_opt, xi=xi, kappa=kappa)
+        return out, {name: M for name in out}
+
     def score_pruned(self, cand=None, M=None, seed=0, first_index=0, acq="EI", y_opt=0.0, xi=0.01, kappa=1.96):
         k = {"EI": 0, "PI": 1, "LCB": 2}[acq]
         out = self.score(cand, M=M, seed=seed, first_index=first_index, acq_mask=1 << k, y_opt=y_opt, xi=xi, kappa=kappa)

@@ -79,8 +79,8 @@ def test_observe_then_gp_suggest(fake, acq):
         (tp,) = a.suggest(1)
         assert tp in t
         a.observe([tp], [{"objective": objective(t.reverse(tp)), "constraint": [], "gradient": None}])
-    per_suggest = 3 if acq == "gp_hedge" else 1  # the hedge portfolio scores EI, LCB and PI (pruned, one call each)
-    assert len(a._y) == 8 and fake.calls["fit"] == 3 and fake.calls["score"] == 3 * per_suggest
+    # the hedge portfolio scores EI, LCB and PI in ONE pruned call (shared mean-only pass)
+    assert len(a._y) == 8 and fake.calls["fit"] == 3 and fake.calls["score"] == 3
     # lies without an objective are ignored, whole-history observe is accepted
     a.observe([tp], [{"objective": None}])
     assert len(a._y) == 8

@@ -246,3 +246,23 @@ def test_host_entry_point_overlapped_copy_equals_device_path(engine):
     b = engine.score(torch.as_tensor(C).cuda(), acq_mask=7, y_opt=float(y.min()))
     assert a == b
     assert engine.score_host(C, acq_mask=7, y_opt=float(y.min())) == b  # pageable host memory too
+
+
+def test_pruned_portfolio_shares_the_mean_pass_and_matches_the_dense_winners(engine):
+    X, y = gp_problem(300, 6, seed=9)
+    engine.fit(X, y, alpha=1e-4, normalize_y=True, length_scale=0.8)
+    C = torch.as_tensor(np.random.RandomState(4).rand(40000, 6)).cuda()
+    y_opt = float(y.min())
+    dense = engine.score(C, acq_mask=7, y_opt=y_opt)
+    before = engine.launches
+    multi, scored = engine.score_pruned_multi(C, acq_mask=7, y_opt=y_opt)
+    launches_multi = engine.launches - before
+    assert multi == {k: dense[k] for k in ("EI", "PI", "LCB")}
+    assert set(scored) == {"EI", "PI", "LCB"} and all(0 < v <= 40000 for v in scored.values())
+    before = engine.launches
+    for name in ("EI", "PI", "LCB"):
+        one, n_one = engine.score_pruned(C, acq=name, y_opt=y_opt)
+        assert one[name] == dense[name] and n_one == scored[name]
+    assert launches_multi < engine.launches - before          # two mean-only passes saved
+    two, scored2 = engine.score_pruned_multi(C, acq_mask=5, y_opt=y_opt)
+    assert set(two) == {"EI", "LCB"} and two["EI"] == dense["EI"] and two["LCB"] == dense["LCB"]
