@@ -197,3 +197,29 @@ def test_lbfgs_refinement_never_loses_to_the_best_sample(fake, acq):
         assert ei(p_l) > ei(p_s)                  # 300 samples in 2-D leave room for the ascent
     with pytest.raises(ValueError):
         BayesianOptimizer(t, acq_optimizer="newton")
+
+
+def test_observation_cache_is_path_independent_and_survives_copies_and_lies(fake):
+    t = build_required_space("real", small_space())
+    a = BayesianOptimizer(t, seed=3, n_initial_points=4, acq_func="EI", n_points=200, fit_hyperparameters=False)
+    pts = a.suggest(4)
+    ys = [objective(t.reverse(p)) for p in pts]
+    for p, v in zip(pts, ys):                                   # one by one
+        a.observe([p], [{"objective": v}])
+        a._data()
+    Xa, ya, da = a._data()
+    b = BayesianOptimizer(t, seed=3, n_initial_points=4, acq_func="EI", n_points=200, fit_hyperparameters=False)
+    b.observe(pts, [{"objective": v} for v in ys])              # all at once (restart)
+    Xb, yb, db = b._data()
+    assert np.array_equal(Xa, Xb) and np.array_equal(ya, yb) and da == db
+    c = copy.deepcopy(a)
+    c.observe([pts[0]], [{"objective": 9.0}])
+    assert c._data()[0].shape[0] == 5 and a._data()[0].shape[0] == 4 and a._data()[2] == da
+    n_fit = fake.calls["fit"]
+    a.suggest(3)                                                # two constant-liar refits on top of the real fit
+    assert fake.calls["fit"] == n_fit + 3
+    assert len(a._y) == 4 and a._data()[2] == da                # lies and their cache entries are gone
+    a.suggest(1)
+    assert fake.calls["fit"] == n_fit + 4                       # the engine holds the last liar fit: one refit, then cached
+    a.suggest(1)
+    assert fake.calls["fit"] == n_fit + 4
