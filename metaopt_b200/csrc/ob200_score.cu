@@ -124,6 +124,8 @@ __device__ unsigned long long g_sc_prof[1024 * 8];
 #define SC_PROF_MARK(K)
 #endif
 
+// MEAN_ONLY: phase 1 only (pruned scoring, pass 1) -- its own instantiation, so the dense kernel carries none of it
+template <bool MEAN_ONLY>
 __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int D_pad = a.D_pad, nd4 = D_pad >> 2;
@@ -196,7 +198,7 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
         }
       }
       __syncthreads();  // (A) consumers finished phase 1, k* slice written
-      if (is_issuer && !a.mean_only) {
+      if (is_issuer && !MEAN_ONLY) {
         // ---- phase 2 producer: inv(L) tiles + k* tiles
         const int nJ = a.n_pad / SC_BK;
         for (int I = 0; I < n_rb; ++I) {
@@ -258,9 +260,14 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
     SC_PROF_MARK(0)  // candidate staging
     // ---- phase 1: k* = kernel(cand, X) and mu partials; warp w owns obs8 block w of each chunk
     {
-      double ccr[SC_NCF], mup[SC_NCF], kmx[SC_NCF];  // kmx: largest kernel value against a real observation (mean-only pass)
+      double ccr[SC_NCF], mup[SC_NCF];
+      // Mean-only pass: (a lower bound of) the largest kernel value against a real observation, kept as the HIGH WORD of
+      // the bit pattern.  Kernel values are >= 0, so integer order is numeric order, one 32-bit max per value runs on
+      // the integer pipe instead of the busy FP64 one, and dropping the low word can only make the value smaller
+      // (by < 2^-20 relative), which keeps the sigma bound derived from it on the safe side.
+      int kmx[SC_NCF];
 #pragma unroll
-      for (int cf = 0; cf < SC_NCF; ++cf) { ccr[cf] = cc[cf * 8 + g]; mup[cf] = 0.0; kmx[cf] = 0.0; }
+      for (int cf = 0; cf < SC_NCF; ++cf) { ccr[cf] = cc[cf * 8 + g]; mup[cf] = 0.0; kmx[cf] = 0; }
       for (int c = 0; c < n_chunks1; ++c, ++it1) {
         const int s = it1 % P1S;
         const uint32_t ph = (it1 / P1S) & 1;
@@ -291,8 +298,10 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
           kv.y = kernel_from_d2(a.kind, d21, a.amplitude, exp_tab);
           mup[cf] = fma(kv.x, al0, mup[cf]);
           mup[cf] = fma(kv.y, al1, mup[cf]);
-          if (!a.mean_only) dst[cf * 32] = kv;
-          else kmx[cf] = fmax(kmx[cf], fmax(ob * 8 + 2 * q < a.n ? kv.x : 0.0, ob * 8 + 2 * q + 1 < a.n ? kv.y : 0.0));
+          if (!MEAN_ONLY) dst[cf * 32] = kv;
+          else if (ob * 8 + 8 <= a.n) kmx[cf] = max(kmx[cf], max(__double2hiint(kv.x), __double2hiint(kv.y)));
+          else kmx[cf] = max(kmx[cf], max(ob * 8 + 2 * q < a.n ? __double2hiint(kv.x) : 0,
+                                           ob * 8 + 2 * q + 1 < a.n ? __double2hiint(kv.y) : 0));  // padded observations
         }
       }
       // mu: reduce over q (4 lanes) then across warps through shared memory
@@ -303,11 +312,11 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
         v += __shfl_xor_sync(0xffffffffu, v, 2);
         if (q == 0) mured[warp * SC_BN + cf * 8 + g] = v;
 #if SC_WN == 1
-        if (a.mean_only) {  // ssred is idle in this mode: it carries the per-warp maxima to phase 3
-          double kx = kmx[cf];
-          kx = fmax(kx, __shfl_xor_sync(0xffffffffu, kx, 1));
-          kx = fmax(kx, __shfl_xor_sync(0xffffffffu, kx, 2));
-          if (q == 0) ssred[warp * SC_BN + cf * 8 + g] = kx;
+        if (MEAN_ONLY) {  // ssred is idle in this mode: it carries the per-warp maxima to phase 3
+          int kx = kmx[cf];
+          kx = max(kx, __shfl_xor_sync(0xffffffffu, kx, 1));
+          kx = max(kx, __shfl_xor_sync(0xffffffffu, kx, 2));
+          if (q == 0) ssred[warp * SC_BN + cf * 8 + g] = __hiloint2double(kx, 0);
         }
 #endif
       }
@@ -322,7 +331,7 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
     double ss[SC_FN][2];
 #pragma unroll
     for (int j = 0; j < SC_FN; ++j) ss[j][0] = ss[j][1] = 0.0;
-    for (int I = 0; I < (a.mean_only ? 0 : n_rb); ++I) {
+    for (int I = 0; I < (MEAN_ONLY ? 0 : n_rb); ++I) {
       double acc[SC_FM][SC_FN][2];
 #pragma unroll
       for (int t = 0; t < SC_FM; ++t)
@@ -419,7 +428,7 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
     }
     SC_PROF_MARK(3)  // phase 2 (incl. pipeline fill)
     // reduce over the 8 row lanes (g), then across the SC_WM row warps via shared memory
-    if (!a.mean_only)
+    if (!MEAN_ONLY)
 #pragma unroll
     for (int j = 0; j < SC_FN; ++j)
 #pragma unroll
@@ -442,7 +451,7 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
       for (int w = 0; w < SC_CONSUMER_WARPS; ++w) m += mured[w * SC_BN + tid];
       const double mu = a.y_std * m + a.y_mean;
       const long long row = row0 + tid;
-      if (a.mean_only) {
+      if (MEAN_ONLY) {
         a.mu_out[row] = mu;
         if (a.sigma_out) {
           // Conditioning on ONE observation j already gives var <= amp - k_j^2 / (amp + diag), and more observations
@@ -627,7 +636,8 @@ int score_launch(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M,
   a.mean_only = mean_only;
   a.diag = h.diag;
   a.index_map = index_map;
-  OB_CUDA(ctx, cudaFuncSetAttribute(score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  auto kernel = mean_only ? score_kernel<true> : score_kernel<false>;
+  OB_CUDA(ctx, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   // k* slices -> persisting L2 lines for this launch (the window is a launch-time stream attribute)
   const size_t slices = (size_t)grid * h.n_pad * SC_BN * sizeof(double);
   const bool persist = ctx->l2_persist_max > 0 && !mean_only;
@@ -641,7 +651,7 @@ int score_launch(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M,
     attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
     OB_CUDA(ctx, cudaStreamSetAttribute(ctx->stream, cudaStreamAttributeAccessPolicyWindow, &attr));
   }
-  score_kernel<<<grid, SC_THREADS, smem, ctx->stream>>>(a);
+  kernel<<<grid, SC_THREADS, smem, ctx->stream>>>(a);
   OB_LAUNCH_CHECK(ctx);
   if (persist) {  // later launches on this (caller-owned) stream must not inherit the window
     cudaStreamAttrValue attr{};
