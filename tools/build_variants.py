@@ -23,6 +23,7 @@ VARIANTS = {
     # sampler with one half switched off (wrong output): which half bounds it?
     "st_db4": ["ST_NBUF=2", "ST_MIN_CTAS=4"],
     "st_db4w8": ["ST_NBUF=2", "ST_MIN_CTAS=2", "ST_THREADS=256", "ST_ROWS=64"],
+    "st_rb128": ["ST_ROW_BULK_MIN=128"],
     "st7": ["ST_MIN_CTAS=7"],
     "st6": ["ST_MIN_CTAS=6"],
     "st5": ["ST_MIN_CTAS=5"],
