@@ -27,8 +27,8 @@
 
 namespace {
 
-#ifndef ST_ROWS
-#define ST_ROWS 32       // rows per tile (one row group)
+#ifndef ST_TILE_BYTES
+#define ST_TILE_BYTES 26624   // target size of a CTA's tile: rows per tile = as many 32-row groups as fit (>= 1)
 #endif
 #ifndef ST_THREADS
 #define ST_THREADS 128   // 4 warps share the slot pairs of the tile; many small independent CTAs per SM
@@ -302,12 +302,12 @@ __device__ __forceinline__ void pair_op(const dslot* __restrict__ sp, const doub
 template <int MODE>
 __global__ void __launch_bounds__(ST_THREADS, ST_MIN_CTAS)
 sample_transform_kernel(const dslot* __restrict__ slots_g, int n_dslots, int n_slots, const double* __restrict__ cdf_g, int n_cdf,
-                        int d_out, int stride, const __grid_constant__ philox_keys rk, uint64_t first_index, int64_t count,
+                        int d_out, int stride, int tile_rows, const __grid_constant__ philox_keys rk, uint64_t first_index, int64_t count,
                         int normalise, double* __restrict__ out, int64_t ld, const double* __restrict__ variates,
                         int bulk_ok, int vec_lanes, int* __restrict__ status) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  const size_t tile_elems = ((size_t)ST_ROWS * stride + 1) & ~(size_t)1;                 // 16-byte aligned
-  double* tile0 = reinterpret_cast<double*>(smem_raw);                                  // ST_NBUF x [ST_ROWS][stride]
+  const size_t tile_elems = ((size_t)tile_rows * stride + 1) & ~(size_t)1;               // 16-byte aligned
+  double* tile0 = reinterpret_cast<double*>(smem_raw);                                  // ST_NBUF x [tile_rows][stride]
   dslot* slots = reinterpret_cast<dslot*>(tile0 + ST_NBUF * tile_elems);
   double* cdf = reinterpret_cast<double*>(slots + n_dslots);
   const double* exp_tab = g_exp2_tab;
@@ -318,15 +318,15 @@ sample_transform_kernel(const dslot* __restrict__ slots_g, int n_dslots, int n_s
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n_pairs = n_dslots >> 1;
-  const int64_t n_tiles = (count + ST_ROWS - 1) / ST_ROWS;
+  const int64_t n_tiles = (count + tile_rows - 1) / tile_rows;
   const uint32_t row_bytes = (uint32_t)d_out * 8u;
 
   int buf = 0;
   for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x, buf ^= (ST_NBUF - 1)) {
     double* tile = tile0 + (size_t)buf * tile_elems;
     const uint32_t tile_sa = (uint32_t)__cvta_generic_to_shared(tile);
-    const int64_t row0 = t * ST_ROWS;
-    const int rows = (int)min((int64_t)ST_ROWS, count - row0);
+    const int64_t row0 = t * tile_rows;
+    const int rows = (int)min((int64_t)tile_rows, count - row0);
 #ifdef ST_DEBUG_NO_COMPUTE  // timing experiment only: copy-out without generation
     const int n_rg = 0;
 #else
@@ -454,9 +454,15 @@ int ob200_sample_launch(ob200_ctx* ctx, uint64_t seed, uint64_t first_index, int
 #endif
   else if (aligned && d_out * 8 >= ST_ROW_BULK_MIN) bulk_ok = 1;
   else if (aligned) { vec_lanes = 1; while (vec_lanes < 32 && vec_lanes < d_out / 2) vec_lanes <<= 1; }
-  const size_t smem = (ST_NBUF * (((size_t)ST_ROWS * stride + 1) & ~(size_t)1) + (size_t)ctx->n_cdf) * sizeof(double) + (size_t)ctx->n_dslots * sizeof(dslot);
+  // rows per tile: narrow spaces get several 32-row groups per CTA (the slot pairs of ONE group do not divide evenly
+  // among the warps and the per-tile barriers / copy-out would dominate), wide ones a single group
+  int tile_rows = 32 * (int)(ST_TILE_BYTES / ((size_t)32 * stride * 8));
+  if (tile_rows < 32) tile_rows = 32;
+  if (tile_rows > 256) tile_rows = 256;
+  if (const char* env = getenv("OB200_TILE_ROWS")) { const int v = atoi(env); if (v >= 32 && v <= 1024 && v % 32 == 0) tile_rows = v; }
+  const size_t smem = (ST_NBUF * (((size_t)tile_rows * stride + 1) & ~(size_t)1) + (size_t)ctx->n_cdf) * sizeof(double) + (size_t)ctx->n_dslots * sizeof(dslot);
   if (smem > 227 * 1024) OB_FAIL(ctx, OB200_EINVAL, "D_out=%d too wide for the sampler tile", d_out);
-  const int64_t n_tiles = (count + ST_ROWS - 1) / ST_ROWS;
+  const int64_t n_tiles = (count + tile_rows - 1) / tile_rows;
   auto kernel = variates_dev ? sample_transform_kernel<MODE_VARIATES>
                              : (normalise ? sample_transform_kernel<MODE_NORM> : sample_transform_kernel<MODE_RAW>);
   OB_CUDA(ctx, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -471,7 +477,7 @@ int ob200_sample_launch(ob200_ctx* ctx, uint64_t seed, uint64_t first_index, int
     for (int r = 0; r < 10; ++r) { rk.k0[r] = k0; rk.k1[r] = k1; k0 += 0x9E3779B9u; k1 += 0xBB67AE85u; }
   }
   kernel<<<grid, ST_THREADS, smem, ctx->stream>>>(reinterpret_cast<const dslot*>(ctx->dslots_dev), ctx->n_dslots, ctx->n_slots, ctx->cdf_dev, ctx->n_cdf, d_out,
-                                                  stride, rk, first_index, count, normalise, out_dev, ld, variates_dev, bulk_ok, vec_lanes,
+                                                  stride, tile_rows, rk, first_index, count, normalise, out_dev, ld, variates_dev, bulk_ok, vec_lanes,
                                                   ctx->status_dev);
   OB_LAUNCH_CHECK(ctx);
   return OB200_OK;
