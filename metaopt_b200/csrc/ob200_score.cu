@@ -110,8 +110,8 @@ static_assert(SC_BM % SC_P1_OBS == 0, "row block must be a multiple of the phase
 static_assert(SC_BN % 32 == 0 && SC_BN <= SC_CONSUMER_WARPS * 32, "candidate tile shape");
 static_assert(SC_BK % 8 == 0, "stage depth");
 
-__host__ __device__ inline size_t score_union_elems(int D_pad, int p1_stages) {
-  size_t un = (size_t)SC_STAGES * (SC_BM * SC_BK + SC_BK * SC_BN);
+__host__ __device__ inline size_t score_union_elems(int D_pad, int p1_stages, bool mean_only) {
+  const size_t un = mean_only ? 0 : (size_t)SC_STAGES * (SC_BM * SC_BK + SC_BK * SC_BN);  // the mean-only pass has no phase 2
   const size_t p1 = (size_t)SC_BN * D_pad + (size_t)p1_stages * (SC_P1_OBS * D_pad + 2 * SC_P1_OBS);
   return p1 > un ? p1 : un;
 }
@@ -125,8 +125,11 @@ __device__ unsigned long long g_sc_prof[1024 * 8];
 #endif
 
 // MEAN_ONLY: phase 1 only (pruned scoring, pass 1) -- its own instantiation, so the dense kernel carries none of it
+// (two CTAs per SM there: phase 1 is FP64-latency-bound and needs neither the phase-2 buffers nor its registers; no
+// setmaxnreg either, so ONE producer warp is enough: 13 warps, 72 registers)
+#define SC_MEAN_THREADS ((SC_CONSUMER_WARPS + 1) * 32)
 template <bool MEAN_ONLY>
-__global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
+__global__ void __launch_bounds__(MEAN_ONLY ? SC_MEAN_THREADS : SC_THREADS, MEAN_ONLY ? 2 : 1) score_kernel(score_args a) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int D_pad = a.D_pad, nd4 = D_pad >> 2;
   const int p1_stage_elems = SC_P1_OBS * D_pad + 2 * SC_P1_OBS;
@@ -138,7 +141,7 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
   double* Abuf = un;                              // SC_STAGES x (SC_BM*SC_BK)
   double* Bbuf = un + SC_STAGES * SC_BM * SC_BK;  // SC_STAGES x (SC_BK*SC_BN)
   const int P1S = a.p1_stages;
-  double* small = un + score_union_elems(D_pad, P1S);
+  double* small = un + score_union_elems(D_pad, P1S, MEAN_ONLY);
   double* cc = small;                                   // [SC_BN]
   double* mured = cc + SC_BN;                           // [SC_CONSUMER_WARPS][SC_BN]
   double* ssred = mured + SC_CONSUMER_WARPS * SC_BN;    // [SC_WM][SC_BN]
@@ -181,7 +184,7 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
   if (is_producer) {
     // register rebalancing: each role keeps its own tile loop so the register budget is decided by
     // dominance (per SM sub-partition: consumers x SC_CONSUMER_REGS + 1 producer x 40 <= 512).
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+    if (!MEAN_ONLY) asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
     for (long long tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
       if (is_issuer) {
         // ---- phase 1 producer: observed-point chunks
@@ -220,7 +223,7 @@ __global__ void __launch_bounds__(SC_THREADS, 1) score_kernel(score_args a) {
   }
 
   // =============================== consumers ===============================
-  asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(SC_CONSUMER_REGS));
+  if (!MEAN_ONLY) asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(SC_CONSUMER_REGS));
 
   // running best per acquisition (threads 0..SC_BN-1 own one candidate column each)
   best_t best[3];
@@ -595,8 +598,8 @@ __global__ void __launch_bounds__(256) acq_partial_kernel(const double* __restri
   }
 }
 
-size_t score_smem_bytes(int D_pad, int p1_stages) {
-  return (score_union_elems(D_pad, p1_stages) + SC_BN + SC_CONSUMER_WARPS * SC_BN + SC_WM * SC_BN) * sizeof(double) +
+size_t score_smem_bytes(int D_pad, int p1_stages, bool mean_only = false) {
+  return (score_union_elems(D_pad, p1_stages, mean_only) + SC_BN + SC_CONSUMER_WARPS * SC_BN + SC_WM * SC_BN) * sizeof(double) +
          (2 * P1_STAGES + 2 * SC_STAGES) * sizeof(uint64_t) + 32 * sizeof(double) + 128;
 }
 
@@ -612,8 +615,20 @@ int score_launch(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M,
   size_t smem = score_smem_bytes(h.D_pad, p1_stages);
   while (smem > 227 * 1024 && p1_stages > 1) { --p1_stages; smem = score_smem_bytes(h.D_pad, p1_stages); }
   if (smem > 227 * 1024) OB_FAIL(ctx, OB200_EINVAL, "D=%d too wide for the score kernel's shared-memory tile", h.D);
+  int ctas_per_sm = 1;
+  if (mean_only) {  // phase 1 alone: two CTAs per SM when a ring of at least two stages fits in half the shared memory
+    smem = score_smem_bytes(h.D_pad, p1_stages, true);
+    int st2 = p1_stages;
+    while (st2 > 2 && score_smem_bytes(h.D_pad, st2, true) > 112 * 1024) --st2;
+    if (score_smem_bytes(h.D_pad, st2, true) <= 112 * 1024 && !getenv("OB200_MEAN_1CTA")) {
+      p1_stages = st2;
+      smem = score_smem_bytes(h.D_pad, st2, true);
+      ctas_per_sm = 2;
+    }
+  }
   const int64_t n_tiles = (M + SC_BN - 1) / SC_BN;
-  const int grid = (int)(n_tiles < ctx->num_sms ? n_tiles : ctx->num_sms);
+  const int64_t max_grid = (int64_t)ctx->num_sms * ctas_per_sm;
+  const int grid = (int)(n_tiles < max_grid ? n_tiles : max_grid);
   int rc;
   if ((rc = ob_reserve(ctx, &ctx->kstar_dev, &ctx->kstar_cap, (int64_t)ctx->num_sms * h.n_pad * SC_BN))) return rc;
   if ((rc = ob_reserve(ctx, &ctx->partial_dev, &ctx->partial_cap, (int64_t)4096 * 3 * (int64_t)sizeof(best_t)))) return rc;
@@ -651,7 +666,7 @@ int score_launch(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M,
     attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
     OB_CUDA(ctx, cudaStreamSetAttribute(ctx->stream, cudaStreamAttributeAccessPolicyWindow, &attr));
   }
-  kernel<<<grid, SC_THREADS, smem, ctx->stream>>>(a);
+  kernel<<<grid, mean_only ? SC_MEAN_THREADS : SC_THREADS, smem, ctx->stream>>>(a);
   OB_LAUNCH_CHECK(ctx);
   if (persist) {  // later launches on this (caller-owned) stream must not inherit the window
     cudaStreamAttrValue attr{};
