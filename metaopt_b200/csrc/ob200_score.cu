@@ -925,6 +925,65 @@ __global__ void __launch_bounds__(256) globalise_kernel(long long* __restrict__ 
 
 namespace {
 
+// union of the first batches of several acquisitions: keep row i if ub_k[i] >= tau_k for some requested k
+// (tau_k = +inf for acquisitions that are not requested; NaN bounds of a requested one are always kept)
+__global__ void __launch_bounds__(256) compact_union_kernel(const double* __restrict__ ub0, const double* __restrict__ ub1,
+                                                            const double* __restrict__ ub2, long long M, double tau0, double tau1,
+                                                            double tau2, int acq_mask, long long* __restrict__ rows,
+                                                            unsigned long long* __restrict__ counter) {
+  for (long long i0 = (long long)blockIdx.x * 256; i0 < M; i0 += (long long)gridDim.x * 256) {
+    const long long i = i0 + threadIdx.x;
+    bool keep = false;
+    if (i < M) {
+      if (acq_mask & 1) { const double v = ub0[i]; keep |= !(v == v) || v >= tau0; }
+      if (acq_mask & 2) { const double v = ub1[i]; keep |= !(v == v) || v >= tau1; }
+      if (acq_mask & 4) { const double v = ub2[i]; keep |= !(v == v) || v >= tau2; }
+    }
+    const unsigned mask = __ballot_sync(0xffffffffu, keep);
+    if (mask) {
+      const int lane = threadIdx.x & 31, leader = __ffs(mask) - 1;
+      unsigned long long base = 0;
+      if (lane == leader) base = atomicAdd(counter, (unsigned long long)__popc(mask));
+      base = __shfl_sync(0xffffffffu, base, leader);
+      if (keep) rows[base + __popc(mask & ((1u << lane) - 1))] = i;
+    }
+  }
+}
+
+// bound array of one acquisition -> threshold tau such that about `quota` candidates have ub >= tau (-inf: all)
+int prune_tau(ob200_ctx* ctx, const double* mu, const double* sig, int64_t M, int acq, double y_opt, double xi, double kappa,
+              double* ub, int64_t quota, double* tau_out) {
+  cudaStream_t st = ctx->stream;
+  const int nblk = ctx->num_sms * 8;
+  double* blk = reinterpret_cast<double*>(ctx->prune_small_dev);
+  int* hist = reinterpret_cast<int*>(ctx->prune_small_dev + (size_t)nblk * 16);
+  ub_kernel<<<nblk, 256, 0, st>>>(mu, sig, M, acq, y_opt, xi, kappa, ub, blk);
+  OB_LAUNCH_CHECK(ctx);
+  std::vector<double> h_blk((size_t)nblk * 2);
+  OB_CUDA(ctx, cudaMemcpyAsync(h_blk.data(), blk, (size_t)nblk * 16, cudaMemcpyDeviceToHost, st));
+  OB_CUDA(ctx, cudaMemsetAsync(hist, 0, PR_BINS * 4 + 64, st));
+  OB_CUDA(ctx, cudaStreamSynchronize(st));
+  double lo = INFINITY, hi = -INFINITY;
+  for (int b = 0; b < nblk; ++b) { if (h_blk[2 * b] < lo) lo = h_blk[2 * b]; if (h_blk[2 * b + 1] > hi) hi = h_blk[2 * b + 1]; }
+  double tau = -INFINITY;
+  if (hi > lo && lo > -INFINITY && hi < INFINITY) {
+    const double width = (hi - lo) / PR_BINS;
+    hist_kernel<<<nblk, 256, 0, st>>>(ub, M, lo, 1.0 / width, hist);
+    OB_LAUNCH_CHECK(ctx);
+    std::vector<int> h_hist(PR_BINS);
+    OB_CUDA(ctx, cudaMemcpyAsync(h_hist.data(), hist, PR_BINS * 4, cudaMemcpyDeviceToHost, st));
+    OB_CUDA(ctx, cudaStreamSynchronize(st));
+    int64_t acc_count = 0;
+    for (int b = PR_BINS - 1; b >= 0; --b) {
+      acc_count += h_hist[b];
+      if (acc_count >= quota) { tau = lo + width * b; break; }
+    }
+    tau = tau - 1e-9 * fabs(tau);  // bin edges are computed differently on the device: err on the inclusive side
+  }
+  *tau_out = tau;
+  return OB200_OK;
+}
+
 // Selection for ONE acquisition on top of the shared mean-only pass (mu, sigma bound per candidate): utility bounds,
 // batch A (largest bounds) -> incumbent, batch B (bounds that still reach it).
 int prune_select(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M, uint64_t first_index, int acq, double y_opt,
@@ -1017,6 +1076,82 @@ int prune_select(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M,
   return OB200_OK;
 }
 
+// Selection for SEVERAL acquisitions (the gp_hedge portfolio): their first batches share ONE score launch -- each gets
+// a third (or half) of the one-tile-per-CTA budget, the union is scored for all of them at once -- and only the second
+// batches, usually empty, run per acquisition.  Same exactness argument as prune_select: everything whose bound
+// reaches an acquisition's incumbent is scored for it.
+int prune_select_multi(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M, uint64_t first_index, int acq_mask,
+                       double y_opt, double xi, double kappa, const double* mu, const double* sig, double* ub3,
+                       ob200_best* best_out, int64_t* n_scored_out) {
+  const int D = ctx->hdr.D;
+  const int64_t batch = (int64_t)ctx->num_sms * SC_BN;
+  cudaStream_t st = ctx->stream;
+  const int nblk = ctx->num_sms * 8;
+  unsigned long long* counter = reinterpret_cast<unsigned long long*>(ctx->prune_small_dev + (size_t)nblk * 16 + PR_BINS * 4);
+  int n_acq = 0, rc, grid = 0;
+  for (int k = 0; k < 3; ++k) n_acq += (acq_mask >> k) & 1;
+  double tau[3] = {INFINITY, INFINITY, INFINITY};
+  double* ub[3] = {ub3, ub3 + M, ub3 + 2 * M};
+  for (int k = 0; k < 3; ++k)
+    if (acq_mask & (1 << k))
+      if ((rc = prune_tau(ctx, mu, sig, M, k, y_opt, xi, kappa, ub[k], batch / n_acq, &tau[k]))) return rc;
+  // batch A: union of the candidates with the largest bounds of each acquisition (prune_tau left the counter at zero)
+  unsigned long long h_count = 0;
+  compact_union_kernel<<<nblk, 256, 0, st>>>(ub[0], ub[1], ub[2], M, tau[0], tau[1], tau[2], acq_mask, ctx->idx_dev, counter);
+  OB_LAUNCH_CHECK(ctx);
+  OB_CUDA(ctx, cudaMemcpyAsync(&h_count, counter, 8, cudaMemcpyDeviceToHost, st));
+  OB_CUDA(ctx, cudaStreamSynchronize(st));
+  ob200_best incumbent[3];
+  for (int k = 0; k < 3; ++k) { incumbent[k] = ob200_best{}; incumbent[k].value = -INFINITY; }
+  const int64_t nA = (int64_t)h_count;
+  if (nA > 0) {
+    if ((rc = ob_reserve(ctx, &ctx->gather_dev, &ctx->gather_cap, nA * D))) return rc;
+    gather_kernel<<<nblk, 256, 0, st>>>(cand_dev, ldc, D, ctx->idx_dev, nA, first_index, ctx->gather_dev);
+    OB_LAUNCH_CHECK(ctx);
+    globalise_kernel<<<nblk, 256, 0, st>>>(ctx->idx_dev, nA, first_index);
+    OB_LAUNCH_CHECK(ctx);
+    if ((rc = score_launch(ctx, ctx->gather_dev, D, nA, 0, acq_mask, y_opt, xi, kappa, nullptr, nullptr, nullptr, 0, &grid, 0, ctx->idx_dev))) return rc;
+    reduce_best_kernel<<<1, 256, 0, st>>>(reinterpret_cast<const best_t*>(ctx->partial_dev), grid, acq_mask, ctx->best_dev);
+    OB_LAUNCH_CHECK(ctx);
+    OB_CUDA(ctx, cudaMemcpyAsync(ctx->best_pinned, ctx->best_dev, 3 * sizeof(ob200_best), cudaMemcpyDeviceToHost, st));
+    OB_CUDA(ctx, cudaStreamSynchronize(st));
+    for (int k = 0; k < 3; ++k) if (acq_mask & (1 << k)) incumbent[k] = ctx->best_pinned[k];
+  }
+  // batch B, per acquisition: bounds below its tau that still reach its incumbent (rows that entered batch A through
+  // another acquisition may be scored again: harmless)
+  for (int k = 0; k < 3; ++k) {
+    if (!(acq_mask & (1 << k))) continue;
+    int64_t n_scored = nA;
+    const double thr = incumbent[k].value - 1e-12 * fabs(incumbent[k].value) - 1e-300;
+    if (thr < tau[k]) {
+      OB_CUDA(ctx, cudaMemsetAsync(counter, 0, 8, st));
+      compact_kernel<<<nblk, 256, 0, st>>>(ub[k], M, thr, tau[k], first_index, ctx->idx_dev, counter);
+      OB_LAUNCH_CHECK(ctx);
+      OB_CUDA(ctx, cudaMemcpyAsync(&h_count, counter, 8, cudaMemcpyDeviceToHost, st));
+      OB_CUDA(ctx, cudaStreamSynchronize(st));
+      if (h_count > 0) {
+        const int64_t nB = (int64_t)h_count;
+        if ((rc = ob_reserve(ctx, &ctx->gather_dev, &ctx->gather_cap, nB * D))) return rc;
+        gather_kernel<<<nblk, 256, 0, st>>>(cand_dev, ldc, D, ctx->idx_dev, nB, first_index, ctx->gather_dev);
+        OB_LAUNCH_CHECK(ctx);
+        globalise_kernel<<<nblk, 256, 0, st>>>(ctx->idx_dev, nB, first_index);
+        OB_LAUNCH_CHECK(ctx);
+        if ((rc = score_launch(ctx, ctx->gather_dev, D, nB, 0, 1 << k, y_opt, xi, kappa, nullptr, nullptr, nullptr, 0, &grid, 0, ctx->idx_dev))) return rc;
+        reduce_best_kernel<<<1, 256, 0, st>>>(reinterpret_cast<const best_t*>(ctx->partial_dev), grid, 1 << k, ctx->best_dev);
+        OB_LAUNCH_CHECK(ctx);
+        OB_CUDA(ctx, cudaMemcpyAsync(ctx->best_pinned, ctx->best_dev, 3 * sizeof(ob200_best), cudaMemcpyDeviceToHost, st));
+        OB_CUDA(ctx, cudaStreamSynchronize(st));
+        const ob200_best b = ctx->best_pinned[k];
+        if (b.value > incumbent[k].value || (b.value == incumbent[k].value && b.index < incumbent[k].index)) incumbent[k] = b;
+        n_scored += nB;
+      }
+    }
+    best_out[k] = incumbent[k];
+    if (n_scored_out) n_scored_out[k] = n_scored;
+  }
+  return OB200_OK;
+}
+
 }  // namespace
 
 extern "C" int ob200_score_pruned_multi(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M, uint64_t seed,
@@ -1047,7 +1182,7 @@ extern "C" int ob200_score_pruned_multi(ob200_ctx* ctx, const double* cand_dev, 
     cand_dev = ctx->cand_tmp;
     ldc = D;
   }
-  if ((rc = ob_reserve(ctx, &ctx->ub_dev, &ctx->ub_cap, 3 * M))) return rc;
+  if ((rc = ob_reserve(ctx, &ctx->ub_dev, &ctx->ub_cap, 5 * M))) return rc;
   if ((rc = ob_reserve(ctx, &ctx->idx_dev, &ctx->idx_cap, M))) return rc;
   const int nblk = ctx->num_sms * 8;
   const int64_t small_bytes = (int64_t)nblk * 16 + PR_BINS * 4 + 64;
@@ -1057,11 +1192,15 @@ extern "C" int ob200_score_pruned_multi(ob200_ctx* ctx, const double* cand_dev, 
   // nearest observation
   int grid = 0;
   if ((rc = score_launch(ctx, cand_dev, ldc, M, first_index, acq_mask, y_opt, xi, kappa, mu, sig, nullptr, 0, &grid, 1, nullptr))) return rc;
-  for (int k = 0; k < 3; ++k) {
-    if (!(acq_mask & (1 << k))) continue;
-    int64_t ns = 0;
-    if ((rc = prune_select(ctx, cand_dev, ldc, M, first_index, k, y_opt, xi, kappa, mu, sig, ub, &best_host[k], &ns))) return rc;
-    if (n_scored_host) n_scored_host[k] = ns;
+  if ((acq_mask & (acq_mask - 1)) != 0 && !getenv("OB200_PRUNE_SEPARATE")) {  // several acquisitions: shared first batch
+    if ((rc = prune_select_multi(ctx, cand_dev, ldc, M, first_index, acq_mask, y_opt, xi, kappa, mu, sig, ub, best_host, n_scored_host))) return rc;
+  } else {
+    for (int k = 0; k < 3; ++k) {
+      if (!(acq_mask & (1 << k))) continue;
+      int64_t ns = 0;
+      if ((rc = prune_select(ctx, cand_dev, ldc, M, first_index, k, y_opt, xi, kappa, mu, sig, ub, &best_host[k], &ns))) return rc;
+      if (n_scored_host) n_scored_host[k] = ns;
+    }
   }
   ob_l2_release(ctx);
   if (cand_dev == ctx->cand_tmp) return ob200_sample_status(ctx);
