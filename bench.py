@@ -303,8 +303,8 @@ def run_ours(args):
         from metaopt_b200.algo import BayesianOptimizer
         tspace = build_required_space("real", space)
 
-        def plugin_latency(calls, **extra):
-            algo = BayesianOptimizer(tspace, seed=1, n_initial_points=10, acq_func="EI", alpha=ALPHA, noise="gaussian",
+        def plugin_latency(calls, acq_func="EI", **extra):
+            algo = BayesianOptimizer(tspace, seed=1, n_initial_points=10, acq_func=acq_func, alpha=ALPHA, noise="gaussian",
                                      noise_level=NOISE, normalize_y=True, n_points=M, xi=XI, device=local,
                                      fit_hyperparameters=False, **extra)
             pts = [tuple(float(v) for v in row) for row in X]
@@ -318,7 +318,9 @@ def run_ours(args):
             return statistics.median(lat), len(lat)
         p50_dense, n_dense = plugin_latency(max(5, min(20, args.steps * 2)), prune=False)
         p50_pruned, n_calls = plugin_latency(50, prune=True)
-        suggest_latency = {"p50_ms_dense": p50_dense, "p50_ms_pruned": p50_pruned, "calls_dense": n_dense, "calls_pruned": n_calls, "n_points": M,
+        p50_hedge, _ = plugin_latency(50, acq_func="gp_hedge", prune=True)  # the plugin's default portfolio (EI, LCB, PI)
+        suggest_latency = {"p50_ms_dense": p50_dense, "p50_ms_pruned": p50_pruned, "p50_ms_pruned_gp_hedge": p50_hedge,
+                           "calls_dense": n_dense, "calls_pruned": n_calls, "n_points": M,
                            "n_obs": N_OBS, "api": "BayesianOptimizer.suggest(1) (host wall clock, fit cached)"}
 
     if rank != 0:
