@@ -97,9 +97,7 @@ class BayesianOptimizer(BaseAlgorithm):
     ('EI' | 'PI' | 'LCB' | 'gp_hedge'), `alpha`, `n_restarts_optimizer`, `noise`, `normalize_y`.
     Additive keys (defaults keep reference behaviour): `n_points` (candidates per suggest, skopt's
     default 10000), `xi`, `kappa`, `kernel` ('matern52' | 'rbf'), `length_scale`, `amplitude`,
-    `noise_level` (variance folded into the diagonal when `noise == 'gaussian'`), `device` (an index, or a
-    list of indices to shard the candidates of every suggest over several GPUs of this process), `prune`
-    (exact mean-only pruning of hopeless candidates for single acquisitions; same winner, faster),
+    `noise_level` (variance folded into the diagonal when `noise == 'gaussian'`),
     `fit_hyperparameters` (maximise the log marginal likelihood over amplitude, per-dimension length
     scales and -- when `noise == 'gaussian'` -- the noise level, like the reference's scikit-learn
     estimator does, with `n_restarts_optimizer` extra starts; `length_scale`/`amplitude`/`noise_level`
@@ -107,6 +105,15 @@ class BayesianOptimizer(BaseAlgorithm):
     candidates; 'lbfgs': skopt's default for this space -- the best candidate of each of `acq_n_restarts`
     (5) slices of the candidate stream starts an L-BFGS-B ascent of the acquisition inside the unit box,
     `metaopt_b200/acq_opt.py`, and the best end point is proposed).
+
+    Host placement is NOT an algorithm hyper-parameter: Orion stores `configuration` as `experiment.algorithms`
+    and raises a conflict (branches the experiment) when two workers disagree on it
+    (`src/orion/core/evc/conflicts.py:1034-1038`), so two workers pinned to different GPUs must not differ
+    there.  `device` (an index, or a list of indices to shard the candidates of every suggest over several GPUs
+    of this process) and `prune` (exact mean-only pruning of hopeless candidates; same winner, faster) are
+    therefore read from the environment -- `OB200_DEVICE` ("0", "0,1,2,3"), `OB200_PRUNE` ("1"/"0") -- or
+    passed as constructor keywords by code that builds the object itself; either way they never enter
+    `configuration`.
     """
 
     requires = "real"
@@ -114,8 +121,8 @@ class BayesianOptimizer(BaseAlgorithm):
     # pylint: disable=too-many-arguments
     def __init__(self, space, seed=None, n_initial_points=10, acq_func="gp_hedge", alpha=1e-10,
                  n_restarts_optimizer=0, noise="gaussian", normalize_y=False, n_points=10000, xi=0.01,
-                 kappa=1.96, kernel="matern52", length_scale=1.0, amplitude=1.0, noise_level=1e-4, device=0,
-                 prune=True, fit_hyperparameters=True, acq_optimizer="sampling", acq_n_restarts=5):
+                 kappa=1.96, kernel="matern52", length_scale=1.0, amplitude=1.0, noise_level=1e-4, device=None,
+                 prune=None, fit_hyperparameters=True, acq_optimizer="sampling", acq_n_restarts=5):
         self._seed = None
         self._offset = 0          # next unused global candidate index of the Philox stream
         self._X = []              # observed points, flat + normalised
@@ -125,10 +132,12 @@ class BayesianOptimizer(BaseAlgorithm):
         self._hedge_pending = None
         self._theta = None        # last fitted (amplitude, length_scale[D], noise): warm start of the next fit
         self._cache = None        # stacked observations + chained digest (see _data)
+        self._device = _placement(device)
+        self._prune = _env_flag("OB200_PRUNE", True) if prune is None else bool(prune)
         super().__init__(space, seed=seed, n_initial_points=n_initial_points, acq_func=acq_func, alpha=alpha,
                          n_restarts_optimizer=n_restarts_optimizer, noise=noise, normalize_y=normalize_y,
                          n_points=n_points, xi=xi, kappa=kappa, kernel=kernel, length_scale=length_scale,
-                         amplitude=amplitude, noise_level=noise_level, device=device, prune=prune,
+                         amplitude=amplitude, noise_level=noise_level,
                          fit_hyperparameters=fit_hyperparameters, acq_optimizer=acq_optimizer,
                          acq_n_restarts=acq_n_restarts)
         if str(acq_optimizer) not in ("sampling", "lbfgs"):
@@ -140,6 +149,15 @@ class BayesianOptimizer(BaseAlgorithm):
             raise ValueError("kernel must be 'matern52' or 'rbf'; got %r" % (kernel,))
         if self._seed is None:
             self.seed_rng(None)
+
+    @property
+    def device(self):
+        """CUDA device index (or list of indices) this process scores on; not part of `configuration`."""
+        return self._device
+
+    @property
+    def prune(self):
+        return self._prune
 
     # ---- BaseAlgorithm API ---------------------------------------------------------------
     def seed_rng(self, seed):
@@ -190,9 +208,10 @@ class BayesianOptimizer(BaseAlgorithm):
         comp = self._get_compiled()
         eng = self._engine()
         compiler.upload(eng, comp)
-        points = []
+        points, rows = [], []
         n_real = len(self._y)
         saved_fit, saved_cache = self.fit_hyperparameters, self._cache
+        hedge_state = None
         try:
             for k in range(int(num)):
                 if n_real < max(int(self.n_initial_points), 1):
@@ -200,18 +219,29 @@ class BayesianOptimizer(BaseAlgorithm):
                     self._offset += 1
                 else:
                     row = self._suggest_gp(eng, comp)
+                    if hedge_state is None:  # portfolio state after the pick made on REAL data only
+                        hedge_state = (list(self._hedge_gains), copy.deepcopy(self._hedge_pending))
                     if k + 1 < int(num):  # constant liar: pretend this point returned the incumbent
                         self._X.append(comp.normalise(np.asarray(row, dtype=float)))
                         self._y.append(float(min(self._y[:n_real])))
                         if self._theta is not None:
                             self.fit_hyperparameters = False  # lies must not move the hyper-parameters
+                rows.append(np.asarray(row, dtype=np.float64))
                 points.append(compiler.regroup_row(comp, row, transformed=True))
+            # the check Orion makes point by point in Python right after this call (`primary_algo.py:74-81`), done
+            # once for the whole batch: a proposal outside the space is a bug here, not something to hand back
+            inside = compiler.contains_rows(comp, np.stack(rows))
+            if not inside.all():
+                bad = int(np.flatnonzero(~inside)[0])
+                raise ValueError("Point is not contained in space:\nPoint: {}\nSpace: {}".format(points[bad], self._space))
         finally:
             del self._X[n_real:]
             del self._y[n_real:]
             self.fit_hyperparameters = saved_fit
             if int(num) > 1:
                 self._cache = saved_cache
+                if hedge_state is not None:  # skopt asks for a batch on a COPY of the optimiser: lies leave no trace
+                    self._hedge_gains, self._hedge_pending = hedge_state
         return points
 
     def observe(self, points, results):
@@ -224,7 +254,6 @@ class BayesianOptimizer(BaseAlgorithm):
             flat = np.asarray(compiler.flatten_point(comp, point), dtype=float)
             self._X.append(comp.normalise(flat))
             self._y.append(float(objective))
-        self._settle_hedge()
 
     # ---- internals -------------------------------------------------------------------------
     def _engine(self):
@@ -310,6 +339,7 @@ class BayesianOptimizer(BaseAlgorithm):
                         alpha=self._diag_noise(), normalize_y=bool(self.normalize_y))
             eng._fit_token = token
             eng._fit_theta = copy.deepcopy(self._theta)
+            self._settle_hedge(eng)
         elif self.fit_hyperparameters and getattr(eng, "_fit_theta", None) is not None:
             # another copy of this algorithm (producer.py:161) already fitted these data: adopt its optimum
             self._theta = copy.deepcopy(eng._fit_theta)
@@ -363,7 +393,11 @@ class BayesianOptimizer(BaseAlgorithm):
             probs = np.exp(logits) / np.exp(logits).sum()
             u = float(self._uniform())
             pick = names[int(min(np.searchsorted(np.cumsum(probs), u, side="right"), 2))]
-            self._hedge_pending = [(res[n]["index"], res[n]["mu"]) for n in names]
+            # [n_obs at the pick, the three proposals as normalised rows]: their gains are settled by the first
+            # refit that has seen a newer observation (_settle_hedge)
+            self._hedge_pending = [len(self._y)] + [np.asarray(comp.normalise(rows[n]) if refine else
+                                              eng.sample(self._seed, res[n]["index"], 1, normalise=True).cpu().numpy()[0],
+                                              dtype=np.float64).tolist() for n in names]
         else:
             pick = self.acq_func
         if refine:
@@ -377,12 +411,39 @@ class BayesianOptimizer(BaseAlgorithm):
         self._offset += 1
         return u
 
-    def _settle_hedge(self):
-        # gains_ -= predicted mean of each proposal (skopt: `self.gains_ -= est.predict(next_xs)`)
-        if self._hedge_pending:
-            for k, (_, mu) in enumerate(self._hedge_pending):
-                self._hedge_gains[k] -= float(mu)
+    def _settle_hedge(self, eng):
+        """skopt's `tell` does `gains_ -= est.predict(next_xs_)` with the estimator REFITTED on the new
+        observation and `next_xs_` the three proposals of the previous round.  Called right after a refit: the
+        posterior mean of the pending proposals under the new model is subtracted from the gains.  Two
+        departures that follow from Orion's protocol, not from the arithmetic: a second `suggest` without an
+        `observe` in between replaces the pending proposals (skopt's `ask` would return the same point again), and
+        in a producer whose naive copy observed lies (`producer.py:159-174`, only when other trials are in
+        flight) the refit that settles the gains contains those lies."""
+        if self._hedge_pending and self.acq_func == "gp_hedge" and len(self._y) > self._hedge_pending[0]:
+            mu = eng.predict_grad(np.asarray(self._hedge_pending[1:], dtype=np.float64))[0]
+            for k in range(3):
+                self._hedge_gains[k] -= float(mu[k])
             self._hedge_pending = None
+
+
+def _env_flag(name, default):
+    import os
+    v = os.environ.get(name)
+    return default if v is None or v == "" else v.strip().lower() not in ("0", "false", "no", "off")
+
+
+def _placement(device):
+    """Device index or list of indices: the constructor keyword, else `OB200_DEVICE`, else 0."""
+    import os
+    if device is None:
+        env = os.environ.get("OB200_DEVICE", "").strip()
+        if not env:
+            return 0
+        ids = [int(t) for t in env.replace(";", ",").split(",") if t.strip()]
+        return ids[0] if len(ids) == 1 else ids
+    if isinstance(device, (list, tuple)):
+        return [int(d) for d in device]
+    return int(device)
 
 
 def saved_theta_ok(theta, d):

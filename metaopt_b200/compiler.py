@@ -151,6 +151,83 @@ def regroup_row(compiled, row, transformed=True):
     return tuple(out)
 
 
+def _slot_columns(compiled):
+    """Per-kind flat column indices and bounds, cached on the compiled space."""
+    cache = getattr(compiled, "_cols", None)
+    if cache is None:
+        real = [s for s in compiled.slots if s["kind"] == _lib.KIND_REAL]
+        integer = [s for s in compiled.slots if s["kind"] == _lib.KIND_INT]
+        col = lambda group: np.asarray([s["out_col"] for s in group], dtype=np.intp)
+        bound = lambda group, key: np.asarray([s[key] for s in group], dtype=np.float64)
+        cache = dict(real=col(real), real_lo=bound(real, "low"), real_hi=bound(real, "high"),
+                     int=col(integer), int_lo=bound(integer, "low"), int_hi=bound(integer, "high"))
+        compiled._cols = cache
+    return cache
+
+
+def contains_rows(compiled, rows):
+    """Vectorised `point in transformed_space` for a `[num x D_out]` array of flat, un-normalised rows of the
+    `requires='real'` space: one boolean per row.
+
+    Replaces the per-point Python check Orion runs on every suggestion (`primary_algo.py:74-81` ->
+    `TransformedDimension.__contains__` `transformer.py:394-402` = `reverse`, then the original dimension's
+    `__contains__`), with the same outcome:
+      * real column: `low <= x < high` with `interval()`'s bounds, upper bound EXCLUSIVE (`space.py:336-356`);
+      * integer column (`Reverse(Quantize)`): the reverse is `floor(x)` (`transformer.py:250`), which is integral by
+        construction, so the test is `low <= floor(x) < high` with the integer interval (`space.py:425-448,467-483`);
+      * categorical columns: `argmax` / `> 0.5` / zeros always name a valid category (`transformer.py:325-343`,
+        `space.py:565-576`) -- nothing to check;
+      * NaN fails every comparison, as it does in numpy."""
+    rows = np.asarray(rows, dtype=np.float64)
+    if rows.ndim != 2 or rows.shape[1] != compiled.d_out:
+        raise ValueError("rows must be [num x %d]; got %r" % (compiled.d_out, rows.shape))
+    c = _slot_columns(compiled)
+    ok = np.ones(rows.shape[0], dtype=bool)
+    if c["real"].size:
+        x = rows[:, c["real"]]
+        ok &= np.all((x >= c["real_lo"]) & (x < c["real_hi"]), axis=1)
+    if c["int"].size:
+        x = np.floor(rows[:, c["int"]])
+        ok &= np.all((x >= c["int_lo"]) & (x < c["int_hi"]), axis=1)
+    return ok
+
+
+def reverse_rows(compiled, rows):
+    """Vectorised `TransformedSpace.reverse` (`transformer.py:375,478-481`) for a `[num x D_out]` array of flat,
+    un-normalised transformed rows: a list of `num` points of the ORIGINAL space (floats, Python ints after `floor`,
+    category objects; 1-D arrays for shaped dimensions), equal to what the reference's per-point reverse returns."""
+    rows = np.asarray(rows, dtype=np.float64)
+    if rows.ndim != 2 or rows.shape[1] != compiled.d_out:
+        raise ValueError("rows must be [num x %d]; got %r" % (compiled.d_out, rows.shape))
+    num = rows.shape[0]
+    columns = []  # per dimension: a [num] or [num x m] array (or object array) of reversed values
+    for item in compiled.layout:
+        c0, m, k, shape = item["col"], item["m"], item["k"], item["shape"]
+        if item["kind"] == "categorical":
+            width = k if k > 2 else 1
+            block = rows[:, c0:c0 + m * width].reshape(num, m, width)
+            if k > 2:
+                idx = block.argmax(axis=2)
+            elif k == 2:
+                idx = (block[:, :, 0] > 0.5).astype(np.intp)
+            else:
+                idx = np.zeros((num, m), dtype=np.intp)
+            cats = np.empty(len(item["categories"]), dtype=object)
+            for j, cat in enumerate(item["categories"]):
+                cats[j] = cat
+            vals = cats[idx]
+        elif item["kind"] == "integer":
+            vals = np.floor(rows[:, c0:c0 + m]).astype(np.int64)
+        else:
+            vals = rows[:, c0:c0 + m]
+        columns.append(vals if shape else vals[:, 0])
+    points = []
+    for i in range(num):
+        points.append(tuple(col[i].copy() if col.ndim == 2 else (col[i] if col.dtype == object else col[i].item())
+                            for col in columns))
+    return points
+
+
 def flatten_point(compiled, point):
     """Inverse of `regroup_row(..., transformed=True)`: tuple of scalars / 1-D arrays -> flat row."""
     flat = []

@@ -52,6 +52,14 @@ class Engine:
         self.n = self.D = 0
         self._fit_host = None   # (kernel key, X) of the last fit from host arrays: lets fit() append one row
         self.n_appends = 0
+        # Cache keys of whoever drives this engine (algo.py, compiler.upload).  They live HERE, on the object that
+        # owns the device state, and every call that replaces that state clears them, so two holders of the same
+        # device (a `device=[0, 1]` and a `device=0` algorithm, or a test calling fit() directly) cannot score
+        # against each other's GP or space.  `fit_generation` counts replacements (MultiEngine replicates on it).
+        self._fit_token = None
+        self._fit_theta = None
+        self._space_key = None
+        self.fit_generation = 0
         self.use_torch_stream()
 
     def close(self):
@@ -86,6 +94,7 @@ class Engine:
             for k, _ in Slot._fields_:
                 setattr(arr[i], k, s[k])
         cdf_arr = (C.c_double * max(len(cdf), 1))(*cdf)
+        self._space_key = None
         self._check(self.lib.ob200_space_set(self.ctx, arr, len(slots), cdf_arr, len(cdf)))
         self.n_slots = len(slots)
         self.d_out = max(s["out_col"] + s["width"] for s in slots)
@@ -128,6 +137,8 @@ class Engine:
         k = Kernel(kind, len(ls), float(amplitude), ls.ctypes.data_as(C.POINTER(C.c_double)))
         key = None
         prev, self._fit_host = self._fit_host, None
+        self._fit_token = self._fit_theta = None
+        self.fit_generation += 1
         if isinstance(X, torch.Tensor):
             X = X.to(self.tdev, torch.float64).contiguous()
             y = torch.as_tensor(y).to(self.tdev, torch.float64).contiguous()
@@ -209,6 +220,8 @@ class Engine:
     def import_state(self, blob, n, D):
         self.use_torch_stream()
         assert blob.dtype == torch.uint8 and blob.is_cuda and blob.is_contiguous()
+        self._fit_token = self._fit_theta = None
+        self.fit_generation += 1
         self._check(self.lib.ob200_gp_import(self.ctx, _ptr(blob), blob.numel()))
         self.n, self.D = n, D
         self._fit_host = None

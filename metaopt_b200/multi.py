@@ -22,10 +22,7 @@ class MultiEngine:
             raise ValueError("devices must be a non-empty list of distinct CUDA device indices: %r" % (devices,))
         self.engines = [get_engine(d) for d in self.devices]
         self.pool = ThreadPoolExecutor(max_workers=len(self.engines))
-        self._replicated = False   # do the other devices hold the current fit?
-        self._space_key = None
-        self._fit_token = None
-        self._fit_theta = None
+        self._replicated_gen = None   # primary.fit_generation the other devices hold a copy of
 
     # ---- pass-throughs to the first device ---------------------------------------------------
     @property
@@ -35,6 +32,38 @@ class MultiEngine:
     @property
     def tdev(self):
         return self.primary.tdev
+
+    # The cache keys of the driver (algo.py / compiler.upload) live on the engines that own the device state, so a
+    # single-device holder of the primary that refits or re-registers a space invalidates this wrapper's view too.
+    @property
+    def _fit_token(self):
+        return self.primary._fit_token
+
+    @_fit_token.setter
+    def _fit_token(self, value):
+        self.primary._fit_token = value
+
+    @property
+    def _fit_theta(self):
+        return self.primary._fit_theta
+
+    @_fit_theta.setter
+    def _fit_theta(self, value):
+        self.primary._fit_theta = value
+
+    @property
+    def _space_key(self):
+        keys = {e._space_key for e in self.engines}
+        return keys.pop() if len(keys) == 1 else None
+
+    @_space_key.setter
+    def _space_key(self, value):
+        for e in self.engines:
+            e._space_key = value
+
+    @property
+    def fit_generation(self):
+        return self.primary.fit_generation
 
     @property
     def launches(self):
@@ -62,22 +91,20 @@ class MultiEngine:
     def set_space(self, slots, cdf):
         for e in self.engines:
             e.set_space(slots, cdf)
-            e._space_key = None
         self.d_out = self.primary.d_out
 
     def fit(self, X, y, **kwargs):
         self.primary.fit(X, y, **kwargs)
-        self._replicated = False
 
     def _replicate(self):
-        if self._replicated or len(self.engines) == 1:
-            return
         src = self.primary
+        if self._replicated_gen == src.fit_generation or len(self.engines) == 1:
+            return
         blob = src.export_state()
         src.sync()
         for e in self.engines[1:]:
             e.import_state(blob.to(e.tdev), src.n, src.D)
-        self._replicated = True
+        self._replicated_gen = src.fit_generation
 
     # ---- sharded scoring -------------------------------------------------------------------------
     def _shards(self, M, first_index):

@@ -1,4 +1,6 @@
-"""Import the UNMODIFIED reference (Orion) from /root/reference with harness-side shims.
+"""Import the UNMODIFIED reference (Orion) with harness-side shims: from /root/reference/src in the build
+container, else from the pip-installed copy under `baseline/_ref` (made by `baseline/install_ref.sh`; it is
+git-ignored but travels to the GPU box, where /root/reference does not exist).
 
 Test infrastructure only (see oracle/__init__.py).  Nothing is copied or edited: the reference's
 `src/` is put on `sys.path` and three things it expects from its 2019 environment are supplied
@@ -7,8 +9,7 @@ in memory:
   2. `pymongo`  -> a stub with the names `core/io/database/mongodb.py` imports (never used with
                    PickledDB / EphemeralDB);
   3. `numpy.object` -> `object` (removed in numpy >= 1.24; used at `algo/space.py:549,572`).
-The reference does not exist on the GPU box: `available()` is False there and every user of this
-module skips.
+`available()` is False when neither location exists and every user of this module skips.
 """
 import importlib.util
 import os
@@ -16,11 +17,34 @@ import sys
 import types
 
 REF_ROOT = "/root/reference"
-REF_SRC = os.path.join(REF_ROOT, "src")
+INSTALLED = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "baseline", "_ref")
+REF_SRC = os.environ.get("OB200_REF_SRC") or next((p for p in (os.path.join(REF_ROOT, "src"), INSTALLED) if os.path.isdir(os.path.join(p, "orion"))),
+               os.path.join(REF_ROOT, "src"))
 
 
 def available():
     return os.path.isdir(os.path.join(REF_SRC, "orion"))
+
+
+def installed_available():
+    """The pip-installed copy (it has dist-info metadata, which entry-point loading checks)."""
+    return os.path.isdir(os.path.join(INSTALLED, "orion"))
+
+
+def write_dist_shims(directory):
+    """Empty `pymongo` / `appdirs` distributions for a sys.path directory: the on-disk twin of the in-memory module
+    shims above.  `pkg_resources` verifies a distribution's `install_requires` chain when the reference's factory
+    loads an entry point (`src/orion/core/utils/__init__.py:111-112`); neither package is in the offline image."""
+    for name, version in (("pymongo", "3.99"), ("appdirs", "1.4.4")):
+        d = os.path.join(directory, "%s-%s.dist-info" % (name, version))
+        os.makedirs(d, exist_ok=True)
+        with open(os.path.join(d, "METADATA"), "w") as f:
+            f.write("Metadata-Version: 2.1\nName: %s\nVersion: %s\n" % (name, version))
+
+
+def source_tree_available():
+    """The reference's own tests/docs (only in the build container), as opposed to the installed package."""
+    return os.path.isdir(os.path.join(REF_ROOT, "tests"))
 
 
 def _install_shims():

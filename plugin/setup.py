@@ -8,7 +8,7 @@ from setuptools import setup
 
 setup(
     name="orion.algo.b200",
-    version="0.1.0",
+    version="0.2.0",
     description="B200-native GP-EI Bayesian optimiser for Oríon (drop-in for orion.algo.skopt's BayesianOptimizer)",
     packages=["orion.algo"],
     package_dir={"": "src"},

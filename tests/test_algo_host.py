@@ -223,3 +223,50 @@ def test_observation_cache_is_path_independent_and_survives_copies_and_lies(fake
     assert fake.calls["fit"] == n_fit + 4                       # the engine holds the last liar fit: one refit, then cached
     a.suggest(1)
     assert fake.calls["fit"] == n_fit + 4
+
+
+def test_placement_and_speed_knobs_stay_out_of_the_stored_configuration(monkeypatch):
+    """Orion stores `configuration` as `experiment.algorithms` and raises AlgorithmConflict when two workers differ
+    there (`src/orion/core/evc/conflicts.py:1034-1038`): which GPU a worker uses must not be part of it."""
+    a = BayesianOptimizer(None, device=3, prune=False)
+    b = BayesianOptimizer(None, device=[0, 1])
+    assert a.configuration == b.configuration
+    conf = a.configuration["bayesianoptimizer"]
+    assert "device" not in conf and "prune" not in conf and not any(k.startswith("_") for k in conf)
+    assert a.device == 3 and a.prune is False and b.device == [0, 1] and b.prune is True
+    monkeypatch.setenv("OB200_DEVICE", "2,5")
+    monkeypatch.setenv("OB200_PRUNE", "0")
+    c = BayesianOptimizer(None)
+    assert c.device == [2, 5] and c.prune is False and c.configuration == a.configuration
+    monkeypatch.setenv("OB200_DEVICE", "1")
+    assert BayesianOptimizer(None).device == 1
+    assert copy.deepcopy(c).device == [2, 5]
+
+
+def test_hedge_gains_are_settled_with_the_refitted_model(fake):
+    """skopt: `gains_ -= est.predict(next_xs_)` with `est` refitted on the new observation."""
+    t = build_required_space("real", small_space())
+    a = BayesianOptimizer(t, seed=2, n_initial_points=4, acq_func="gp_hedge", n_points=200, fit_hyperparameters=False)
+    for p in a.suggest(4):
+        a.observe([p], [{"objective": objective(t.reverse(p))}])
+    (p,) = a.suggest(1)
+    pending = np.asarray(a._hedge_pending[1:])
+    assert a._hedge_pending[0] == 4 and pending.shape == (3, 5) and a._hedge_gains == [0.0, 0.0, 0.0]
+    a.observe([p], [{"objective": objective(t.reverse(p))}])
+    assert a._hedge_gains == [0.0, 0.0, 0.0]            # nothing happens before the refit
+    b = copy.deepcopy(a)                                 # what the producer does: the copy suggests ...
+    b.suggest(1)
+    mu_new = fake.model.predict(pending)[0]              # ... after refitting on 5 observations
+    assert len(fake.model.X) == 5
+    np.testing.assert_allclose(b._hedge_gains, -mu_new, rtol=1e-12)
+    a.set_state(b.state_dict)                            # ... and its state comes back (`producer.py:84`)
+    np.testing.assert_allclose(a._hedge_gains, -mu_new, rtol=1e-12)
+    # a constant-liar batch leaves the portfolio as the first (real-data) pick left it
+    gains = list(a._hedge_gains)
+    a.observe([p], [{"objective": 0.123}])
+    a.suggest(3)
+    settled = list(a._hedge_gains)
+    assert settled != gains and len(a._hedge_pending) == 4 and a._hedge_pending[0] == 6
+    c = copy.deepcopy(a)
+    c.suggest(1)                                         # same data, no refit of new data -> pending replaced, gains kept
+    assert c._hedge_gains == settled

@@ -70,6 +70,19 @@ def test_cfg2_shape_n2000_d20(engine):
     _compare(engine, X, y, C)
 
 
+def test_cfg3_shape_n4000_d60(engine):
+    """BASELINE config 3 at its real size (n = 4000, D = 60 after one-hot) at a CPU-checkable candidate count:
+    observations AND candidates are points of the mixed space (10 Integer, 10 Categorical k=4, 10 Real),
+    normalised with the bounds of `interval()` (one-hot columns live in (-0.1, 1.1))."""
+    comp = compiler.compile_space(transformed(cfg3_space()))
+    assert comp.d_out == 60
+    compiler.upload(engine, comp)
+    X = engine.sample(3, 0, 4000).cpu().numpy()
+    y = ((X - 0.5) ** 2).sum(axis=1) + 0.01 * np.random.RandomState(0).randn(4000)
+    C = engine.sample(11, 0, 5000).cpu().numpy()
+    _compare(engine, X, y, C)
+
+
 def test_largest_supported_fit_n8000_d100(engine):
     """BASELINE config 4 shape at a CPU-checkable candidate count: the n = 8000 Cholesky / inverse / alpha path."""
     X, y = gp_problem(8000, 100, seed=5)

@@ -250,3 +250,60 @@ def test_transformed_mirror_matches_reference_transformed_space():
             ri, mi = rd.interval(), md.interval()
             assert (float(np.ravel(ri[0])[0]), float(np.ravel(ri[1])[0])) == (float(np.ravel(mi[0])[0]), float(np.ravel(mi[1])[0]))
             assert tuple(rd.shape or ()) == md.shape
+
+
+def _random_rows(comp, num, rng):
+    """Rows of the transformed space that straddle every bound: inside, on the bounds, just outside, NaN."""
+    rows = np.zeros((num, comp.d_out))
+    for s in comp.slots:
+        c0, w = s["out_col"], s["width"]
+        if s["kind"] == 2:  # categorical: anything goes (soft one-hot vectors, out-of-range scalars)
+            rows[:, c0:c0 + w] = rng.uniform(-0.5, 1.5, size=(num, w))
+            continue
+        lo, hi = max(s["low"], -60.0), min(s["high"], 60.0)
+        v = rng.uniform(lo - 0.2 * (hi - lo), hi + 0.2 * (hi - lo), size=num)
+        special = np.array([lo, hi, np.nextafter(hi, lo), np.nextafter(lo, lo - 1), lo + 0.5, hi - 0.5, hi + 0.5, np.floor(hi)])
+        where = rng.uniform(size=num) < 0.25
+        v[where] = rng.choice(special, size=int(where.sum()))
+        inside = rng.uniform(size=num) < 0.8   # most entries inside, so that whole rows are accepted often enough
+        v[inside] = rng.uniform(lo, hi, size=int(inside.sum()))
+        v[rng.uniform(size=num) < 0.1] = rng.choice(special, size=1)[0]
+        rows[:, c0] = v
+    rows[rng.randint(num, size=3), rng.randint(comp.d_out, size=3)] = np.nan
+    return rows
+
+
+@needs_ref
+def test_vectorised_contains_and_reverse_match_the_reference_point_by_point():
+    """`compiler.contains_rows` / `reverse_rows` against the reference's own per-point path
+    (`primary_algo.py:74-81`: `point in transformed_space`, `transformed_space.reverse(point)`)."""
+    rs, ms = _ref_and_mirror()
+    from orion.core.worker.transformer import build_required_space as ref_build
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        rt = ref_build("real", rs)
+        comp = compiler.compile_space(rt)
+        rng = np.random.RandomState(11)
+        rows = _random_rows(comp, 10000, rng)
+        ok = compiler.contains_rows(comp, rows)
+        assert 500 < ok.sum() < 9500                   # both outcomes are well represented
+        points = [compiler.regroup_row(comp, row, transformed=True) for row in rows]
+        want = np.array([bool(p in rt) for p in points])
+        assert np.array_equal(ok, want), np.flatnonzero(ok != want)[:10]
+        back = compiler.reverse_rows(comp, rows[ok][:2000])
+        for p, mine in zip([q for q, o in zip(points, ok) if o][:2000], back):
+            theirs = rt.reverse(p)
+            assert mine in rs
+            for a, b in zip(theirs, mine):
+                assert np.array_equal(np.asarray(a, dtype=object), np.asarray(b, dtype=object)), (theirs, mine)
+                if np.asarray(a).dtype.kind in "if":   # ints stay ints, floats stay floats (categories: 0-d object arrays there)
+                    assert np.asarray(a).dtype.kind == np.asarray(b).dtype.kind
+    # the exclusive upper bound (`space.py:356`): x == high is rejected, the float just below is accepted
+    row = rows[ok][0].copy()
+    s = [s for s in comp.slots if s["kind"] == 0][0]
+    row[s["out_col"]] = s["high"]
+    assert not compiler.contains_rows(comp, row[None])[0]
+    row[s["out_col"]] = np.nextafter(s["high"], s["low"])
+    assert compiler.contains_rows(comp, row[None])[0]
+    with pytest.raises(ValueError):
+        compiler.contains_rows(comp, rows[:, :-1])

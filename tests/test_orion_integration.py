@@ -1,9 +1,12 @@
 """The plugin under the UNMODIFIED reference: `PrimaryAlgo`, the Producer's deepcopy/set_state
 protocol and a real `orion hunt` run (BASELINE config 1 shape, shortened) on PickledDB.
 
-Runs only where /root/reference exists (the build container, which has no GPU), so the device is the
-oracle-backed stand-in `OracleEngine`; the same plugin code runs against the real CUDA engine in
-tests/test_gpu_algo.py on the GPU box."""
+Every test runs in two flavours: `oracle` (CPU: the device is the oracle-backed stand-in `OracleEngine`; this is
+what the build container, which has no GPU, can run) and `cuda` (marked gpu: the SAME unmodified reference --
+pip-installed under `baseline/_ref` by `baseline/install_ref.sh`, which travels to the GPU box -- drives the real
+CUDA engine through the real `orion.algo.base.BaseAlgorithm`, `PrimaryAlgo` and `orion hunt`).  The `cuda` flavour
+also runs BASELINE config 1 as stated (2-D Rosenbrock, 50 trials, 10 000 candidates, default plugin mode) with a
+per-suggest parity replay against the oracle on the same candidates."""
 import copy
 import os
 import sys
@@ -15,11 +18,29 @@ import pytest
 
 from oracle import ref_loader
 
-pytestmark = pytest.mark.skipif(not ref_loader.available(), reason="/root/reference is only in the build container")
+pytestmark = pytest.mark.skipif(not ref_loader.available(),
+                                reason="needs the reference: /root/reference or baseline/_ref (baseline/install_ref.sh)")
 
 
-@pytest.fixture()
-def orion_env(monkeypatch):
+class _Counted:
+    """The real engine with call counters on the three entry points the tests look at."""
+
+    def __init__(self, eng, monkeypatch):
+        self.eng = eng
+        self.calls = {"sample": 0, "fit": 0, "score": 0}
+        for name, key in (("sample", "sample"), ("fit", "fit"), ("score", "score"), ("score_pruned", "score"),
+                          ("score_pruned_multi", "score")):
+            monkeypatch.setattr(eng, name, self._wrap(getattr(eng, name), key))
+
+    def _wrap(self, fn, key):
+        def call(*a, **k):
+            self.calls[key] += 1
+            return fn(*a, **k)
+        return call
+
+
+@pytest.fixture(params=["oracle", pytest.param("cuda", marks=pytest.mark.gpu)])
+def orion_env(request, monkeypatch):
     warnings.simplefilter("ignore")
     ref_loader.load()
     # numpy >= 2 returns a tuple from meshgrid; the 2019 reference concatenates it with a list
@@ -27,14 +48,26 @@ def orion_env(monkeypatch):
     real_meshgrid = np.meshgrid
     monkeypatch.setattr(np, "meshgrid", lambda *a, **k: list(real_meshgrid(*a, **k)))
     import metaopt_b200.engine as engine_mod
-    from fake_engine import OracleEngine
-    eng = OracleEngine()
-    monkeypatch.setattr(engine_mod, "get_engine", lambda device=None: eng)
+    if request.param == "oracle":
+        from fake_engine import OracleEngine
+        eng = OracleEngine()
+        monkeypatch.setattr(engine_mod, "get_engine", lambda device=None: eng)
+    else:
+        eng = _Counted(engine_mod.get_engine(0), monkeypatch)   # libob200.so on cuda:0, nothing replaced
+    eng.flavour = request.param
     import importlib
     from metaopt_b200 import algo
     if not algo.HAVE_ORION:  # imported earlier in this process, before the reference was on sys.path
         importlib.reload(algo)
     algo.register()
+    # the reference's storage/database are process-wide singletons: every test starts without them
+    # (what the reference's own `tests/conftest.py:201-209` fixture does)
+    from orion.core.io.database import Database
+    from orion.core.io.database.pickleddb import PickledDB
+    from orion.storage.base import Storage
+    from orion.storage.legacy import Legacy
+    for cls in (Storage, Legacy, Database, PickledDB):
+        cls.instance = None
     return eng
 
 
@@ -62,6 +95,8 @@ def test_plugin_is_a_real_basealgorithm_and_is_discoverable(orion_env):
     a = OptimizationAlgorithm("BayesianOptimizer", _space(), seed=1, n_points=50)
     assert isinstance(a, BayesianOptimizer) and a.n_points == 50
     assert a.configuration["bayesianoptimizer"]["acq_func"] == "gp_hedge"
+    # `base.py:87-119`: a `seed` kwarg calls seed_rng() during super().__init__, before the subclass body ends
+    assert a._seed is not None and a._offset == 0 and a.configuration["bayesianoptimizer"]["seed"] == 1
 
 
 def test_primary_algo_drives_the_plugin(orion_env):
@@ -151,3 +186,83 @@ def test_orion_hunt_end_to_end(orion_env, tmp_path, monkeypatch):
         x = [p["value"] for p in t["params"] if p["name"] == "/x"][0]
         y = [p["value"] for p in t["params"] if p["name"] == "/y"][0]
         assert -2 <= x < 4 and -1 <= y < 4  # Orion prior strings are uniform(low, high)
+
+
+@pytest.mark.parametrize("orion_env", [pytest.param("cuda", marks=pytest.mark.gpu)], indirect=True)
+def test_cfg1_orion_hunt_50_trials_10k_candidates_on_the_device(orion_env, tmp_path, monkeypatch):
+    """BASELINE config 1 as stated: `orion hunt` (unmodified reference: CLI -> experiment -> worker -> Producer ->
+    PrimaryAlgo) on 2-D Rosenbrock, 50 trials, 10 000 candidates per suggest, default plugin mode for the GP
+    (hyper-parameters fitted on the device), EI.  Every GP suggestion is recorded and replayed afterwards against
+    the oracle (scikit-learn GP with the SAME fitted hyper-parameters + restated EI) on the same candidates."""
+    from oracle import acquisition as oacq
+    from oracle import gp as ogp
+    from oracle import sampling as osamp
+    from metaopt_b200 import algo as algo_mod
+    from metaopt_b200 import compiler
+    from orion.storage.base import Storage
+    from orion.storage.legacy import Legacy
+    if "legacy" not in Storage.typenames:
+        Storage.types.append(Legacy)
+        Storage.typenames.append("legacy")
+    records = []
+    real_suggest_gp = algo_mod.BayesianOptimizer._suggest_gp
+
+    def recording(self, eng, comp):
+        before = self._offset
+        row = real_suggest_gp(self, eng, comp)
+        records.append(dict(offset=before, seed=self._seed, X=np.array(self._X), y=np.array(self._y),
+                            theta=copy.deepcopy(self._theta), row=np.array(row), comp=comp))
+        return row
+    monkeypatch.setattr(algo_mod.BayesianOptimizer, "_suggest_gp", recording)
+
+    script = tmp_path / "rosen.py"
+    script.write_text(textwrap.dedent("""\
+        #!%s
+        import argparse, json, os
+        p = argparse.ArgumentParser(); p.add_argument("-x", type=float); p.add_argument("-y", type=float)
+        a = p.parse_args()
+        f = (1 - a.x) ** 2 + 100 * (a.y - a.x ** 2) ** 2
+        json.dump([dict(name="rosen", type="objective", value=f)], open(os.environ["ORION_RESULTS_PATH"], "w"))
+        """ % sys.executable))
+    script.chmod(0o755)
+    cfg = tmp_path / "cfg.yaml"
+    cfg.write_text(textwrap.dedent("""\
+        name: b200-rosen-cfg1
+        max_trials: 50
+        pool_size: 1
+        algorithms:
+          bayesianoptimizer:
+            seed: 1
+            n_initial_points: 10
+            acq_func: EI
+            n_points: 10000
+            normalize_y: true
+        database:
+          type: pickleddb
+          host: %s
+        """ % (tmp_path / "db.pkl")))
+    monkeypatch.chdir(tmp_path)
+    import orion.core.cli
+    orion.core.cli.main(["hunt", "--config", str(cfg), str(script), "-x~uniform(-2, 2)", "-y~uniform(-1, 3)"])
+    import pickle
+    db = pickle.load(open(tmp_path / "db.pkl", "rb"))
+    done = [t for t in db.read("trials", {}) if t["status"] == "completed"]
+    assert len(done) >= 50
+    objectives = [r["value"] for t in done for r in t["results"] if r["type"] == "objective"]
+    # random search at equal budget from the reference's own sampler
+    from orion.algo.space import Real, Space
+    space = Space()
+    space.register(Real("/x", "uniform", -2, 4))   # scipy notation (loc, scale) == Orion prior uniform(-2, 2)
+    space.register(Real("/y", "uniform", -1, 4))
+    rnd = [(1 - x) ** 2 + 100 * (y - x ** 2) ** 2 for x, y in space.sample(50, seed=1)]
+    assert min(objectives) < min(rnd)
+    assert orion_env.calls["score"] >= 40 and len(records) >= 40
+    # per-suggest parity replay
+    for rec in records:
+        comp = rec["comp"]
+        C, _ = osamp.sample_transform(comp.slots, comp.cdf, rec["seed"], rec["offset"], 10000, True)
+        amp, ls, noise = rec["theta"]
+        model = ogp.SklearnGP(0, amp, np.broadcast_to(np.asarray(ls, float), (2,)).copy(), 1e-10 + noise, True).fit(rec["X"], rec["y"])
+        mu, sd = model.predict(C)
+        pick = oacq.pick(oacq.ACQ_EI, mu, sd, float(rec["y"].min()))
+        np.testing.assert_allclose(rec["row"], comp.denormalise(C[pick]), rtol=1e-12, atol=1e-12)
