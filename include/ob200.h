@@ -194,12 +194,28 @@ int ob200_score_async(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64
 int ob200_score_pruned(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M, uint64_t seed,
                        uint64_t first_index, int acq, double y_opt, double xi, double kappa,
                        ob200_best* best_host, int64_t* n_scored_host);
-/* The same for several acquisitions at once (acq_mask bits 1 << OB200_ACQ_*; the gp_hedge portfolio): the mean-only
- * pass is shared, the selection runs per acquisition.  best_host [3] and n_scored_host [3] (may be NULL) are indexed
- * by OB200_ACQ_*; entries outside the mask are zeroed. */
+/* The same for several acquisitions at once (acq_mask bits 1 << OB200_ACQ_*; the gp_hedge portfolio): one bound
+ * pass, one selection (the union over the acquisitions), every selected candidate scored for all of them.
+ * best_host [3] and n_scored_host [3] (may be NULL) are indexed by OB200_ACQ_*; entries outside the mask are zeroed.
+ * The bound pass runs in FP32 on the TF32 tensor cores with a rigorous error budget (mu_lb <= mu, sigma_ub >= sigma;
+ * csrc/ob200_bound.cu); candidates it cannot exclude get exact FP64 bounds before the O(n^2) scoring, so the winner
+ * stays bit-identical to the dense call.  OB200_BOUND_F32=0 in the environment selects the FP64 bound pass for
+ * everything.  -LCB with kappa < 0 is not increasing in sigma: such calls take the dense path.  y_opt, xi, kappa must
+ * be finite (OB200_EINVAL otherwise, in every score entry point).  One host synchronisation per call. */
 int ob200_score_pruned_multi(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M, uint64_t seed,
                              uint64_t first_index, int acq_mask, double y_opt, double xi, double kappa,
                              ob200_best* best_host, int64_t* n_scored_host);
+
+/* Pass 1 of the pruned path on its own (no reference counterpart; used by the tests and tools to check the
+ * bounds): mu_lb_dev[i] <= posterior mean and sigma_ub_dev[i] >= posterior std of candidate i, same units as
+ * ob200_score.  *used_f32 (may be NULL) = 1 when the FP32 bound kernel produced them, 0 when the FP64 mean-only
+ * kernel did (mu_lb is then the mean itself).  Asynchronous on the context's stream. */
+int ob200_score_bounds(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M, double* mu_lb_dev,
+                       double* sigma_ub_dev, int* used_f32);
+/* Counters of the last ob200_score_pruned[_multi] call that took the pruned path: out[0] = FP32 bound pass used,
+ * out[1] = candidates in the first batch, out[2] = candidates the pass-1 bounds left for the second batch,
+ * out[3] = of those, the ones still standing after their bounds were recomputed in FP64 (0 when out[0] == 0). */
+int ob200_prune_stats(const ob200_ctx* ctx, int64_t out[4]);
 
 /* a16-a17 alone: acquisition + first-occurrence argmax over given posterior arrays
  * (skopt.acquisition.gaussian_ei/pi/lcb + numpy.argmin).  mu_dev, sigma_dev [M]. */
@@ -222,7 +238,9 @@ int ob200_acq_argmax(ob200_ctx* ctx, const double* mu_dev, const double* sigma_d
  *     stream capture.
  *   - all calls share the one scratch array (it keeps the previous call's records, none of which
  *     a later call reads before overwriting): two calls that overlap on the GPU -- different
- *     streams or host threads -- race on it; serialise them. */
+ *     streams or host threads -- race on it; serialise them.
+ *   - the looked-up address is cached per device for the life of the process; a host that calls
+ *     cudaDeviceReset() invalidates it and must not call this function on that device again. */
 int ob200_acq_argmax_static(const double* mu_dev, const double* sigma_dev, int64_t M, uint64_t first_index,
                             int acq_mask, double y_opt, double xi, double kappa, ob200_best* best_dev,
                             double* acq_dev, void* cuda_stream, char* errbuf, int errbuf_len);

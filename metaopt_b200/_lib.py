@@ -73,6 +73,8 @@ SIGNATURES = {
     "ob200_score_async": (_i, [_vp, _vp, _i64, _i64, _u64, _u64, _i, _d, _d, _d, _vp, _vp, _vp, _vp]),
     "ob200_score_pruned": (_i, [_vp, _vp, _i64, _i64, _u64, _u64, _i, _d, _d, _d, C.POINTER(Best), C.POINTER(_i64)]),
     "ob200_score_pruned_multi": (_i, [_vp, _vp, _i64, _i64, _u64, _u64, _i, _d, _d, _d, C.POINTER(Best), C.POINTER(_i64)]),
+    "ob200_score_bounds": (_i, [_vp, _vp, _i64, _i64, _vp, _vp, C.POINTER(_i)]),
+    "ob200_prune_stats": (_i, [_vp, C.POINTER(_i64)]),
     "ob200_acq_argmax": (_i, [_vp, _vp, _vp, _i64, _u64, _i, _d, _d, _d, C.POINTER(Best), _vp]),
     "ob200_acq_argmax_static": (_i, [_vp, _vp, _i64, _u64, _i, _d, _d, _d, _vp, _vp, _vp, C.c_char_p, _i]),
 }

@@ -6,7 +6,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
-SOURCES = ["ob200_ctx.cu", "ob200_sample.cu", "ob200_fit.cu", "ob200_score.cu"]
+SOURCES = ["ob200_ctx.cu", "ob200_sample.cu", "ob200_fit.cu", "ob200_score.cu", "ob200_bound.cu"]
 LIB = os.path.join(HERE, "libob200.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

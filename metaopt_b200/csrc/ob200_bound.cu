@@ -1,0 +1,417 @@
+// Bound pass of the exact pruned scoring: for every candidate, a LOWER bound of the posterior mean and an UPPER
+// bound of the posterior standard deviation, from the cross-kernel alone, in FP32 on the TF32 tensor cores.
+//
+// Why it may be inexact: the pruned path (ob200_score.cu) only needs U(mu_lb, sigma_ub) >= U(mu, sigma); every
+// candidate whose bound reaches the incumbent is re-scored by the FP64 score kernel, so the argmax and the
+// winner's values stay bit-identical to the dense call however loose the bound is.  What the bound must be is
+// RIGOROUS, so this kernel carries its own error budget:
+//     mu~   = sum_j k~_j alpha_j              (k~ = FP32 kernel value, alpha rounded to FP32)
+//     S~    = sum_j k~_j |alpha_j|
+//     |mu - mu~| <= y_std * S~ * rel(c)       rel(c) = relative error bound of one kernel value for candidate c
+//     k_max >= k~_max * (1 - rel(c))          (nearest observation -> sigma bound, see score_kernel<MEAN_ONLY>)
+// rel(c) is assembled below (`bound_rel`) from: the 3xTF32 split of the distance contraction (dropped lo*lo term
+// and split residuals), a deliberately generous model of the tensor core's FP32 accumulation, the FP32 roundings of
+// ||c||^2, ||x||^2, the MUFU.SQRT / MUFU.EX2 approximations and the FP32 partial sums (flushed into FP64 every
+// observation chunk).  tests/test_gpu_bound.py checks mu_lb <= mu and sigma_ub >= sigma against the FP64 kernel on
+// every candidate of the fuzz cases and reports how much of the budget is actually used.
+//
+// Replaces (for the bound only) sklearn kernels.py:1720-1729 / :1569-1570 and _gpr.py:446-447.
+//
+// Work decomposition: CTA tile = CT candidates (128 / 64 / 32, the largest whose A fragments fit) x all observed
+// points; 8 consumer warps as WC x WO, each with a 32-candidate x (128 / WO)-observation register tile of
+// mma.sync.m16n8k8 TF32 accumulators; observed points arrive in chunks of 128, pre-split into TF32 hi/lo B
+// fragments at fit time, staged by bulk async copies (TMA engine) from a producer warp through an mbarrier ring.
+// The distance is in "T units": coordinates are pre-scaled so that Matern-5/2 is (1 + t + t^2/3) e^-t with
+// t = sqrt(T) and RBF is e^-T.
+#include <math.h>
+#include <stdlib.h>
+
+#include "ob200_internal.cuh"
+
+namespace {
+
+#define BD_OBC 128            // observed points per chunk
+#define BD_WARPS 8            // consumer warps
+#define BD_THREADS ((BD_WARPS + 1) * 32)
+#define BD_STAGES_MAX 4
+
+struct bound_args {
+  const double* cand; long long ldc; long long M;
+  const double* ls;
+  const float4* bp;     // [chunk][kslice][obs8 (16)][kstep in slice (ksl)][lane] {hi b0, hi b1, lo b0, lo b1}
+  const float4* aux;    // [obs8][q] {T-space ||x||^2 of obs 2q, 2q+1, amplitude-free alpha of obs 2q, 2q+1}
+  int n_chunks, D, nk, ksl, n_slices, kind, stages;
+  double scale;         // coordinate scale: T = ||scale (c - x) / ls||^2
+  double amplitude, y_mean, y_std, diag;
+  const double* xx_max; // device scalar: the largest T-space ||x||^2 over the real observations
+  double g_T;           // absolute error of T~ per unit of (sqrt(cc) + sqrt(xx_max))^2
+  double c0, c1;        // function-evaluation error: c0 + c1 * t_max
+  double tiny;          // absolute slack (flushed denormals)
+  double* mu_lb; double* sigma_ub;
+  long long n_tiles;
+};
+
+__device__ __forceinline__ uint32_t to_tf32(float v) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
+  return r;
+}
+__device__ __forceinline__ float sqrt_approx(float v) {
+  float r;
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(v));
+  return r;
+}
+__device__ __forceinline__ float ex2_approx(float v) {
+  float r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(v));
+  return r;
+}
+// D(16x8, f32) += A(16x8, tf32, row) * B(8x8, tf32, col)
+// lane (g = lane/4, q = lane%4): a0 = A[g][q], a1 = A[g+8][q], a2 = A[g][q+4], a3 = A[g+8][q+4];
+// b0 = B[q][g], b1 = B[q+4][g]; c0 = C[g][2q], c1 = C[g][2q+1], c2 = C[g+8][2q], c3 = C[g+8][2q+1]
+__device__ __forceinline__ void mma_tf32(float (&c)[4], const uint32_t a0, const uint32_t a1, const uint32_t a2,
+                                         const uint32_t a3, const uint32_t b0, const uint32_t b1) {
+  asm("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+      : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+__host__ __device__ inline size_t bound_smem_bytes(int ct, int nk, int ksl, int stages) {
+  return (size_t)(ct / 16) * nk * 1024            // A fragments (hi plane + lo plane)
+         + (size_t)stages * ksl * 8192            // B stages
+         + (size_t)ct * 8                         // cc
+         + (size_t)3 * 256 * 8                    // cross-warp reduction (mu, S, kmax): WO x CT = 256 entries each
+         + 2 * BD_STAGES_MAX * 8 + 128;
+}
+
+template <int KIND>
+__device__ __forceinline__ float kernel_T(float T) {
+  if (KIND == OB200_KERNEL_MATERN52) {
+    const float t = sqrt_approx(T);
+    const float p = fmaf(t, fmaf(t, 0.333333343f, 1.0f), 1.0f);
+    return p * ex2_approx(t * -1.44269504f);
+  }
+  return ex2_approx(T * -1.44269504f);
+}
+
+// WC = warps along the candidates (CT = 32 WC); WO = 8 / WC warps along the observations; NB = n8 blocks per warp
+template <int WC, int KIND>
+__global__ void __launch_bounds__(BD_THREADS, 1) bound_kernel(bound_args a) {
+  constexpr int CT = 32 * WC, WO = BD_WARPS / WC, NB = (BD_OBC / 8) / WO;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  const int nk = a.nk, ksl = a.ksl;
+  float4* As = reinterpret_cast<float4*>(smem_raw);                                   // [CT/16][nk][hi | lo][32]
+  float4* Bs = As + (size_t)(CT / 16) * nk * 64;                                      // stages x [16][ksl][32]
+  double* cc = reinterpret_cast<double*>(Bs + (size_t)a.stages * ksl * 512);          // [CT]
+  double* red = cc + CT;                                                              // [3][WO][CT]
+  uint64_t* full = reinterpret_cast<uint64_t*>(red + 3 * WO * CT);
+  uint64_t* empty = full + BD_STAGES_MAX;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int g = lane >> 2, q = lane & 3;
+  if (tid == 0) {
+    for (int s = 0; s < BD_STAGES_MAX; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], BD_WARPS); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+
+  uint32_t it = 0;
+  const uint32_t stage_bytes = (uint32_t)ksl * 8192u;
+  if (warp == BD_WARPS) {   // ---- producer warp: B stages for every tile this CTA owns
+    if (lane == 0) {
+      for (long long tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x)
+        for (int c = 0; c < a.n_chunks; ++c)
+          for (int s = 0; s < a.n_slices; ++s, ++it) {
+            const int st = it % a.stages;
+            const uint32_t ph = (it / a.stages) & 1;
+            mbar_wait(&empty[st], ph ^ 1);
+            mbar_expect_tx(&full[st], stage_bytes);
+            bulk_g2s(Bs + (size_t)st * ksl * 512, a.bp + ((size_t)c * a.n_slices + s) * ksl * 512, stage_bytes, &full[st]);
+          }
+    }
+    return;
+  }
+
+  const int wc = warp / WO, wo = warp % WO;
+  for (long long tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+    const long long row0 = tile * CT;
+    // ---- stage the candidate tile: u = scale * c / ls -> TF32 hi/lo A fragments; cc = ||u||^2 in FP64.
+    // Two threads per row (even / odd columns).
+    {
+      const int r = tid >> 1, half = tid & 1;
+      const bool live = r < CT && row0 + r < a.M;
+      double acc = 0.0;
+      if (r < CT) {
+        const int mb = r >> 4, rr = r & 15, gg = rr & 7, hi8 = rr >> 3;
+        const double* src = a.cand + (size_t)(row0 + r) * a.ldc;
+        for (int d = half; d < nk * 8; d += 2) {
+          double u = 0.0;
+          if (live && d < a.D) u = a.scale * src[d] / a.ls[d];
+          acc = fma(u, u, acc);
+          const float uf = (float)u;
+          const uint32_t hi = to_tf32(uf);
+          const uint32_t lo = to_tf32(uf - __uint_as_float(hi));
+          const int ks = d >> 3, kk = d & 7, qq = kk & 3, hi4 = kk >> 2;
+          uint32_t* dst = reinterpret_cast<uint32_t*>(As + (size_t)(mb * nk + ks) * 64 + (gg * 4 + qq));
+          dst[hi8 + 2 * hi4] = hi;
+          dst[32 * 4 + hi8 + 2 * hi4] = lo;
+        }
+      }
+      acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+      if (r < CT && half == 0) cc[r] = acc;
+    }
+    asm volatile("bar.sync 1, %0;" ::"n"(BD_WARPS * 32) : "memory");
+
+    float ccr[2][2];
+#pragma unroll
+    for (int mb = 0; mb < 2; ++mb) { ccr[mb][0] = (float)cc[wc * 32 + mb * 16 + g]; ccr[mb][1] = (float)cc[wc * 32 + mb * 16 + g + 8]; }
+    double mu64[2][2] = {{0.0, 0.0}, {0.0, 0.0}}, s64[2][2] = {{0.0, 0.0}, {0.0, 0.0}};
+    float kmx[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
+    const float4* Aw = As + (size_t)(wc * 2) * nk * 64 + lane;
+
+    for (int c = 0; c < a.n_chunks; ++c) {
+      float acc[2][NB][4];
+#pragma unroll
+      for (int mb = 0; mb < 2; ++mb)
+#pragma unroll
+        for (int nb = 0; nb < NB; ++nb)
+#pragma unroll
+          for (int e = 0; e < 4; ++e) acc[mb][nb][e] = 0.f;
+      const float4* axp = a.aux + ((size_t)(c * (BD_OBC / 8) + wo * NB)) * 4 + q;   // this lane's observation constants
+
+      for (int s = 0; s < a.n_slices; ++s, ++it) {
+        const int st = it % a.stages;
+        const uint32_t ph = (it / a.stages) & 1;
+        mbar_wait(&full[st], ph);
+        const float4* Bw = Bs + (size_t)st * ksl * 512 + (size_t)(wo * NB) * ksl * 32 + lane;
+        const int jn = min(ksl, nk - s * ksl);
+        for (int j = 0; j < jn; ++j) {
+          const int ks = s * ksl + j;
+          float4 ah[2], al[2];
+#pragma unroll
+          for (int mb = 0; mb < 2; ++mb) { ah[mb] = Aw[(size_t)(mb * nk + ks) * 64]; al[mb] = Aw[(size_t)(mb * nk + ks) * 64 + 32]; }
+#pragma unroll
+          for (int nb = 0; nb < NB; ++nb) {
+            const float4 b = Bw[(size_t)(nb * ksl + j) * 32];
+            const uint32_t bh0 = __float_as_uint(b.x), bh1 = __float_as_uint(b.y), bl0 = __float_as_uint(b.z), bl1 = __float_as_uint(b.w);
+#pragma unroll
+            for (int mb = 0; mb < 2; ++mb) {
+              const uint32_t h0 = __float_as_uint(ah[mb].x), h1 = __float_as_uint(ah[mb].y), h2 = __float_as_uint(ah[mb].z), h3 = __float_as_uint(ah[mb].w);
+              mma_tf32(acc[mb][nb], __float_as_uint(al[mb].x), __float_as_uint(al[mb].y), __float_as_uint(al[mb].z), __float_as_uint(al[mb].w), bh0, bh1);
+              mma_tf32(acc[mb][nb], h0, h1, h2, h3, bl0, bl1);
+              mma_tf32(acc[mb][nb], h0, h1, h2, h3, bh0, bh1);
+            }
+          }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty[st]);
+      }
+      // ---- epilogue of the chunk: kernel values, mean / |mean| partial sums, nearest observation
+      float mu32[2][2] = {{0.f, 0.f}, {0.f, 0.f}}, s32[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
+#pragma unroll
+      for (int nb = 0; nb < NB; ++nb) {
+        const float4 ax = __ldg(axp + nb * 4);
+        const float xx0 = ax.x, xx1 = ax.y, al0 = ax.z, al1 = ax.w;
+        const float ab0 = fabsf(al0), ab1 = fabsf(al1);
+#pragma unroll
+        for (int mb = 0; mb < 2; ++mb)
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const float T0 = fmaxf(fmaf(-2.f, acc[mb][nb][2 * h], ccr[mb][h] + xx0), 0.f);
+            const float T1 = fmaxf(fmaf(-2.f, acc[mb][nb][2 * h + 1], ccr[mb][h] + xx1), 0.f);
+            const float k0 = kernel_T<KIND>(T0), k1 = kernel_T<KIND>(T1);
+            mu32[mb][h] = fmaf(k0, al0, mu32[mb][h]);
+            mu32[mb][h] = fmaf(k1, al1, mu32[mb][h]);
+            s32[mb][h] = fmaf(k0, ab0, s32[mb][h]);
+            s32[mb][h] = fmaf(k1, ab1, s32[mb][h]);
+            kmx[mb][h] = fmaxf(kmx[mb][h], fmaxf(k0, k1));
+          }
+      }
+#pragma unroll
+      for (int mb = 0; mb < 2; ++mb)
+#pragma unroll
+        for (int h = 0; h < 2; ++h) { mu64[mb][h] += (double)mu32[mb][h]; s64[mb][h] += (double)s32[mb][h]; }
+    }
+
+    // ---- reduce over the 4 column lanes, then over the WO observation warps through shared memory
+#pragma unroll
+    for (int mb = 0; mb < 2; ++mb)
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        double m = mu64[mb][h], s = s64[mb][h];
+        float k = kmx[mb][h];
+        m += __shfl_xor_sync(0xffffffffu, m, 1); m += __shfl_xor_sync(0xffffffffu, m, 2);
+        s += __shfl_xor_sync(0xffffffffu, s, 1); s += __shfl_xor_sync(0xffffffffu, s, 2);
+        k = fmaxf(k, __shfl_xor_sync(0xffffffffu, k, 1)); k = fmaxf(k, __shfl_xor_sync(0xffffffffu, k, 2));
+        if (q == 0) {
+          const int r = wc * 32 + mb * 16 + h * 8 + g;
+          red[(0 * WO + wo) * CT + r] = m;
+          red[(1 * WO + wo) * CT + r] = s;
+          red[(2 * WO + wo) * CT + r] = (double)k;
+        }
+      }
+    asm volatile("bar.sync 1, %0;" ::"n"(BD_WARPS * 32) : "memory");
+    if (tid < CT && row0 + tid < a.M) {
+      double m = 0.0, s = 0.0, k = 0.0;
+#pragma unroll
+      for (int w = 0; w < WO; ++w) { m += red[(0 * WO + w) * CT + tid]; s += red[(1 * WO + w) * CT + tid]; k = fmax(k, red[(2 * WO + w) * CT + tid]); }
+      const double xm = *a.xx_max;
+      const double rc = sqrt(cc[tid]) + sqrt(xm);   // >= sqrt(T) for every observation; rc^2 >= cc + xx + 2|G|
+      const double dT = a.g_T * rc * rc;
+      double rel = (KIND == OB200_KERNEL_MATERN52 ? dT * (1.0 / 6.0) : dT) * 1.02 + a.c0 + a.c1 * (KIND == OB200_KERNEL_MATERN52 ? rc : rc * rc);
+      if (!(xm < 1e29)) rel = 1.0;   // coordinates beyond the FP32 range of this pass: vacuous (but valid) bounds
+      // S~ itself carries the relative error rel: sum k|alpha| <= S~ / (1 - rel)
+      const double eps = rel < 0.5 ? a.y_std * (a.amplitude * s * rel / (1.0 - rel) * 1.001 + a.tiny) : INFINITY;
+      a.mu_lb[row0 + tid] = a.y_std * (a.amplitude * m) + a.y_mean - eps;
+      const double klo = rel < 0.5 ? a.amplitude * k * (1.0 - rel) : 0.0;
+      const double var_ub = fmin(fmax(a.amplitude - klo * klo / (a.amplitude + a.diag), 0.0) + 1e-6 * a.amplitude, a.amplitude);
+      a.sigma_ub[row0 + tid] = a.y_std * sqrt(var_ub);
+    }
+    asm volatile("bar.sync 1, %0;" ::"n"(BD_WARPS * 32) : "memory");   // As / cc / red are rewritten by the next tile
+  }
+}
+
+// Observed points of the fit blob (fragment-packed X/ls for the DMMA kernel) -> TF32 hi/lo B fragments in T units,
+// plus per-observation {T-space ||x||^2, alpha}; padded observations get ||x||^2 = 1e30 (kernel value 0) and alpha 0.
+// Also the largest real ||x||^2 (one block: the table is small).
+__global__ void __launch_bounds__(256) bound_pack_kernel(const double* __restrict__ xs, const double* __restrict__ xx,
+                                                         const double* __restrict__ alpha, int n, int n_pad, int D_pad, int nk,
+                                                         int ksl, int n_slices, int n_chunks, double scale,
+                                                         float4* __restrict__ bp, float4* __restrict__ aux,
+                                                         double* __restrict__ xx_max_out) {
+  const int nd4 = D_pad >> 2;
+  const long long total = (long long)n_chunks * n_slices * 16 * ksl * 32;
+  for (long long e = (long long)blockIdx.x * 256 + threadIdx.x; e < total; e += (long long)gridDim.x * 256) {
+    const int lane = (int)(e & 31);
+    long long t = e >> 5;
+    const int j = (int)(t % ksl); t /= ksl;
+    const int o = (int)(t % 16); t /= 16;
+    const int s = (int)(t % n_slices);
+    const int c = (int)(t / n_slices);
+    const int g = lane >> 2, q = lane & 3;
+    const int obs = c * BD_OBC + o * 8 + g, ks = s * ksl + j;
+    float v[2] = {0.f, 0.f};
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int d = ks * 8 + q + 4 * h;
+      if (obs < n && d < D_pad && ks < nk)
+        v[h] = (float)(scale * xs[((size_t)(obs >> 3) * nd4 + (d >> 2)) * 32 + (obs & 7) * 4 + (d & 3)]);
+    }
+    const uint32_t h0 = to_tf32(v[0]), h1 = to_tf32(v[1]);
+    float4 out;
+    out.x = __uint_as_float(h0); out.y = __uint_as_float(h1);
+    out.z = __uint_as_float(to_tf32(v[0] - __uint_as_float(h0)));
+    out.w = __uint_as_float(to_tf32(v[1] - __uint_as_float(h1)));
+    bp[e] = out;
+  }
+  const long long n_aux = (long long)n_chunks * (BD_OBC / 8) * 4;
+  for (long long e = (long long)blockIdx.x * 256 + threadIdx.x; e < n_aux; e += (long long)gridDim.x * 256) {
+    const int q = (int)(e & 3);
+    const long long ob = e >> 2;
+    float4 out;
+    const long long j0 = ob * 8 + 2 * q, j1 = j0 + 1;
+    // round the squared norm UP-or-nearest is irrelevant: its rounding is part of the error budget (g_T)
+    out.x = j0 < n ? (float)(scale * scale * xx[j0]) : 1e30f;
+    out.y = j1 < n ? (float)(scale * scale * xx[j1]) : 1e30f;
+    out.z = j0 < n ? (float)alpha[j0] : 0.f;
+    out.w = j1 < n ? (float)alpha[j1] : 0.f;
+    aux[e] = out;
+  }
+  if (blockIdx.x == 0) {
+    __shared__ double sm[256];
+    double m = 0.0;
+    for (int j = threadIdx.x; j < n; j += 256) m = fmax(m, xx[j]);
+    sm[threadIdx.x] = m;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) { if (threadIdx.x < s) sm[threadIdx.x] = fmax(sm[threadIdx.x], sm[threadIdx.x + s]); __syncthreads(); }
+    if (threadIdx.x == 0) *xx_max_out = sm[0] * scale * scale;
+  }
+}
+
+template <int WC>
+int launch_wc(ob200_ctx* ctx, const bound_args& a, int grid, size_t smem) {
+  auto kern = a.kind == OB200_KERNEL_MATERN52 ? bound_kernel<WC, OB200_KERNEL_MATERN52> : bound_kernel<WC, OB200_KERNEL_RBF>;
+  OB_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  kern<<<grid, BD_THREADS, smem, ctx->stream>>>(a);
+  OB_LAUNCH_CHECK(ctx);
+  return OB200_OK;
+}
+
+}  // namespace
+
+// FP32 bound pass over `M` candidates: mu_lb[i] <= posterior mean, sigma_ub[i] >= posterior std.
+// Returns OB200_OK and sets *done = 1 when the pass ran; *done = 0 when this fit cannot use it (D too wide for the
+// shared-memory tile, OB200_BOUND_F32=0) and the caller must run the FP64 mean-only pass instead.
+int ob200_bound_f32_launch(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M, double* mu_lb_dev,
+                           double* sigma_ub_dev, int* done) {
+  *done = 0;
+  if (const char* env = getenv("OB200_BOUND_F32")) if (env[0] == '0') return OB200_OK;
+  const ob200_fit_header& h = ctx->hdr;
+  const ob200_blob_layout lay = ob_blob_layout(h.n_pad, h.D_pad);
+  const int nk = (h.D_pad + 7) / 8;
+  const int n_slices = (nk + 3) / 4, ksl = (nk + n_slices - 1) / n_slices;
+  const int n_chunks = (h.n + BD_OBC - 1) / BD_OBC;
+  // tile shape: the most candidates per CTA whose A fragments + at least two B stages fit
+  int wc = 4, stages = BD_STAGES_MAX;
+  size_t smem = 0;
+  for (;; ) {
+    stages = BD_STAGES_MAX;
+    while (stages > 2 && bound_smem_bytes(32 * wc, nk, ksl, stages) > 220 * 1024) --stages;
+    smem = bound_smem_bytes(32 * wc, nk, ksl, stages);
+    if (smem <= 220 * 1024) break;
+    if (wc == 1) return OB200_OK;   // not even a 32-candidate tile fits: FP64 pass
+    wc >>= 1;
+  }
+  // One CTA per SM: the 32 x 64 register tile (64 accumulators, 8 kernel evaluations in flight per n8 block) gives
+  // each warp enough independent MUFU / FFMA chains; the kernel needs ~170 registers per thread for that.
+  const int ctas_per_sm = 1;
+  const int64_t bp_elems = (int64_t)n_chunks * n_slices * 16 * ksl * 32;   // float4
+  const int64_t aux_elems = (int64_t)n_chunks * (BD_OBC / 8) * 4;
+  int rc;
+  if ((rc = ob_reserve(ctx, &ctx->b32_dev, &ctx->b32_cap, (bp_elems + aux_elems) * 4 + 64))) return rc;
+  float4* bp = reinterpret_cast<float4*>(ctx->b32_dev);
+  float4* aux = bp + bp_elems;
+  double* xx_max_dev = reinterpret_cast<double*>(aux + aux_elems);
+  const double scale = h.kernel_kind == OB200_KERNEL_MATERN52 ? 2.23606797749979 : 0.7071067811865476;
+  bound_pack_kernel<<<ctx->num_sms, 256, 0, ctx->stream>>>(
+      reinterpret_cast<const double*>(ctx->blob + lay.off_xs), reinterpret_cast<const double*>(ctx->blob + lay.off_xx),
+      reinterpret_cast<const double*>(ctx->blob + lay.off_alpha), h.n, h.n_pad, h.D_pad, nk, ksl, n_slices, n_chunks, scale, bp, aux,
+      xx_max_dev);
+  OB_LAUNCH_CHECK(ctx);
+
+  bound_args a{};
+  a.cand = cand_dev; a.ldc = ldc; a.M = M;
+  a.ls = reinterpret_cast<const double*>(ctx->blob + lay.off_ls);
+  a.bp = bp; a.aux = aux;
+  a.n_chunks = n_chunks; a.D = h.D; a.nk = nk; a.ksl = ksl; a.n_slices = n_slices; a.kind = h.kernel_kind; a.stages = stages;
+  a.scale = scale;
+  a.amplitude = h.amplitude; a.y_mean = h.y_mean; a.y_std = h.y_std; a.diag = h.diag;
+  a.xx_max = xx_max_dev;
+  // ---- error budget (see the header comment).  u = 2^-24 (FP32 unit round-off), tf = 2^-11 (TF32).
+  //   G~ = sum of 3 nk MMAs.  Split: c = ch + cl + rc, |rc| <= tf^2 |c| (+ 2u from the FP64 -> FP32 rounding), same
+  //   for x; dropped cl*xl, rc*x, c*rx: <= (3 tf^2 + 4u) |c||x|.  Tensor-core accumulation: modelled, generously,
+  //   as 2^-19 of sum |c_i||x_i| per MMA (published measurements put it near 2^-23 per added term).
+  //   On T~ = cc + xx - 2 G~:  2 |dG| <= 2 (3 nk 2^-19 + 3 tf^2 + 4u) sqrt(cc xx) <= 0.5 (...) (sqrt cc + sqrt xx)^2,
+  //   plus u (cc + xx) for the rounded norms and 2u (cc + xx + 2|G|) for the add and the fma.
+  const double u = ldexp(1.0, -24), tf2 = ldexp(1.0, -22);
+  a.g_T = 0.5 * (3.0 * nk * ldexp(1.0, -19) + 3.0 * tf2 + 4.0 * u) + 3.0 * u;
+  //   function evaluation: sqrt.approx and ex2.approx (2^-21 each, generous), the argument product t * log2(e)
+  //   (relative 2u of an exponent of size 1.4427 t -> relative ln2 * 1.4427 t * 2u = 2 t u of the result), the two
+  //   polynomial FMAs and the final product (3u), alpha rounded to FP32 (u), the FMA into the partial sum (u), the
+  //   FP32 partial sums (at most 2 * 128 / (4 WO) <= 64 terms per flush: 64u).  Matern: d ln k / dt <= 1, so the
+  //   sqrt error 2^-21 t enters as 2^-21 t.
+  a.c0 = 2.0 * ldexp(1.0, -21) + 70.0 * u;
+  a.c1 = ldexp(1.0, -21) + 2.0 * u;
+  a.tiny = 1e-20;   // kernel values flushed to zero (< 2^-126) times any plausible ||alpha||_1
+  a.mu_lb = mu_lb_dev; a.sigma_ub = sigma_ub_dev;
+  const int ct = 32 * wc;
+  a.n_tiles = (M + ct - 1) / ct;
+  const int64_t max_grid = (int64_t)ctx->num_sms * ctas_per_sm;
+  const int grid = (int)(a.n_tiles < max_grid ? a.n_tiles : max_grid);
+  if (wc == 4) rc = launch_wc<4>(ctx, a, grid, smem);
+  else if (wc == 2) rc = launch_wc<2>(ctx, a, grid, smem);
+  else rc = launch_wc<1>(ctx, a, grid, smem);
+  if (rc) return rc;
+  *done = 1;
+  return OB200_OK;
+}

@@ -69,12 +69,14 @@ void ob200_ctx_destroy(ob200_ctx* ctx) {
   cudaFree(ctx->idx_dev);
   cudaFree(ctx->gather_dev);
   cudaFree(ctx->prune_small_dev);
+  cudaFree(ctx->b32_dev);
   cudaFree(ctx->best_dev);
   if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
   if (ctx->ev_main) cudaEventDestroy(ctx->ev_main);
   if (ctx->ev_copy) cudaEventDestroy(ctx->ev_copy);
   if (ctx->best_pinned) cudaFreeHost(ctx->best_pinned);
   if (ctx->pinned) cudaFreeHost(ctx->pinned);
+  if (ctx->ctl_pinned) cudaFreeHost(ctx->ctl_pinned);
   delete ctx;
 }
 

@@ -59,6 +59,7 @@ struct ob200_ctx {
   int num_sms = OB200_NUM_SMS_FALLBACK;
   bool l2_dirty = false;   // persisting lines of a finished score launch have not been released yet
   bool l2_limit_on = false;  // the device-wide persisting-L2 carve-out is currently set (only around score launches)
+  size_t l2_prev_limit = 0;  // what the host had set before ob_l2_acquire (restored by ob_l2_release)
   size_t l2_persist_max = 0, l2_window_max = 0;  // persisting-L2 set-aside for the k* slices (0 = unavailable/disabled)
   cudaStream_t stream = 0;
   std::string err;
@@ -108,8 +109,13 @@ struct ob200_ctx {
   int64_t idx_cap = 0;
   double* gather_dev = nullptr;    // pruned scoring: gathered survivor rows
   int64_t gather_cap = 0;
-  char* prune_small_dev = nullptr; // histogram, counters, block min/max
+  char* prune_small_dev = nullptr; // pruned scoring: device-resident control block (histograms, thresholds, counters)
   int64_t prune_small_cap = 0;
+  void* ctl_pinned = nullptr;      // pinned read-back of the control block's counters
+  int last_prune_f32 = 0;          // statistics of the last pruned call (ob200_prune_stats)
+  int64_t last_prune_counts[3] = {0, 0, 0};
+  float* b32_dev = nullptr;        // FP32 bound pass: TF32 hi/lo B fragments + per-observation constants
+  int64_t b32_cap = 0;
   cudaStream_t copy_stream = nullptr;  // H2D of the candidate tail overlapped with scoring of the head
   cudaEvent_t ev_main = nullptr, ev_copy = nullptr;
   double* pinned = nullptr;        // pinned staging for host entry points
@@ -279,13 +285,17 @@ __device__ __forceinline__ double ob_exp_tab(double t, const double* __restrict_
 // device drop from 7.4 to 2.8 TB/s (tools/l2_persist_probe.py).  It is therefore switched on for score launches
 // only and handed back as soon as a score call has been synchronised.
 inline void ob_l2_acquire(ob200_ctx* ctx) {
-  if (ctx->l2_persist_max > 0 && !ctx->l2_limit_on &&
-      cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, ctx->l2_persist_max) == cudaSuccess)
+  if (ctx->l2_persist_max == 0 || ctx->l2_limit_on) return;
+  size_t prev = 0;
+  if (cudaDeviceGetLimit(&prev, cudaLimitPersistingL2CacheSize) != cudaSuccess) prev = 0;
+  if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, ctx->l2_persist_max) == cudaSuccess) {
+    ctx->l2_prev_limit = prev;   // the host framework's own set-aside (usually 0) comes back on release
     ctx->l2_limit_on = true;
+  }
 }
 inline void ob_l2_release(ob200_ctx* ctx) {
   if (ctx->l2_dirty) { cudaCtxResetPersistingL2Cache(); ctx->l2_dirty = false; }
-  if (ctx->l2_limit_on) { cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, 0); ctx->l2_limit_on = false; }
+  if (ctx->l2_limit_on) { cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, ctx->l2_prev_limit); ctx->l2_limit_on = false; }
 }
 
 #endif  // __CUDACC__
@@ -293,3 +303,5 @@ inline void ob_l2_release(ob200_ctx* ctx) {
 // internal cross-TU entry points
 int ob200_sample_launch(ob200_ctx* ctx, uint64_t seed, uint64_t first_index, int64_t count, int normalise,
                         double* out_dev, int64_t ld, const double* variates_dev);
+int ob200_bound_f32_launch(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M, double* mu_lb_dev,
+                           double* sigma_ub_dev, int* done);

@@ -53,7 +53,9 @@ struct score_args {
   int p1_stages;     // phase-1 ring depth (1..P1_STAGES, the deepest that fits in shared memory)
   int mean_only;     // 1: phase 1 only, write mu_out (pruned scoring, pass 1) and, if sigma_out is set, an upper bound of sigma
   double diag;       // term added to the diagonal of K (alpha + noise)
-  const long long* index_map;  // optional: global index of row r (gathered survivors); else first_index + r
+  const long long* row_map;    // optional: row r of this launch is row row_map[r] of `cand` (pruned scoring: survivors);
+                               // global index = first_index + row_map[r]; dense outputs stay indexed by r
+  const long long* M_dev;      // optional: the number of rows is read from device memory at kernel start
 };
 
 // ---- branch-free FP64 math for the cross-kernel epilogue ------------------------------------
@@ -154,6 +156,9 @@ __global__ void __launch_bounds__(MEAN_ONLY ? SC_MEAN_THREADS : SC_THREADS, MEAN
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int g = lane >> 2, q = lane & 3;
+  // batch size: a launch argument, or read from device memory (written by an earlier kernel of the stream)
+  const long long n_rows = a.M_dev ? *a.M_dev : a.M;
+  const long long n_tiles = a.M_dev ? (n_rows + SC_BN - 1) / SC_BN : a.n_tiles;
   const bool is_producer = (warp >= SC_CONSUMER_WARPS);   // last warpgroup; only its first lane issues copies
   const bool is_issuer = (warp == SC_CONSUMER_WARPS) && (lane == 0);
 
@@ -185,7 +190,7 @@ __global__ void __launch_bounds__(MEAN_ONLY ? SC_MEAN_THREADS : SC_THREADS, MEAN
     // register rebalancing: each role keeps its own tile loop so the register budget is decided by
     // dominance (per SM sub-partition: consumers x SC_CONSUMER_REGS + 1 producer x 40 <= 512).
     if (!MEAN_ONLY) asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
-    for (long long tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+    for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
       if (is_issuer) {
         // ---- phase 1 producer: observed-point chunks
         const uint32_t xs_bytes = (uint32_t)(SC_P1_OBS * D_pad * 8);
@@ -238,14 +243,14 @@ __global__ void __launch_bounds__(MEAN_ONLY ? SC_MEAN_THREADS : SC_THREADS, MEAN
   long long prof_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   long long prof_t = clock64();
 #endif
-  for (long long tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+  for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     const long long row0 = tile * SC_BN;
     SC_PROF_MARK(7)  // (loop overhead / before the first tile)
     // ---- stage the candidate tile: Cs = cand / ls in A-fragment order, cc = ||Cs||^2
     for (int e = tid; e < SC_BN * D_pad; e += SC_CONSUMER_WARPS * 32) {
       const int r = e / D_pad, d = e - r * D_pad;
       double v = 0.0;
-      if (d < a.D && row0 + r < a.M) v = a.cand[(size_t)(row0 + r) * a.ldc + d] / a.ls[d];
+      if (d < a.D && row0 + r < n_rows) v = a.cand[(size_t)(a.row_map ? a.row_map[row0 + r] : row0 + r) * a.ldc + d] / a.ls[d];
       Cs[((size_t)(r >> 3) * nd4 + (d >> 2)) * 32 + (r & 7) * 4 + (d & 3)] = v;
     }
     consumer_bar();
@@ -445,7 +450,7 @@ __global__ void __launch_bounds__(MEAN_ONLY ? SC_MEAN_THREADS : SC_THREADS, MEAN
     consumer_bar();
 
     // ---- phase 3: posterior, acquisition, running argmax (one thread per candidate)
-    if (tid < SC_BN && row0 + tid < a.M) {
+    if (tid < SC_BN && row0 + tid < n_rows) {
       double s2 = 0.0;
 #pragma unroll
       for (int w = 0; w < SC_WM; ++w) s2 += ssred[w * SC_BN + tid];
@@ -478,7 +483,7 @@ __global__ void __launch_bounds__(MEAN_ONLY ? SC_MEAN_THREADS : SC_THREADS, MEAN
         acquisition(mu, sigma, a.y_opt, a.xi, a.kappa, acq);
         if (a.mu_out) a.mu_out[row] = mu;
         if (a.sigma_out) a.sigma_out[row] = sigma;
-        const long long gidx = a.index_map ? a.index_map[row] : (long long)a.first_index + row;
+        const long long gidx = (long long)a.first_index + (a.row_map ? a.row_map[row] : row);
 #pragma unroll
         for (int k = 0; k < 3; ++k) {
           if (!(a.acq_mask & (1 << k))) continue;
@@ -498,6 +503,7 @@ __global__ void __launch_bounds__(MEAN_ONLY ? SC_MEAN_THREADS : SC_THREADS, MEAN
 #endif
 
   // ---- per-CTA winner: warp-shuffle argmax inside the SC_BN/32 owner warps, then through smem
+  if (MEAN_ONLY) return;   // no acquisition was evaluated: the partials (possibly an earlier batch's) stay untouched
   if (warp < SC_BN / 32) {
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
@@ -605,7 +611,7 @@ size_t score_smem_bytes(int D_pad, int p1_stages, bool mean_only = false) {
 
 int score_launch(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M, uint64_t first_index, int acq_mask,
                  double y_opt, double xi, double kappa, double* mu_dev, double* sigma_dev, double* acq_dev, int accumulate,
-                 int* grid_out, int mean_only = 0, const long long* index_map = nullptr) {
+                 int* grid_out, int mean_only = 0, const long long* row_map = nullptr, const long long* M_dev = nullptr) {
   const ob200_fit_header& h = ctx->hdr;
   const ob200_blob_layout lay = ob_blob_layout(h.n_pad, h.D_pad);
   // phase-1 ring depth: the deepest that fits (observed-point chunks are small, so the bulk-copy latency has
@@ -628,7 +634,7 @@ int score_launch(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M,
   }
   const int64_t n_tiles = (M + SC_BN - 1) / SC_BN;
   const int64_t max_grid = (int64_t)ctx->num_sms * ctas_per_sm;
-  const int grid = (int)(n_tiles < max_grid ? n_tiles : max_grid);
+  const int grid = (int)((n_tiles < max_grid && !M_dev) ? n_tiles : max_grid);   // device-sized batches: full persistent grid
   int rc;
   if ((rc = ob_reserve(ctx, &ctx->kstar_dev, &ctx->kstar_cap, (int64_t)ctx->num_sms * h.n_pad * SC_BN))) return rc;
   if ((rc = ob_reserve(ctx, &ctx->partial_dev, &ctx->partial_cap, (int64_t)4096 * 3 * (int64_t)sizeof(best_t)))) return rc;
@@ -650,7 +656,8 @@ int score_launch(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M,
   a.p1_stages = p1_stages;
   a.mean_only = mean_only;
   a.diag = h.diag;
-  a.index_map = index_map;
+  a.row_map = row_map;
+  a.M_dev = M_dev;
   auto kernel = mean_only ? score_kernel<true> : score_kernel<false>;
   OB_CUDA(ctx, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   // k* slices -> persisting L2 lines for this launch (the window is a launch-time stream attribute)
@@ -678,8 +685,16 @@ int score_launch(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M,
   return OB200_OK;
 }
 
-int check_score_args(ob200_ctx* ctx, int64_t M, int acq_mask, const void* best) {
+// the persisting-L2 carve-out is handed back on every exit path of a synchronous entry point
+struct l2_scope {
+  ob200_ctx* ctx;
+  explicit l2_scope(ob200_ctx* c) : ctx(c) {}
+  ~l2_scope() { ob_l2_release(ctx); }
+};
+
+int check_score_args(ob200_ctx* ctx, int64_t M, int acq_mask, const void* best, double y_opt, double xi, double kappa) {
   if (!ctx->fitted) OB_FAIL(ctx, OB200_ESTATE, "ob200_score called before ob200_gp_fit / ob200_gp_import");
+  if (!isfinite(y_opt) || !isfinite(xi) || !isfinite(kappa)) OB_FAIL(ctx, OB200_EINVAL, "y_opt, xi and kappa must be finite");
   if (M < 1) OB_FAIL(ctx, OB200_EINVAL, "M must be >= 1");
   if ((acq_mask & 7) == 0 || (acq_mask & ~7)) OB_FAIL(ctx, OB200_EINVAL, "acq_mask must select EI(1), PI(2) and/or LCB(4)");
   if (!best) OB_FAIL(ctx, OB200_EINVAL, "best is null");
@@ -700,7 +715,7 @@ int ob200_score_async(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64
                       int acq_mask, double y_opt, double xi, double kappa, ob200_best* best_dev, double* mu_dev,
                       double* sigma_dev, double* acq_dev) {
   if (!ctx) return OB200_EINVAL;
-  int rc = check_score_args(ctx, M, acq_mask, best_dev);
+  int rc = check_score_args(ctx, M, acq_mask, best_dev, y_opt, xi, kappa);
   if (rc) return rc;
   OB_CUDA(ctx, cudaSetDevice(ctx->device));
   const int D = ctx->hdr.D;
@@ -743,6 +758,7 @@ int ob200_score(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M, 
                 double* sigma_dev, double* acq_dev) {
   if (!ctx) return OB200_EINVAL;
   if (!best_host) OB_FAIL(ctx, OB200_EINVAL, "best_host is null");
+  l2_scope l2(ctx);
   int rc = ob200_score_async(ctx, cand_dev, ldc, M, seed, first_index, acq_mask, y_opt, xi, kappa, ctx->best_dev, mu_dev,
                              sigma_dev, acq_dev);
   if (rc) return rc;
@@ -758,11 +774,12 @@ int ob200_score_host(ob200_ctx* ctx, const double* cand_host, int64_t ldc, int64
                      double kappa, ob200_best* best_host, double* mu_host, double* sigma_host, double* acq_host) {
   if (!ctx) return OB200_EINVAL;
   if (!cand_host) OB_FAIL(ctx, OB200_EINVAL, "cand_host is null");
-  int rc = check_score_args(ctx, M, acq_mask, best_host);
+  int rc = check_score_args(ctx, M, acq_mask, best_host, y_opt, xi, kappa);
   if (rc) return rc;
   const int D = ctx->hdr.D;
   if (ldc < D) OB_FAIL(ctx, OB200_EINVAL, "ldc=%lld < D=%d", (long long)ldc, D);
   OB_CUDA(ctx, cudaSetDevice(ctx->device));
+  l2_scope l2(ctx);
   if ((rc = ob_reserve(ctx, &ctx->cand_tmp, &ctx->cand_cap, M * D))) return rc;
   const int64_t dense = (mu_host ? M : 0) + (sigma_host ? M : 0) + (acq_host ? 3 * M : 0);
   if (dense && (rc = ob_reserve(ctx, &ctx->dense_tmp, &ctx->dense_cap, dense))) return rc;
@@ -836,320 +853,227 @@ int ob200_acq_argmax(ob200_ctx* ctx, const double* mu_dev, const double* sigma_d
 }  // extern "C"
 
 // ---------------------------------------------------------------------------------------------
-// Exact pruned scoring.  EI, PI (for y_opt - xi - mu <= 0) and -LCB are increasing in
-// sigma, and sigma^2 <= (amplitude - k_max^2 / (amplitude + diag)) * y_std^2, the variance left by the nearest
-// observation alone (k_max = largest kernel value of the candidate against the observations; at worst the prior
-// variance), so U(mu, sigma_ub) is an upper bound of the utility that needs only the O(nD) cross-kernel.  Pass 1
-// computes mu and sigma_ub for every candidate (phase 1 of the score kernel), a first batch with the largest bounds is scored in full to get an
-// incumbent, and only candidates whose bound reaches the incumbent are scored after that.  Every
-// candidate left out has utility <= bound < incumbent <= maximum, so the argmax (ties included) and
-// the winner's values are bit-identical to the dense call.
+// Exact pruned scoring.  EI, PI (for y_opt - xi - mu <= 0) and -LCB are increasing in sigma and
+// decreasing in mu, and sigma^2 <= (amplitude - k_max^2 / (amplitude + diag)) * y_std^2, the variance left by the
+// nearest observation alone (k_max = largest kernel value of the candidate against the observations; at worst the
+// prior variance), so U(mu_lb, sigma_ub) is an upper bound of the utility that needs only the O(nD) cross-kernel.
+//
+//   pass 1   mu_lb, sigma_ub for every candidate: the FP32 / TF32 bound kernel (ob200_bound.cu, rigorous error
+//            budget), or -- when that kernel cannot take the fit -- phase 1 of the FP64 score kernel;
+//   batch A  the candidates with the largest bounds (at most one tile per CTA; the union over the requested
+//            acquisitions) are scored in full -> incumbents;
+//   batch B  every other candidate whose bound still reaches an incumbent; when pass 1 was FP32 their bounds are
+//            first recomputed by the FP64 mean-only kernel (9 ns per candidate instead of 125) and only the ones that
+//            still reach the incumbent are scored.
+// Every candidate left out has utility <= bound < incumbent <= maximum, so the argmax (ties included) and the
+// winner's values are bit-identical to the dense call.  The whole selection is device-resident: thresholds come
+// from a two-level radix histogram of the bounds (the last block to finish a histogram kernel turns it into the
+// threshold), batch sizes live in device memory and the score launches read them from there (persistent grid, idle
+// CTAs fall through), so a call has ONE host synchronisation: the read-back of the winners.
 namespace {
 
-#define PR_BINS 2048
+#define PR_BINS 4096   // 12 bits of the order-preserving key per histogram level
 
-__device__ __forceinline__ double upper_bound_utility(int acq, double mu, double sigma_max, double y_opt, double xi, double kappa) {
+struct prune_ctl {
+  unsigned long long count_a, count_b, count_b2;   // rows in batch A / B (pass-1 bounds) / B after the FP64 refinement
+  unsigned long long tau_key[3];                   // batch A of acquisition k = {key(ub_k) >= tau_key[k]}
+  long long rem[3];                                // quota left for level 2
+  int b1[3];                                       // level-1 bin that holds the threshold
+  unsigned int ticket1, ticket2;
+  unsigned int hist1[3][PR_BINS];
+  unsigned int hist2[3][PR_BINS];
+};
+
+// order-preserving map double -> uint64 (NaN -> largest key: a NaN bound is always selected)
+__device__ __forceinline__ unsigned long long ord_key(double v) {
+  if (!(v == v)) return ~0ull;
+  const unsigned long long u = (unsigned long long)__double_as_longlong(v);
+  return (u >> 63) ? ~u : (u | 0x8000000000000000ull);
+}
+
+__device__ __forceinline__ double upper_bound_utility(int acq, double mu_lb, double sigma_ub, double y_opt, double xi, double kappa) {
   double u[3];
-  acquisition(mu, sigma_max, y_opt, xi, kappa, u);
-  if (acq == OB200_ACQ_PI && (y_opt - xi - mu) > 0.0) return 1.0;  // PI decreases in sigma when the mean already improves
+  acquisition(mu_lb, sigma_ub, y_opt, xi, kappa, u);
+  if (acq == OB200_ACQ_PI && (y_opt - xi - mu_lb) > 0.0) return 1.0;  // PI decreases in sigma when the mean already improves
   return u[acq];
 }
 
-__global__ void __launch_bounds__(256) ub_kernel(const double* __restrict__ mu, const double* __restrict__ sig, long long M, int acq,
-                                                 double y_opt, double xi, double kappa, double* __restrict__ ub,
-                                                 double* __restrict__ blk_minmax) {
-  __shared__ double smin[256], smax[256];
-  double lo = INFINITY, hi = -INFINITY;
-  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < M; i += (long long)gridDim.x * 256) {
-    const double v = upper_bound_utility(acq, mu[i], sig[i], y_opt, xi, kappa);
-    ub[i] = v;
-    if (v == v) { lo = fmin(lo, v); hi = fmax(hi, v); }
-  }
-  smin[threadIdx.x] = lo; smax[threadIdx.x] = hi;
+__device__ __forceinline__ void block_hist_flush(unsigned int* sh, unsigned int* __restrict__ gl) {
   __syncthreads();
-  for (int s = 128; s > 0; s >>= 1) {
-    if (threadIdx.x < s) { smin[threadIdx.x] = fmin(smin[threadIdx.x], smin[threadIdx.x + s]); smax[threadIdx.x] = fmax(smax[threadIdx.x], smax[threadIdx.x + s]); }
-    __syncthreads();
-  }
-  if (threadIdx.x == 0) { blk_minmax[2 * blockIdx.x] = smin[0]; blk_minmax[2 * blockIdx.x + 1] = smax[0]; }
+  for (int b = threadIdx.x; b < PR_BINS; b += blockDim.x) { const unsigned int c = sh[b]; if (c) atomicAdd(&gl[b], c); sh[b] = 0; }
+  __syncthreads();
 }
 
-__global__ void __launch_bounds__(256) hist_kernel(const double* __restrict__ ub, long long M, double lo, double inv_width, int* __restrict__ hist) {
-  __shared__ int sh[PR_BINS];
+// true in exactly one block: the last one to get here (all of its predecessors' global writes are visible)
+__device__ __forceinline__ bool last_block(unsigned int* ticket) {
+  __shared__ bool is_last;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) is_last = (atomicAdd(ticket, 1u) == gridDim.x - 1);
+  __syncthreads();
+  if (is_last) __threadfence();
+  return is_last;
+}
+
+// From the top bin downwards: the largest set of whole bins holding at most `quota` entries.  Returns the lowest
+// bin taken (PR_BINS if none) and the number of entries taken; *next = the bin below (the one that did not fit).
+__device__ void scan_from_top(const unsigned int* __restrict__ hist, long long quota, bool force_first, int* lowest, long long* taken,
+                              unsigned int* sh) {
+  // 256 threads: chunk sums of 16 bins, then a serial walk over 256 + 16 values
+  unsigned int s = 0;
+  for (int b = 0; b < PR_BINS / 256; ++b) s += __ldcg(&hist[threadIdx.x * (PR_BINS / 256) + b]);
+  sh[threadIdx.x] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    long long cum = 0;
+    int low = PR_BINS;
+    int c = 255;
+    for (; c >= 0; --c) { if (cum + sh[c] > quota) break; cum += sh[c]; low = c * (PR_BINS / 256); }
+    if (c >= 0)
+      for (int b = c * (PR_BINS / 256) + PR_BINS / 256 - 1; b >= c * (PR_BINS / 256); --b) {
+        const unsigned int h = __ldcg(&hist[b]);
+        if (cum + h > quota && !(force_first && cum == 0 && h > 0)) break;   // force_first: never return an empty set
+        cum += h; low = b;
+        if (cum > quota) break;
+      }
+    *lowest = low; *taken = cum;
+  }
+  __syncthreads();
+}
+
+// utility bounds of the requested acquisitions + level-1 histogram (top 12 key bits); the last block picks, per
+// acquisition, the level-1 bin that holds the threshold
+__global__ void __launch_bounds__(256) ub_hist1_kernel(const double* __restrict__ mu, const double* __restrict__ sig, long long M, int acq_mask,
+                                                       double y_opt, double xi, double kappa, double* __restrict__ ub3, long long quota,
+                                                       prune_ctl* __restrict__ ctl) {
+  __shared__ unsigned int sh[PR_BINS];
   for (int b = threadIdx.x; b < PR_BINS; b += 256) sh[b] = 0;
   __syncthreads();
-  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < M; i += (long long)gridDim.x * 256) {
-    const double v = ub[i];
-    int b = (int)((v - lo) * inv_width);
-    b = b < 0 ? 0 : (b >= PR_BINS ? PR_BINS - 1 : b);
-    if (v == v) atomicAdd(&sh[b], 1);
-  }
-  __syncthreads();
-  for (int b = threadIdx.x; b < PR_BINS; b += 256) if (sh[b]) atomicAdd(&hist[b], sh[b]);
-}
-
-// indices with lo <= ub < hi (NaN bounds are always kept: they must be scored), order irrelevant
-__global__ void __launch_bounds__(256) compact_kernel(const double* __restrict__ ub, long long M, double lo, double hi,
-                                                      unsigned long long first_index, long long* __restrict__ rows,
-                                                      unsigned long long* __restrict__ counter) {
-  for (long long i0 = (long long)blockIdx.x * 256; i0 < M; i0 += (long long)gridDim.x * 256) {
-    const long long i = i0 + threadIdx.x;
-    bool keep = false;
-    if (i < M) { const double v = ub[i]; keep = !(v == v) ? (hi == INFINITY) : (v >= lo && v < hi); }
-    const unsigned mask = __ballot_sync(0xffffffffu, keep);
-    if (mask) {
-      const int lane = threadIdx.x & 31, leader = __ffs(mask) - 1;
-      unsigned long long base = 0;
-      if (lane == leader) base = atomicAdd(counter, (unsigned long long)__popc(mask));
-      base = __shfl_sync(0xffffffffu, base, leader);
-      if (keep) rows[base + __popc(mask & ((1u << lane) - 1))] = i;
-    }
-  }
-}
-
-// gather survivor rows into a dense [count x D] matrix and turn row numbers into global indices
-__global__ void __launch_bounds__(256) gather_kernel(const double* __restrict__ cand, long long ldc, int D, long long* __restrict__ rows,
-                                                     long long count, unsigned long long first_index, double* __restrict__ out) {
-  const long long total = count * D;
-  for (long long e = (long long)blockIdx.x * 256 + threadIdx.x; e < total; e += (long long)gridDim.x * 256) {
-    const long long r = e / D;
-    const int d = (int)(e - r * D);
-    out[e] = cand[rows[r] * ldc + d];
-  }
-}
-__global__ void __launch_bounds__(256) globalise_kernel(long long* __restrict__ rows, long long count, unsigned long long first_index) {
-  for (long long r = (long long)blockIdx.x * 256 + threadIdx.x; r < count; r += (long long)gridDim.x * 256) rows[r] += (long long)first_index;
-}
-
-}  // namespace
-
-namespace {
-
-// union of the first batches of several acquisitions: keep row i if ub_k[i] >= tau_k for some requested k
-// (tau_k = +inf for acquisitions that are not requested; NaN bounds of a requested one are always kept)
-__global__ void __launch_bounds__(256) compact_union_kernel(const double* __restrict__ ub0, const double* __restrict__ ub1,
-                                                            const double* __restrict__ ub2, long long M, double tau0, double tau1,
-                                                            double tau2, int acq_mask, long long* __restrict__ rows,
-                                                            unsigned long long* __restrict__ counter) {
-  for (long long i0 = (long long)blockIdx.x * 256; i0 < M; i0 += (long long)gridDim.x * 256) {
-    const long long i = i0 + threadIdx.x;
-    bool keep = false;
-    if (i < M) {
-      if (acq_mask & 1) { const double v = ub0[i]; keep |= !(v == v) || v >= tau0; }
-      if (acq_mask & 2) { const double v = ub1[i]; keep |= !(v == v) || v >= tau1; }
-      if (acq_mask & 4) { const double v = ub2[i]; keep |= !(v == v) || v >= tau2; }
-    }
-    const unsigned mask = __ballot_sync(0xffffffffu, keep);
-    if (mask) {
-      const int lane = threadIdx.x & 31, leader = __ffs(mask) - 1;
-      unsigned long long base = 0;
-      if (lane == leader) base = atomicAdd(counter, (unsigned long long)__popc(mask));
-      base = __shfl_sync(0xffffffffu, base, leader);
-      if (keep) rows[base + __popc(mask & ((1u << lane) - 1))] = i;
-    }
-  }
-}
-
-// bound array of one acquisition -> threshold tau such that about `quota` candidates have ub >= tau (-inf: all)
-int prune_tau(ob200_ctx* ctx, const double* mu, const double* sig, int64_t M, int acq, double y_opt, double xi, double kappa,
-              double* ub, int64_t quota, double* tau_out) {
-  cudaStream_t st = ctx->stream;
-  const int nblk = ctx->num_sms * 8;
-  double* blk = reinterpret_cast<double*>(ctx->prune_small_dev);
-  int* hist = reinterpret_cast<int*>(ctx->prune_small_dev + (size_t)nblk * 16);
-  ub_kernel<<<nblk, 256, 0, st>>>(mu, sig, M, acq, y_opt, xi, kappa, ub, blk);
-  OB_LAUNCH_CHECK(ctx);
-  std::vector<double> h_blk((size_t)nblk * 2);
-  OB_CUDA(ctx, cudaMemcpyAsync(h_blk.data(), blk, (size_t)nblk * 16, cudaMemcpyDeviceToHost, st));
-  OB_CUDA(ctx, cudaMemsetAsync(hist, 0, PR_BINS * 4 + 64, st));
-  OB_CUDA(ctx, cudaStreamSynchronize(st));
-  double lo = INFINITY, hi = -INFINITY;
-  for (int b = 0; b < nblk; ++b) { if (h_blk[2 * b] < lo) lo = h_blk[2 * b]; if (h_blk[2 * b + 1] > hi) hi = h_blk[2 * b + 1]; }
-  double tau = -INFINITY;
-  if (hi > lo && lo > -INFINITY && hi < INFINITY) {
-    const double width = (hi - lo) / PR_BINS;
-    hist_kernel<<<nblk, 256, 0, st>>>(ub, M, lo, 1.0 / width, hist);
-    OB_LAUNCH_CHECK(ctx);
-    std::vector<int> h_hist(PR_BINS);
-    OB_CUDA(ctx, cudaMemcpyAsync(h_hist.data(), hist, PR_BINS * 4, cudaMemcpyDeviceToHost, st));
-    OB_CUDA(ctx, cudaStreamSynchronize(st));
-    int64_t acc_count = 0;
-    for (int b = PR_BINS - 1; b >= 0; --b) {
-      acc_count += h_hist[b];
-      if (acc_count >= quota) { tau = lo + width * b; break; }
-    }
-    tau = tau - 1e-9 * fabs(tau);  // bin edges are computed differently on the device: err on the inclusive side
-  }
-  *tau_out = tau;
-  return OB200_OK;
-}
-
-// Selection for ONE acquisition on top of the shared mean-only pass (mu, sigma bound per candidate): utility bounds,
-// batch A (largest bounds) -> incumbent, batch B (bounds that still reach it).
-int prune_select(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M, uint64_t first_index, int acq, double y_opt,
-                 double xi, double kappa, const double* mu, const double* sig, double* ub, ob200_best* best_out,
-                 int64_t* n_scored_out) {
-  const int mask = 1 << acq, D = ctx->hdr.D;
-  const int64_t batch = (int64_t)ctx->num_sms * SC_BN;  // one tile per CTA
-  cudaStream_t st = ctx->stream;
-  const int nblk = ctx->num_sms * 8;
-  double* blk = reinterpret_cast<double*>(ctx->prune_small_dev);
-  int* hist = reinterpret_cast<int*>(ctx->prune_small_dev + (size_t)nblk * 16);
-  unsigned long long* counter = reinterpret_cast<unsigned long long*>(ctx->prune_small_dev + (size_t)nblk * 16 + PR_BINS * 4);
-  int rc;
-  ub_kernel<<<nblk, 256, 0, st>>>(mu, sig, M, acq, y_opt, xi, kappa, ub, blk);
-  OB_LAUNCH_CHECK(ctx);
-  std::vector<double> h_blk((size_t)nblk * 2);
-  OB_CUDA(ctx, cudaMemcpyAsync(h_blk.data(), blk, (size_t)nblk * 16, cudaMemcpyDeviceToHost, st));
-  OB_CUDA(ctx, cudaMemsetAsync(hist, 0, PR_BINS * 4 + 64, st));
-  OB_CUDA(ctx, cudaStreamSynchronize(st));
-  double lo = INFINITY, hi = -INFINITY;
-  for (int b = 0; b < nblk; ++b) { if (h_blk[2 * b] < lo) lo = h_blk[2 * b]; if (h_blk[2 * b + 1] > hi) hi = h_blk[2 * b + 1]; }
-  double tau = -INFINITY;  // first batch = {ub >= tau}
-  if (hi > lo && lo > -INFINITY && hi < INFINITY) {
-    const double width = (hi - lo) / PR_BINS;
-    hist_kernel<<<nblk, 256, 0, st>>>(ub, M, lo, 1.0 / width, hist);
-    OB_LAUNCH_CHECK(ctx);
-    std::vector<int> h_hist(PR_BINS);
-    OB_CUDA(ctx, cudaMemcpyAsync(h_hist.data(), hist, PR_BINS * 4, cudaMemcpyDeviceToHost, st));
-    OB_CUDA(ctx, cudaStreamSynchronize(st));
-    int64_t acc_count = 0;
-    for (int b = PR_BINS - 1; b >= 0; --b) {
-      acc_count += h_hist[b];
-      if (acc_count >= batch) { tau = lo + width * b; break; }
-    }
-    tau = tau - 1e-9 * fabs(tau);  // bin edges are computed differently on the device: err on the inclusive side
-  }
-  // batch A: the candidates with the largest bounds
-  int grid = 0;
-  int64_t n_scored = 0;
-  unsigned long long h_count = 0;
-  compact_kernel<<<nblk, 256, 0, st>>>(ub, M, tau, INFINITY, first_index, ctx->idx_dev, counter);
-  OB_LAUNCH_CHECK(ctx);
-  OB_CUDA(ctx, cudaMemcpyAsync(&h_count, counter, 8, cudaMemcpyDeviceToHost, st));
-  OB_CUDA(ctx, cudaStreamSynchronize(st));
-  ob200_best incumbent{};
-  incumbent.value = -INFINITY;
-  if (h_count > 0) {
-    const int64_t nA = (int64_t)h_count;
-    if ((rc = ob_reserve(ctx, &ctx->gather_dev, &ctx->gather_cap, nA * D))) return rc;
-    gather_kernel<<<nblk, 256, 0, st>>>(cand_dev, ldc, D, ctx->idx_dev, nA, first_index, ctx->gather_dev);
-    OB_LAUNCH_CHECK(ctx);
-    globalise_kernel<<<nblk, 256, 0, st>>>(ctx->idx_dev, nA, first_index);
-    OB_LAUNCH_CHECK(ctx);
-    if ((rc = score_launch(ctx, ctx->gather_dev, D, nA, 0, mask, y_opt, xi, kappa, nullptr, nullptr, nullptr, 0, &grid, 0, ctx->idx_dev))) return rc;
-    reduce_best_kernel<<<1, 256, 0, st>>>(reinterpret_cast<const best_t*>(ctx->partial_dev), grid, mask, ctx->best_dev);
-    OB_LAUNCH_CHECK(ctx);
-    OB_CUDA(ctx, cudaMemcpyAsync(ctx->best_pinned, ctx->best_dev, 3 * sizeof(ob200_best), cudaMemcpyDeviceToHost, st));
-    OB_CUDA(ctx, cudaStreamSynchronize(st));
-    incumbent = ctx->best_pinned[acq];
-    n_scored += nA;
-  }
-  // batch B: everything else whose bound still reaches the incumbent (with a rounding margin)
-  const double thr = incumbent.value - 1e-12 * fabs(incumbent.value) - 1e-300;
-  if (thr < tau) {
-    OB_CUDA(ctx, cudaMemsetAsync(counter, 0, 8, st));
-    compact_kernel<<<nblk, 256, 0, st>>>(ub, M, thr, tau, first_index, ctx->idx_dev, counter);
-    OB_LAUNCH_CHECK(ctx);
-    OB_CUDA(ctx, cudaMemcpyAsync(&h_count, counter, 8, cudaMemcpyDeviceToHost, st));
-    OB_CUDA(ctx, cudaStreamSynchronize(st));
-    if (h_count > 0) {
-      const int64_t nB = (int64_t)h_count;
-      if ((rc = ob_reserve(ctx, &ctx->gather_dev, &ctx->gather_cap, nB * D))) return rc;
-      gather_kernel<<<nblk, 256, 0, st>>>(cand_dev, ldc, D, ctx->idx_dev, nB, first_index, ctx->gather_dev);
-      OB_LAUNCH_CHECK(ctx);
-      globalise_kernel<<<nblk, 256, 0, st>>>(ctx->idx_dev, nB, first_index);
-      OB_LAUNCH_CHECK(ctx);
-      // a wider grid than batch A's would read uninitialised partials: run it as a fresh launch and merge on the host
-      if ((rc = score_launch(ctx, ctx->gather_dev, D, nB, 0, mask, y_opt, xi, kappa, nullptr, nullptr, nullptr, 0, &grid, 0, ctx->idx_dev))) return rc;
-      reduce_best_kernel<<<1, 256, 0, st>>>(reinterpret_cast<const best_t*>(ctx->partial_dev), grid, mask, ctx->best_dev);
-      OB_LAUNCH_CHECK(ctx);
-      OB_CUDA(ctx, cudaMemcpyAsync(ctx->best_pinned, ctx->best_dev, 3 * sizeof(ob200_best), cudaMemcpyDeviceToHost, st));
-      OB_CUDA(ctx, cudaStreamSynchronize(st));
-      const ob200_best b = ctx->best_pinned[acq];
-      if (b.value > incumbent.value || (b.value == incumbent.value && b.index < incumbent.index)) incumbent = b;
-      n_scored += nB;
-    }
-  }
-  *best_out = incumbent;
-  *n_scored_out = n_scored;
-  return OB200_OK;
-}
-
-// Selection for SEVERAL acquisitions (the gp_hedge portfolio): their first batches share ONE score launch -- each gets
-// a third (or half) of the one-tile-per-CTA budget, the union is scored for all of them at once -- and only the second
-// batches, usually empty, run per acquisition.  Same exactness argument as prune_select: everything whose bound
-// reaches an acquisition's incumbent is scored for it.
-int prune_select_multi(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M, uint64_t first_index, int acq_mask,
-                       double y_opt, double xi, double kappa, const double* mu, const double* sig, double* ub3,
-                       ob200_best* best_out, int64_t* n_scored_out) {
-  const int D = ctx->hdr.D;
-  const int64_t batch = (int64_t)ctx->num_sms * SC_BN;
-  cudaStream_t st = ctx->stream;
-  const int nblk = ctx->num_sms * 8;
-  unsigned long long* counter = reinterpret_cast<unsigned long long*>(ctx->prune_small_dev + (size_t)nblk * 16 + PR_BINS * 4);
-  int n_acq = 0, rc, grid = 0;
-  for (int k = 0; k < 3; ++k) n_acq += (acq_mask >> k) & 1;
-  double tau[3] = {INFINITY, INFINITY, INFINITY};
-  double* ub[3] = {ub3, ub3 + M, ub3 + 2 * M};
-  for (int k = 0; k < 3; ++k)
-    if (acq_mask & (1 << k))
-      if ((rc = prune_tau(ctx, mu, sig, M, k, y_opt, xi, kappa, ub[k], batch / n_acq, &tau[k]))) return rc;
-  // batch A: union of the candidates with the largest bounds of each acquisition (prune_tau left the counter at zero)
-  unsigned long long h_count = 0;
-  compact_union_kernel<<<nblk, 256, 0, st>>>(ub[0], ub[1], ub[2], M, tau[0], tau[1], tau[2], acq_mask, ctx->idx_dev, counter);
-  OB_LAUNCH_CHECK(ctx);
-  OB_CUDA(ctx, cudaMemcpyAsync(&h_count, counter, 8, cudaMemcpyDeviceToHost, st));
-  OB_CUDA(ctx, cudaStreamSynchronize(st));
-  ob200_best incumbent[3];
-  for (int k = 0; k < 3; ++k) { incumbent[k] = ob200_best{}; incumbent[k].value = -INFINITY; }
-  const int64_t nA = (int64_t)h_count;
-  if (nA > 0) {
-    if ((rc = ob_reserve(ctx, &ctx->gather_dev, &ctx->gather_cap, nA * D))) return rc;
-    gather_kernel<<<nblk, 256, 0, st>>>(cand_dev, ldc, D, ctx->idx_dev, nA, first_index, ctx->gather_dev);
-    OB_LAUNCH_CHECK(ctx);
-    globalise_kernel<<<nblk, 256, 0, st>>>(ctx->idx_dev, nA, first_index);
-    OB_LAUNCH_CHECK(ctx);
-    if ((rc = score_launch(ctx, ctx->gather_dev, D, nA, 0, acq_mask, y_opt, xi, kappa, nullptr, nullptr, nullptr, 0, &grid, 0, ctx->idx_dev))) return rc;
-    reduce_best_kernel<<<1, 256, 0, st>>>(reinterpret_cast<const best_t*>(ctx->partial_dev), grid, acq_mask, ctx->best_dev);
-    OB_LAUNCH_CHECK(ctx);
-    OB_CUDA(ctx, cudaMemcpyAsync(ctx->best_pinned, ctx->best_dev, 3 * sizeof(ob200_best), cudaMemcpyDeviceToHost, st));
-    OB_CUDA(ctx, cudaStreamSynchronize(st));
-    for (int k = 0; k < 3; ++k) if (acq_mask & (1 << k)) incumbent[k] = ctx->best_pinned[k];
-  }
-  // batch B, per acquisition: bounds below its tau that still reach its incumbent (rows that entered batch A through
-  // another acquisition may be scored again: harmless)
   for (int k = 0; k < 3; ++k) {
     if (!(acq_mask & (1 << k))) continue;
-    int64_t n_scored = nA;
-    const double thr = incumbent[k].value - 1e-12 * fabs(incumbent[k].value) - 1e-300;
-    if (thr < tau[k]) {
-      OB_CUDA(ctx, cudaMemsetAsync(counter, 0, 8, st));
-      compact_kernel<<<nblk, 256, 0, st>>>(ub[k], M, thr, tau[k], first_index, ctx->idx_dev, counter);
-      OB_LAUNCH_CHECK(ctx);
-      OB_CUDA(ctx, cudaMemcpyAsync(&h_count, counter, 8, cudaMemcpyDeviceToHost, st));
-      OB_CUDA(ctx, cudaStreamSynchronize(st));
-      if (h_count > 0) {
-        const int64_t nB = (int64_t)h_count;
-        if ((rc = ob_reserve(ctx, &ctx->gather_dev, &ctx->gather_cap, nB * D))) return rc;
-        gather_kernel<<<nblk, 256, 0, st>>>(cand_dev, ldc, D, ctx->idx_dev, nB, first_index, ctx->gather_dev);
-        OB_LAUNCH_CHECK(ctx);
-        globalise_kernel<<<nblk, 256, 0, st>>>(ctx->idx_dev, nB, first_index);
-        OB_LAUNCH_CHECK(ctx);
-        if ((rc = score_launch(ctx, ctx->gather_dev, D, nB, 0, 1 << k, y_opt, xi, kappa, nullptr, nullptr, nullptr, 0, &grid, 0, ctx->idx_dev))) return rc;
-        reduce_best_kernel<<<1, 256, 0, st>>>(reinterpret_cast<const best_t*>(ctx->partial_dev), grid, 1 << k, ctx->best_dev);
-        OB_LAUNCH_CHECK(ctx);
-        OB_CUDA(ctx, cudaMemcpyAsync(ctx->best_pinned, ctx->best_dev, 3 * sizeof(ob200_best), cudaMemcpyDeviceToHost, st));
-        OB_CUDA(ctx, cudaStreamSynchronize(st));
-        const ob200_best b = ctx->best_pinned[k];
-        if (b.value > incumbent[k].value || (b.value == incumbent[k].value && b.index < incumbent[k].index)) incumbent[k] = b;
-        n_scored += nB;
+    double* ub = ub3 + (size_t)k * M;
+    for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < M; i += (long long)gridDim.x * 256) {
+      const double v = upper_bound_utility(k, mu[i], sig[i], y_opt, xi, kappa);
+      ub[i] = v;
+      atomicAdd(&sh[ord_key(v) >> 52], 1u);
+    }
+    block_hist_flush(sh, ctl->hist1[k]);
+  }
+  if (!last_block(&ctl->ticket1)) return;
+  __shared__ int low;
+  __shared__ long long taken;
+  for (int k = 0; k < 3; ++k) {
+    if (!(acq_mask & (1 << k))) continue;
+    scan_from_top(ctl->hist1[k], quota, false, &low, &taken, sh);
+    if (threadIdx.x == 0) { ctl->b1[k] = low - 1; ctl->rem[k] = quota - taken; }   // low - 1: the bin that did not fit (-1: all fit)
+    __syncthreads();
+  }
+}
+
+// level 2: the next 12 key bits inside the level-1 bin; the last block fixes tau_key
+__global__ void __launch_bounds__(256) hist2_kernel(const double* __restrict__ ub3, long long M, int acq_mask, long long quota,
+                                                    prune_ctl* __restrict__ ctl) {
+  __shared__ unsigned int sh[PR_BINS];
+  for (int b = threadIdx.x; b < PR_BINS; b += 256) sh[b] = 0;
+  __syncthreads();
+  for (int k = 0; k < 3; ++k) {
+    if (!(acq_mask & (1 << k))) continue;
+    const int b1 = ctl->b1[k];
+    if (b1 >= 0) {
+      const double* ub = ub3 + (size_t)k * M;
+      for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < M; i += (long long)gridDim.x * 256) {
+        const unsigned long long key = ord_key(ub[i]);
+        if ((int)(key >> 52) == b1) atomicAdd(&sh[(key >> 40) & (PR_BINS - 1)], 1u);
       }
     }
-    best_out[k] = incumbent[k];
-    if (n_scored_out) n_scored_out[k] = n_scored;
+    block_hist_flush(sh, ctl->hist2[k]);
   }
-  return OB200_OK;
+  if (!last_block(&ctl->ticket2)) return;
+  __shared__ int low;
+  __shared__ long long taken;
+  for (int k = 0; k < 3; ++k) {
+    if (!(acq_mask & (1 << k))) continue;
+    const int b1 = ctl->b1[k];
+    if (b1 < 0) { if (threadIdx.x == 0) ctl->tau_key[k] = 0ull; __syncthreads(); continue; }   // everything fits the quota
+    scan_from_top(ctl->hist2[k], ctl->rem[k], ctl->rem[k] == quota, &low, &taken, sh);   // nothing taken above: batch A must not be empty
+    if (threadIdx.x == 0) {
+      unsigned long long key;
+      if (low < PR_BINS) key = ((unsigned long long)b1 << 52) | ((unsigned long long)low << 40);
+      else if (b1 + 1 < PR_BINS) key = (unsigned long long)(b1 + 1) << 52;   // nothing of this bin fits: only the bins above
+      else key = ~0ull;
+      ctl->tau_key[k] = key;
+    }
+    __syncthreads();
+  }
+}
+
+// batch A (phase 0): rows with key(ub_k) >= tau_key[k] for some requested k.
+// batch B (phase 1): rows NOT in batch A whose bound reaches the incumbent of some requested k.
+__global__ void __launch_bounds__(256) compact_kernel(const double* __restrict__ ub3, long long M, int acq_mask, int phase,
+                                                      const ob200_best* __restrict__ incumbent, prune_ctl* __restrict__ ctl,
+                                                      long long* __restrict__ rows) {
+  unsigned long long tau[3];
+  double thr[3];
+  for (int k = 0; k < 3; ++k) {
+    tau[k] = ctl->tau_key[k];
+    const double v = incumbent ? incumbent[k].value : 0.0;
+    thr[k] = v - 1e-12 * fabs(v) - 1e-300;   // rounding margin between the bound's and the score kernel's arithmetic
+  }
+  unsigned long long* counter = phase == 0 ? &ctl->count_a : &ctl->count_b;
+  for (long long i0 = (long long)blockIdx.x * 256; i0 < M; i0 += (long long)gridDim.x * 256) {
+    const long long i = i0 + threadIdx.x;
+    bool in_a = false, reach = false;
+    if (i < M) {
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        if (!(acq_mask & (1 << k))) continue;
+        const double v = ub3[(size_t)k * M + i];
+        in_a |= ord_key(v) >= tau[k];
+        reach |= v >= thr[k];
+      }
+    }
+    const bool keep = phase == 0 ? in_a : (!in_a && reach);
+    const unsigned mask = __ballot_sync(0xffffffffu, keep);
+    if (mask) {
+      const int lane = threadIdx.x & 31, leader = __ffs(mask) - 1;
+      unsigned long long base = 0;
+      if (lane == leader) base = atomicAdd(counter, (unsigned long long)__popc(mask));
+      base = __shfl_sync(0xffffffffu, base, leader);
+      if (keep) rows[base + __popc(mask & ((1u << lane) - 1))] = i;
+    }
+  }
+}
+
+// batch B after the FP64 refinement: mu / sigma_ub of the count_b rows were recomputed exactly (local arrays); keep
+// the rows whose refined bound still reaches an incumbent
+__global__ void __launch_bounds__(256) compact_refined_kernel(const double* __restrict__ mu, const double* __restrict__ sig, int acq_mask,
+                                                              double y_opt, double xi, double kappa, const ob200_best* __restrict__ incumbent,
+                                                              prune_ctl* __restrict__ ctl, const long long* __restrict__ rows_in,
+                                                              long long* __restrict__ rows_out) {
+  const long long n = (long long)ctl->count_b;
+  double thr[3];
+  for (int k = 0; k < 3; ++k) { const double v = incumbent[k].value; thr[k] = v - 1e-12 * fabs(v) - 1e-300; }
+  for (long long i0 = (long long)blockIdx.x * 256; i0 < n; i0 += (long long)gridDim.x * 256) {
+    const long long i = i0 + threadIdx.x;
+    bool keep = false;
+    if (i < n) {
+      const double m = mu[i], s = sig[i];
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        if (!(acq_mask & (1 << k))) continue;
+        const double v = upper_bound_utility(k, m, s, y_opt, xi, kappa);
+        keep |= !(v == v) || v >= thr[k];
+      }
+    }
+    const unsigned mask = __ballot_sync(0xffffffffu, keep);
+    if (mask) {
+      const int lane = threadIdx.x & 31, leader = __ffs(mask) - 1;
+      unsigned long long base = 0;
+      if (lane == leader) base = atomicAdd(&ctl->count_b2, (unsigned long long)__popc(mask));
+      base = __shfl_sync(0xffffffffu, base, leader);
+      if (keep) rows_out[base + __popc(mask & ((1u << lane) - 1))] = rows_in[i];
+    }
+  }
 }
 
 }  // namespace
@@ -1158,20 +1082,23 @@ extern "C" int ob200_score_pruned_multi(ob200_ctx* ctx, const double* cand_dev, 
                                         uint64_t first_index, int acq_mask, double y_opt, double xi, double kappa,
                                         ob200_best* best_host, int64_t* n_scored_host) {
   if (!ctx) return OB200_EINVAL;
-  int rc = check_score_args(ctx, M, acq_mask, best_host);
+  int rc = check_score_args(ctx, M, acq_mask, best_host, y_opt, xi, kappa);
   if (rc) return rc;
   OB_CUDA(ctx, cudaSetDevice(ctx->device));
   const int D = ctx->hdr.D;
-  const int64_t batch = (int64_t)ctx->num_sms * SC_BN;
+  const int64_t batch = (int64_t)ctx->num_sms * SC_BN;   // one tile per CTA
   for (int k = 0; k < 3; ++k) { best_host[k] = ob200_best{}; if (n_scored_host) n_scored_host[k] = 0; }
-  // small problems, or candidate sets that do not fit in one resident buffer: dense path
+  // Dense path: small problems; candidate sets that do not fit in one resident buffer; -LCB with kappa < 0, which
+  // DEcreases in sigma, so U(mu_lb, sigma_ub) would not bound it.
   const bool too_big = !cand_dev && (M * (int64_t)D * 8 > ((int64_t)1 << 31));
-  if (M <= 4 * batch || too_big) {
+  const bool lcb_not_monotone = (acq_mask & (1 << OB200_ACQ_LCB)) && kappa < 0.0;
+  if (M <= 4 * batch || too_big || lcb_not_monotone) {
     rc = ob200_score(ctx, cand_dev, ldc, M, seed, first_index, acq_mask, y_opt, xi, kappa, best_host, nullptr, nullptr, nullptr);
     if (rc) return rc;
     for (int k = 0; k < 3; ++k) if (n_scored_host && (acq_mask & (1 << k))) n_scored_host[k] = M;
     return OB200_OK;
   }
+  l2_scope l2(ctx);
   if (cand_dev) {
     if (ldc < D) OB_FAIL(ctx, OB200_EINVAL, "ldc=%lld < D=%d", (long long)ldc, D);
   } else {
@@ -1182,27 +1109,65 @@ extern "C" int ob200_score_pruned_multi(ob200_ctx* ctx, const double* cand_dev, 
     cand_dev = ctx->cand_tmp;
     ldc = D;
   }
-  if ((rc = ob_reserve(ctx, &ctx->ub_dev, &ctx->ub_cap, 5 * M))) return rc;
-  if ((rc = ob_reserve(ctx, &ctx->idx_dev, &ctx->idx_cap, M))) return rc;
+  if ((rc = ob_reserve(ctx, &ctx->ub_dev, &ctx->ub_cap, 7 * M))) return rc;
+  if ((rc = ob_reserve(ctx, &ctx->idx_dev, &ctx->idx_cap, 2 * M))) return rc;
+  if ((rc = ob_reserve(ctx, &ctx->prune_small_dev, &ctx->prune_small_cap, (int64_t)sizeof(prune_ctl)))) return rc;
+  if (!ctx->ctl_pinned) OB_CUDA(ctx, cudaMallocHost((void**)&ctx->ctl_pinned, 64));
+  double *mu = ctx->ub_dev, *sig = ctx->ub_dev + M, *ub3 = ctx->ub_dev + 2 * M, *mu_b = ctx->ub_dev + 5 * M, *sig_b = ctx->ub_dev + 6 * M;
+  long long *rows0 = ctx->idx_dev, *rows1 = ctx->idx_dev + M;
+  prune_ctl* ctl = reinterpret_cast<prune_ctl*>(ctx->prune_small_dev);
+  cudaStream_t st = ctx->stream;
   const int nblk = ctx->num_sms * 8;
-  const int64_t small_bytes = (int64_t)nblk * 16 + PR_BINS * 4 + 64;
-  if ((rc = ob_reserve(ctx, &ctx->prune_small_dev, &ctx->prune_small_cap, small_bytes))) return rc;
-  double *mu = ctx->ub_dev, *sig = ctx->ub_dev + M, *ub = ctx->ub_dev + 2 * M;
-  // pass 1 (shared by the acquisitions): posterior mean of every candidate and an upper bound of its sigma from the
-  // nearest observation
-  int grid = 0;
-  if ((rc = score_launch(ctx, cand_dev, ldc, M, first_index, acq_mask, y_opt, xi, kappa, mu, sig, nullptr, 0, &grid, 1, nullptr))) return rc;
-  if ((acq_mask & (acq_mask - 1)) != 0 && !getenv("OB200_PRUNE_SEPARATE")) {  // several acquisitions: shared first batch
-    if ((rc = prune_select_multi(ctx, cand_dev, ldc, M, first_index, acq_mask, y_opt, xi, kappa, mu, sig, ub, best_host, n_scored_host))) return rc;
-  } else {
-    for (int k = 0; k < 3; ++k) {
-      if (!(acq_mask & (1 << k))) continue;
-      int64_t ns = 0;
-      if ((rc = prune_select(ctx, cand_dev, ldc, M, first_index, k, y_opt, xi, kappa, mu, sig, ub, &best_host[k], &ns))) return rc;
-      if (n_scored_host) n_scored_host[k] = ns;
-    }
+  int n_acq = 0, grid = 0;
+  for (int k = 0; k < 3; ++k) n_acq += (acq_mask >> k) & 1;
+  OB_CUDA(ctx, cudaMemsetAsync(ctl, 0, sizeof(prune_ctl), st));
+  // pass 1 (shared by the acquisitions)
+  int f32_done = 0;
+  if ((rc = ob200_bound_f32_launch(ctx, cand_dev, ldc, M, mu, sig, &f32_done))) return rc;
+  if (!f32_done && (rc = score_launch(ctx, cand_dev, ldc, M, first_index, acq_mask, y_opt, xi, kappa, mu, sig, nullptr, 0, &grid, 1))) return rc;
+  // thresholds of the first batches
+  ub_hist1_kernel<<<nblk, 256, 0, st>>>(mu, sig, M, acq_mask, y_opt, xi, kappa, ub3, batch / n_acq, ctl);
+  OB_LAUNCH_CHECK(ctx);
+  hist2_kernel<<<nblk, 256, 0, st>>>(ub3, M, acq_mask, batch / n_acq, ctl);
+  OB_LAUNCH_CHECK(ctx);
+  // batch A
+  compact_kernel<<<nblk, 256, 0, st>>>(ub3, M, acq_mask, 0, nullptr, ctl, rows0);
+  OB_LAUNCH_CHECK(ctx);
+  if ((rc = score_launch(ctx, cand_dev, ldc, M, first_index, acq_mask, y_opt, xi, kappa, nullptr, nullptr, nullptr, 0, &grid, 0, rows0,
+                         reinterpret_cast<const long long*>(&ctl->count_a)))) return rc;
+  reduce_best_kernel<<<1, 256, 0, st>>>(reinterpret_cast<const best_t*>(ctx->partial_dev), grid, acq_mask, ctx->best_dev);
+  OB_LAUNCH_CHECK(ctx);
+  // batch B
+  compact_kernel<<<nblk, 256, 0, st>>>(ub3, M, acq_mask, 1, ctx->best_dev, ctl, rows1);
+  OB_LAUNCH_CHECK(ctx);
+  const long long* rows_b = rows1;
+  const unsigned long long* count_b = &ctl->count_b;
+  if (f32_done) {  // exact bounds for the rows the FP32 bounds could not exclude
+    int g2 = 0;
+    if ((rc = score_launch(ctx, cand_dev, ldc, M, first_index, acq_mask, y_opt, xi, kappa, mu_b, sig_b, nullptr, 0, &g2, 1, rows1,
+                           reinterpret_cast<const long long*>(&ctl->count_b)))) return rc;
+    compact_refined_kernel<<<nblk, 256, 0, st>>>(mu_b, sig_b, acq_mask, y_opt, xi, kappa, ctx->best_dev, ctl, rows1, rows0);
+    OB_LAUNCH_CHECK(ctx);
+    rows_b = rows0;
+    count_b = &ctl->count_b2;
   }
-  ob_l2_release(ctx);
+  int grid_b = 0;
+  if ((rc = score_launch(ctx, cand_dev, ldc, M, first_index, acq_mask, y_opt, xi, kappa, nullptr, nullptr, nullptr, 1, &grid_b, 0, rows_b,
+                         reinterpret_cast<const long long*>(count_b)))) return rc;
+  reduce_best_kernel<<<1, 256, 0, st>>>(reinterpret_cast<const best_t*>(ctx->partial_dev), grid, acq_mask, ctx->best_dev);
+  OB_LAUNCH_CHECK(ctx);
+  OB_CUDA(ctx, cudaMemcpyAsync(ctx->best_pinned, ctx->best_dev, 3 * sizeof(ob200_best), cudaMemcpyDeviceToHost, st));
+  OB_CUDA(ctx, cudaMemcpyAsync(ctx->ctl_pinned, ctl, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+  OB_CUDA(ctx, cudaStreamSynchronize(st));
+  const unsigned long long* counts = reinterpret_cast<const unsigned long long*>(ctx->ctl_pinned);
+  const int64_t n_scored = (int64_t)counts[0] + (int64_t)(f32_done ? counts[2] : counts[1]);
+  ctx->last_prune_f32 = f32_done;
+  ctx->last_prune_counts[0] = (int64_t)counts[0]; ctx->last_prune_counts[1] = (int64_t)counts[1]; ctx->last_prune_counts[2] = (int64_t)counts[2];
+  for (int k = 0; k < 3; ++k) {
+    if (!(acq_mask & (1 << k))) continue;
+    best_host[k] = ctx->best_pinned[k];
+    if (n_scored_host) n_scored_host[k] = n_scored;
+  }
   if (cand_dev == ctx->cand_tmp) return ob200_sample_status(ctx);
   return OB200_OK;
 }
@@ -1218,6 +1183,29 @@ extern "C" int ob200_score_pruned(ob200_ctx* ctx, const double* cand_dev, int64_
   if (rc) return rc;
   best_host[0] = best[acq];
   if (n_scored_host) *n_scored_host = ns[acq];
+  return OB200_OK;
+}
+
+// Pass 1 of the pruned path on its own (tests, tools): mu_lb[i] <= posterior mean and sigma_ub[i] >= posterior std of
+// candidate i, from the FP32 bound kernel (*used_f32 = 1) or the FP64 mean-only kernel (*used_f32 = 0, mu_lb exact).
+extern "C" int ob200_score_bounds(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M, double* mu_lb_dev, double* sigma_ub_dev,
+                                  int* used_f32) {
+  if (!ctx) return OB200_EINVAL;
+  if (!ctx->fitted) OB_FAIL(ctx, OB200_ESTATE, "ob200_score_bounds called before ob200_gp_fit / ob200_gp_import");
+  if (!cand_dev || !mu_lb_dev || !sigma_ub_dev || M < 1 || ldc < ctx->hdr.D) OB_FAIL(ctx, OB200_EINVAL, "bad cand/mu/sigma/M/ldc");
+  OB_CUDA(ctx, cudaSetDevice(ctx->device));
+  int done = 0, grid = 0, rc;
+  if ((rc = ob200_bound_f32_launch(ctx, cand_dev, ldc, M, mu_lb_dev, sigma_ub_dev, &done))) return rc;
+  if (!done && (rc = score_launch(ctx, cand_dev, ldc, M, 0, 1, 0.0, 0.0, 0.0, mu_lb_dev, sigma_ub_dev, nullptr, 0, &grid, 1))) return rc;
+  if (used_f32) *used_f32 = done;
+  return OB200_OK;
+}
+
+// Counters of the last ob200_score_pruned[_multi] call that took the pruned path: used_f32, rows in batch A, rows the
+// pass-1 bounds left for batch B, rows left after the FP64 refinement of those bounds.
+extern "C" int ob200_prune_stats(const ob200_ctx* ctx, int64_t out[4]) {
+  if (!ctx || !out) return OB200_EINVAL;
+  out[0] = ctx->last_prune_f32; out[1] = ctx->last_prune_counts[0]; out[2] = ctx->last_prune_counts[1]; out[3] = ctx->last_prune_counts[2];
   return OB200_OK;
 }
 

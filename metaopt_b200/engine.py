@@ -286,6 +286,23 @@ class Engine:
         names = {0: "EI", 1: "PI", 2: "LCB"}
         return self._bests(best, acq_mask), {names[k]: int(n_scored[k]) for k in range(3) if acq_mask & (1 << k)}
 
+    def score_bounds(self, cand):
+        """(mu_lb [M], sigma_ub [M], used_f32): pass 1 of the pruned path for the CUDA tensor `cand` [M x >=D]."""
+        self.use_torch_stream()
+        assert cand.dtype == torch.float64 and cand.is_cuda and cand.stride(1) == 1
+        M = cand.shape[0]
+        mu = torch.empty(M, dtype=torch.float64, device=self.tdev)
+        sg = torch.empty(M, dtype=torch.float64, device=self.tdev)
+        used = C.c_int()
+        self._check(self.lib.ob200_score_bounds(self.ctx, _ptr(cand), cand.stride(0), M, _ptr(mu), _ptr(sg), C.byref(used)))
+        return mu, sg, bool(used.value)
+
+    def prune_stats(self):
+        """Counters of the last pruned call: dict(f32, batch_a, batch_b, batch_b_refined)."""
+        out = (C.c_int64 * 4)()
+        self._check(self.lib.ob200_prune_stats(self.ctx, out))
+        return dict(f32=bool(out[0]), batch_a=int(out[1]), batch_b=int(out[2]), batch_b_refined=int(out[3]))
+
     def score_host(self, cand, acq_mask=1, y_opt=0.0, xi=0.01, kappa=1.96, dense=False):
         """Same through host buffers (numpy in, numpy out): H2D/D2H copies happen inside the call."""
         self.use_torch_stream()

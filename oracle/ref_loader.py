@@ -89,8 +89,22 @@ def load():
         return None
     sys.dont_write_bytecode = True  # the reference tree is read-only
     _install_shims()
-    if REF_SRC not in sys.path:
-        sys.path.insert(0, REF_SRC)
+    paths = [REF_SRC]
+    if os.path.isdir(os.path.join(REF_SRC, "orion-0+unknown.dist-info")) or any(
+            name.endswith(".dist-info") and name.startswith("orion") for name in os.listdir(REF_SRC)):
+        # The pip-installed copy advertises entry points, and loading one makes pkg_resources verify the `orion`
+        # distribution's install_requires (pymongo, AppDirs): give it the on-disk twins of the module shims.
+        import tempfile
+        shim_dir = tempfile.mkdtemp(prefix="orion_dist_shims_")
+        write_dist_shims(shim_dir)
+        paths.append(shim_dir)
+    for path in paths:
+        if path not in sys.path:
+            sys.path.insert(0, path)
+    if "pkg_resources" in sys.modules:  # imported before the paths existed: tell its working set
+        import pkg_resources
+        for path in paths:
+            pkg_resources.working_set.add_entry(path)
     import orion  # noqa: F401
     import orion.algo.space  # noqa: F401
     import orion.algo.base  # noqa: F401

