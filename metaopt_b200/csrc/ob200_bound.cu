@@ -18,8 +18,9 @@
 // Replaces (for the bound only) sklearn kernels.py:1720-1729 / :1569-1570 and _gpr.py:446-447.
 //
 // Work decomposition: CTA tile = CT candidates (128 / 64 / 32, the largest whose A fragments fit) x all observed
-// points; 8 consumer warps as WC x WO, each with a 32-candidate x (128 / WO)-observation register tile of
-// mma.sync.m16n8k8 TF32 accumulators; observed points arrive in chunks of 128, pre-split into TF32 hi/lo B
+// points; WC x 4 consumer warps (16 / 8 / 4), each with a 32-candidate x 32-observation register tile of
+// mma.sync.m16n8k8 TF32 accumulators (four warps per SM sub-partition: the HMMA, MUFU and FFMA phases of different
+// warps overlap; ncu of the first version, 8 warps with 32 x 64 tiles, showed all three pipes at ~40 % each); observed points arrive in chunks of 128, pre-split into TF32 hi/lo B
 // fragments at fit time, staged by bulk async copies (TMA engine) from a producer warp through an mbarrier ring.
 // The distance is in "T units": coordinates are pre-scaled so that Matern-5/2 is (1 + t + t^2/3) e^-t with
 // t = sqrt(T) and RBF is e^-T.
@@ -31,9 +32,12 @@
 namespace {
 
 #define BD_OBC 128            // observed points per chunk
-#define BD_WARPS 8            // consumer warps
-#define BD_THREADS ((BD_WARPS + 1) * 32)
 #define BD_STAGES_MAX 4
+#ifdef BD_RSQ
+#define BD_T_FLOOR 1e-30f     // t = T * rsqrt(T) needs T > 0; the shift is far below the error budget
+#else
+#define BD_T_FLOOR 0.f
+#endif
 
 struct bound_args {
   const double* cand; long long ldc; long long M;
@@ -61,6 +65,11 @@ __device__ __forceinline__ float sqrt_approx(float v) {
   asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(v));
   return r;
 }
+__device__ __forceinline__ float rsqrt_approx(float v) {
+  float r;
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(v));
+  return r;
+}
 __device__ __forceinline__ float ex2_approx(float v) {
   float r;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(v));
@@ -71,6 +80,9 @@ __device__ __forceinline__ float ex2_approx(float v) {
 // b0 = B[q][g], b1 = B[q+4][g]; c0 = C[g][2q], c1 = C[g][2q+1], c2 = C[g+8][2q], c3 = C[g+8][2q+1]
 __device__ __forceinline__ void mma_tf32(float (&c)[4], const uint32_t a0, const uint32_t a1, const uint32_t a2,
                                          const uint32_t a3, const uint32_t b0, const uint32_t b1) {
+#ifdef BD_DBG_NOMMA
+  c[0] += __uint_as_float(a0 ^ b0); return;    // timing experiment only
+#endif
   asm("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
       : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
       : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
@@ -80,35 +92,92 @@ __host__ __device__ inline size_t bound_smem_bytes(int ct, int nk, int ksl, int 
   return (size_t)(ct / 16) * nk * 1024            // A fragments (hi plane + lo plane)
          + (size_t)stages * ksl * 8192            // B stages
          + (size_t)ct * 8                         // cc
-         + (size_t)3 * 256 * 8                    // cross-warp reduction (mu, S, kmax): WO x CT = 256 entries each
-         + 2 * BD_STAGES_MAX * 8 + 128;
+         + (size_t)3 * 4 * ct * 8                 // cross-warp reduction (mu, S, kmax): WO (<= 4) x CT entries each
+         + 2 * BD_STAGES_MAX * 8 + (size_t)nk * 64 + 128;
 }
 
 template <int KIND>
 __device__ __forceinline__ float kernel_T(float T) {
   if (KIND == OB200_KERNEL_MATERN52) {
+#if defined(BD_DBG_NOSQRT)
+    const float t = T * 0.25f;                 // timing experiment only
+#elif defined(BD_RSQ)
+    const float t = T * rsqrt_approx(T);       // (T >= 1e-30 here)
+#else
     const float t = sqrt_approx(T);
+#endif
     const float p = fmaf(t, fmaf(t, 0.333333343f, 1.0f), 1.0f);
+#if defined(BD_DBG_NOEX2)
+    return p * fmaf(t, -0.01f, 1.0f);          // timing experiment only
+#else
     return p * ex2_approx(t * -1.44269504f);
+#endif
   }
   return ex2_approx(T * -1.44269504f);
 }
 
-// WC = warps along the candidates (CT = 32 WC); WO = 8 / WC warps along the observations; NB = n8 blocks per warp
-template <int WC, int KIND>
-__global__ void __launch_bounds__(BD_THREADS, 1) bound_kernel(bound_args a) {
-  constexpr int CT = 32 * WC, WO = BD_WARPS / WC, NB = (BD_OBC / 8) / WO;
+// D = A * B (no accumulator input: the first product of a tile needs no zeroed registers)
+__device__ __forceinline__ void mma_tf32_first(float (&c)[4], const uint32_t a0, const uint32_t a1, const uint32_t a2,
+                                               const uint32_t a3, const uint32_t b0, const uint32_t b1) {
+  asm("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%10,%10,%10};"
+      : "=f"(c[0]), "=f"(c[1]), "=f"(c[2]), "=f"(c[3])
+      : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1), "f"(0.f));
+}
+
+// the producer's wait: back off between polls so that the spinning lane does not eat its sub-partition's issue slots
+__device__ __forceinline__ void mbar_wait_backoff(uint64_t* bar, uint32_t parity) {
+  uint32_t done = 0;
+  for (;;) {
+    asm volatile(
+        "{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}\n"
+        : "=r"(done) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    if (done) break;
+    __nanosleep(200);
+  }
+}
+
+// kernel values of one n8 block (32 candidates x 8 observations per warp): mean / |mean| partial sums, nearest observation
+template <int KIND>
+__device__ __forceinline__ void epilogue_nb(const float (&acc)[2][4], const float4 ax, const float (&ccr)[2][2], float (&mu32)[2][2],
+                                            float (&s32)[2][2], float (&kmx)[2][2]) {
+  const float xx0 = ax.x, xx1 = ax.y, al0 = ax.z, al1 = ax.w;
+  const float ab0 = fabsf(al0), ab1 = fabsf(al1);
+#pragma unroll
+  for (int mb = 0; mb < 2; ++mb)
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const float T0 = fmaxf(fmaf(-2.f, acc[mb][2 * h], ccr[mb][h] + xx0), BD_T_FLOOR);
+      const float T1 = fmaxf(fmaf(-2.f, acc[mb][2 * h + 1], ccr[mb][h] + xx1), BD_T_FLOOR);
+      const float k0 = kernel_T<KIND>(T0), k1 = kernel_T<KIND>(T1);
+      mu32[mb][h] = fmaf(k0, al0, mu32[mb][h]);
+      mu32[mb][h] = fmaf(k1, al1, mu32[mb][h]);
+      s32[mb][h] = fmaf(k0, ab0, s32[mb][h]);
+      s32[mb][h] = fmaf(k1, ab1, s32[mb][h]);
+      kmx[mb][h] = fmaxf(kmx[mb][h], fmaxf(k0, k1));
+    }
+}
+
+// WC x WO consumer warps: WC along the candidates (CT = 32 WC), WO along the 128 observations of a chunk (NB = 16 / WO n8
+// blocks per warp).  NKR > 0: the space has exactly NKR k-steps (D <= 8 NKR <= 32) -- the warp keeps its A fragments in
+// registers for the whole tile and walks the chunk n8 block by n8 block, MMAs of block nb + 1 next to the kernel
+// evaluations of block nb in one unrolled instruction stream, so the tensor, MUFU and FFMA pipes overlap inside a warp.
+// NKR == 0: any width; A fragments re-read from shared memory per k-step, all MMAs of a chunk before its evaluations.
+template <int WC, int WO, int KIND, int NKR>
+__global__ void __launch_bounds__((WC * WO + 1) * 32, 1) bound_kernel(bound_args a) {
+  constexpr int BD_WARPS = WC * WO, CT = 32 * WC, NB = (BD_OBC / 8) / WO;
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  const int nk = a.nk, ksl = a.ksl;
+  const int nk = NKR > 0 ? NKR : a.nk, ksl = NKR > 0 ? NKR : a.ksl;
   float4* As = reinterpret_cast<float4*>(smem_raw);                                   // [CT/16][nk][hi | lo][32]
   float4* Bs = As + (size_t)(CT / 16) * nk * 64;                                      // stages x [16][ksl][32]
   double* cc = reinterpret_cast<double*>(Bs + (size_t)a.stages * ksl * 512);          // [CT]
   double* red = cc + CT;                                                              // [3][WO][CT]
   uint64_t* full = reinterpret_cast<uint64_t*>(red + 3 * WO * CT);
   uint64_t* empty = full + BD_STAGES_MAX;
+  double* sl = reinterpret_cast<double*>(empty + BD_STAGES_MAX);                      // [8 nk] scale / ls (0 beyond D)
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int g = lane >> 2, q = lane & 3;
+  for (int d = tid; d < nk * 8; d += blockDim.x) sl[d] = d < a.D ? a.scale / a.ls[d] : 0.0;
   if (tid == 0) {
     for (int s = 0; s < BD_STAGES_MAX; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], BD_WARPS); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -124,7 +193,7 @@ __global__ void __launch_bounds__(BD_THREADS, 1) bound_kernel(bound_args a) {
           for (int s = 0; s < a.n_slices; ++s, ++it) {
             const int st = it % a.stages;
             const uint32_t ph = (it / a.stages) & 1;
-            mbar_wait(&empty[st], ph ^ 1);
+            mbar_wait_backoff(&empty[st], ph ^ 1);
             mbar_expect_tx(&full[st], stage_bytes);
             bulk_g2s(Bs + (size_t)st * ksl * 512, a.bp + ((size_t)c * a.n_slices + s) * ksl * 512, stage_bytes, &full[st]);
           }
@@ -136,29 +205,35 @@ __global__ void __launch_bounds__(BD_THREADS, 1) bound_kernel(bound_args a) {
   for (long long tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
     const long long row0 = tile * CT;
     // ---- stage the candidate tile: u = scale * c / ls -> TF32 hi/lo A fragments; cc = ||u||^2 in FP64.
-    // Two threads per row (even / odd columns).
+    // (32 WO / CT = WO / WC ... ) TPR threads per row (columns d = part, part + TPR, ...).
     {
-      const int r = tid >> 1, half = tid & 1;
-      const bool live = r < CT && row0 + r < a.M;
+      constexpr int TPR = (BD_WARPS * 32) / CT;   // = WO: 2 or 4 threads per row
+      const int r = tid / TPR, part = tid % TPR;
+      const bool live = row0 + r < a.M;
       double acc = 0.0;
-      if (r < CT) {
-        const int mb = r >> 4, rr = r & 15, gg = rr & 7, hi8 = rr >> 3;
-        const double* src = a.cand + (size_t)(row0 + r) * a.ldc;
-        for (int d = half; d < nk * 8; d += 2) {
-          double u = 0.0;
-          if (live && d < a.D) u = a.scale * src[d] / a.ls[d];
-          acc = fma(u, u, acc);
-          const float uf = (float)u;
-          const uint32_t hi = to_tf32(uf);
-          const uint32_t lo = to_tf32(uf - __uint_as_float(hi));
-          const int ks = d >> 3, kk = d & 7, qq = kk & 3, hi4 = kk >> 2;
-          uint32_t* dst = reinterpret_cast<uint32_t*>(As + (size_t)(mb * nk + ks) * 64 + (gg * 4 + qq));
-          dst[hi8 + 2 * hi4] = hi;
-          dst[32 * 4 + hi8 + 2 * hi4] = lo;
-        }
+      const int mb = r >> 4, rr = r & 15, gg = rr & 7, hi8 = rr >> 3;
+      const double* src = a.cand + (size_t)(row0 + r) * a.ldc;
+      {  // the next tile of this CTA: pull its rows towards L2 / L1 while this one is processed
+        const long long nrow = row0 + (long long)gridDim.x * CT + r;
+        if (nrow < a.M && part == 0)
+          for (int b = 0; b < a.D * 8; b += 128) asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const char*>(a.cand + (size_t)nrow * a.ldc) + b));
       }
-      acc += __shfl_xor_sync(0xffffffffu, acc, 1);
-      if (r < CT && half == 0) cc[r] = acc;
+#pragma unroll 4
+      for (int d = part; d < nk * 8; d += TPR) {
+        double u = 0.0;
+        if (live && d < a.D) u = src[d] * sl[d];   // (one rounding away from scale * c / ls: far inside the budget)
+        acc = fma(u, u, acc);
+        const float uf = (float)u;
+        const uint32_t hi = to_tf32(uf);
+        const uint32_t lo = to_tf32(uf - __uint_as_float(hi));
+        const int ks = d >> 3, kk = d & 7, qq = kk & 3, hi4 = kk >> 2;
+        uint32_t* dst = reinterpret_cast<uint32_t*>(As + (size_t)(mb * nk + ks) * 64 + (gg * 4 + qq));
+        dst[hi8 + 2 * hi4] = hi;
+        dst[32 * 4 + hi8 + 2 * hi4] = lo;
+      }
+#pragma unroll
+      for (int o = 1; o < TPR; o <<= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+      if (part == 0) cc[r] = acc;
     }
     asm volatile("bar.sync 1, %0;" ::"n"(BD_WARPS * 32) : "memory");
 
@@ -169,68 +244,110 @@ __global__ void __launch_bounds__(BD_THREADS, 1) bound_kernel(bound_args a) {
     float kmx[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
     const float4* Aw = As + (size_t)(wc * 2) * nk * 64 + lane;
 
-    for (int c = 0; c < a.n_chunks; ++c) {
-      float acc[2][NB][4];
+    if constexpr (NKR > 0) {
+      uint32_t Ah[2][NKR][4], Al[2][NKR][4];
 #pragma unroll
       for (int mb = 0; mb < 2; ++mb)
 #pragma unroll
-        for (int nb = 0; nb < NB; ++nb)
-#pragma unroll
-          for (int e = 0; e < 4; ++e) acc[mb][nb][e] = 0.f;
-      const float4* axp = a.aux + ((size_t)(c * (BD_OBC / 8) + wo * NB)) * 4 + q;   // this lane's observation constants
-
-      for (int s = 0; s < a.n_slices; ++s, ++it) {
+        for (int ks = 0; ks < NKR; ++ks) {
+          const float4 h = Aw[(size_t)(mb * NKR + ks) * 64], l = Aw[(size_t)(mb * NKR + ks) * 64 + 32];
+          Ah[mb][ks][0] = __float_as_uint(h.x); Ah[mb][ks][1] = __float_as_uint(h.y); Ah[mb][ks][2] = __float_as_uint(h.z); Ah[mb][ks][3] = __float_as_uint(h.w);
+          Al[mb][ks][0] = __float_as_uint(l.x); Al[mb][ks][1] = __float_as_uint(l.y); Al[mb][ks][2] = __float_as_uint(l.z); Al[mb][ks][3] = __float_as_uint(l.w);
+        }
+      for (int c = 0; c < a.n_chunks; ++c, ++it) {
+        const float4* axp = a.aux + ((size_t)(c * (BD_OBC / 8) + wo * NB)) * 4 + q;   // this lane's observation constants
         const int st = it % a.stages;
         const uint32_t ph = (it / a.stages) & 1;
         mbar_wait(&full[st], ph);
-        const float4* Bw = Bs + (size_t)st * ksl * 512 + (size_t)(wo * NB) * ksl * 32 + lane;
-        const int jn = min(ksl, nk - s * ksl);
-        for (int j = 0; j < jn; ++j) {
-          const int ks = s * ksl + j;
-          float4 ah[2], al[2];
+        const float4* Bw = Bs + (size_t)st * NKR * 512 + (size_t)(wo * NB) * NKR * 32 + lane;
+        float mu32[2][2] = {{0.f, 0.f}, {0.f, 0.f}}, s32[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
+        // Two n8 blocks at a time: four independent accumulators (2 x mb) take turns, so an HMMA never waits for the
+        // one issued just before it (the chain into one accumulator is 3 NKR long); small terms first.
 #pragma unroll
-          for (int mb = 0; mb < 2; ++mb) { ah[mb] = Aw[(size_t)(mb * nk + ks) * 64]; al[mb] = Aw[(size_t)(mb * nk + ks) * 64 + 32]; }
+        for (int nb = 0; nb < NB; nb += 2) {
+          float acc[2][2][4];
+          uint32_t bh[2][NKR][2], bl[2][NKR][2];
 #pragma unroll
-          for (int nb = 0; nb < NB; ++nb) {
-            const float4 b = Bw[(size_t)(nb * ksl + j) * 32];
-            const uint32_t bh0 = __float_as_uint(b.x), bh1 = __float_as_uint(b.y), bl0 = __float_as_uint(b.z), bl1 = __float_as_uint(b.w);
+          for (int e = 0; e < 2; ++e)
 #pragma unroll
-            for (int mb = 0; mb < 2; ++mb) {
-              const uint32_t h0 = __float_as_uint(ah[mb].x), h1 = __float_as_uint(ah[mb].y), h2 = __float_as_uint(ah[mb].z), h3 = __float_as_uint(ah[mb].w);
-              mma_tf32(acc[mb][nb], __float_as_uint(al[mb].x), __float_as_uint(al[mb].y), __float_as_uint(al[mb].z), __float_as_uint(al[mb].w), bh0, bh1);
-              mma_tf32(acc[mb][nb], h0, h1, h2, h3, bl0, bl1);
-              mma_tf32(acc[mb][nb], h0, h1, h2, h3, bh0, bh1);
+            for (int ks = 0; ks < NKR; ++ks) {
+              const float4 b = Bw[(size_t)((nb + e) * NKR + ks) * 32];
+              bh[e][ks][0] = __float_as_uint(b.x); bh[e][ks][1] = __float_as_uint(b.y); bl[e][ks][0] = __float_as_uint(b.z); bl[e][ks][1] = __float_as_uint(b.w);
             }
-          }
+#pragma unroll
+          for (int ks = 0; ks < NKR; ++ks)
+#pragma unroll
+            for (int e = 0; e < 2; ++e)
+#pragma unroll
+              for (int mb = 0; mb < 2; ++mb) {
+                if (ks == 0) mma_tf32_first(acc[e][mb], Al[mb][ks][0], Al[mb][ks][1], Al[mb][ks][2], Al[mb][ks][3], bh[e][ks][0], bh[e][ks][1]);
+                else mma_tf32(acc[e][mb], Al[mb][ks][0], Al[mb][ks][1], Al[mb][ks][2], Al[mb][ks][3], bh[e][ks][0], bh[e][ks][1]);
+              }
+#pragma unroll
+          for (int ks = 0; ks < NKR; ++ks)
+#pragma unroll
+            for (int e = 0; e < 2; ++e)
+#pragma unroll
+              for (int mb = 0; mb < 2; ++mb) mma_tf32(acc[e][mb], Ah[mb][ks][0], Ah[mb][ks][1], Ah[mb][ks][2], Ah[mb][ks][3], bl[e][ks][0], bl[e][ks][1]);
+#pragma unroll
+          for (int ks = 0; ks < NKR; ++ks)
+#pragma unroll
+            for (int e = 0; e < 2; ++e)
+#pragma unroll
+              for (int mb = 0; mb < 2; ++mb) mma_tf32(acc[e][mb], Ah[mb][ks][0], Ah[mb][ks][1], Ah[mb][ks][2], Ah[mb][ks][3], bh[e][ks][0], bh[e][ks][1]);
+#pragma unroll
+          for (int e = 0; e < 2; ++e) epilogue_nb<KIND>(acc[e], __ldg(axp + (nb + e) * 4), ccr, mu32, s32, kmx);
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(&empty[st]);
-      }
-      // ---- epilogue of the chunk: kernel values, mean / |mean| partial sums, nearest observation
-      float mu32[2][2] = {{0.f, 0.f}, {0.f, 0.f}}, s32[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
-#pragma unroll
-      for (int nb = 0; nb < NB; ++nb) {
-        const float4 ax = __ldg(axp + nb * 4);
-        const float xx0 = ax.x, xx1 = ax.y, al0 = ax.z, al1 = ax.w;
-        const float ab0 = fabsf(al0), ab1 = fabsf(al1);
 #pragma unroll
         for (int mb = 0; mb < 2; ++mb)
 #pragma unroll
-          for (int h = 0; h < 2; ++h) {
-            const float T0 = fmaxf(fmaf(-2.f, acc[mb][nb][2 * h], ccr[mb][h] + xx0), 0.f);
-            const float T1 = fmaxf(fmaf(-2.f, acc[mb][nb][2 * h + 1], ccr[mb][h] + xx1), 0.f);
-            const float k0 = kernel_T<KIND>(T0), k1 = kernel_T<KIND>(T1);
-            mu32[mb][h] = fmaf(k0, al0, mu32[mb][h]);
-            mu32[mb][h] = fmaf(k1, al1, mu32[mb][h]);
-            s32[mb][h] = fmaf(k0, ab0, s32[mb][h]);
-            s32[mb][h] = fmaf(k1, ab1, s32[mb][h]);
-            kmx[mb][h] = fmaxf(kmx[mb][h], fmaxf(k0, k1));
-          }
+          for (int h = 0; h < 2; ++h) { mu64[mb][h] += (double)mu32[mb][h]; s64[mb][h] += (double)s32[mb][h]; }
       }
+    } else {
+      for (int c = 0; c < a.n_chunks; ++c) {
+        float acc[NB][2][4];
+        const float4* axp = a.aux + ((size_t)(c * (BD_OBC / 8) + wo * NB)) * 4 + q;
+        for (int s = 0; s < a.n_slices; ++s, ++it) {
+          const int st = it % a.stages;
+          const uint32_t ph = (it / a.stages) & 1;
+          mbar_wait(&full[st], ph);
+          const float4* Bw = Bs + (size_t)st * ksl * 512 + (size_t)(wo * NB) * ksl * 32 + lane;
+          const int jn = min(ksl, nk - s * ksl);
+          for (int j = 0; j < jn; ++j) {
+            const int ks = s * ksl + j;
+            float4 ah[2], al[2];
 #pragma unroll
-      for (int mb = 0; mb < 2; ++mb)
+            for (int mb = 0; mb < 2; ++mb) { ah[mb] = Aw[(size_t)(mb * nk + ks) * 64]; al[mb] = Aw[(size_t)(mb * nk + ks) * 64 + 32]; }
+            // split products in the OUTER position: the three MMAs into one accumulator are 2 NB instructions apart
 #pragma unroll
-        for (int h = 0; h < 2; ++h) { mu64[mb][h] += (double)mu32[mb][h]; s64[mb][h] += (double)s32[mb][h]; }
+            for (int term = 0; term < 3; ++term)
+#pragma unroll
+              for (int nb = 0; nb < NB; ++nb) {
+                const float4 b = Bw[(size_t)(nb * ksl + j) * 32];
+                const uint32_t b0 = __float_as_uint(term == 1 ? b.z : b.x), b1 = __float_as_uint(term == 1 ? b.w : b.y);
+#pragma unroll
+                for (int mb = 0; mb < 2; ++mb) {
+                  const float4 av = term == 0 ? al[mb] : ah[mb];
+                  if (term == 0 && ks == 0)
+                    mma_tf32_first(acc[nb][mb], __float_as_uint(av.x), __float_as_uint(av.y), __float_as_uint(av.z), __float_as_uint(av.w), b0, b1);
+                  else
+                    mma_tf32(acc[nb][mb], __float_as_uint(av.x), __float_as_uint(av.y), __float_as_uint(av.z), __float_as_uint(av.w), b0, b1);
+                }
+              }
+          }
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&empty[st]);
+        }
+        float mu32[2][2] = {{0.f, 0.f}, {0.f, 0.f}}, s32[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
+#pragma unroll
+        for (int nb = 0; nb < NB; ++nb) epilogue_nb<KIND>(acc[nb], __ldg(axp + nb * 4), ccr, mu32, s32, kmx);
+#pragma unroll
+        for (int mb = 0; mb < 2; ++mb)
+#pragma unroll
+          for (int h = 0; h < 2; ++h) { mu64[mb][h] += (double)mu32[mb][h]; s64[mb][h] += (double)s32[mb][h]; }
+      }
     }
 
     // ---- reduce over the 4 column lanes, then over the WO observation warps through shared memory
@@ -328,11 +445,11 @@ __global__ void __launch_bounds__(256) bound_pack_kernel(const double* __restric
   }
 }
 
-template <int WC>
-int launch_wc(ob200_ctx* ctx, const bound_args& a, int grid, size_t smem) {
-  auto kern = a.kind == OB200_KERNEL_MATERN52 ? bound_kernel<WC, OB200_KERNEL_MATERN52> : bound_kernel<WC, OB200_KERNEL_RBF>;
+template <int WC, int WO, int NKR>
+int launch_cfg(ob200_ctx* ctx, const bound_args& a, int grid, size_t smem) {
+  auto kern = a.kind == OB200_KERNEL_MATERN52 ? bound_kernel<WC, WO, OB200_KERNEL_MATERN52, NKR> : bound_kernel<WC, WO, OB200_KERNEL_RBF, NKR>;
   OB_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  kern<<<grid, BD_THREADS, smem, ctx->stream>>>(a);
+  kern<<<grid, (WC * WO + 1) * 32, smem, ctx->stream>>>(a);
   OB_LAUNCH_CHECK(ctx);
   return OB200_OK;
 }
@@ -362,9 +479,7 @@ int ob200_bound_f32_launch(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, 
     if (wc == 1) return OB200_OK;   // not even a 32-candidate tile fits: FP64 pass
     wc >>= 1;
   }
-  // One CTA per SM: the 32 x 64 register tile (64 accumulators, 8 kernel evaluations in flight per n8 block) gives
-  // each warp enough independent MUFU / FFMA chains; the kernel needs ~170 registers per thread for that.
-  const int ctas_per_sm = 1;
+  const int ctas_per_sm = 1;   // one CTA of 4 WC + 1 warps per SM
   const int64_t bp_elems = (int64_t)n_chunks * n_slices * 16 * ksl * 32;   // float4
   const int64_t aux_elems = (int64_t)n_chunks * (BD_OBC / 8) * 4;
   int rc;
@@ -408,9 +523,13 @@ int ob200_bound_f32_launch(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, 
   a.n_tiles = (M + ct - 1) / ct;
   const int64_t max_grid = (int64_t)ctx->num_sms * ctas_per_sm;
   const int grid = (int)(a.n_tiles < max_grid ? a.n_tiles : max_grid);
-  if (wc == 4) rc = launch_wc<4>(ctx, a, grid, smem);
-  else if (wc == 2) rc = launch_wc<2>(ctx, a, grid, smem);
-  else rc = launch_wc<1>(ctx, a, grid, smem);
+  if (wc == 4 && nk == 1) rc = launch_cfg<4, 2, 1>(ctx, a, grid, smem);        // D <= 8
+  else if (wc == 4 && nk == 2) rc = launch_cfg<4, 2, 2>(ctx, a, grid, smem);   // D <= 16
+  else if (wc == 4 && nk == 3) rc = launch_cfg<4, 2, 3>(ctx, a, grid, smem);   // D <= 24 (BASELINE config 2)
+  else if (wc == 4 && nk == 4) rc = launch_cfg<4, 2, 4>(ctx, a, grid, smem);   // D <= 32
+  else if (wc == 4) rc = launch_cfg<4, 4, 0>(ctx, a, grid, smem);
+  else if (wc == 2) rc = launch_cfg<2, 4, 0>(ctx, a, grid, smem);
+  else rc = launch_cfg<1, 4, 0>(ctx, a, grid, smem);
   if (rc) return rc;
   *done = 1;
   return OB200_OK;
