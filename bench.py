@@ -522,8 +522,9 @@ def run_ours(args):
     dgemm = dgemm_tflops(torch, dev) if rank == 0 or multi else None
     configs = bench_other_configs(torch, eng, comp, rank, world, multi, dgemm, peaks, peak_src, barrier, rmax, obdist, compiler,
                                   build_required_space)
-    # restore the cfg2 space on the engine (the legs above registered other spaces)
+    # restore the cfg2 space and fit on the engine (the legs above registered other spaces and fits)
     compiler.upload(eng, comp)
+    eng.fit(X, y, amplitude=1.0, length_scale=np.ones(DIM), alpha=ALPHA + NOISE, normalize_y=True)
 
     if rank != 0:
         if multi:

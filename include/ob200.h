@@ -199,8 +199,10 @@ int ob200_score_pruned(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int6
  * best_host [3] and n_scored_host [3] (may be NULL) are indexed by OB200_ACQ_*; entries outside the mask are zeroed.
  * The bound pass runs in FP32 on the TF32 tensor cores with a rigorous error budget (mu_lb <= mu, sigma_ub >= sigma;
  * csrc/ob200_bound.cu); candidates it cannot exclude get exact FP64 bounds before the O(n^2) scoring, so the winner
- * stays bit-identical to the dense call.  OB200_BOUND_F32=0 in the environment selects the FP64 bound pass for
- * everything.  -LCB with kappa < 0 is not increasing in sigma: such calls take the dense path.  y_opt, xi, kappa must
+ * stays bit-identical to the dense call.  The FP32 pass is used only for fits whose error budget leaves a usable
+ * bound (decided once per fit from ||alpha||_1); OB200_BOUND_F32=0 in the environment selects the FP64 bound pass for
+ * everything.  When many candidates are still standing after that, a GP on 192 evenly spaced observations bounds
+ * their variance from above once more (conditioning on a subset can only raise it) before the O(n^2) scoring.  -LCB with kappa < 0 is not increasing in sigma: such calls take the dense path.  y_opt, xi, kappa must
  * be finite (OB200_EINVAL otherwise, in every score entry point).  One host synchronisation per call. */
 int ob200_score_pruned_multi(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M, uint64_t seed,
                              uint64_t first_index, int acq_mask, double y_opt, double xi, double kappa,
@@ -214,8 +216,10 @@ int ob200_score_bounds(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int6
                        double* sigma_ub_dev, int* used_f32);
 /* Counters of the last ob200_score_pruned[_multi] call that took the pruned path: out[0] = FP32 bound pass used,
  * out[1] = candidates in the first batch, out[2] = candidates the pass-1 bounds left for the second batch,
- * out[3] = of those, the ones still standing after their bounds were recomputed in FP64 (0 when out[0] == 0). */
-int ob200_prune_stats(const ob200_ctx* ctx, int64_t out[4]);
+ * out[3] = of those, the ones still standing after their bounds were recomputed in FP64 (0 when out[0] == 0),
+ * out[4] = the ones still standing after the subset-GP variance bound (-1 when that step did not run: it is taken
+ * only when more than four first batches' worth of candidates are left). */
+int ob200_prune_stats(const ob200_ctx* ctx, int64_t out[5]);
 
 /* a16-a17 alone: acquisition + first-occurrence argmax over given posterior arrays
  * (skopt.acquisition.gaussian_ei/pi/lcb + numpy.argmin).  mu_dev, sigma_dev [M]. */

@@ -33,6 +33,7 @@ namespace {
 
 #define BD_OBC 128            // observed points per chunk
 #define BD_STAGES_MAX 4
+#define BD_PROBES 64          // observations at which the size of sum k |alpha| is sampled for the per-fit verdict
 #ifdef BD_RSQ
 #define BD_T_FLOOR 1e-30f     // t = T * rsqrt(T) needs T > 0; the shift is far below the error budget
 #else
@@ -393,7 +394,7 @@ __global__ void __launch_bounds__((WC * WO + 1) * 32, 1) bound_kernel(bound_args
 // Also the largest real ||x||^2 (one block: the table is small).
 __global__ void __launch_bounds__(256) bound_pack_kernel(const double* __restrict__ xs, const double* __restrict__ xx,
                                                          const double* __restrict__ alpha, int n, int n_pad, int D_pad, int nk,
-                                                         int ksl, int n_slices, int n_chunks, double scale,
+                                                         int ksl, int n_slices, int n_chunks, double scale, int kind,
                                                          float4* __restrict__ bp, float4* __restrict__ aux,
                                                          double* __restrict__ xx_max_out) {
   const int nd4 = D_pad >> 2;
@@ -434,14 +435,39 @@ __global__ void __launch_bounds__(256) bound_pack_kernel(const double* __restric
     out.w = j1 < n ? (float)alpha[j1] : 0.f;
     aux[e] = out;
   }
-  if (blockIdx.x == 0) {
-    __shared__ double sm[256];
-    double m = 0.0;
-    for (int j = threadIdx.x; j < n; j += 256) m = fmax(m, xx[j]);
-    sm[threadIdx.x] = m;
+  if (blockIdx.x == 0) {   // xx_max_out[0] = largest T-space ||x||^2, [1] = ||alpha||_1
+    __shared__ double sm[256], sa[256];
+    double m = 0.0, l1 = 0.0;
+    for (int j = threadIdx.x; j < n; j += 256) { m = fmax(m, xx[j]); l1 += fabs(alpha[j]); }
+    sm[threadIdx.x] = m; sa[threadIdx.x] = l1;
     __syncthreads();
-    for (int s = 128; s > 0; s >>= 1) { if (threadIdx.x < s) sm[threadIdx.x] = fmax(sm[threadIdx.x], sm[threadIdx.x + s]); __syncthreads(); }
-    if (threadIdx.x == 0) *xx_max_out = sm[0] * scale * scale;
+    for (int s = 128; s > 0; s >>= 1) {
+      if (threadIdx.x < s) { sm[threadIdx.x] = fmax(sm[threadIdx.x], sm[threadIdx.x + s]); sa[threadIdx.x] += sa[threadIdx.x + s]; }
+      __syncthreads();
+    }
+    if (threadIdx.x == 0) { xx_max_out[0] = sm[0] * scale * scale; xx_max_out[1] = sa[0]; }
+  }
+  // blocks 1 .. BD_PROBES: S_p = sum_j k(x_p, x_j) |alpha_j| (kernel without the amplitude) at BD_PROBES evenly spaced
+  // observations, in FP64 -- the size of the sum whose relative error the FP32 pass has to absorb (verdict per fit)
+  if (blockIdx.x >= 1 && blockIdx.x <= BD_PROBES) {
+    __shared__ double sp[256];
+    const int pr = (int)((long long)(blockIdx.x - 1) * n / BD_PROBES);
+    double acc = 0.0;
+    for (int j = threadIdx.x; j < n; j += 256) {
+      double d2 = 0.0;
+      for (int d = 0; d < D_pad; ++d) {
+        const double a = xs[((size_t)(pr >> 3) * nd4 + (d >> 2)) * 32 + (pr & 7) * 4 + (d & 3)];
+        const double b = xs[((size_t)(j >> 3) * nd4 + (d >> 2)) * 32 + (j & 7) * 4 + (d & 3)];
+        d2 = fma(a - b, a - b, d2);
+      }
+      const double T = scale * scale * d2, t = sqrt(T);
+      const double k = kind == OB200_KERNEL_MATERN52 ? (1.0 + t + T * (1.0 / 3.0)) * exp(-t) : exp(-T);
+      acc = fma(k, fabs(alpha[j]), acc);
+    }
+    sp[threadIdx.x] = acc;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) { if (threadIdx.x < s) sp[threadIdx.x] += sp[threadIdx.x + s]; __syncthreads(); }
+    if (threadIdx.x == 0) xx_max_out[2 + blockIdx.x - 1] = sp[0];
   }
 }
 
@@ -483,16 +509,50 @@ int ob200_bound_f32_launch(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, 
   const int64_t bp_elems = (int64_t)n_chunks * n_slices * 16 * ksl * 32;   // float4
   const int64_t aux_elems = (int64_t)n_chunks * (BD_OBC / 8) * 4;
   int rc;
-  if ((rc = ob_reserve(ctx, &ctx->b32_dev, &ctx->b32_cap, (bp_elems + aux_elems) * 4 + 64))) return rc;
+  if ((rc = ob_reserve(ctx, &ctx->b32_dev, &ctx->b32_cap, (bp_elems + aux_elems) * 4 + 2 * (2 + BD_PROBES) + 16))) return rc;
   float4* bp = reinterpret_cast<float4*>(ctx->b32_dev);
   float4* aux = bp + bp_elems;
   double* xx_max_dev = reinterpret_cast<double*>(aux + aux_elems);
   const double scale = h.kernel_kind == OB200_KERNEL_MATERN52 ? 2.23606797749979 : 0.7071067811865476;
-  bound_pack_kernel<<<ctx->num_sms, 256, 0, ctx->stream>>>(
-      reinterpret_cast<const double*>(ctx->blob + lay.off_xs), reinterpret_cast<const double*>(ctx->blob + lay.off_xx),
-      reinterpret_cast<const double*>(ctx->blob + lay.off_alpha), h.n, h.n_pad, h.D_pad, nk, ksl, n_slices, n_chunks, scale, bp, aux,
-      xx_max_dev);
-  OB_LAUNCH_CHECK(ctx);
+  // ---- error budget (see the header comment).  u = 2^-24 (FP32 unit round-off), tf = 2^-11 (TF32).
+  //   G~ = sum of 3 nk MMAs.  Split: c = ch + cl + rc, |rc| <= tf^2 |c| (+ 2u from the FP64 -> FP32 rounding), same
+  //   for x; dropped cl*xl, rc*x, c*rx: <= (3 tf^2 + 4u) |c||x|.  Tensor-core accumulation: modelled, generously,
+  //   as 2^-19 of sum |c_i||x_i| per MMA (published measurements put it near 2^-23 per added term).
+  //   On T~ = cc + xx - 2 G~:  2 |dG| <= 2 (3 nk 2^-19 + 3 tf^2 + 4u) sqrt(cc xx) <= 0.5 (...) (sqrt cc + sqrt xx)^2,
+  //   plus u (cc + xx) for the rounded norms and 2u (cc + xx + 2|G|) for the add and the fma.
+  const double u = ldexp(1.0, -24), tf2 = ldexp(1.0, -22);
+  const double g_T = 0.5 * (3.0 * nk * ldexp(1.0, -19) + 3.0 * tf2 + 4.0 * u) + 3.0 * u;
+  //   function evaluation: sqrt.approx and ex2.approx (2^-21 each, generous), the argument product t * log2(e)
+  //   (relative 2u of an exponent of size 1.4427 t -> relative ln2 * 1.4427 t * 2u = 2 t u of the result), the two
+  //   polynomial FMAs and the final product (3u), alpha rounded to FP32 (u), the FMA into the partial sum (u), the
+  //   FP32 partial sums (at most 2 * 128 / (4 WO) <= 64 terms per flush: 64u).  Matern: d ln k / dt <= 1, so the
+  //   sqrt error 2^-21 t enters as 2^-21 t.
+  const double c0 = 2.0 * ldexp(1.0, -21) + 70.0 * u, c1 = ldexp(1.0, -21) + 2.0 * u;
+  if (ctx->b32_serial != ctx->fit_serial) {
+    // once per fit: pack the observations, and decide whether the budget leaves a usable bound.  The mean's error is
+    // y_std * amplitude * S * rel with S = sum_j k_j |alpha_j|; S is sampled (in FP64) at BD_PROBES observations and rel
+    // taken at a candidate as far out as the farthest observation.  When that exceeds half a standard deviation of y
+    // (tiny noise, long length scales, huge amplitude: |alpha| explodes while the mean stays O(1) by cancellation)
+    // FP32 kernel values say nothing about the mean: FP64 pass.
+    bound_pack_kernel<<<ctx->num_sms > BD_PROBES ? ctx->num_sms : BD_PROBES + 1, 256, 0, ctx->stream>>>(
+        reinterpret_cast<const double*>(ctx->blob + lay.off_xs), reinterpret_cast<const double*>(ctx->blob + lay.off_xx),
+        reinterpret_cast<const double*>(ctx->blob + lay.off_alpha), h.n, h.n_pad, h.D_pad, nk, ksl, n_slices, n_chunks, scale,
+        h.kernel_kind, bp, aux, xx_max_dev);
+    OB_LAUNCH_CHECK(ctx);
+    double stats[2 + BD_PROBES];
+    OB_CUDA(ctx, cudaMemcpyAsync(stats, xx_max_dev, sizeof stats, cudaMemcpyDeviceToHost, ctx->stream));
+    OB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    double s_max = 0.0;
+    for (int p = 0; p < BD_PROBES; ++p) s_max = stats[2 + p] > s_max ? stats[2 + p] : s_max;
+    const double rc0 = 2.0 * sqrt(stats[0]);
+    const bool matern = h.kernel_kind == OB200_KERNEL_MATERN52;
+    const double rel0 = (matern ? g_T * rc0 * rc0 / 6.0 : g_T * rc0 * rc0) + c0 + c1 * (matern ? rc0 : rc0 * rc0);
+    double limit = 0.5;
+    if (const char* env = getenv("OB200_BOUND_F32_LIMIT")) limit = atof(env);   // (tuning / testing hook)
+    ctx->b32_ok = stats[0] < 1e29 && s_max == s_max && h.amplitude * s_max * rel0 <= limit;
+    ctx->b32_serial = ctx->fit_serial;
+  }
+  if (!ctx->b32_ok) return OB200_OK;
 
   bound_args a{};
   a.cand = cand_dev; a.ldc = ldc; a.M = M;
@@ -502,21 +562,7 @@ int ob200_bound_f32_launch(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, 
   a.scale = scale;
   a.amplitude = h.amplitude; a.y_mean = h.y_mean; a.y_std = h.y_std; a.diag = h.diag;
   a.xx_max = xx_max_dev;
-  // ---- error budget (see the header comment).  u = 2^-24 (FP32 unit round-off), tf = 2^-11 (TF32).
-  //   G~ = sum of 3 nk MMAs.  Split: c = ch + cl + rc, |rc| <= tf^2 |c| (+ 2u from the FP64 -> FP32 rounding), same
-  //   for x; dropped cl*xl, rc*x, c*rx: <= (3 tf^2 + 4u) |c||x|.  Tensor-core accumulation: modelled, generously,
-  //   as 2^-19 of sum |c_i||x_i| per MMA (published measurements put it near 2^-23 per added term).
-  //   On T~ = cc + xx - 2 G~:  2 |dG| <= 2 (3 nk 2^-19 + 3 tf^2 + 4u) sqrt(cc xx) <= 0.5 (...) (sqrt cc + sqrt xx)^2,
-  //   plus u (cc + xx) for the rounded norms and 2u (cc + xx + 2|G|) for the add and the fma.
-  const double u = ldexp(1.0, -24), tf2 = ldexp(1.0, -22);
-  a.g_T = 0.5 * (3.0 * nk * ldexp(1.0, -19) + 3.0 * tf2 + 4.0 * u) + 3.0 * u;
-  //   function evaluation: sqrt.approx and ex2.approx (2^-21 each, generous), the argument product t * log2(e)
-  //   (relative 2u of an exponent of size 1.4427 t -> relative ln2 * 1.4427 t * 2u = 2 t u of the result), the two
-  //   polynomial FMAs and the final product (3u), alpha rounded to FP32 (u), the FMA into the partial sum (u), the
-  //   FP32 partial sums (at most 2 * 128 / (4 WO) <= 64 terms per flush: 64u).  Matern: d ln k / dt <= 1, so the
-  //   sqrt error 2^-21 t enters as 2^-21 t.
-  a.c0 = 2.0 * ldexp(1.0, -21) + 70.0 * u;
-  a.c1 = ldexp(1.0, -21) + 2.0 * u;
+  a.g_T = g_T; a.c0 = c0; a.c1 = c1;
   a.tiny = 1e-20;   // kernel values flushed to zero (< 2^-126) times any plausible ||alpha||_1
   a.mu_lb = mu_lb_dev; a.sigma_ub = sigma_ub_dev;
   const int ct = 32 * wc;

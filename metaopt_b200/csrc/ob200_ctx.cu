@@ -49,6 +49,7 @@ void ob200_ctx_destroy(ob200_ctx* ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   cudaDeviceSynchronize();
+  if (ctx->sub) { ob200_ctx_destroy(ctx->sub); ctx->sub = nullptr; }
   ob_l2_release(ctx);
   cudaFree(ctx->slots_dev);
   cudaFree(ctx->dslots_dev);

@@ -1029,6 +1029,7 @@ int ob200_gp_fit(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n
   ctx->blob_bytes = lay.total;
   ctx->fitted = true;
   ctx->have_local_fit = true;
+  ctx->fit_serial++;
   ctx->w_Xs_off = w_Xs;
   ctx->w_y_off = w_y;
   ctx->w_t_off = w_t;
@@ -1203,6 +1204,7 @@ int ob200_gp_append(ob200_ctx* ctx, const double* x_new_dev, const double* y_dev
             "parameter of your GaussianProcessRegressor estimator.", info, n + 1);
   ctx->fitted = true;
   ctx->have_local_fit = true;
+  ctx->fit_serial++;
   return OB200_OK;
 }
 
@@ -1260,6 +1262,7 @@ int ob200_gp_import(ob200_ctx* ctx, const void* blob_dev, int64_t bytes) {
   ctx->hdr = h;
   ctx->blob_bytes = lay.total;
   ctx->fitted = true;
+  ctx->fit_serial++;
   return OB200_OK;
 }
 

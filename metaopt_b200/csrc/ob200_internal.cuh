@@ -113,7 +113,12 @@ struct ob200_ctx {
   int64_t prune_small_cap = 0;
   void* ctl_pinned = nullptr;      // pinned read-back of the control block's counters
   int last_prune_f32 = 0;          // statistics of the last pruned call (ob200_prune_stats)
-  int64_t last_prune_counts[3] = {0, 0, 0};
+  int64_t last_prune_counts[4] = {0, 0, 0, -1};
+  int64_t fit_serial = 0;          // bumped by every fit / append / import: keys the caches below
+  int64_t b32_serial = -1;         // fit the FP32 pack (b32_dev) and its verdict belong to
+  int b32_ok = 0;                  // this fit may use the FP32 bound pass (its error budget is not vacuous)
+  ob200_ctx* sub = nullptr;        // pruned scoring: GP on a subset of the observations (variance upper bound)
+  int64_t sub_serial = -1;
   float* b32_dev = nullptr;        // FP32 bound pass: TF32 hi/lo B fragments + per-observation constants
   int64_t b32_cap = 0;
   cudaStream_t copy_stream = nullptr;  // H2D of the candidate tail overlapped with scoring of the head

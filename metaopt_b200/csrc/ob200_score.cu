@@ -875,7 +875,7 @@ namespace {
 #define PR_BINS 4096   // 12 bits of the order-preserving key per histogram level
 
 struct prune_ctl {
-  unsigned long long count_a, count_b, count_b2;   // rows in batch A / B (pass-1 bounds) / B after the FP64 refinement
+  unsigned long long count_a, count_b, count_b2, count_c;   // rows in batch A / B (pass-1 bounds) / B after the FP64 refinement / B after the subset bound
   unsigned long long tau_key[3];                   // batch A of acquisition k = {key(ub_k) >= tau_key[k]}
   long long rem[3];                                // quota left for level 2
   int b1[3];                                       // level-1 bin that holds the threshold
@@ -1049,15 +1049,17 @@ __global__ void __launch_bounds__(256) compact_kernel(const double* __restrict__
 __global__ void __launch_bounds__(256) compact_refined_kernel(const double* __restrict__ mu, const double* __restrict__ sig, int acq_mask,
                                                               double y_opt, double xi, double kappa, const ob200_best* __restrict__ incumbent,
                                                               prune_ctl* __restrict__ ctl, const long long* __restrict__ rows_in,
-                                                              long long* __restrict__ rows_out) {
+                                                              long long* __restrict__ rows_out, double* __restrict__ mu_out,
+                                                              double* __restrict__ sig_out) {
   const long long n = (long long)ctl->count_b;
   double thr[3];
   for (int k = 0; k < 3; ++k) { const double v = incumbent[k].value; thr[k] = v - 1e-12 * fabs(v) - 1e-300; }
   for (long long i0 = (long long)blockIdx.x * 256; i0 < n; i0 += (long long)gridDim.x * 256) {
     const long long i = i0 + threadIdx.x;
     bool keep = false;
+    double m = 0.0, s = 0.0;
     if (i < n) {
-      const double m = mu[i], s = sig[i];
+      m = mu[i]; s = sig[i];
 #pragma unroll
       for (int k = 0; k < 3; ++k) {
         if (!(acq_mask & (1 << k))) continue;
@@ -1071,9 +1073,96 @@ __global__ void __launch_bounds__(256) compact_refined_kernel(const double* __re
       unsigned long long base = 0;
       if (lane == leader) base = atomicAdd(&ctl->count_b2, (unsigned long long)__popc(mask));
       base = __shfl_sync(0xffffffffu, base, leader);
+      if (keep) {   // the refined mean / sigma bound travel with the row (the subset-GP step reads them by position)
+        const unsigned long long pos = base + __popc(mask & ((1u << lane) - 1));
+        rows_out[pos] = rows_in[i];
+        mu_out[pos] = m;
+        sig_out[pos] = s;
+      }
+    }
+  }
+}
+
+// Batch B with a second variance bound: sigma_s[r] = posterior std (normalised units) of row rows_in[r] under a GP on
+// a SUBSET of the observations (conditioning on fewer points can only raise the variance).  mu / sig are the mean and
+// the nearest-observation bound of the same rows: indexed by r (`local` = 1: the arrays of the FP64 refinement) or by
+// rows_in[r] (`local` = 0: the arrays of an FP64 pass 1).
+__global__ void __launch_bounds__(256) compact_subset_kernel(const double* __restrict__ mu, const double* __restrict__ sig,
+                                                             const double* __restrict__ sigma_s, int local, double y_std, double slack,
+                                                             int acq_mask, double y_opt, double xi, double kappa,
+                                                             const ob200_best* __restrict__ incumbent, const unsigned long long* __restrict__ n_in,
+                                                             unsigned long long* __restrict__ n_out, const long long* __restrict__ rows_in,
+                                                             long long* __restrict__ rows_out) {
+  const long long n = (long long)*n_in;
+  double thr[3];
+  for (int k = 0; k < 3; ++k) { const double v = incumbent[k].value; thr[k] = v - 1e-12 * fabs(v) - 1e-300; }
+  for (long long i0 = (long long)blockIdx.x * 256; i0 < n; i0 += (long long)gridDim.x * 256) {
+    const long long i = i0 + threadIdx.x;
+    bool keep = false;
+    if (i < n) {
+      const long long src = local ? i : rows_in[i];
+      const double m = mu[src];
+      const double s = fmin(sig[src], y_std * sigma_s[i] + slack);
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        if (!(acq_mask & (1 << k))) continue;
+        const double v = upper_bound_utility(k, m, s, y_opt, xi, kappa);
+        keep |= !(v == v) || v >= thr[k];
+      }
+    }
+    const unsigned mask = __ballot_sync(0xffffffffu, keep);
+    if (mask) {
+      const int lane = threadIdx.x & 31, leader = __ffs(mask) - 1;
+      unsigned long long base = 0;
+      if (lane == leader) base = atomicAdd(n_out, (unsigned long long)__popc(mask));
+      base = __shfl_sync(0xffffffffu, base, leader);
       if (keep) rows_out[base + __popc(mask & ((1u << lane) - 1))] = rows_in[i];
     }
   }
+}
+
+// observation i of the subset = observation floor(i n / m) of the fit, un-scaled back from the blob's packed X / ls
+__global__ void __launch_bounds__(256) gather_subset_kernel(const double* __restrict__ xs, const double* __restrict__ ls, int n, int D,
+                                                            int D_pad, int m, double* __restrict__ out) {
+  const int nd4 = D_pad >> 2;
+  for (int e = blockIdx.x * 256 + threadIdx.x; e < m * D; e += gridDim.x * 256) {
+    const int i = e / D, d = e - i * D;
+    const int obs = (int)((long long)i * n / m);
+    out[e] = xs[((size_t)(obs >> 3) * nd4 + (d >> 2)) * 32 + (obs & 7) * 4 + (d & 3)] * ls[d];
+  }
+}
+
+#define PR_SUBSET_M SC_BM   // one row block of the score kernel (192 observations)
+
+// GP with the fit's kernel on PR_SUBSET_M evenly spaced observations, in a context of its own (ctx->sub); built once
+// per fit, when a pruned call first needs the second variance bound.
+int ensure_subset_fit(ob200_ctx* ctx) {
+  if (ctx->sub && ctx->sub_serial == ctx->fit_serial) return OB200_OK;
+  const ob200_fit_header& h = ctx->hdr;
+  const ob200_blob_layout lay = ob_blob_layout(h.n_pad, h.D_pad);
+  if (!ctx->sub) {
+    const int rc = ob200_ctx_create(ctx->device, &ctx->sub);
+    if (rc) OB_FAIL(ctx, rc, "cannot create the context of the subset GP");
+  }
+  ob200_ctx* sub = ctx->sub;
+  sub->stream = ctx->stream;
+  const int m = h.n < PR_SUBSET_M ? h.n : PR_SUBSET_M, D = h.D;
+  int rc;
+  if ((rc = ob_reserve(ctx, &ctx->gather_dev, &ctx->gather_cap, (int64_t)m * D + m))) return rc;
+  std::vector<double> ls((size_t)h.D_pad);
+  OB_CUDA(ctx, cudaMemcpyAsync(ls.data(), ctx->blob + lay.off_ls, (size_t)h.D_pad * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  gather_subset_kernel<<<ctx->num_sms, 256, 0, ctx->stream>>>(reinterpret_cast<const double*>(ctx->blob + lay.off_xs),
+                                                              reinterpret_cast<const double*>(ctx->blob + lay.off_ls), h.n, D, h.D_pad, m,
+                                                              ctx->gather_dev);
+  OB_LAUNCH_CHECK(ctx);
+  OB_CUDA(ctx, cudaMemsetAsync(ctx->gather_dev + (size_t)m * D, 0, (size_t)m * 8, ctx->stream));   // y = 0: only the variance is used
+  OB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  ob200_kernel kern{};
+  kern.kind = h.kernel_kind; kern.n_length_scale = D; kern.amplitude = h.amplitude; kern.length_scale_host = ls.data();
+  rc = ob200_gp_fit(sub, ctx->gather_dev, ctx->gather_dev + (size_t)m * D, m, D, &kern, h.diag, 0);
+  if (rc) OB_FAIL(ctx, rc, "subset GP: %s", sub->err.c_str());
+  ctx->sub_serial = ctx->fit_serial;
+  return OB200_OK;
 }
 
 }  // namespace
@@ -1146,10 +1235,42 @@ extern "C" int ob200_score_pruned_multi(ob200_ctx* ctx, const double* cand_dev, 
     int g2 = 0;
     if ((rc = score_launch(ctx, cand_dev, ldc, M, first_index, acq_mask, y_opt, xi, kappa, mu_b, sig_b, nullptr, 0, &g2, 1, rows1,
                            reinterpret_cast<const long long*>(&ctl->count_b)))) return rc;
-    compact_refined_kernel<<<nblk, 256, 0, st>>>(mu_b, sig_b, acq_mask, y_opt, xi, kappa, ctx->best_dev, ctl, rows1, rows0);
+    compact_refined_kernel<<<nblk, 256, 0, st>>>(mu_b, sig_b, acq_mask, y_opt, xi, kappa, ctx->best_dev, ctl, rows1, rows0, ub3, ub3 + M);
     OB_LAUNCH_CHECK(ctx);
     rows_b = rows0;
     count_b = &ctl->count_b2;
+  }
+  // Escalation: when many rows are still standing, the nearest-observation variance bound is the weak part (long
+  // length scales: every kernel value is close to the amplitude).  A GP on a subset of the observations bounds the
+  // variance from above as well, at (192 / n)^2 of the cost of the full posterior.
+  long long* rows_c = (rows_b == rows0) ? rows1 : rows0;
+  OB_CUDA(ctx, cudaMemcpyAsync(ctx->ctl_pinned, ctl, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+  OB_CUDA(ctx, cudaStreamSynchronize(st));
+  {
+    const unsigned long long* c = reinterpret_cast<const unsigned long long*>(ctx->ctl_pinned);
+    const int64_t standing = (int64_t)(f32_done ? c[2] : c[1]);
+    int64_t escalate_at = 4 * batch;
+    if (const char* env = getenv("OB200_PRUNE_SUBSET_AT")) escalate_at = atoll(env);   // (testing hook; < 0 disables)
+    ctx->last_prune_counts[3] = -1;
+    if (escalate_at >= 0 && standing > escalate_at && ctx->hdr.n > PR_SUBSET_M) {
+      if ((rc = ensure_subset_fit(ctx))) return rc;
+      ob200_ctx* sub = ctx->sub;
+      l2_scope l2s(sub);
+      int gs = 0;
+      double* sig_s = ub3 + 2 * M;   // (the utility bounds of pass 1 are not needed any more: ub3 = refined mu | sigma | this)
+      if ((rc = score_launch(sub, cand_dev, ldc, M, first_index, 1, 0.0, 0.0, 0.0, nullptr, sig_s, nullptr, 0, &gs, 0, rows_b,
+                             reinterpret_cast<const long long*>(count_b)))) OB_FAIL(ctx, rc, "subset GP: %s", sub->err.c_str());
+      ctx->launches += 1;
+      unsigned long long* count_c = &ctl->count_c;
+      // slack: the rounding of the subset posterior (cancellation ~ cond(K_S) eps), as for the nearest-observation bound
+      compact_subset_kernel<<<nblk, 256, 0, st>>>(f32_done ? ub3 : mu, f32_done ? ub3 + M : sig, sig_s, f32_done ? 1 : 0, ctx->hdr.y_std,
+                                                  ctx->hdr.y_std * sqrt(1e-6 * ctx->hdr.amplitude), acq_mask, y_opt, xi, kappa,
+                                                  ctx->best_dev, count_b, count_c, rows_b, rows_c);
+      OB_LAUNCH_CHECK(ctx);
+      rows_b = rows_c;
+      count_b = count_c;
+      ctx->last_prune_counts[3] = 0;
+    }
   }
   int grid_b = 0;
   if ((rc = score_launch(ctx, cand_dev, ldc, M, first_index, acq_mask, y_opt, xi, kappa, nullptr, nullptr, nullptr, 1, &grid_b, 0, rows_b,
@@ -1157,12 +1278,14 @@ extern "C" int ob200_score_pruned_multi(ob200_ctx* ctx, const double* cand_dev, 
   reduce_best_kernel<<<1, 256, 0, st>>>(reinterpret_cast<const best_t*>(ctx->partial_dev), grid, acq_mask, ctx->best_dev);
   OB_LAUNCH_CHECK(ctx);
   OB_CUDA(ctx, cudaMemcpyAsync(ctx->best_pinned, ctx->best_dev, 3 * sizeof(ob200_best), cudaMemcpyDeviceToHost, st));
-  OB_CUDA(ctx, cudaMemcpyAsync(ctx->ctl_pinned, ctl, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+  OB_CUDA(ctx, cudaMemcpyAsync(ctx->ctl_pinned, ctl, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
   OB_CUDA(ctx, cudaStreamSynchronize(st));
   const unsigned long long* counts = reinterpret_cast<const unsigned long long*>(ctx->ctl_pinned);
-  const int64_t n_scored = (int64_t)counts[0] + (int64_t)(f32_done ? counts[2] : counts[1]);
+  const bool escalated = ctx->last_prune_counts[3] >= 0;
+  const int64_t n_scored = (int64_t)counts[0] + (int64_t)(escalated ? counts[3] : (f32_done ? counts[2] : counts[1]));
   ctx->last_prune_f32 = f32_done;
   ctx->last_prune_counts[0] = (int64_t)counts[0]; ctx->last_prune_counts[1] = (int64_t)counts[1]; ctx->last_prune_counts[2] = (int64_t)counts[2];
+  if (escalated) ctx->last_prune_counts[3] = (int64_t)counts[3];
   for (int k = 0; k < 3; ++k) {
     if (!(acq_mask & (1 << k))) continue;
     best_host[k] = ctx->best_pinned[k];
@@ -1202,10 +1325,12 @@ extern "C" int ob200_score_bounds(ob200_ctx* ctx, const double* cand_dev, int64_
 }
 
 // Counters of the last ob200_score_pruned[_multi] call that took the pruned path: used_f32, rows in batch A, rows the
-// pass-1 bounds left for batch B, rows left after the FP64 refinement of those bounds.
-extern "C" int ob200_prune_stats(const ob200_ctx* ctx, int64_t out[4]) {
+// pass-1 bounds left for batch B, rows left after the FP64 refinement of those bounds, rows left after the subset-GP
+// variance bound (-1: that step did not run).
+extern "C" int ob200_prune_stats(const ob200_ctx* ctx, int64_t out[5]) {
   if (!ctx || !out) return OB200_EINVAL;
   out[0] = ctx->last_prune_f32; out[1] = ctx->last_prune_counts[0]; out[2] = ctx->last_prune_counts[1]; out[3] = ctx->last_prune_counts[2];
+  out[4] = ctx->last_prune_counts[3];
   return OB200_OK;
 }
 

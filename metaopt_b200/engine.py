@@ -298,10 +298,11 @@ class Engine:
         return mu, sg, bool(used.value)
 
     def prune_stats(self):
-        """Counters of the last pruned call: dict(f32, batch_a, batch_b, batch_b_refined)."""
-        out = (C.c_int64 * 4)()
+        """Counters of the last pruned call: dict(f32, batch_a, batch_b, batch_b_refined, batch_b_subset)."""
+        out = (C.c_int64 * 5)()
         self._check(self.lib.ob200_prune_stats(self.ctx, out))
-        return dict(f32=bool(out[0]), batch_a=int(out[1]), batch_b=int(out[2]), batch_b_refined=int(out[3]))
+        return dict(f32=bool(out[0]), batch_a=int(out[1]), batch_b=int(out[2]), batch_b_refined=int(out[3]),
+                    batch_b_subset=int(out[4]))
 
     def score_host(self, cand, acq_mask=1, y_opt=0.0, xi=0.01, kappa=1.96, dense=False):
         """Same through host buffers (numpy in, numpy out): H2D/D2H copies happen inside the call."""

@@ -25,16 +25,18 @@ def _bounds_vs_exact(engine, C, y_opt):
     return mu_lb, sg_ub, mu, sg, used
 
 
-@pytest.mark.parametrize("n,d,kind,ls,alpha,amp", [
-    (2000, 20, 0, 1.0, 1e-4, 1.0),      # BASELINE config 2
-    (500, 6, 0, 0.7, 1e-4, 1.0),
-    (300, 2, 0, 0.05, 1e-10, 3.0),      # short length scale, no noise term: large ||alpha||_1
-    (777, 33, 1, 2.5, 1e-6, 0.5),       # RBF, D not a multiple of 8
-    (1030, 100, 0, 3.0, 1e-4, 1.7),     # BASELINE config 4 width
-    (129, 150, 0, 4.0, 1e-3, 1.0),      # wide: smaller candidate tiles
-    (64, 3, 1, 0.3, 1e-8, 1.0),
+@pytest.mark.parametrize("n,d,kind,ls,alpha,amp,limit", [
+    (2000, 20, 0, 1.0, 1e-4, 1.0, None),      # BASELINE config 2
+    (500, 6, 0, 0.7, 1e-4, 1.0, None),
+    (300, 2, 0, 0.05, 1e-10, 3.0, "1e30"),    # short length scale, no noise term: large ||alpha||_1 (FP32 pass forced)
+    (777, 33, 1, 2.5, 1e-6, 0.5, "1e30"),     # RBF, D not a multiple of 8
+    (1030, 100, 0, 3.0, 1e-4, 1.7, "1e30"),   # BASELINE config 4 width
+    (129, 150, 0, 4.0, 1e-3, 1.0, None),      # wide: smaller candidate tiles
+    (64, 3, 1, 0.3, 1e-8, 1.0, None),
 ])
-def test_bounds_are_rigorous_and_tight(engine, n, d, kind, ls, alpha, amp):
+def test_bounds_are_rigorous_and_tight(engine, n, d, kind, ls, alpha, amp, limit, monkeypatch):
+    if limit:   # the per-fit verdict would send this fit to the FP64 pass: the FP32 bounds must be rigorous all the same
+        monkeypatch.setenv("OB200_BOUND_F32_LIMIT", limit)
     X, y = gp_problem(n, d, seed=n + d)
     engine.fit(X, y, kind=kind, amplitude=amp, length_scale=ls, alpha=alpha, normalize_y=True)
     C = torch.as_tensor(np.random.RandomState(5).uniform(size=(20_003, d))).cuda()
@@ -123,3 +125,50 @@ def test_degenerate_bounds_all_equal(engine):
     dense = engine.score(C, acq_mask=7, y_opt=float(y.min()), first_index=9)
     pruned, _ = engine.score_pruned_multi(C, acq_mask=7, y_opt=float(y.min()), first_index=9)
     assert pruned == dense and pruned["EI"]["index"] == 9
+
+
+def _smooth_long_length_scale_fit(engine, n=2000, d=20):
+    """What the plugin's default mode ends up with on a smooth objective: huge amplitude, length scales far beyond the
+    unit cube, small noise -- every kernel value is close to the amplitude, |alpha| is enormous, the posterior std tiny."""
+    X, y = gp_problem(n, d, seed=0)
+    engine.fit(X, y, amplitude=1000.0, length_scale=19.3, alpha=1e-10 + 2.9e-4, normalize_y=True)
+    return X, y
+
+
+@pytest.mark.parametrize("acq", ["EI", "LCB", "PI"])
+def test_long_length_scales_use_the_fp64_pass_and_the_subset_variance_bound(engine, acq):
+    X, y = _smooth_long_length_scale_fit(engine)
+    C = torch.as_tensor(np.random.RandomState(1).uniform(size=(200_000, 20))).cuda()
+    y_opt = float(y.min())
+    k = {"EI": 0, "PI": 1, "LCB": 2}[acq]
+    dense = engine.score(C, acq_mask=1 << k, y_opt=y_opt)
+    pruned, n_scored = engine.score_pruned(C, acq=acq, y_opt=y_opt)
+    st = engine.prune_stats()
+    assert pruned == dense
+    assert not st["f32"]                      # ||alpha||_1 makes the FP32 error budget vacuous: decided per fit, FP64 pass
+    mu_lb, sg_ub, used = engine.score_bounds(C[:50_000])
+    assert not used
+    if acq == "LCB":                          # the nearest-observation bound alone leaves most candidates standing ...
+        assert st["batch_b"] > 50_000 and 0 <= st["batch_b_subset"] < st["batch_b"] // 20   # ... the subset GP removes them
+        assert n_scored < 20_000
+
+
+def test_subset_variance_bound_is_an_upper_bound(engine, monkeypatch):
+    """Force the escalation on an ordinary fit and check the winner; then check sigma_S >= sigma directly."""
+    X, y = gp_problem(700, 5, seed=3)
+    engine.fit(X, y, alpha=1e-4, normalize_y=True, length_scale=1.5)
+    C = torch.as_tensor(np.random.RandomState(2).uniform(size=(80_000, 5))).cuda()
+    y_opt = float(y.min())
+    dense = engine.score(C, acq_mask=7, y_opt=y_opt, dense=True)
+    monkeypatch.setenv("OB200_PRUNE_SUBSET_AT", "0")
+    pruned, _ = engine.score_pruned_multi(C, acq_mask=7, y_opt=y_opt)
+    st = engine.prune_stats()
+    assert pruned == {k: dense[k] for k in ("EI", "PI", "LCB")}
+    assert st["batch_b_subset"] >= 0 or st["batch_b"] == 0
+    # a GP on every 4th observation (what the subset step builds, here by hand): its std bounds the full one
+    idx = (np.arange(192) * 700 // 192)
+    sigma_full = dense["sigma"]
+    engine.fit(X[idx], np.zeros(192), alpha=1e-4, normalize_y=False, length_scale=1.5)
+    sub = engine.score(C, acq_mask=1, y_opt=0.0, dense=True)["sigma"]
+    _, y_std, _ = (None, float(np.std(y)), None)
+    assert bool(torch.all(sub * y_std + 1e-9 >= sigma_full))
