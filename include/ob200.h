@@ -127,6 +127,13 @@ int ob200_gp_fit(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n
                  const ob200_kernel* kernel, double alpha, int normalize_y);
 int ob200_gp_fit_host(ob200_ctx* ctx, const double* X_host, const double* y_host, int n, int D,
                       const ob200_kernel* kernel, double alpha, int normalize_y);
+/* ob200_gp_fit for ONE evaluation of a hyper-parameter search (what sklearn's fit does inside
+ * `_constrained_optimization`, _gpr.py:299-340: log_marginal_likelihood(theta, eval_gradient=True) per step): same
+ * arguments; produces everything ob200_gp_lml and ob200_gp_lml_grad read (L, inv(L), alpha, the LML), skips the
+ * Newton-Schulz refinement of inv(L) and the tile packing the score kernel needs, and leaves the context NOT
+ * scoreable (ob200_score* return OB200_ESTATE) until the next ob200_gp_fit / ob200_gp_import. */
+int ob200_gp_fit_search(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n, int D,
+                        const ob200_kernel* kernel, double alpha, int normalize_y);
 /* Append ONE observation to the current fit in O(n^2) instead of refitting in O(n^3): new row of L from
  * inv(L) k, new row of inv(L), alpha_ recomputed in full from inv(L) (the y statistics move with every observation
  * when normalize_y is on), same hyper-parameters and diagonal term as the fit.  Counterpart of what

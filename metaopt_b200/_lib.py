@@ -58,6 +58,7 @@ SIGNATURES = {
     "ob200_sample_status": (_i, [_vp]),
     "ob200_sample_transform_host": (_i, [_vp, _u64, _u64, _i64, _i, _vp, _i64, _vp]),
     "ob200_gp_fit": (_i, [_vp, _vp, _vp, _i, _i, C.POINTER(Kernel), _d, _i]),
+    "ob200_gp_fit_search": (_i, [_vp, _vp, _vp, _i, _i, C.POINTER(Kernel), _d, _i]),
     "ob200_gp_fit_host": (_i, [_vp, _vp, _vp, _i, _i, C.POINTER(Kernel), _d, _i]),
     "ob200_gp_append": (_i, [_vp, _vp, _vp, _i, _i]),
     "ob200_gp_lml": (_i, [_vp, _pd]),

@@ -73,6 +73,9 @@ void ob200_ctx_destroy(ob200_ctx* ctx) {
   cudaFree(ctx->b32_dev);
   cudaFree(ctx->best_dev);
   if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
+  if (ctx->fit_stream) cudaStreamDestroy(ctx->fit_stream);
+  if (ctx->ev_panel) cudaEventDestroy(ctx->ev_panel);
+  if (ctx->ev_trail) cudaEventDestroy(ctx->ev_trail);
   if (ctx->ev_main) cudaEventDestroy(ctx->ev_main);
   if (ctx->ev_copy) cudaEventDestroy(ctx->ev_copy);
   if (ctx->best_pinned) cudaFreeHost(ctx->best_pinned);

@@ -240,22 +240,14 @@ __device__ __forceinline__ void fwd_subst64(const double* __restrict__ L, const 
 
 #define FBS (FB + 2)  // shared-memory row stride of the 64 x 64 blocks (even: 16-byte aligned rows)
 
-__global__ void __launch_bounds__(256) chol_diag_kernel(double* __restrict__ A, int ld, int kb, double* __restrict__ Dinv,
-                                                        int* __restrict__ info) {
-  extern __shared__ double diag_sm[];
-  double* S = diag_sm;                 // [FB][FBS] the block, then its factor
-  double* Inv = diag_sm + FB * FBS;    // [FB][FBS] inverse of the factor
-  __shared__ double piv_s[FB], rdiag[FB];
-  __shared__ int bad;
-  double* blk = A + (size_t)kb * FB * ld + (size_t)kb * FB;
-  const int tid = threadIdx.x;
-  if (tid == 0) bad = 0;
-  for (int e = tid; e < FB * FB; e += 256) { const int r = e >> 6, c = e & 63; S[r * FBS + c] = (c <= r) ? blk[(size_t)r * ld + c] : 0.0; }
+// Left-looking factorisation of a 64 x 64 block held in shared memory (lower triangle, upper part zero), by the first
+// two warps: one thread per row, the own row in registers, fully unrolled; column j of row i is
+// (a_ij - sum_{k<j} l_ik l_jk) / l_jj with row j read from shared memory (broadcast).  Per column: the split dot product,
+// the pivot through shared memory, one sqrt, two 64-thread barriers.  Every thread of the CTA must call it.  On return
+// S = L, rdiag[j] = 1 / l_jj; returns the 1-based index of the first non-positive pivot (0 = ok).
+__device__ __forceinline__ int factor64(double* S, double* piv_s, double* rdiag, int* bad_s, int tid) {
+  if (tid == 0) *bad_s = 0;
   __syncthreads();
-  if (*info != 0) return;  // an earlier block already failed
-  // Left-looking factorisation, one thread per row (first two warps), the own row in registers, fully unrolled:
-  // column j of row i is (a_ij - sum_{k<j} l_ik l_jk) / l_jj with row j read from shared memory (broadcast).
-  // Per column: the split dot product, the pivot through shared memory, one rsqrt, two 64-thread barriers.
   if (tid < FB) {
     const int i = tid;
     double l[FB];
@@ -277,7 +269,7 @@ __global__ void __launch_bounds__(256) chol_diag_kernel(double* __restrict__ A, 
       asm volatile("bar.sync 1, 64;" ::: "memory");
       const double piv = piv_s[j];
       if (!(piv > 0.0)) {  // also catches NaN (uniform: everybody reads the same pivot)
-        if (tid == 0) { bad = 1; *info = kb * FB + j + 1; }
+        if (tid == 0) *bad_s = j + 1;
         break;
       }
       const double d = sqrt(piv), rd = 1.0 / d;
@@ -288,23 +280,77 @@ __global__ void __launch_bounds__(256) chol_diag_kernel(double* __restrict__ A, 
     }
   }
   __syncthreads();
-  if (bad) return;
-  // inverse of the factor: thread c solves L x = e_c (rows < c come out as exact zeros)
-  if (tid < FB) {
-    double x[FB];
-#pragma unroll
-    for (int k = 0; k < FB; ++k) x[k] = (k == tid) ? 1.0 : 0.0;
-    fwd_subst64<FBS>(S, rdiag, x);
-#pragma unroll
-    for (int k = 0; k < FB; ++k) Inv[k * FBS + tid] = x[k];
+  return *bad_s;
+}
+
+// One step of the blocked Cholesky in ONE launch: block 0 factors the diagonal block A[kb,kb], inverts the factor
+// (Dinv[kb], for the recursive-doubling inverse) and stores the factor in Lfac[kb]; block b >= 1 factors the SAME
+// diagonal block redundantly in its own shared memory (6 us of arithmetic, identical bits) and solves its 64 rows of
+// the panel P = A21 L11^-T by forward substitution (a GEMM with inv(L11) loses cond(L11) digits: 7e-6 instead of
+// 3e-8 in the posterior variance at cond(K) = 1e12, tools/illcond_probe.py).  No block waits for another, so the
+// diagonal factor costs no launch of its own.  The diagonal block itself stays untouched in A until the factor blocks
+// are copied in after the last step (the panel CTAs of this launch still read the original values).
+__global__ void __launch_bounds__(256) chol_step_kernel(double* __restrict__ A, int ld, int kb, double* __restrict__ Dinv,
+                                                        double* __restrict__ Lfac, int* __restrict__ info) {
+  extern __shared__ double diag_sm[];
+  double* S = diag_sm;                 // [FB][FBS] the diagonal block, then its factor
+  double* W = diag_sm + FB * FBS;      // block 0: [FB][FBS] inverse of the factor; others: [FB][FB + 1] panel tile, transposed
+  __shared__ double piv_s[FB], rdiag[FB];
+  __shared__ int bad;
+  const double* blk = A + (size_t)kb * FB * ld + (size_t)kb * FB;
+  const int tid = threadIdx.x;
+  double* At = nullptr;
+  for (int e = tid; e < FB * FB; e += 256) { const int r = e >> 6, c = e & 63; S[r * FBS + c] = (c <= r) ? blk[(size_t)r * ld + c] : 0.0; }
+  if (blockIdx.x > 0) {
+    At = A + (size_t)(kb + blockIdx.x) * FB * ld + (size_t)kb * FB;
+    for (int e = tid; e < FB * FB; e += 256) { const int r = e >> 6, c = e & 63; W[c * (FB + 1) + r] = At[(size_t)r * ld + c]; }
   }
   __syncthreads();
-  double* dinv = Dinv + (size_t)kb * FB * FB;
-  for (int e = tid; e < FB * FB; e += 256) {
-    const int r = e >> 6, c = e & 63;
-    blk[(size_t)r * ld + c] = S[r * FBS + c];
-    dinv[e] = Inv[r * FBS + c];
+  if (*info != 0) return;  // an earlier step already failed
+  const int fail = factor64(S, piv_s, rdiag, &bad, tid);
+  if (fail) { if (blockIdx.x == 0 && tid == 0) *info = kb * FB + fail; return; }
+  if (blockIdx.x == 0) {
+    // inverse of the factor: thread c solves L x = e_c (rows < c come out as exact zeros)
+    if (tid < FB) {
+      double x[FB];
+#pragma unroll
+      for (int k = 0; k < FB; ++k) x[k] = (k == tid) ? 1.0 : 0.0;
+      fwd_subst64<FBS>(S, rdiag, x);
+#pragma unroll
+      for (int k = 0; k < FB; ++k) W[k * FBS + tid] = x[k];
+    }
+    __syncthreads();
+    double* dinv = Dinv + (size_t)kb * FB * FB;
+    double* lf = Lfac + (size_t)kb * FB * FB;
+    for (int e = tid; e < FB * FB; e += 256) {
+      const int r = e >> 6, c = e & 63;
+      lf[e] = S[r * FBS + c];
+      dinv[e] = W[r * FBS + c];
+    }
+  } else {
+    // x L11^T = a, i.e. L11 x^T = a^T: one thread per row of the panel, true forward substitution, see fwd_subst64
+    if (tid < FB) {
+      double x[FB];
+#pragma unroll
+      for (int k = 0; k < FB; ++k) x[k] = W[k * (FB + 1) + tid];
+      fwd_subst64<FBS>(S, rdiag, x);
+#pragma unroll
+      for (int k = 0; k < FB; ++k) W[k * (FB + 1) + tid] = x[k];
+    }
+    __syncthreads();
+    for (int e = tid; e < FB * FB; e += 256) {
+      const int r = e >> 6, c = e & 63;
+      At[(size_t)r * ld + c] = W[c * (FB + 1) + r];
+    }
   }
+}
+
+// the factored diagonal blocks (upper triangle zero) go into L after the last step
+__global__ void __launch_bounds__(256) chol_copy_diag_kernel(double* __restrict__ A, int ld, const double* __restrict__ Lfac) {
+  const int kb = blockIdx.x;
+  double* blk = A + (size_t)kb * FB * ld + (size_t)kb * FB;
+  const double* lf = Lfac + (size_t)kb * FB * FB;
+  for (int e = threadIdx.x; e < FB * FB; e += 256) blk[(size_t)(e >> 6) * ld + (e & 63)] = lf[e];
 }
 
 
@@ -316,42 +362,6 @@ __global__ void trtri_init_kernel(double* __restrict__ X, int ld, const double* 
   double* blk = X + (size_t)kb * FB * ld + (size_t)kb * FB;
   const double* d = Dinv + (size_t)kb * FB * FB;
   for (int e = threadIdx.x; e < FB * FB; e += blockDim.x) blk[(size_t)(e >> 6) * ld + (e & 63)] = d[e];
-}
-
-// Panel of the blocked Cholesky: P = A21 * L11^-T by forward substitution, four lanes per row, 64 rows per
-// CTA.  (Multiplying by an explicitly inverted L11 loses cond(L11) digits: 7e-6 instead of 3e-8 in the
-// posterior variance at cond(K) = 1e12, see tools/illcond_probe.py.)
-__global__ void __launch_bounds__(256) chol_panel_trsm_kernel(double* __restrict__ A, int ld, int kb, const double* __restrict__ Dinv) {
-  extern __shared__ double psm[];
-  double* Lk = psm;                    // [FB][FBS] L11
-  double* Xt = psm + FB * FBS;         // [FB][FB + 1] row tile, transposed: Xt[k][row]
-  __shared__ double rdiag[FB];
-  const int tid = threadIdx.x;
-  const size_t r0 = (size_t)(kb + 1 + blockIdx.x) * FB;
-  const double* Ld = A + (size_t)kb * FB * ld + (size_t)kb * FB;
-  double* At = A + r0 * ld + (size_t)kb * FB;
-  for (int e = tid; e < FB * FB; e += 256) {
-    const int r = e >> 6, c = e & 63;
-    Lk[r * FBS + c] = Ld[(size_t)r * ld + c];
-    Xt[c * (FB + 1) + r] = At[(size_t)r * ld + c];
-  }
-  if (tid < FB) rdiag[tid] = Dinv[(size_t)kb * FB * FB + tid * FB + tid];  // 1 / l_jj from the diagonal-block kernel
-  __syncthreads();
-  // x L11^T = a, i.e. L11 x^T = a^T: one thread per row of the panel, true forward substitution (the explicit
-  // inverse of L11 would lose digits when K is ill-conditioned), see fwd_subst64
-  if (tid < FB) {
-    double x[FB];
-#pragma unroll
-    for (int k = 0; k < FB; ++k) x[k] = Xt[k * (FB + 1) + tid];
-    fwd_subst64<FBS>(Lk, rdiag, x);
-#pragma unroll
-    for (int k = 0; k < FB; ++k) Xt[k * (FB + 1) + tid] = x[k];
-  }
-  __syncthreads();
-  for (int e = tid; e < FB * FB; e += 256) {
-    const int r = e >> 6, c = e & 63;
-    At[(size_t)r * ld + c] = Xt[c * (FB + 1) + r];
-  }
 }
 
 
@@ -832,11 +842,12 @@ int solve_alpha(ob200_ctx* ctx, const double* Xinv, const double* L, const doubl
   return OB200_OK;
 }
 
-int launch_gemm(ob200_ctx* ctx, bool trans_b, const gemm_args& g, int batch) {
+int launch_gemm(ob200_ctx* ctx, bool trans_b, const gemm_args& g, int batch, cudaStream_t stream = nullptr) {
   dim3 grid(g.N / 64, g.M / 64, batch);
   if (grid.x == 0 || grid.y == 0 || batch == 0) return OB200_OK;
-  if (trans_b) gemm64_kernel<true><<<grid, 128, 0, ctx->stream>>>(g);
-  else gemm64_kernel<false><<<grid, 128, 0, ctx->stream>>>(g);
+  cudaStream_t st = stream ? stream : ctx->stream;
+  if (trans_b) gemm64_kernel<true><<<grid, 128, 0, st>>>(g);
+  else gemm64_kernel<false><<<grid, 128, 0, st>>>(g);
   OB_LAUNCH_CHECK(ctx);
   return OB200_OK;
 }
@@ -853,8 +864,14 @@ int ob200_gp_state_bytes(ob200_ctx* ctx, int n, int D, int64_t* bytes) {
   return OB200_OK;
 }
 
-int ob200_gp_fit(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n, int D, const ob200_kernel* kernel,
-                 double alpha, int normalize_y) {
+}  // extern "C"
+
+namespace {
+// search = 1: the fit of one log-marginal-likelihood evaluation of a hyper-parameter search -- L, inv(L), alpha and
+// the LML are produced (everything ob200_gp_lml / ob200_gp_lml_grad read), the Newton-Schulz refinement of inv(L) and
+// the tile packing for the score kernel are skipped, and the context is left NOT scoreable.
+int fit_impl(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n, int D, const ob200_kernel* kernel,
+             double alpha, int normalize_y, int search) {
   if (!ctx) return OB200_EINVAL;
   if (!X_dev || !y_dev || !kernel) OB_FAIL(ctx, OB200_EINVAL, "null argument");
   if (n < 1 || n > OB200_MAX_N) OB_FAIL(ctx, OB200_EINVAL, "n_obs=%d outside [1, %d]", n, OB200_MAX_N);
@@ -877,11 +894,11 @@ int ob200_gp_fit(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n
   if ((rc = ob_reserve(ctx, &ctx->L_dev, &ctx->L_cap, (int64_t)n_pad * n_pad))) return rc;
   // workspace: X (n_pad^2) | T (n_pad^2 / 2) | Dinv (nb*64*64) | Xs (n_pad*D_pad) | y_norm | tvec | ls | stats(4) | info
   const int64_t w_X = 0, w_T = w_X + (int64_t)n_pad * n_pad, w_X2 = w_T + (int64_t)n_pad * n_pad, w_Dinv = w_X2 + (int64_t)n_pad * n_pad,
-                w_Xs = w_Dinv + (int64_t)nb * FB * FB, w_y = w_Xs + (int64_t)n_pad * D_pad, w_t = w_y + n_pad,
+                w_Lf = w_Dinv + (int64_t)nb * FB * FB, w_Xs = w_Lf + (int64_t)nb * FB * FB, w_y = w_Xs + (int64_t)n_pad * D_pad, w_t = w_y + n_pad,
                 w_ls = w_t + n_pad, w_stats = w_ls + D_pad, w_end = w_stats + 8;
   if ((rc = ob_reserve(ctx, &ctx->work_dev, &ctx->work_cap, w_end))) return rc;
   double* W = ctx->work_dev;
-  double *Xinv = W + w_X, *T = W + w_T, *X2 = W + w_X2, *Dinv = W + w_Dinv, *Xs = W + w_Xs, *ynorm = W + w_y, *tvec = W + w_t,
+  double *Xinv = W + w_X, *T = W + w_T, *X2 = W + w_X2, *Dinv = W + w_Dinv, *Lfac = W + w_Lf, *Xs = W + w_Xs, *ynorm = W + w_y, *tvec = W + w_t,
          *ls_dev = W + w_ls, *stats = W + w_stats;
   int* info_dev = reinterpret_cast<int*>(stats + 6);
   double* lml_dev = stats + 4;
@@ -914,32 +931,54 @@ int ob200_gp_fit(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n
     OB_LAUNCH_CHECK(ctx);
   }
   mark();
-  // ---- right-looking blocked Cholesky ----------------------------------------------------
+  // ---- right-looking blocked Cholesky with a one-step look-ahead --------------------------------
+  // Per 64-column step: ONE launch factors the diagonal block and solves the panel (chol_step_kernel); the trailing
+  // update A22 -= P P^T is split into (a) the next block column, on the main stream -- all the next step needs -- and
+  // (b) the rest, on a second stream, where it overlaps the next step's factor + panel.  (a) of step k + 1 waits for
+  // (b) of step k (they accumulate into the same tiles, in a fixed order).  The sequential chain per step is
+  // factor + panel + one column of tiles instead of three full launches (2.1 -> see DESIGN.md at n = 2000).
   double* Lm = ctx->L_dev;
   const size_t diag_smem = (size_t)2 * FB * (FB + 2) * sizeof(double);
-  const size_t panel_smem = diag_smem;
-  OB_CUDA(ctx, cudaFuncSetAttribute(chol_panel_trsm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)panel_smem));
-  OB_CUDA(ctx, cudaFuncSetAttribute(chol_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)diag_smem));
-  for (int kb = 0; kb < nb; ++kb) {
-#ifndef FIT_DEBUG_SKIP_DIAG
-    chol_diag_kernel<<<1, 256, diag_smem, st>>>(Lm, n_pad, kb, Dinv, info_dev);
-    OB_LAUNCH_CHECK(ctx);
-#endif
-    const int rem = n_pad - (kb + 1) * FB;
-    if (rem <= 0) break;
-#ifndef FIT_DEBUG_SKIP_PANEL
-    chol_panel_trsm_kernel<<<rem / FB, 256, panel_smem, st>>>(Lm, n_pad, kb, Dinv);
-    OB_LAUNCH_CHECK(ctx);
-#endif
-    const double* panel = Lm + (size_t)(kb + 1) * FB * n_pad + (size_t)kb * FB;
-    gemm_args s{};
-    s.A = panel; s.lda = n_pad; s.B = panel; s.ldb = n_pad;
-    s.C = Lm + (size_t)(kb + 1) * FB * n_pad + (size_t)(kb + 1) * FB; s.ldc = n_pad;
-    s.M = rem; s.N = rem; s.K = FB; s.alpha = -1.0; s.beta = 1.0; s.lower_only = 1;
-#ifndef FIT_DEBUG_SKIP_SYRK
-    if ((rc = launch_gemm(ctx, true, s, 1))) return rc;
-#endif
+  OB_CUDA(ctx, cudaFuncSetAttribute(chol_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)diag_smem));
+  if (!ctx->fit_stream) {
+    OB_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->fit_stream, cudaStreamNonBlocking));
+    OB_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_panel, cudaEventDisableTiming));
+    OB_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_trail, cudaEventDisableTiming));
   }
+  cudaStream_t side = ctx->fit_stream;
+  const bool lookahead = getenv("OB200_FIT_NO_LOOKAHEAD") == nullptr;   // (testing hook: everything on one stream)
+  bool trail_pending = false;
+  for (int kb = 0; kb < nb; ++kb) {
+    const int rem = n_pad - (kb + 1) * FB;
+    chol_step_kernel<<<1 + (rem > 0 ? rem / FB : 0), 256, diag_smem, st>>>(Lm, n_pad, kb, Dinv, Lfac, info_dev);
+    OB_LAUNCH_CHECK(ctx);
+    if (rem <= 0) break;
+    const double* panel = Lm + (size_t)(kb + 1) * FB * n_pad + (size_t)kb * FB;
+    gemm_args a{};   // (a) block column kb + 1: C[(kb+1):, kb+1] -= P P[0:64]^T
+    a.A = panel; a.lda = n_pad; a.B = panel; a.ldb = n_pad;
+    a.C = Lm + (size_t)(kb + 1) * FB * n_pad + (size_t)(kb + 1) * FB; a.ldc = n_pad;
+    a.M = rem; a.N = FB; a.K = FB; a.alpha = -1.0; a.beta = 1.0; a.lower_only = 1;
+    gemm_args b = a;  // (b) the rest: rows and columns from block kb + 2
+    b.A = panel + (size_t)FB * n_pad; b.B = b.A;
+    b.C = Lm + (size_t)(kb + 2) * FB * n_pad + (size_t)(kb + 2) * FB;
+    b.M = rem - FB; b.N = rem - FB;
+    if (lookahead && b.M > 0) {
+      OB_CUDA(ctx, cudaEventRecord(ctx->ev_panel, st));
+      if (trail_pending) OB_CUDA(ctx, cudaStreamWaitEvent(st, ctx->ev_trail, 0));   // (b) of the previous step
+      if ((rc = launch_gemm(ctx, true, a, 1))) return rc;
+      OB_CUDA(ctx, cudaStreamWaitEvent(side, ctx->ev_panel, 0));
+      if ((rc = launch_gemm(ctx, true, b, 1, side))) return rc;
+      OB_CUDA(ctx, cudaEventRecord(ctx->ev_trail, side));
+      trail_pending = true;
+    } else {
+      if (trail_pending) { OB_CUDA(ctx, cudaStreamWaitEvent(st, ctx->ev_trail, 0)); trail_pending = false; }
+      if ((rc = launch_gemm(ctx, true, a, 1))) return rc;
+      if (b.M > 0 && (rc = launch_gemm(ctx, true, b, 1))) return rc;
+    }
+  }
+  if (trail_pending) OB_CUDA(ctx, cudaStreamWaitEvent(st, ctx->ev_trail, 0));
+  chol_copy_diag_kernel<<<nb, 256, 0, st>>>(Lm, n_pad, Lfac);
+  OB_LAUNCH_CHECK(ctx);
   int info = 0;
   OB_CUDA(ctx, cudaMemcpyAsync(&info, info_dev, sizeof(int), cudaMemcpyDeviceToHost, st));
   OB_CUDA(ctx, cudaStreamSynchronize(st));
@@ -981,7 +1020,7 @@ int ob200_gp_fit(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n
   // One Newton-Schulz step X <- X + X (I - L X): the recursive-doubling products compound rounding errors
   // level by level (residual ~1e-6 at cond(K) = 1e12); the residual I - L X is computed to cond(L) eps, so one
   // step brings inv(L) to the accuracy of a backward-stable triangular solve (tools/illcond_probe.py).
-  if (!getenv("OB200_NO_NS")) {  // (testing hook: measure what the refinement buys)
+  if (!search && !getenv("OB200_NO_NS")) {  // (testing hook: measure what the refinement buys)
     gemm_args r{};  // T = L X  (lower x lower -> lower tiles, triangular k range)
     r.A = Lm; r.lda = n_pad; r.B = Xinv; r.ldb = n_pad; r.C = T; r.ldc = n_pad;
     r.M = n_pad; r.N = n_pad; r.K = n_pad; r.alpha = 1.0; r.beta = 0.0; r.lower_only = 1; r.tri_k = 1;
@@ -1002,10 +1041,12 @@ int ob200_gp_fit(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n
     append_lml_kernel<<<1, 1024, 0, st>>>(Lm, n_pad, n, ynorm, b_alpha, lml_dev);
     OB_LAUNCH_CHECK(ctx);
   }
-  pack_linv_kernel<<<ctx->num_sms * 8, 256, 0, st>>>(Xinv, n, n_pad, b_linv);
-  OB_LAUNCH_CHECK(ctx);
-  pack_xs_kernel<<<ctx->num_sms * 2, 256, 0, st>>>(Xs, n_pad, D_pad, b_xs);
-  OB_LAUNCH_CHECK(ctx);
+  if (!search) {
+    pack_linv_kernel<<<ctx->num_sms * 8, 256, 0, st>>>(Xinv, n, n_pad, b_linv);
+    OB_LAUNCH_CHECK(ctx);
+    pack_xs_kernel<<<ctx->num_sms * 2, 256, 0, st>>>(Xs, n_pad, D_pad, b_xs);
+    OB_LAUNCH_CHECK(ctx);
+  }
   ob200_fit_header h{};
   h.magic = OB200_FIT_MAGIC; h.n = n; h.D = D; h.n_pad = n_pad; h.D_pad = D_pad; h.kernel_kind = kernel->kind;
   h.amplitude = kernel->amplitude;
@@ -1027,7 +1068,7 @@ int ob200_gp_fit(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n
     for (int i = 0; i <= n_tev; ++i) cudaEventDestroy(tev[i]);
   }
   ctx->blob_bytes = lay.total;
-  ctx->fitted = true;
+  ctx->fitted = !search;
   ctx->have_local_fit = true;
   ctx->fit_serial++;
   ctx->w_Xs_off = w_Xs;
@@ -1036,6 +1077,19 @@ int ob200_gp_fit(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n
   ctx->w_stats_off = w_stats;
   ctx->fit_alpha = alpha;
   return OB200_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int ob200_gp_fit(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n, int D, const ob200_kernel* kernel,
+                 double alpha, int normalize_y) {
+  return fit_impl(ctx, X_dev, y_dev, n, D, kernel, alpha, normalize_y, 0);
+}
+
+int ob200_gp_fit_search(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n, int D, const ob200_kernel* kernel,
+                        double alpha, int normalize_y) {
+  return fit_impl(ctx, X_dev, y_dev, n, D, kernel, alpha, normalize_y, 1);
 }
 
 int ob200_gp_fit_host(ob200_ctx* ctx, const double* X_host, const double* y_host, int n, int D, const ob200_kernel* kernel,
@@ -1052,14 +1106,14 @@ int ob200_gp_fit_host(ob200_ctx* ctx, const double* X_host, const double* y_host
 
 int ob200_gp_lml(ob200_ctx* ctx, double* lml_host) {
   if (!ctx || !lml_host) return OB200_EINVAL;
-  if (!ctx->fitted) OB_FAIL(ctx, OB200_ESTATE, "no fit");
+  if (!ctx->fitted && !ctx->have_local_fit) OB_FAIL(ctx, OB200_ESTATE, "no fit");
   *lml_host = ctx->hdr.lml;
   return OB200_OK;
 }
 
 int ob200_gp_lml_grad(ob200_ctx* ctx, double* lml_host, double* grad_host, int n_grad) {
   if (!ctx || !grad_host) return OB200_EINVAL;
-  if (!ctx->fitted || !ctx->have_local_fit) OB_FAIL(ctx, OB200_ESTATE, "the gradient needs a fit made on this context");
+  if (!ctx->have_local_fit) OB_FAIL(ctx, OB200_ESTATE, "the gradient needs a fit made on this context");
   const int n = ctx->hdr.n, n_pad = ctx->hdr.n_pad, D = ctx->hdr.D, D_pad = ctx->hdr.D_pad;
   if (n_grad != D + 2) OB_FAIL(ctx, OB200_EINVAL, "n_grad must be D + 2 = %d (amplitude, D length scales, diagonal)", D + 2);
   OB_CUDA(ctx, cudaSetDevice(ctx->device));

@@ -121,6 +121,8 @@ struct ob200_ctx {
   int64_t sub_serial = -1;
   float* b32_dev = nullptr;        // FP32 bound pass: TF32 hi/lo B fragments + per-observation constants
   int64_t b32_cap = 0;
+  cudaStream_t fit_stream = nullptr;   // trailing updates of the Cholesky look-ahead
+  cudaEvent_t ev_panel = nullptr, ev_trail = nullptr;
   cudaStream_t copy_stream = nullptr;  // H2D of the candidate tail overlapped with scoring of the head
   cudaEvent_t ev_main = nullptr, ev_copy = nullptr;
   double* pinned = nullptr;        // pinned staging for host entry points

@@ -167,6 +167,21 @@ class Engine:
         if key is not None:
             self._fit_host = (key, X.copy())
 
+    def fit_search(self, X, y, kind=_lib.KERNEL_MATERN52, amplitude=1.0, length_scale=1.0, alpha=1e-10, normalize_y=False):
+        """Fit for ONE log-marginal-likelihood evaluation of a hyper-parameter search (device tensors): `lml()` /
+        `lml_grad()` work afterwards, scoring does not until the next `fit`."""
+        self.use_torch_stream()
+        ls = np.atleast_1d(np.asarray(length_scale, dtype=np.float64)).copy()
+        k = Kernel(kind, len(ls), float(amplitude), ls.ctypes.data_as(C.POINTER(C.c_double)))
+        self._fit_host = None
+        self._fit_token = self._fit_theta = None
+        self.fit_generation += 1
+        X = X.to(self.tdev, torch.float64).contiguous()
+        y = torch.as_tensor(y).to(self.tdev, torch.float64).contiguous()
+        n, D = X.shape
+        self._check(self.lib.ob200_gp_fit_search(self.ctx, _ptr(X), _ptr(y), n, D, C.byref(k), float(alpha), int(bool(normalize_y))))
+        self.n, self.D = n, D
+
     def ystats(self):
         a, b, c = C.c_double(), C.c_double(), C.c_double()
         self._check(self.lib.ob200_gp_get_ystats(self.ctx, C.byref(a), C.byref(b), C.byref(c)))

@@ -33,6 +33,8 @@ def optimise(engine, X, y, kind, amplitude, length_scale, noise, alpha, normaliz
     theta0 = np.concatenate([[np.log(amplitude)], np.log(ls0), [np.log(max(noise, NOISE_BOUNDS[0]))] if optimise_noise else []])
     bounds = [tuple(np.log(AMP_BOUNDS))] + [tuple(np.log(LS_BOUNDS))] * n_ls + ([tuple(np.log(NOISE_BOUNDS))] if optimise_noise else [])
     n_evals = [0]
+    # search evaluations need L, alpha and inv(L) only: `fit_search` skips what only the score kernel reads
+    fit = engine.fit_search if hasattr(engine, "fit_search") and hasattr(X, "is_cuda") else engine.fit
 
     def unpack(theta):
         amp = float(np.exp(theta[0]))
@@ -44,7 +46,7 @@ def optimise(engine, X, y, kind, amplitude, length_scale, noise, alpha, normaliz
         amp, ls, nz = unpack(theta)
         n_evals[0] += 1
         try:
-            engine.fit(X, y, kind=kind, amplitude=amp, length_scale=ls, alpha=alpha + nz, normalize_y=normalize_y)
+            fit(X, y, kind=kind, amplitude=amp, length_scale=ls, alpha=alpha + nz, normalize_y=normalize_y)
         except _lib.NotPositiveDefinite:
             return 1e25, np.zeros_like(theta)  # sklearn returns -inf for the likelihood here
         lml, g = engine.lml_grad()

@@ -96,6 +96,9 @@ class MultiEngine:
     def fit(self, X, y, **kwargs):
         self.primary.fit(X, y, **kwargs)
 
+    def fit_search(self, X, y, **kwargs):
+        self.primary.fit_search(X, y, **kwargs)
+
     def _replicate(self):
         src = self.primary
         if self._replicated_gen == src.fit_generation or len(self.engines) == 1:

@@ -28,5 +28,11 @@ for n, d in ((50, 2), (200, 10), (500, 20), (2000, 20), (4000, 60), (8000, 100))
         eng.fit(X, y, alpha=1e-4, normalize_y=True)
         eng.lml_grad()
     both_ms = (time.perf_counter() - t0) / reps * 1e3
-    out["n%d_d%d" % (n, d)] = dict(fit_ms=round(fit_ms, 3), fit_plus_grad_ms=round(both_ms, 3))
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        eng.fit_search(X, y, alpha=1e-4, normalize_y=True)
+        eng.lml_grad()
+    search_ms = (time.perf_counter() - t0) / reps * 1e3
+    eng.fit(X, y, alpha=1e-4, normalize_y=True)
+    out["n%d_d%d" % (n, d)] = dict(fit_ms=round(fit_ms, 3), fit_plus_grad_ms=round(both_ms, 3), search_eval_ms=round(search_ms, 3))
     print(json.dumps(out), flush=True)

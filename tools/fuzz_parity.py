@@ -1,7 +1,9 @@
 """GPU box: randomised parity sweep of the device path against the oracle (shapes, seeds and spaces the fixed
 parametrisations of tests/ do not hit).  Stops at the first mismatch with the generating recipe; prints a summary.
 usage: python tools/fuzz_parity.py [seconds] [seed]"""
+import collections
 import json
+import os
 import sys
 import time
 import traceback
@@ -24,7 +26,7 @@ from oracle import sampling as osamp  # noqa: E402
 BUDGET = float(sys.argv[1]) if len(sys.argv) > 1 else 240.0
 rng = np.random.RandomState(int(sys.argv[2]) if len(sys.argv) > 2 else 0)
 eng = get_engine(0)
-counts = {"sample": 0, "score": 0, "generated": 0, "pruned": 0, "grad": 0}
+counts = collections.Counter({"sample": 0, "score": 0, "generated": 0, "pruned": 0, "grad": 0})
 
 
 def random_space():
@@ -185,11 +187,63 @@ def fuzz_generated():
     return recipe
 
 
+def fuzz_pruned():
+    """The pruned path proper (M above the dense-fallback threshold): FP32 bound pass, FP64 refinement, subset-GP variance
+    bound, device-resident selection.  Winners must equal the dense call bit for bit; the pass-1 bounds must be rigorous
+    (mu_lb <= mu, sigma_ub >= sigma for every candidate).  alpha from 1e-10 to 1e-2, amplitudes to 1e3, length scales from
+    a fraction of the cube to far beyond it (what a fitted GP on a smooth objective looks like)."""
+    n = int(rng.choice([13, 192, 193, 500, int(rng.randint(2, 900))]))
+    d = int(rng.choice([1, 2, 5, 8, 9, 20, 24, 25, 33, int(rng.randint(1, 70))]))
+    M = int(rng.choice([18945, 19000, 40001, int(rng.randint(18945, 60000))]))
+    kind = int(rng.randint(0, 2))
+    amp = float(10 ** rng.uniform(-1, 3))
+    ls_scale = float(10 ** rng.uniform(-0.7, 1.3))
+    ls = (rng.uniform(0.5, 1.5, size=d) * ls_scale * np.sqrt(d) / 2) if rng.rand() < 0.5 else ls_scale * np.sqrt(d) / 2
+    alpha = float(10 ** rng.uniform(-10, -2))
+    kappa = float(rng.choice([1.96, 0.0, 10.0, -1.0]))
+    recipe = dict(kind="pruned", n=n, d=d, M=M, kernel=kind, amp=amp, ls=np.asarray(ls).tolist(), alpha=alpha, kappa=kappa)
+    rs = np.random.RandomState(int(rng.randint(0, 2 ** 31)))
+    X = rs.uniform(size=(n, d))
+    y = ((X - 0.5) ** 2).sum(axis=1) * float(10 ** rng.uniform(-2, 2)) + 0.01 * rs.randn(n) + float(rng.uniform(-10, 10))
+    try:
+        eng.fit(X, y, kind=kind, amplitude=amp, length_scale=ls, alpha=alpha, normalize_y=True)
+    except Exception as exc:  # not positive definite at alpha = 1e-10 with long length scales: sklearn raises too
+        if "positive definite" in str(exc):
+            counts["pruned_not_spd"] += 1
+            return recipe
+        raise
+    Cd = torch.as_tensor(rs.uniform(size=(M, d))).cuda()
+    y_opt = float(y.min())
+    dense = eng.score(Cd, acq_mask=7, y_opt=y_opt, kappa=kappa, dense=True)
+    if rng.rand() < 0.3:
+        os.environ["OB200_PRUNE_SUBSET_AT"] = "0"      # force the subset-GP step
+    if rng.rand() < 0.3:
+        os.environ["OB200_BOUND_F32_LIMIT"] = "1e30"   # force the FP32 pass whatever its budget
+    try:
+        multi, _ = eng.score_pruned_multi(Cd, acq_mask=7, y_opt=y_opt, kappa=kappa)
+        st = eng.prune_stats()
+        assert multi == {k: dense[k] for k in ("EI", "PI", "LCB")}, (recipe, multi, {k: dense[k] for k in ("EI", "PI", "LCB")}, st)
+        name = ("EI", "PI", "LCB")[int(rng.randint(0, 3))]
+        one, _ = eng.score_pruned(Cd, acq=name, y_opt=y_opt, kappa=kappa)
+        assert one[name] == dense[name], (recipe, name, one[name], dense[name], eng.prune_stats())
+        mu_lb, sg_ub, used = eng.score_bounds(Cd)
+        assert bool(torch.all(mu_lb <= dense["mu"])) and bool(torch.all(sg_ub >= dense["sigma"])), (recipe, used)
+    finally:
+        os.environ.pop("OB200_PRUNE_SUBSET_AT", None)
+        os.environ.pop("OB200_BOUND_F32_LIMIT", None)
+    counts["pruned_big"] += 1
+    counts["pruned_big_f32"] += int(st["f32"])
+    counts["pruned_big_subset"] += int(st["batch_b_subset"] >= 0)
+    counts["pruned_big_scored"] += st["batch_a"] + max(st["batch_b_subset"], 0 if st["batch_b_subset"] >= 0 else (st["batch_b_refined"] if st["f32"] else st["batch_b"]))
+    counts["pruned_big_candidates"] += M
+    return recipe
+
+
 def main():
     t0 = time.time()
     k = 0
     while time.time() - t0 < BUDGET:
-        fn = (fuzz_sample, fuzz_score, fuzz_generated)[k % 3]
+        fn = (fuzz_sample, fuzz_score, fuzz_generated, fuzz_pruned)[k % 4]
         k += 1
         state = rng.get_state()
         try:
