@@ -66,7 +66,7 @@ struct ob200_ctx {
   int64_t launches = 0;
 
   // space
-  int n_slots = 0, d_out = 0, n_cdf = 0, n_dslots = 0;
+  int n_slots = 0, d_out = 0, n_cdf = 0, n_dslots = 0, n_narrow = 0;
   ob200_slot* slots_dev = nullptr;   // device copy of the ABI table (kept for reference)
   char* dslots_dev = nullptr;        // packed 64-byte device slots used by the sampler kernel
   double* cdf_dev = nullptr;

@@ -17,10 +17,14 @@
 //
 // RNG contract (restated in oracle/philox.py + oracle/sampling.py, checked bit-exactly):
 //   key = (seed_lo, seed_hi); counter = (index_lo, index_hi, c2, try)
-//   Slots are grouped by operation (uniform real, uniform int, loguniform real, loguniform int,
-//   normal real, normal int, one-hot, small categorical -- in that order, table order inside a
-//   group, each group padded to an even size); q = position of the slot in that grouped order.
-//   uniform / loguniform / choice slot: c2 = q>>1, uniform = component (q&1) of the pair
+//   RNG contract, version 2 (round 2; restated bit for bit in oracle/sampling.py + oracle/philox.py):
+//   Slots are grouped by operation, table order inside a group.  NARROW groups come first -- uniform int, one-hot,
+//   small categorical, each padded to a multiple of FOUR slots: such a slot needs no more than 32 random bits, so one
+//   Philox call serves four of them (u = r_sel * 2^-32, exact in a double) -- then the WIDE groups -- uniform real,
+//   loguniform real, loguniform int, normal real, normal int, each padded to an even size: two 53-bit uniforms per call.
+//   q = position of the slot in that order; n_narrow = number of narrow positions (a multiple of 4).
+//   item(q) = q >> 2 for narrow slots, n_narrow / 4 + (q - n_narrow) / 2 for wide ones; sel = q & 3 resp. q & 1.
+//   uniform / loguniform / choice slot: c2 = item(q), component sel of the call
 //   normal slot: c2 = 0x80000000|q, Box-Muller of the pair
 //   try t = 0..3 (Real.sample's 4-try rejection, space.py:379-389); exhausted -> status latch.
 #include "ob200_internal.cuh"
@@ -37,7 +41,8 @@ namespace {
 #define ST_NBUF 1        // tile buffers per CTA: with 2, a tile drains through the TMA engine while the next one is generated
 #endif
 #ifndef ST_MIN_CTAS
-#define ST_MIN_CTAS 7   // 72 registers: the paired slot code spills at 64, and one CTA less per SM costs nothing
+#define ST_MIN_CTAS 6   // 80 registers: with the quad (four narrow slots per Philox call) code the kernel spills 128 B at 72; measured
+                        // on cfg5 3.74 TB/s with 7 CTAs / 72 registers, 4.04 with 6 / 80, 3.75 with 5 / 96
 #endif
 
 // Slot as the kernel reads it: 64 bytes = four 16-byte shared-memory loads, everything that only
@@ -89,6 +94,9 @@ __device__ __forceinline__ double u53_fast(uint32_t lo, uint32_t hi) {
   return fma((double)top, 0x1.0p-21, (double)bot * 0x1.0p-53);
 }
 
+// r * 2^-32: 32 random bits as a uniform in [0, 1) (exact: one conversion and a power-of-two scale)
+__device__ __forceinline__ double u32_unit(uint32_t r) { return (double)r * 0x1.0p-32; }
+
 __device__ __forceinline__ double box_muller(philox_out r) {
   const double ua = u53_fast(r.r0, r.r1), ub = u53_fast(r.r2, r.r3);
   return __dmul_rn(sqrt(__dmul_rn(-2.0, log(__dsub_rn(1.0, ua)))), cos(__dmul_rn(6.283185307179586, ub)));
@@ -116,13 +124,18 @@ __device__ __forceinline__ double draw_op(const dslot& s, double u, double z, co
 }
 
 // Real.sample's retries (space.py:379-389), tries 1..3.  Rare: out of line.  NaN = all rejected.
-__device__ __noinline__ double retry_slot(const dslot* s, int q, uint64_t index, const philox_keys* rk, const double* exp_tab) {
+__device__ __noinline__ double retry_slot(const dslot* s, int q, int n_narrow, uint64_t index, const philox_keys* rk, const double* exp_tab) {
   for (int t = 1; t < 4; ++t) {
     double u = 0.0, z = 0.0;
     if (s->op == OP_NORMAL || s->op == OP_NORMAL_INT) {
       z = box_muller(philox_rk((uint32_t)index, (uint32_t)(index >> 32), 0x80000000u | (uint32_t)q, (uint32_t)t, *rk));
+    } else if (q < n_narrow) {   // narrow slot: 32 bits of call q >> 2
+      const philox_out r = philox_rk((uint32_t)index, (uint32_t)(index >> 32), (uint32_t)(q >> 2), (uint32_t)t, *rk);
+      const int sel = q & 3;
+      u = u32_unit(sel == 0 ? r.r0 : (sel == 1 ? r.r1 : (sel == 2 ? r.r2 : r.r3)));
     } else {
-      const philox_out r = philox_rk((uint32_t)index, (uint32_t)(index >> 32), (uint32_t)(q >> 1), (uint32_t)t, *rk);
+      const philox_out r = philox_rk((uint32_t)index, (uint32_t)(index >> 32), (uint32_t)((n_narrow >> 2) + ((q - n_narrow) >> 1)),
+                                     (uint32_t)t, *rk);
       u = (q & 1) ? u53_fast(r.r2, r.r3) : u53_fast(r.r0, r.r1);
     }
     double xt;
@@ -158,7 +171,7 @@ struct row_ctx {
 };
 
 template <int OP, int MODE>
-__device__ __forceinline__ void real_slot(const dslot* __restrict__ sp, int q, const row_ctx& rc, const philox_keys& rk, double u0,
+__device__ __forceinline__ void real_slot(const dslot* __restrict__ sp, int q, int n_narrow, const row_ctx& rc, const philox_keys& rk, double u0,
                                           int normalise, int* __restrict__ status, const double* __restrict__ exp_tab) {
   const dslot s = *sp;  // four LDS.128, broadcast
   double x;
@@ -174,7 +187,7 @@ __device__ __forceinline__ void real_slot(const dslot* __restrict__ sp, int q, c
     x = draw_op<OP>(s, u0, z, exp_tab);
     ok = (x >= s.low) && (x < s.high);
     if (__any_sync(0xffffffffu, !ok)) {
-      if (!ok) { x = retry_slot(sp, q, rc.index, &rk, exp_tab); ok = (x == x); }
+      if (!ok) { x = retry_slot(sp, q, n_narrow, rc.index, &rk, exp_tab); ok = (x == x); }
     }
   }
   if (!ok) { if (rc.active) atomicOr(status, 1); x = 0.0; }
@@ -232,7 +245,7 @@ __device__ __forceinline__ void cat_slot(const dslot* __restrict__ sp, const dou
 // are independent, so keeping them in one basic block lets the scheduler overlap them.  A padding second slot
 // (all-zero parameters) is computed too and just not stored.
 template <int OP, int MODE>
-__device__ __forceinline__ void real_pair(const dslot* __restrict__ sp, int q, const row_ctx& rc, const philox_keys& rk, double ua,
+__device__ __forceinline__ void real_pair(const dslot* __restrict__ sp, int q, int n_narrow, const row_ctx& rc, const philox_keys& rk, double ua,
                                           double ub, int normalise, int* __restrict__ status, const double* __restrict__ exp_tab) {
   const dslot s0 = sp[0], s1 = sp[1];
   const bool two = s1.op != OP_NONE;
@@ -244,8 +257,8 @@ __device__ __forceinline__ void real_pair(const dslot* __restrict__ sp, int q, c
   double x0 = draw_op<OP>(s0, ua, z0, exp_tab), x1 = draw_op<OP>(s1, ub, z1, exp_tab);
   bool ok0 = (x0 >= s0.low) && (x0 < s0.high), ok1 = !two || ((x1 >= s1.low) && (x1 < s1.high));
   if (__any_sync(0xffffffffu, !(ok0 && ok1))) {
-    if (!ok0) { x0 = retry_slot(sp, q, rc.index, &rk, exp_tab); ok0 = (x0 == x0); }
-    if (!ok1) { x1 = retry_slot(sp + 1, q + 1, rc.index, &rk, exp_tab); ok1 = (x1 == x1); }
+    if (!ok0) { x0 = retry_slot(sp, q, n_narrow, rc.index, &rk, exp_tab); ok0 = (x0 == x0); }
+    if (!ok1) { x1 = retry_slot(sp + 1, q + 1, n_narrow, rc.index, &rk, exp_tab); ok1 = (x1 == x1); }
     if (!(ok0 && ok1)) {
       if (rc.active) atomicOr(status, 1);
       if (!ok0) x0 = 0.0;
@@ -284,7 +297,7 @@ __device__ __forceinline__ bool onehot4_pair(const dslot* __restrict__ sp, const
 // Both slots of a pair share the operation (groups are padded to even size), so one warp-uniform
 // switch per pair selects straight-line code for the two of them.
 template <int OP, int MODE>
-__device__ __forceinline__ void pair_op(const dslot* __restrict__ sp, const double* __restrict__ cdf, int q, const row_ctx& rc,
+__device__ __forceinline__ void pair_op(const dslot* __restrict__ sp, const double* __restrict__ cdf, int q, int n_narrow, const row_ctx& rc,
                                         const philox_keys& rk, double ua, double ub, int normalise, int* __restrict__ status,
                                         const double* __restrict__ exp_tab) {
   if (OP == OP_ONEHOT || OP == OP_CAT_SMALL) {
@@ -292,16 +305,16 @@ __device__ __forceinline__ void pair_op(const dslot* __restrict__ sp, const doub
     cat_slot<OP == OP_ONEHOT, MODE>(sp, cdf, ua, rc, normalise);
     if (sp[1].op != OP_NONE) cat_slot<OP == OP_ONEHOT, MODE>(sp + 1, cdf, ub, rc, normalise);
   } else if (MODE != MODE_VARIATES) {
-    real_pair<OP, MODE>(sp, q, rc, rk, ua, ub, normalise, status, exp_tab);
+    real_pair<OP, MODE>(sp, q, n_narrow, rc, rk, ua, ub, normalise, status, exp_tab);
   } else {
-    real_slot<OP, MODE>(sp, q, rc, rk, ua, normalise, status, exp_tab);
-    if (sp[1].op != OP_NONE) real_slot<OP, MODE>(sp + 1, q + 1, rc, rk, ub, normalise, status, exp_tab);
+    real_slot<OP, MODE>(sp, q, n_narrow, rc, rk, ua, normalise, status, exp_tab);
+    if (sp[1].op != OP_NONE) real_slot<OP, MODE>(sp + 1, q + 1, n_narrow, rc, rk, ub, normalise, status, exp_tab);
   }
 }
 
 template <int MODE>
 __global__ void __launch_bounds__(ST_THREADS, ST_MIN_CTAS)
-sample_transform_kernel(const dslot* __restrict__ slots_g, int n_dslots, int n_slots, const double* __restrict__ cdf_g, int n_cdf,
+sample_transform_kernel(const dslot* __restrict__ slots_g, int n_dslots, int n_narrow, int n_slots, const double* __restrict__ cdf_g, int n_cdf,
                         int d_out, int stride, int tile_rows, const __grid_constant__ philox_keys rk, uint64_t first_index, int64_t count,
                         int normalise, double* __restrict__ out, int64_t ld, const double* __restrict__ variates,
                         int bulk_ok, int vec_lanes, int* __restrict__ status) {
@@ -317,7 +330,8 @@ sample_transform_kernel(const dslot* __restrict__ slots_g, int n_dslots, int n_s
   __syncthreads();
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n_pairs = n_dslots >> 1;
+  const int n_quads = n_narrow >> 2;
+  const int n_items = n_quads + ((n_dslots - n_narrow) >> 1);   // one Philox call each: a quad of narrow slots or a pair of wide ones
   const int64_t n_tiles = (count + tile_rows - 1) / tile_rows;
   const uint32_t row_bytes = (uint32_t)d_out * 8u;
 
@@ -332,8 +346,11 @@ sample_transform_kernel(const dslot* __restrict__ slots_g, int n_dslots, int n_s
 #else
     const int n_rg = (rows + 31) >> 5;
 #endif
-    // items = (row group, pair), dealt round-robin to the warps: item rg * n_pairs + p goes to warp (item mod W)
-    int p0 = warp;
+    // items = (row group, Philox call), dealt round-robin to the warps -- the narrow calls (four 32-bit slots each) and
+    // the wide calls (two 53-bit slots each) in two loops of their own, so that each loop's switch holds only its
+    // operations and the call's words die right after the conversion (one common loop cost 9 registers and spilled)
+    const int n_wide = n_items - n_quads;
+    int q0 = warp, w0 = warp;
     for (int rg = 0; rg < n_rg; ++rg) {
       const int r = rg * 32 + lane;
       row_ctx rc;
@@ -341,27 +358,44 @@ sample_transform_kernel(const dslot* __restrict__ slots_g, int n_dslots, int n_s
       rc.index = first_index + (uint64_t)(row0 + r);
       rc.row_sa = tile_sa + (uint32_t)r * (uint32_t)stride * 8u;
       rc.var_row = (MODE == MODE_VARIATES) ? variates + (size_t)(row0 + (rc.active ? r : 0)) * n_slots : nullptr;
-      int p = p0;
-      for (; p < n_pairs; p += ST_THREADS / 32) {
-        const dslot* sp = slots + 2 * p;
-        double ua = 0.0, ub = 0.0;
+#define ST_NARROW(SP, Q, UA, UB)                                                                                              \
+  switch ((SP)->op) {                                                                                                           \
+    case OP_UNIFORM_INT: pair_op<OP_UNIFORM_INT, MODE>(SP, cdf, Q, n_narrow, rc, rk, UA, UB, normalise, status, exp_tab); break; \
+    case OP_ONEHOT: pair_op<OP_ONEHOT, MODE>(SP, cdf, Q, n_narrow, rc, rk, UA, UB, normalise, status, exp_tab); break;           \
+    default: pair_op<OP_CAT_SMALL, MODE>(SP, cdf, Q, n_narrow, rc, rk, UA, UB, normalise, status, exp_tab); break;               \
+  }
+      int p = q0;
+      for (; p < n_quads; p += ST_THREADS / 32) {
+        const dslot* sp = slots + 4 * p;
+        double u0 = 0.0, u1 = 0.0, u2 = 0.0, u3 = 0.0;
         if (MODE != MODE_VARIATES) {
           const philox_out pr = philox_rk((uint32_t)rc.index, (uint32_t)(rc.index >> 32), (uint32_t)p, 0u, rk);
+          u0 = u32_unit(pr.r0); u1 = u32_unit(pr.r1); u2 = u32_unit(pr.r2); u3 = u32_unit(pr.r3);
+        }
+        ST_NARROW(sp, 4 * p, u0, u1)
+        if (sp[2].op != OP_NONE) { ST_NARROW(sp + 2, 4 * p + 2, u2, u3) }
+      }
+      q0 = p - n_quads;  // the round-robin continues into the next row group
+#undef ST_NARROW
+      p = w0;
+      for (; p < n_wide; p += ST_THREADS / 32) {
+        const int q = n_narrow + 2 * p;
+        const dslot* sp = slots + q;
+        double ua = 0.0, ub = 0.0;
+        if (MODE != MODE_VARIATES) {
+          const philox_out pr = philox_rk((uint32_t)rc.index, (uint32_t)(rc.index >> 32), (uint32_t)(n_quads + p), 0u, rk);
           ua = u53_fast(pr.r0, pr.r1);
           ub = u53_fast(pr.r2, pr.r3);
         }
         switch (sp->op) {
-          case OP_UNIFORM: pair_op<OP_UNIFORM, MODE>(sp, cdf, 2 * p, rc, rk, ua, ub, normalise, status, exp_tab); break;
-          case OP_UNIFORM_INT: pair_op<OP_UNIFORM_INT, MODE>(sp, cdf, 2 * p, rc, rk, ua, ub, normalise, status, exp_tab); break;
-          case OP_LOGUNIFORM: pair_op<OP_LOGUNIFORM, MODE>(sp, cdf, 2 * p, rc, rk, ua, ub, normalise, status, exp_tab); break;
-          case OP_LOGUNIFORM_INT: pair_op<OP_LOGUNIFORM_INT, MODE>(sp, cdf, 2 * p, rc, rk, ua, ub, normalise, status, exp_tab); break;
-          case OP_NORMAL: pair_op<OP_NORMAL, MODE>(sp, cdf, 2 * p, rc, rk, ua, ub, normalise, status, exp_tab); break;
-          case OP_NORMAL_INT: pair_op<OP_NORMAL_INT, MODE>(sp, cdf, 2 * p, rc, rk, ua, ub, normalise, status, exp_tab); break;
-          case OP_ONEHOT: pair_op<OP_ONEHOT, MODE>(sp, cdf, 2 * p, rc, rk, ua, ub, normalise, status, exp_tab); break;
-          default: pair_op<OP_CAT_SMALL, MODE>(sp, cdf, 2 * p, rc, rk, ua, ub, normalise, status, exp_tab); break;
+          case OP_UNIFORM: pair_op<OP_UNIFORM, MODE>(sp, cdf, q, n_narrow, rc, rk, ua, ub, normalise, status, exp_tab); break;
+          case OP_LOGUNIFORM: pair_op<OP_LOGUNIFORM, MODE>(sp, cdf, q, n_narrow, rc, rk, ua, ub, normalise, status, exp_tab); break;
+          case OP_LOGUNIFORM_INT: pair_op<OP_LOGUNIFORM_INT, MODE>(sp, cdf, q, n_narrow, rc, rk, ua, ub, normalise, status, exp_tab); break;
+          case OP_NORMAL: pair_op<OP_NORMAL, MODE>(sp, cdf, q, n_narrow, rc, rk, ua, ub, normalise, status, exp_tab); break;
+          default: pair_op<OP_NORMAL_INT, MODE>(sp, cdf, q, n_narrow, rc, rk, ua, ub, normalise, status, exp_tab); break;
         }
       }
-      p0 = p - n_pairs;  // the round-robin continues into the next row group
+      w0 = p - n_wide;
     }
     if (bulk_ok) {
       fence_proxy_async();  // generic-proxy smem writes -> async-proxy (TMA) reads
@@ -476,7 +510,7 @@ int ob200_sample_launch(ob200_ctx* ctx, uint64_t seed, uint64_t first_index, int
     uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
     for (int r = 0; r < 10; ++r) { rk.k0[r] = k0; rk.k1[r] = k1; k0 += 0x9E3779B9u; k1 += 0xBB67AE85u; }
   }
-  kernel<<<grid, ST_THREADS, smem, ctx->stream>>>(reinterpret_cast<const dslot*>(ctx->dslots_dev), ctx->n_dslots, ctx->n_slots, ctx->cdf_dev, ctx->n_cdf, d_out,
+  kernel<<<grid, ST_THREADS, smem, ctx->stream>>>(reinterpret_cast<const dslot*>(ctx->dslots_dev), ctx->n_dslots, ctx->n_narrow, ctx->n_slots, ctx->cdf_dev, ctx->n_cdf, d_out,
                                                   stride, tile_rows, rk, first_index, count, normalise, out_dev, ld, variates_dev, bulk_ok, vec_lanes,
                                                   ctx->status_dev);
   OB_LAUNCH_CHECK(ctx);
@@ -517,14 +551,27 @@ int ob200_space_set(ob200_ctx* ctx, const ob200_slot* slots_host, int n_slots, c
   int n_dslots = 0;
   {
     if (n_slots >= 32768 || d_out >= 65536) OB_FAIL(ctx, OB200_EINVAL, "space too wide (slots < 32768, columns < 65536)");
-    // group by operation (even-padded with no-op slots) -- this order defines the RNG position of a slot
+    // group by operation -- this order defines the RNG position of a slot (contract at the top of this file): the
+    // narrow groups first, each padded with no-op slots to a multiple of four, then the wide ones, padded to even
     std::vector<dslot> ds;
-    for (int op = 0; op < OP_NONE; ++op) {
+    static const int narrow_ops[] = {OP_UNIFORM_INT, OP_ONEHOT, OP_CAT_SMALL};
+    static const int wide_ops[] = {OP_UNIFORM, OP_LOGUNIFORM, OP_LOGUNIFORM_INT, OP_NORMAL, OP_NORMAL_INT};
+    dslot pad{};
+    pad.op = OP_NONE;
+    for (int op : narrow_ops) {
       for (int i = 0; i < n_slots; ++i) {
         const dslot d = make_dslot(slots_host[i], i);
         if (d.op == op) ds.push_back(d);
       }
-      if (ds.size() & 1) { dslot pad{}; pad.op = OP_NONE; ds.push_back(pad); }
+      while (ds.size() & 3) ds.push_back(pad);
+    }
+    ctx->n_narrow = (int)ds.size();
+    for (int op : wide_ops) {
+      for (int i = 0; i < n_slots; ++i) {
+        const dslot d = make_dslot(slots_host[i], i);
+        if (d.op == op) ds.push_back(d);
+      }
+      if (ds.size() & 1) ds.push_back(pad);
     }
     n_dslots = (int)ds.size();
     OB_CUDA(ctx, cudaMalloc((void**)&ctx->dslots_dev, ds.size() * sizeof(dslot)));

@@ -7,13 +7,18 @@ Weyl keys 0x9E3779B9/0xBB67AE85, 10 rounds), keyed so that candidate i is the sa
 whatever the sharding.  This file restates the device generator bit for bit so the
 sampled integers/uniforms can be checked exactly.
 
-Counter layout used by `ob200_sample_transform` (metaopt_b200/csrc/ob200_sample.cu):
+Counter layout used by `ob200_sample_transform` (metaopt_b200/csrc/ob200_sample.cu), RNG contract version 2:
   counter = (index_lo, index_hi, c2, try), key = (seed_lo, seed_hi)
-  q = position of the slot in the device's grouped order (oracle.sampling.rng_positions)
-  c2 = q>>1 for uniform/loguniform/choice slots (component q&1 of the pair),
-  c2 = 0x80000000|q for normal slots (Box-Muller of the pair)
-  -> 4 x uint32 (r0..r3) -> two 53-bit uniforms in [0,1):
-       u_a = ((r1<<32 | r0) >> 11) * 2**-53 ,  u_b = ((r3<<32 | r2) >> 11) * 2**-53
+  q = position of the slot in the device's grouped order (oracle.sampling.rng_positions): the NARROW groups first
+      (uniform int, one-hot, small categorical; each padded to a multiple of 4), then the WIDE groups (uniform real,
+      loguniform real, loguniform int, normal real, normal int; each padded to an even size); n_narrow = number of
+      narrow positions
+  narrow slot:  c2 = q >> 2,                                   u = r_(q & 3) * 2**-32            (32 random bits)
+  wide uniform / loguniform slot:  c2 = n_narrow / 4 + (q - n_narrow) // 2,  component (q & 1) of
+       u_a = ((r1<<32 | r0) >> 11) * 2**-53 ,  u_b = ((r3<<32 | r2) >> 11) * 2**-53            (53 random bits)
+  normal slot:  c2 = 0x80000000 | q, Box-Muller of (u_a, u_b)
+(Version 1, round 1, gave every slot 53 bits, two slots per call; a categorical or uniform-integer draw needs no more
+than 32, and the Philox rounds were half of the sampler's instructions.)
 """
 import numpy as np
 
@@ -43,6 +48,13 @@ def philox4x32_10(c0, c1, c2, c3, k0, k1):
         k0 = (k0 + W0) & 0xFFFFFFFF
         k1 = (k1 + W1) & 0xFFFFFFFF
     return c0, c1, c2, c3
+
+
+def words(seed, index, slot, block):
+    """The four raw 32-bit outputs (as uint64 arrays) for (seed, global point index, c2 = slot, try = block)."""
+    seed = int(seed) & 0xFFFFFFFFFFFFFFFF
+    index = np.asarray(index, dtype=np.uint64)
+    return philox4x32_10(index & MASK32, index >> S32, slot, block, seed & 0xFFFFFFFF, seed >> 32)
 
 
 def uniform_pair(seed, index, slot, block):

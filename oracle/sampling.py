@@ -76,17 +76,29 @@ def slot_op(s):
     return base + (1 if s['kind'] == KIND_INT else 0)
 
 
+NARROW_OPS = (1, 6, 7)          # uniform int, one-hot, small categorical: 32 random bits per draw, four slots per call
+WIDE_OPS = (0, 2, 3, 4, 5)      # uniform real, loguniform real / int, normal real / int: 53 bits, two slots per call
+
+
 def rng_positions(slots):
-    """Position q of every slot in the device's RNG order: slots grouped by operation (0..7), table
-    order inside a group, each group padded to an even size (device contract, ob200_sample.cu)."""
+    """(pos, n_narrow): position q of every slot in the device's RNG order (device contract version 2,
+    ob200_sample.cu / oracle/philox.py): narrow groups first, each padded to a multiple of 4, then the wide groups,
+    each padded to an even size; table order inside a group."""
     pos, q = [0] * len(slots), 0
-    for op in range(8):
-        members = [i for i, s in enumerate(slots) if slot_op(s) == op]
-        for i in members:
-            pos[i] = q
-            q += 1
+    for op in NARROW_OPS:
+        for i, s in enumerate(slots):
+            if slot_op(s) == op:
+                pos[i] = q
+                q += 1
+        q += (-q) % 4
+    n_narrow = q
+    for op in WIDE_OPS:
+        for i, s in enumerate(slots):
+            if slot_op(s) == op:
+                pos[i] = q
+                q += 1
         q += q & 1
-    return pos
+    return pos, n_narrow
 
 
 def sample_transform(slots, cdf, seed, first_index, count, normalise=True, variates=None):
@@ -100,7 +112,7 @@ def sample_transform(slots, cdf, seed, first_index, count, normalise=True, varia
     out = np.zeros((count, d_out))
     status = STATUS_OK
     idx = np.arange(first_index, first_index + count, dtype=np.uint64)
-    qpos = rng_positions(slots)
+    qpos, n_narrow = rng_positions(slots)
     for si, s in enumerate(slots):
         q = qpos[si]
         value = np.zeros(count)
@@ -112,8 +124,11 @@ def sample_transform(slots, cdf, seed, first_index, count, normalise=True, varia
             elif s['prior'] == PRIOR_NORMAL:
                 ua, ub = philox.uniform_pair(seed, idx, 0x80000000 | q, t)
                 u, z = None, box_muller(ua, ub)
+            elif q < n_narrow:
+                r = philox.words(seed, idx, q >> 2, t)
+                u, z = r[q & 3].astype(np.float64) * 2.0 ** -32, None
             else:
-                ua, ub = philox.uniform_pair(seed, idx, q >> 1, t)
+                ua, ub = philox.uniform_pair(seed, idx, n_narrow // 4 + (q - n_narrow) // 2, t)
                 u, z = (ua if q % 2 == 0 else ub), None
             if s['kind'] == KIND_CAT:
                 c = np.asarray(cdf[s['cdf_off']:s['cdf_off'] + s['ncat']])
