@@ -18,10 +18,12 @@
 // Replaces (for the bound only) sklearn kernels.py:1720-1729 / :1569-1570 and _gpr.py:446-447.
 //
 // Work decomposition: CTA tile = CT candidates (128 / 64 / 32, the largest whose A fragments fit) x all observed
-// points; WC x 4 consumer warps (16 / 8 / 4), each with a 32-candidate x 32-observation register tile of
-// mma.sync.m16n8k8 TF32 accumulators (four warps per SM sub-partition: the HMMA, MUFU and FFMA phases of different
-// warps overlap; ncu of the first version, 8 warps with 32 x 64 tiles, showed all three pipes at ~40 % each); observed points arrive in chunks of 128, pre-split into TF32 hi/lo B
-// fragments at fit time, staged by bulk async copies (TMA engine) from a producer warp through an mbarrier ring.
+// points; WC x WO consumer warps + one producer warp.  D <= 32 (1..4 k-steps): 4 x 2 warps, each with a 32-candidate
+// x 64-observation share of a chunk, its A fragments in registers for the whole tile, the chunk walked two n8 blocks
+// at a time (MMAs of the next blocks beside the kernel evaluations of the previous ones in one unrolled stream).  Wider
+// spaces: WC x 4 warps with 32 x 32 register tiles, A fragments re-read from shared memory per k-step.  Observed points
+// arrive in chunks of 128, pre-split into TF32 hi/lo B fragments once per fit, staged by bulk async copies (TMA
+// engine) from the producer warp through an mbarrier ring.
 // The distance is in "T units": coordinates are pre-scaled so that Matern-5/2 is (1 + t + t^2/3) e^-t with
 // t = sqrt(T) and RBF is e^-T.
 #include <math.h>
