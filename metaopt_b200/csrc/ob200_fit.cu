@@ -345,6 +345,160 @@ __global__ void __launch_bounds__(256) chol_step_kernel(double* __restrict__ A, 
   }
 }
 
+// ---- compact variant of the step kernel ---------------------------------------------------------------------------
+// Same job as chol_step_kernel (which is 14.7 k instructions of straight-line code executed once per launch, i.e.
+// instruction-fetch-bound: ~40 us whatever the panel height), written as loops over 16-column sub-blocks so that it
+// stays in the instruction cache (~1.5 k instructions):
+//   factor   for each 16-column sub-block of the diagonal block: (1) its 16 x 16 diagonal part by one warp (lane = row,
+//            pivots by shuffle, no CTA barrier), (2) the rows below by forward substitution, one thread per row,
+//            (3) the rank-16 update of the rest of the block by all threads;
+//   panel    X L11^T = A21 by the same sub-blocks: (a) 16 unrolled substitution steps per row, (b) rank-16 update of
+//            the columns to the right by all threads.  Block 0 runs the panel code on the identity: X = inv(L11)^T.
+// The panel is still a true substitution (see the note on cond(K) above); only the summation order differs from the
+// unrolled kernel.
+#define SB 16                 // sub-block width
+#define WS (FB + 1)           // row stride of the panel tile in shared memory (odd: conflict-free column access)
+
+__device__ __forceinline__ double rsqrt_pos(double x) {
+  // 1 / sqrt(x) for a positive double in float range: MUFU.RSQ seed, two Newton steps (23 -> 46 -> 92 bits before rounding)
+  double y = (double)rsqrtf((float)x);
+  y = fma(y, 0.5 * fma(-x * y, y, 1.0), y);
+  y = fma(y, 0.5 * fma(-x * y, y, 1.0), y);
+  return y;
+}
+
+// 16 forward-substitution steps for one row: x <- x * inv(Lsub)^T with Lsub = S[c0.., c0..] (lower) and rd = 1 / diag
+__device__ __forceinline__ void subst16(const double* __restrict__ S, const double* __restrict__ rdiag, int c0, double (&x)[SB]) {
+#pragma unroll
+  for (int k = 0; k < SB; ++k) {
+    double a0 = 0.0, a1 = 0.0;
+#pragma unroll
+    for (int m = 0; m < k; ++m) {
+      const double l = S[(c0 + k) * FBS + c0 + m];
+      if (m & 1) a1 = fma(l, x[m], a1); else a0 = fma(l, x[m], a0);
+    }
+    x[k] = (x[k] - (a0 + a1)) * rdiag[c0 + k];
+  }
+}
+
+__global__ void __launch_bounds__(256) chol_step_compact_kernel(double* __restrict__ A, int ld, int kb, double* __restrict__ Dinv,
+                                                                double* __restrict__ Lfac, int* __restrict__ info) {
+  extern __shared__ double diag_sm[];
+  double* S = diag_sm;                 // [FB][FBS] the diagonal block, then its factor
+  double* W = diag_sm + FB * FBS;      // [FB][WS] panel tile (block 0: the identity, then inv(L11)^T)
+  __shared__ double rdiag[FB];
+  __shared__ int bad;
+  const double* blk = A + (size_t)kb * FB * ld + (size_t)kb * FB;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  double* At = nullptr;
+  for (int e = tid; e < FB * FB; e += 256) { const int r = e >> 6, c = e & 63; S[r * FBS + c] = (c <= r) ? blk[(size_t)r * ld + c] : 0.0; }
+  if (blockIdx.x > 0) {
+    At = A + (size_t)(kb + blockIdx.x) * FB * ld + (size_t)kb * FB;
+    for (int e = tid; e < FB * FB; e += 256) { const int r = e >> 6, c = e & 63; W[r * WS + c] = At[(size_t)r * ld + c]; }
+  } else {
+    for (int e = tid; e < FB * FB; e += 256) { const int r = e >> 6, c = e & 63; W[r * WS + c] = (r == c) ? 1.0 : 0.0; }
+  }
+  if (tid == 0) bad = 0;
+  __syncthreads();
+  if (*info != 0) return;  // an earlier step already failed
+
+  // ---- factor the diagonal block, sub-block by sub-block
+  for (int c0 = 0; c0 < FB; c0 += SB) {
+    if (warp == 0) {
+      // (1) 16 x 16 diagonal part: lane r < 16 owns row c0 + r; left-looking inside the sub-block
+      const int r = lane & 15;
+      double a[SB];
+#pragma unroll
+      for (int k = 0; k < SB; ++k) a[k] = S[(c0 + r) * FBS + c0 + k];
+      int fail = 0;
+#pragma unroll
+      for (int j = 0; j < SB; ++j) {
+        double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+        for (int k = 0; k < j; ++k) {
+          const double l = S[(c0 + j) * FBS + c0 + k];   // row j of the factor, written by lane j in earlier columns
+          if (k & 1) s1 = fma(a[k], l, s1); else s0 = fma(a[k], l, s0);
+        }
+        const double v = a[j] - (s0 + s1);
+        const double piv = __shfl_sync(0xffffffffu, v, j);
+        if (!(piv > 0.0) && !fail) fail = c0 + j + 1;   // also catches NaN; uniform across the warp
+        const double rd = (piv > 1e-30 && piv < 1e30) ? rsqrt_pos(piv) : 1.0 / sqrt(piv);
+        a[j] = (r == j) ? piv * rd : v * rd;
+        if (lane < SB && r >= j) S[(c0 + r) * FBS + c0 + j] = a[j];
+        if (lane == j) rdiag[c0 + j] = rd;
+        __syncwarp();
+      }
+      if (fail && lane == 0) bad = fail;
+    }
+    __syncthreads();
+    if (bad) break;
+    const int below = FB - (c0 + SB);   // rows under the sub-block
+    // (2) rows below: P = A[i, c0:c0+16] * inv(Lsub)^T, one thread per row
+    if (tid < below) {
+      const int i = c0 + SB + tid;
+      double x[SB];
+#pragma unroll
+      for (int k = 0; k < SB; ++k) x[k] = S[i * FBS + c0 + k];
+      subst16(S, rdiag, c0, x);
+#pragma unroll
+      for (int k = 0; k < SB; ++k) S[i * FBS + c0 + k] = x[k];
+    }
+    __syncthreads();
+    // (3) rank-16 update of the rest of the block (lower triangle): S[i][k] -= P[i] . P[k]
+    for (int e = tid; e < below * below; e += 256) {
+      const int ii = e / below, kk = e - ii * below;
+      if (kk > ii) continue;
+      const double* pi = S + (c0 + SB + ii) * FBS + c0;
+      const double* pk = S + (c0 + SB + kk) * FBS + c0;
+      double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+      for (int c = 0; c < SB; c += 2) { s0 = fma(pi[c], pk[c], s0); s1 = fma(pi[c + 1], pk[c + 1], s1); }
+      S[(c0 + SB + ii) * FBS + c0 + SB + kk] -= s0 + s1;
+    }
+    __syncthreads();
+  }
+  if (bad) { if (blockIdx.x == 0 && tid == 0) *info = kb * FB + bad; return; }
+
+  // ---- panel: X L11^T = W, sub-block by sub-block
+  for (int c0 = 0; c0 < FB; c0 += SB) {
+    if (tid < FB) {   // (a) 16 substitution steps for row tid
+      double x[SB];
+#pragma unroll
+      for (int k = 0; k < SB; ++k) x[k] = W[tid * WS + c0 + k];
+      subst16(S, rdiag, c0, x);
+#pragma unroll
+      for (int k = 0; k < SB; ++k) W[tid * WS + c0 + k] = x[k];
+    }
+    __syncthreads();
+    // (b) columns to the right: W[r][cc] -= X[r, c0:c0+16] . L11[cc, c0:c0+16]
+    const int right = FB - (c0 + SB);
+    for (int e = tid; e < FB * right; e += 256) {
+      const int r = e & 63, cc = c0 + SB + (e >> 6);
+      const double* xr = W + r * WS + c0;
+      const double* lc = S + cc * FBS + c0;
+      double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+      for (int c = 0; c < SB; c += 2) { s0 = fma(xr[c], lc[c], s0); s1 = fma(xr[c + 1], lc[c + 1], s1); }
+      W[r * WS + cc] -= s0 + s1;
+    }
+    __syncthreads();
+  }
+  if (blockIdx.x == 0) {
+    double* dinv = Dinv + (size_t)kb * FB * FB;
+    double* lf = Lfac + (size_t)kb * FB * FB;
+    for (int e = tid; e < FB * FB; e += 256) {
+      const int r = e >> 6, c = e & 63;
+      lf[e] = S[r * FBS + c];
+      dinv[e] = (c <= r) ? W[c * WS + r] : 0.0;   // inv(L11) = X^T, lower triangular
+    }
+  } else {
+    for (int e = tid; e < FB * FB; e += 256) {
+      const int r = e >> 6, c = e & 63;
+      At[(size_t)r * ld + c] = W[r * WS + c];
+    }
+  }
+}
+
 // the factored diagonal blocks (upper triangle zero) go into L after the last step
 __global__ void __launch_bounds__(256) chol_copy_diag_kernel(double* __restrict__ A, int ld, const double* __restrict__ Lfac) {
   const int kb = blockIdx.x;
@@ -932,14 +1086,15 @@ int fit_impl(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n, in
   }
   mark();
   // ---- right-looking blocked Cholesky with a one-step look-ahead --------------------------------
-  // Per 64-column step: ONE launch factors the diagonal block and solves the panel (chol_step_kernel); the trailing
-  // update A22 -= P P^T is split into (a) the next block column, on the main stream -- all the next step needs -- and
-  // (b) the rest, on a second stream, where it overlaps the next step's factor + panel.  (a) of step k + 1 waits for
-  // (b) of step k (they accumulate into the same tiles, in a fixed order).  The sequential chain per step is
-  // factor + panel + one column of tiles instead of three full launches (2.1 -> see DESIGN.md at n = 2000).
+  // Per 64-column step: ONE launch factors the diagonal block and solves the panel; the trailing update A22 -= P P^T is
+  // split into (a) the next block column, on the main stream -- all the next step needs -- and (b) the rest, on a second
+  // stream, where it overlaps the next step's factor + panel.  (a) of step k + 1 waits for (b) of step k (they
+  // accumulate into the same tiles, in a fixed order).  (Fusing (a) into the next step's launch was tried: the update
+  // inside the two-warp-wide step kernel cost more than the launch it saved, 1.66 -> 1.82 ms at n = 2000.)
   double* Lm = ctx->L_dev;
   const size_t diag_smem = (size_t)2 * FB * (FB + 2) * sizeof(double);
   OB_CUDA(ctx, cudaFuncSetAttribute(chol_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)diag_smem));
+  const bool compact_step = getenv("OB200_FIT_UNROLLED_STEP") == nullptr;   // (testing hook: the fully unrolled step kernel of round 2a)
   if (!ctx->fit_stream) {
     OB_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->fit_stream, cudaStreamNonBlocking));
     OB_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_panel, cudaEventDisableTiming));
@@ -948,9 +1103,12 @@ int fit_impl(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n, in
   cudaStream_t side = ctx->fit_stream;
   const bool lookahead = getenv("OB200_FIT_NO_LOOKAHEAD") == nullptr;   // (testing hook: everything on one stream)
   bool trail_pending = false;
+  const size_t step_smem = compact_step ? ((size_t)FB * (FB + 2) + (size_t)FB * (FB + 1)) * sizeof(double) : diag_smem;
+  if (compact_step) OB_CUDA(ctx, cudaFuncSetAttribute(chol_step_compact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)step_smem));
   for (int kb = 0; kb < nb; ++kb) {
     const int rem = n_pad - (kb + 1) * FB;
-    chol_step_kernel<<<1 + (rem > 0 ? rem / FB : 0), 256, diag_smem, st>>>(Lm, n_pad, kb, Dinv, Lfac, info_dev);
+    if (compact_step) chol_step_compact_kernel<<<1 + (rem > 0 ? rem / FB : 0), 256, step_smem, st>>>(Lm, n_pad, kb, Dinv, Lfac, info_dev);
+    else chol_step_kernel<<<1 + (rem > 0 ? rem / FB : 0), 256, diag_smem, st>>>(Lm, n_pad, kb, Dinv, Lfac, info_dev);
     OB_LAUNCH_CHECK(ctx);
     if (rem <= 0) break;
     const double* panel = Lm + (size_t)(kb + 1) * FB * n_pad + (size_t)kb * FB;
