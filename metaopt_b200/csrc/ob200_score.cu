@@ -131,7 +131,10 @@ __device__ unsigned long long g_sc_prof[1024 * 8];
 // setmaxnreg either, so ONE producer warp is enough: 13 warps, 72 registers)
 #define SC_MEAN_THREADS ((SC_CONSUMER_WARPS + 1) * 32)
 template <bool MEAN_ONLY>
-__global__ void __launch_bounds__(MEAN_ONLY ? SC_MEAN_THREADS : SC_THREADS, MEAN_ONLY ? 2 : 1) score_kernel(score_args a) {
+#ifndef SC_MEAN_MIN_CTAS
+#define SC_MEAN_MIN_CTAS 2
+#endif
+__global__ void __launch_bounds__(MEAN_ONLY ? SC_MEAN_THREADS : SC_THREADS, MEAN_ONLY ? SC_MEAN_MIN_CTAS : 1) score_kernel(score_args a) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int D_pad = a.D_pad, nd4 = D_pad >> 2;
   const int p1_stage_elems = SC_P1_OBS * D_pad + 2 * SC_P1_OBS;
