@@ -473,6 +473,265 @@ __global__ void __launch_bounds__(256) bound_pack_kernel(const double* __restric
   }
 }
 
+// =====================================================================================================================
+// tcgen05 variant of the bound kernel (D <= 32): the 3xTF32 distance contraction runs on the 5th-generation tensor cores
+// (tcgen05.mma kind::tf32, issued by one thread, accumulators in TMEM) instead of in the warps' own instruction stream
+// (mma.sync = legacy HMMA, 2.25 of the 18.4 instructions per 32 kernel evaluations above, and a pipe that was 41 % busy).
+//   CTA = 10 warps: warp 0 streams the observation chunks (bulk async copies), warp 1 allocates TMEM and issues the
+//   MMAs, warps 2..9 evaluate: an accumulator block is 128 candidates (TMEM lanes) x 256 observations (TMEM columns),
+//   double-buffered over the 512 columns; each evaluating thread owns ONE candidate (its TMEM lane) and 128 of the 256
+//   columns, reads them 32 at a time with tcgen05.ld and keeps mu / S / k_max of its candidate in registers.
+//   Operands are in the UMMA canonical K-major no-swizzle layout: 8-row x 16-byte core matrices, SBO = 128 B between
+//   8-row groups, LBO = bytes between the two 16-byte K chunks of a k-step.
+#define TC_CT 128             // candidates per tile = TMEM lanes
+#define TC_OBC 256            // observations per chunk = accumulator columns
+#define TC_STAGES 3
+#define TC_EPI_WARPS 8
+#define TC_THREADS ((2 + TC_EPI_WARPS) * 32)
+
+struct bound_tc_args {
+  bound_args b;          // cand, ldc, M, ls, D, nk, kind, scale, amplitude, ..., mu_lb, sigma_ub, n_tiles (bp / aux unused)
+  const float* pack;     // per chunk: [B hi | B lo] canonical layout, 2 * 2048 * nk floats
+  const float4* aux2;    // [chunk][obs pair (128)] {xx0, alpha0, xx1, alpha1}
+  int n_chunks, stages;
+};
+
+__device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  return (uint64_t)((smem_addr >> 4) & 0x3FFFu) | ((uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16) |
+         ((uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32) | (1ull << 46);   // version 1 (sm_100), no swizzle, base offset 0
+}
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n}\n" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+// 32 consecutive accumulator columns of this thread's TMEM lane
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
+  uint32_t r[32];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,"
+      "%24,%25,%26,%27,%28,%29,%30,%31}, [%32];\n"
+      "tcgen05.wait::ld.sync.aligned;\n"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+        "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]),
+        "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
+        "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+#pragma unroll
+  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+__host__ __device__ inline size_t bound_tc_smem_bytes(int nk, int stages) {
+  return 1024 + (size_t)nk * 8192 /* A hi + lo */ + (size_t)stages * nk * 16384 /* B stages */ + TC_CT * 8 /* cc */ +
+         (size_t)3 * 2 * TC_CT * 8 /* mu, S, kmax of the two column halves */ + 256;
+}
+
+template <int KIND>
+__global__ void __launch_bounds__(TC_THREADS, 1) bound_tc_kernel(bound_tc_args ta) {
+  const bound_args& a = ta.b;
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  const int nk = a.nk;
+  float* Ahi = reinterpret_cast<float*>(smem_raw);          // [2 nk chunks][16 groups][8][4]
+  float* Alo = Ahi + (size_t)nk * 1024;
+  float* Bst = Alo + (size_t)nk * 1024;                     // stages x ([B hi | B lo] = 2 * 2048 nk floats)
+  const int n_st = ta.stages;
+  double* cc = reinterpret_cast<double*>(Bst + (size_t)n_st * nk * 4096);
+  double* red = cc + TC_CT;                                 // [3][2][TC_CT]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(red + 3 * 2 * TC_CT);
+  uint64_t* full = bars;                  // [TC_STAGES] B stage landed
+  uint64_t* empty = full + TC_STAGES;     // [TC_STAGES] B stage consumed by the MMAs
+  uint64_t* tfull = empty + TC_STAGES;    // [2] accumulator block complete
+  uint64_t* tempty = tfull + 2;           // [2] accumulator block drained
+  uint64_t* a_ready = tempty + 2;         // A tile staged
+  uint32_t* tmem_base_s = reinterpret_cast<uint32_t*>(a_ready + 1);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if (tid == 0) {
+    for (int s = 0; s < TC_STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&tfull[s], 1); mbar_init(&tempty[s], TC_EPI_WARPS); }
+    mbar_init(a_ready, TC_EPI_WARPS);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {   // the whole TMEM: two 256-column accumulator blocks (one CTA per SM by shared-memory size)
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(tmem_base_s)) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_base_s;
+  const uint32_t stage_bytes = (uint32_t)nk * 16384u;
+
+  if (warp == 0) {
+    // ---- producer: B chunks of every tile this CTA owns
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (long long tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x)
+        for (int c = 0; c < ta.n_chunks; ++c, ++it) {
+          const int st = it % n_st;
+          mbar_wait_backoff(&empty[st], ((it / n_st) & 1) ^ 1);
+          mbar_expect_tx(&full[st], stage_bytes);
+          bulk_g2s(Bst + (size_t)st * nk * 4096, ta.pack + (size_t)c * nk * 4096, stage_bytes, &full[st]);
+        }
+    }
+  } else if (warp == 1) {
+    // ---- MMA issuer (one thread): 9 x (M128 N256 K8) per chunk -- lo*hi, hi*lo, hi*hi for each k-step
+    if (lane == 0) {
+      // instruction descriptor: D = F32, A = B = TF32, both K-major, N = 256, M = 128
+      const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TC_OBC >> 3) << 17) | ((uint32_t)(TC_CT >> 4) << 24);
+      const uint32_t a_hi = smem_u32(Ahi), a_lo = smem_u32(Alo);
+      uint32_t it = 0, ch = 0, tl = 0;
+      for (long long tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, ++tl) {
+        mbar_wait(a_ready, tl & 1);
+        for (int c = 0; c < ta.n_chunks; ++c, ++it, ++ch) {
+          const int st = it % n_st, as = ch & 1;
+          mbar_wait(&tempty[as], ((ch >> 1) & 1) ^ 1);
+          mbar_wait(&full[st], (it / n_st) & 1);
+          tc_fence_after();
+          const uint32_t b_hi = smem_u32(Bst + (size_t)st * nk * 4096), b_lo = b_hi + (uint32_t)nk * 8192u;
+          const uint32_t d = tmem_base + (uint32_t)as * TC_OBC;
+          uint32_t acc = 0;
+          for (int ks = 0; ks < nk; ++ks) {
+            // k-step ks = K chunks 2 ks, 2 ks + 1; A: 16 row groups per chunk (2048 B), B: 32 (4096 B)
+            const uint64_t dah = umma_desc(a_hi + ks * 4096u, 2048u, 128u), dal = umma_desc(a_lo + ks * 4096u, 2048u, 128u);
+            const uint64_t dbh = umma_desc(b_hi + ks * 8192u, 4096u, 128u), dbl = umma_desc(b_lo + ks * 8192u, 4096u, 128u);
+            umma_tf32(d, dal, dbh, idesc, acc); acc = 1;
+            umma_tf32(d, dah, dbl, idesc, 1);
+            umma_tf32(d, dah, dbh, idesc, 1);
+          }
+          umma_commit(&empty[st]);    // the stage is free once these MMAs have read it
+          umma_commit(&tfull[as]);    // ... and the accumulator block is complete
+        }
+      }
+    }
+  } else {
+    // ---- evaluating warps
+    const int ew = warp - 2;                    // 0..7
+    const int q = warp & 3, half = ew >> 2;     // TMEM lane quarter of this warp (hardware: warp index mod 4), column half
+    const int row = q * 32 + lane;              // candidate of this thread inside the tile
+    const int et = ew * 32 + lane;              // 0..255
+    uint32_t ch = 0;
+    for (long long tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+      const long long row0 = tile * TC_CT;
+      {  // stage the tile: two threads per candidate row (even / odd columns)
+        const int r = et >> 1, part = et & 1;
+        const bool live = row0 + r < a.M;
+        const double* src = a.cand + (size_t)(row0 + r) * a.ldc;
+        double acc = 0.0;
+        for (int d = part; d < nk * 8; d += 2) {
+          double u = 0.0;
+          if (live && d < a.D) u = a.scale * src[d] / a.ls[d];
+          acc = fma(u, u, acc);
+          const float uf = (float)u;
+          const uint32_t hi = to_tf32(uf);
+          const uint32_t lo = to_tf32(uf - __uint_as_float(hi));
+          const int idx = (((d >> 2) * 16 + (r >> 3)) * 8 + (r & 7)) * 4 + (d & 3);
+          Ahi[idx] = __uint_as_float(hi);
+          Alo[idx] = __uint_as_float(lo);
+        }
+        acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+        if (part == 0) cc[r] = acc;
+      }
+      fence_proxy_async();   // generic-proxy writes of A -> the tensor core's (async proxy) reads
+      asm volatile("bar.sync 1, %0;" ::"n"(TC_EPI_WARPS * 32) : "memory");
+      if (lane == 0) mbar_arrive(a_ready);
+      const float ccr = (float)cc[row];
+      double mu64 = 0.0, s64 = 0.0;
+      float kmx = 0.f;
+      for (int c = 0; c < ta.n_chunks; ++c, ++ch) {
+        const int as = ch & 1;
+        mbar_wait(&tfull[as], (ch >> 1) & 1);
+        tc_fence_after();
+        const float4* axp = ta.aux2 + (size_t)c * (TC_OBC / 2) + half * 64;
+        float mu32 = 0.f, s32 = 0.f;
+#pragma unroll 1
+        for (int sub = 0; sub < 4; ++sub) {
+          float g[32];
+          tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * TC_OBC + half * 128 + sub * 32), g);
+#pragma unroll
+          for (int j = 0; j < 32; j += 2) {
+            const float4 ax = __ldg(axp + sub * 16 + (j >> 1));   // {xx, alpha} of two observations: one address per warp
+            const float T0 = fmaxf(fmaf(-2.f, g[j], ccr + ax.x), BD_T_FLOOR);
+            const float T1 = fmaxf(fmaf(-2.f, g[j + 1], ccr + ax.z), BD_T_FLOOR);
+            const float k0 = kernel_T<KIND>(T0), k1 = kernel_T<KIND>(T1);
+            mu32 = fmaf(k0, ax.y, mu32);
+            mu32 = fmaf(k1, ax.w, mu32);
+            s32 = fmaf(k0, fabsf(ax.y), s32);
+            s32 = fmaf(k1, fabsf(ax.w), s32);
+            kmx = fmaxf(kmx, fmaxf(k0, k1));
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tempty[as]);
+        mu64 += (double)mu32;
+        s64 += (double)s32;
+      }
+      red[(0 * 2 + half) * TC_CT + row] = mu64;
+      red[(1 * 2 + half) * TC_CT + row] = s64;
+      red[(2 * 2 + half) * TC_CT + row] = (double)kmx;
+      asm volatile("bar.sync 1, %0;" ::"n"(TC_EPI_WARPS * 32) : "memory");
+      if (half == 0 && row0 + row < a.M) {
+        const double m = red[0 * TC_CT + row] + red[1 * TC_CT + row];
+        const double sS = red[2 * TC_CT + row] + red[3 * TC_CT + row];
+        const double k = fmax(red[4 * TC_CT + row], red[5 * TC_CT + row]);
+        const double xm = *a.xx_max;
+        const double rc = sqrt(cc[row]) + sqrt(xm);
+        const double dT = a.g_T * rc * rc;
+        double rel = (KIND == OB200_KERNEL_MATERN52 ? dT * (1.0 / 6.0) : dT) * 1.02 + a.c0 + a.c1 * (KIND == OB200_KERNEL_MATERN52 ? rc : rc * rc);
+        if (!(xm < 1e29)) rel = 1.0;
+        const double eps = rel < 0.5 ? a.y_std * (a.amplitude * sS * rel / (1.0 - rel) * 1.001 + a.tiny) : INFINITY;
+        a.mu_lb[row0 + row] = a.y_std * (a.amplitude * m) + a.y_mean - eps;
+        const double klo = rel < 0.5 ? a.amplitude * k * (1.0 - rel) : 0.0;
+        const double var_ub = fmin(fmax(a.amplitude - klo * klo / (a.amplitude + a.diag), 0.0) + 1e-6 * a.amplitude, a.amplitude);
+        a.sigma_ub[row0 + row] = a.y_std * sqrt(var_ub);
+      }
+      asm volatile("bar.sync 1, %0;" ::"n"(TC_EPI_WARPS * 32) : "memory");   // cc / red are rewritten by the next tile
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  __syncwarp();
+  if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
+}
+
+// observations -> UMMA canonical K-major layout (TF32 hi / lo) per 256-observation chunk, and {xx, alpha} pairs
+__global__ void __launch_bounds__(256) bound_pack_tc_kernel(const double* __restrict__ xs, const double* __restrict__ xx,
+                                                            const double* __restrict__ alpha, int n, int D_pad, int nk, int n_chunks,
+                                                            double scale, float* __restrict__ pack, float4* __restrict__ aux2) {
+  const int nd4 = D_pad >> 2;
+  const long long per_chunk = (long long)nk * 2048;   // floats of one of hi / lo
+  const long long total = (long long)n_chunks * per_chunk;
+  for (long long e = (long long)blockIdx.x * 256 + threadIdx.x; e < total; e += (long long)gridDim.x * 256) {
+    const int c = (int)(e / per_chunk);
+    const int i = (int)(e - (long long)c * per_chunk);
+    const int el = i & 3, r0 = (i >> 2) & 7, g = (i >> 5) & 31, kc = i >> 10;   // [kc][g][r0][el]
+    const int obs = c * TC_OBC + g * 8 + r0, d = kc * 4 + el;
+    float v = 0.f;
+    if (obs < n && d < D_pad) v = (float)(scale * xs[((size_t)(obs >> 3) * nd4 + (d >> 2)) * 32 + (obs & 7) * 4 + (d & 3)]);
+    const uint32_t hi = to_tf32(v);
+    pack[(size_t)c * 2 * per_chunk + i] = __uint_as_float(hi);
+    pack[(size_t)c * 2 * per_chunk + per_chunk + i] = __uint_as_float(to_tf32(v - __uint_as_float(hi)));
+  }
+  const long long n_aux = (long long)n_chunks * (TC_OBC / 2);
+  for (long long e = (long long)blockIdx.x * 256 + threadIdx.x; e < n_aux; e += (long long)gridDim.x * 256) {
+    const long long j0 = 2 * e, j1 = j0 + 1;
+    float4 out;
+    out.x = j0 < n ? (float)(scale * scale * xx[j0]) : 1e30f;
+    out.y = j0 < n ? (float)alpha[j0] : 0.f;
+    out.z = j1 < n ? (float)(scale * scale * xx[j1]) : 1e30f;
+    out.w = j1 < n ? (float)alpha[j1] : 0.f;
+    aux2[e] = out;
+  }
+}
+
 template <int WC, int WO, int NKR>
 int launch_cfg(ob200_ctx* ctx, const bound_args& a, int grid, size_t smem) {
   auto kern = a.kind == OB200_KERNEL_MATERN52 ? bound_kernel<WC, WO, OB200_KERNEL_MATERN52, NKR> : bound_kernel<WC, WO, OB200_KERNEL_RBF, NKR>;
@@ -571,6 +830,36 @@ int ob200_bound_f32_launch(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, 
   a.n_tiles = (M + ct - 1) / ct;
   const int64_t max_grid = (int64_t)ctx->num_sms * ctas_per_sm;
   const int grid = (int)(a.n_tiles < max_grid ? a.n_tiles : max_grid);
+  // tcgen05 variant (D <= 32): the contraction on the 5th-generation tensor cores, accumulators in TMEM
+  bool use_tc = nk <= 4;
+  if (const char* env = getenv("OB200_BOUND_TC")) use_tc = use_tc && env[0] != '0';   // (OB200_BOUND_TC=0: the mma.sync kernel)
+  if (use_tc) {
+    const int n_chunks_tc = (h.n + TC_OBC - 1) / TC_OBC;
+    const int64_t pack_floats = (int64_t)n_chunks_tc * 2 * nk * 2048, aux_floats = (int64_t)n_chunks_tc * (TC_OBC / 2) * 4;
+    if ((rc = ob_reserve(ctx, &ctx->tc_dev, &ctx->tc_cap, pack_floats + aux_floats))) return rc;
+    float4* aux2 = reinterpret_cast<float4*>(ctx->tc_dev + pack_floats);
+    if (ctx->tc_serial != ctx->fit_serial) {
+      bound_pack_tc_kernel<<<ctx->num_sms, 256, 0, ctx->stream>>>(
+          reinterpret_cast<const double*>(ctx->blob + lay.off_xs), reinterpret_cast<const double*>(ctx->blob + lay.off_xx),
+          reinterpret_cast<const double*>(ctx->blob + lay.off_alpha), h.n, h.D_pad, nk, n_chunks_tc, scale, ctx->tc_dev, aux2);
+      OB_LAUNCH_CHECK(ctx);
+      ctx->tc_serial = ctx->fit_serial;
+    }
+    bound_tc_args ta{};
+    ta.b = a;
+    ta.b.c0 = c0 + 70.0 * u;   // FP32 partial sums of up to 128 terms per flush here (64 above)
+    ta.b.n_tiles = (M + TC_CT - 1) / TC_CT;
+    ta.pack = ctx->tc_dev; ta.aux2 = aux2; ta.n_chunks = n_chunks_tc;
+    ta.stages = nk <= 3 ? TC_STAGES : 2;
+    const size_t smem_tc = bound_tc_smem_bytes(nk, ta.stages);
+    auto kern = a.kind == OB200_KERNEL_MATERN52 ? bound_tc_kernel<OB200_KERNEL_MATERN52> : bound_tc_kernel<OB200_KERNEL_RBF>;
+    OB_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_tc));
+    const int grid_tc = (int)(ta.b.n_tiles < ctx->num_sms ? ta.b.n_tiles : ctx->num_sms);
+    kern<<<grid_tc, TC_THREADS, smem_tc, ctx->stream>>>(ta);
+    OB_LAUNCH_CHECK(ctx);
+    *done = 1;
+    return OB200_OK;
+  }
   if (wc == 4 && nk == 1) rc = launch_cfg<4, 2, 1>(ctx, a, grid, smem);        // D <= 8
   else if (wc == 4 && nk == 2) rc = launch_cfg<4, 2, 2>(ctx, a, grid, smem);   // D <= 16
   else if (wc == 4 && nk == 3) rc = launch_cfg<4, 2, 3>(ctx, a, grid, smem);   // D <= 24 (BASELINE config 2)

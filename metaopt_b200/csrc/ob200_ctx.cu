@@ -71,6 +71,7 @@ void ob200_ctx_destroy(ob200_ctx* ctx) {
   cudaFree(ctx->gather_dev);
   cudaFree(ctx->prune_small_dev);
   cudaFree(ctx->b32_dev);
+  cudaFree(ctx->tc_dev);
   cudaFree(ctx->best_dev);
   if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
   if (ctx->fit_stream) cudaStreamDestroy(ctx->fit_stream);

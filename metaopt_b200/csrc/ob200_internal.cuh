@@ -119,6 +119,8 @@ struct ob200_ctx {
   int b32_ok = 0;                  // this fit may use the FP32 bound pass (its error budget is not vacuous)
   ob200_ctx* sub = nullptr;        // pruned scoring: GP on a subset of the observations (variance upper bound)
   int64_t sub_serial = -1;
+  float* tc_dev = nullptr;         // FP32 bound pass, tcgen05 variant: observations in the UMMA canonical layout
+  int64_t tc_cap = 0, tc_serial = -1;
   float* b32_dev = nullptr;        // FP32 bound pass: TF32 hi/lo B fragments + per-observation constants
   int64_t b32_cap = 0;
   cudaStream_t fit_stream = nullptr;   // trailing updates of the Cholesky look-ahead
