@@ -491,9 +491,9 @@ __global__ void __launch_bounds__(256) bound_pack_kernel(const double* __restric
 
 struct bound_tc_args {
   bound_args b;          // cand, ldc, M, ls, D, nk, kind, scale, amplitude, ..., mu_lb, sigma_ub, n_tiles (bp / aux unused)
-  const float* pack;     // per chunk: [B hi | B lo] canonical layout, 2 * 2048 * nk floats
+  const float* pack;     // [chunk][k-slice]: [B hi | B lo] of ksl k-steps in the canonical layout, 2 * 2048 * ksl floats
   const float4* aux2;    // [chunk][obs pair (128)] {xx0, alpha0, xx1, alpha1}
-  int n_chunks, stages;
+  int n_chunks, stages, ksl, n_slices;   // a B stage = one k-slice (ksl <= 3 k-steps) of one chunk: 16 KB * ksl whatever D is
 };
 
 __device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
@@ -528,8 +528,8 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
   for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
 }
 
-__host__ __device__ inline size_t bound_tc_smem_bytes(int nk, int stages) {
-  return 1024 + (size_t)nk * 8192 /* A hi + lo */ + (size_t)stages * nk * 16384 /* B stages */ + TC_CT * 8 /* cc */ +
+__host__ __device__ inline size_t bound_tc_smem_bytes(int nk, int ksl, int stages) {
+  return 1024 + (size_t)nk * 8192 /* A hi + lo */ + (size_t)stages * ksl * 16384 /* B stages */ + TC_CT * 8 /* cc */ +
          (size_t)3 * 2 * TC_CT * 8 /* mu, S, kmax of the two column halves */ + 256;
 }
 
@@ -540,9 +540,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) bound_tc_kernel(bound_tc_args t
   const int nk = a.nk;
   float* Ahi = reinterpret_cast<float*>(smem_raw);          // [2 nk chunks][16 groups][8][4]
   float* Alo = Ahi + (size_t)nk * 1024;
-  float* Bst = Alo + (size_t)nk * 1024;                     // stages x ([B hi | B lo] = 2 * 2048 nk floats)
-  const int n_st = ta.stages;
-  double* cc = reinterpret_cast<double*>(Bst + (size_t)n_st * nk * 4096);
+  float* Bst = Alo + (size_t)nk * 1024;                     // stages x ([B hi | B lo] = 2 * 2048 ksl floats)
+  const int n_st = ta.stages, ksl = ta.ksl, n_sl = ta.n_slices;
+  double* cc = reinterpret_cast<double*>(Bst + (size_t)n_st * ksl * 4096);
   double* red = cc + TC_CT;                                 // [3][2][TC_CT]
   uint64_t* bars = reinterpret_cast<uint64_t*>(red + 3 * 2 * TC_CT);
   uint64_t* full = bars;                  // [TC_STAGES] B stage landed
@@ -567,18 +567,18 @@ __global__ void __launch_bounds__(TC_THREADS, 1) bound_tc_kernel(bound_tc_args t
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_base_s;
-  const uint32_t stage_bytes = (uint32_t)nk * 16384u;
+  const uint32_t stage_bytes = (uint32_t)ksl * 16384u;
 
   if (warp == 0) {
     // ---- producer: B chunks of every tile this CTA owns
     if (lane == 0) {
       uint32_t it = 0;
       for (long long tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x)
-        for (int c = 0; c < ta.n_chunks; ++c, ++it) {
+        for (int c = 0; c < ta.n_chunks * n_sl; ++c, ++it) {   // (chunk, k-slice) pairs are contiguous in the pack
           const int st = it % n_st;
           mbar_wait_backoff(&empty[st], ((it / n_st) & 1) ^ 1);
           mbar_expect_tx(&full[st], stage_bytes);
-          bulk_g2s(Bst + (size_t)st * nk * 4096, ta.pack + (size_t)c * nk * 4096, stage_bytes, &full[st]);
+          bulk_g2s(Bst + (size_t)st * ksl * 4096, ta.pack + (size_t)c * ksl * 4096, stage_bytes, &full[st]);
         }
     }
   } else if (warp == 1) {
@@ -590,24 +590,29 @@ __global__ void __launch_bounds__(TC_THREADS, 1) bound_tc_kernel(bound_tc_args t
       uint32_t it = 0, ch = 0, tl = 0;
       for (long long tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, ++tl) {
         mbar_wait(a_ready, tl & 1);
-        for (int c = 0; c < ta.n_chunks; ++c, ++it, ++ch) {
-          const int st = it % n_st, as = ch & 1;
+        for (int c = 0; c < ta.n_chunks; ++c, ++ch) {
+          const int as = ch & 1;
           mbar_wait(&tempty[as], ((ch >> 1) & 1) ^ 1);
-          mbar_wait(&full[st], (it / n_st) & 1);
-          tc_fence_after();
-          const uint32_t b_hi = smem_u32(Bst + (size_t)st * nk * 4096), b_lo = b_hi + (uint32_t)nk * 8192u;
           const uint32_t d = tmem_base + (uint32_t)as * TC_OBC;
           uint32_t acc = 0;
-          for (int ks = 0; ks < nk; ++ks) {
-            // k-step ks = K chunks 2 ks, 2 ks + 1; A: 16 row groups per chunk (2048 B), B: 32 (4096 B)
-            const uint64_t dah = umma_desc(a_hi + ks * 4096u, 2048u, 128u), dal = umma_desc(a_lo + ks * 4096u, 2048u, 128u);
-            const uint64_t dbh = umma_desc(b_hi + ks * 8192u, 4096u, 128u), dbl = umma_desc(b_lo + ks * 8192u, 4096u, 128u);
-            umma_tf32(d, dal, dbh, idesc, acc); acc = 1;
-            umma_tf32(d, dah, dbl, idesc, 1);
-            umma_tf32(d, dah, dbh, idesc, 1);
+          for (int sl = 0; sl < n_sl; ++sl, ++it) {
+            const int st = it % n_st;
+            mbar_wait(&full[st], (it / n_st) & 1);
+            tc_fence_after();
+            const uint32_t b_hi = smem_u32(Bst + (size_t)st * ksl * 4096), b_lo = b_hi + (uint32_t)ksl * 8192u;
+            const int jn = min(ksl, nk - sl * ksl);
+            for (int j = 0; j < jn; ++j) {
+              // k-step = two 16-byte K chunks; A: 16 row groups per chunk (2048 B), B: 32 (4096 B)
+              const uint32_t ka = (uint32_t)(sl * ksl + j) * 4096u, kb = (uint32_t)j * 8192u;
+              const uint64_t dah = umma_desc(a_hi + ka, 2048u, 128u), dal = umma_desc(a_lo + ka, 2048u, 128u);
+              const uint64_t dbh = umma_desc(b_hi + kb, 4096u, 128u), dbl = umma_desc(b_lo + kb, 4096u, 128u);
+              umma_tf32(d, dal, dbh, idesc, acc); acc = 1;
+              umma_tf32(d, dah, dbl, idesc, 1);
+              umma_tf32(d, dah, dbh, idesc, 1);
+            }
+            umma_commit(&empty[st]);    // the stage is free once these MMAs have read it
           }
-          umma_commit(&empty[st]);    // the stage is free once these MMAs have read it
-          umma_commit(&tfull[as]);    // ... and the accumulator block is complete
+          umma_commit(&tfull[as]);      // the accumulator block is complete
         }
       }
     }
@@ -702,23 +707,24 @@ __global__ void __launch_bounds__(TC_THREADS, 1) bound_tc_kernel(bound_tc_args t
   if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
 }
 
-// observations -> UMMA canonical K-major layout (TF32 hi / lo) per 256-observation chunk, and {xx, alpha} pairs
+// observations -> UMMA canonical K-major layout (TF32 hi / lo) per (256-observation chunk, k-slice), and {xx, alpha} pairs
 __global__ void __launch_bounds__(256) bound_pack_tc_kernel(const double* __restrict__ xs, const double* __restrict__ xx,
-                                                            const double* __restrict__ alpha, int n, int D_pad, int nk, int n_chunks,
-                                                            double scale, float* __restrict__ pack, float4* __restrict__ aux2) {
+                                                            const double* __restrict__ alpha, int n, int D_pad, int ksl, int n_slices,
+                                                            int n_chunks, double scale, float* __restrict__ pack, float4* __restrict__ aux2) {
   const int nd4 = D_pad >> 2;
-  const long long per_chunk = (long long)nk * 2048;   // floats of one of hi / lo
-  const long long total = (long long)n_chunks * per_chunk;
+  const long long per_slice = (long long)ksl * 2048;   // floats of one of hi / lo of a slice
+  const long long total = (long long)n_chunks * n_slices * per_slice;
   for (long long e = (long long)blockIdx.x * 256 + threadIdx.x; e < total; e += (long long)gridDim.x * 256) {
-    const int c = (int)(e / per_chunk);
-    const int i = (int)(e - (long long)c * per_chunk);
-    const int el = i & 3, r0 = (i >> 2) & 7, g = (i >> 5) & 31, kc = i >> 10;   // [kc][g][r0][el]
-    const int obs = c * TC_OBC + g * 8 + r0, d = kc * 4 + el;
+    const long long cs = e / per_slice;                 // chunk * n_slices + slice
+    const int i = (int)(e - cs * per_slice);
+    const int c = (int)(cs / n_slices), sl = (int)(cs - (long long)c * n_slices);
+    const int el = i & 3, r0 = (i >> 2) & 7, g = (i >> 5) & 31, kc = i >> 10;   // [kc][g][r0][el] inside the slice
+    const int obs = c * TC_OBC + g * 8 + r0, d = (sl * ksl * 2 + kc) * 4 + el;
     float v = 0.f;
     if (obs < n && d < D_pad) v = (float)(scale * xs[((size_t)(obs >> 3) * nd4 + (d >> 2)) * 32 + (obs & 7) * 4 + (d & 3)]);
     const uint32_t hi = to_tf32(v);
-    pack[(size_t)c * 2 * per_chunk + i] = __uint_as_float(hi);
-    pack[(size_t)c * 2 * per_chunk + per_chunk + i] = __uint_as_float(to_tf32(v - __uint_as_float(hi)));
+    pack[(size_t)cs * 2 * per_slice + i] = __uint_as_float(hi);
+    pack[(size_t)cs * 2 * per_slice + per_slice + i] = __uint_as_float(to_tf32(v - __uint_as_float(hi)));
   }
   const long long n_aux = (long long)n_chunks * (TC_OBC / 2);
   for (long long e = (long long)blockIdx.x * 256 + threadIdx.x; e < n_aux; e += (long long)gridDim.x * 256) {
@@ -830,18 +836,23 @@ int ob200_bound_f32_launch(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, 
   a.n_tiles = (M + ct - 1) / ct;
   const int64_t max_grid = (int64_t)ctx->num_sms * ctas_per_sm;
   const int grid = (int)(a.n_tiles < max_grid ? a.n_tiles : max_grid);
-  // tcgen05 variant (D <= 32): the contraction on the 5th-generation tensor cores, accumulators in TMEM
-  bool use_tc = nk <= 4;
+  // tcgen05 variant: the contraction on the 5th-generation tensor cores, accumulators in TMEM.  A B stage is one k-slice
+  // (<= 3 k-steps = 24 columns) of one 256-observation chunk, so its size does not grow with D; the candidate tile's own
+  // fragments (8 KB per k-step) bound the width: D <= 120.
+  const int n_sl_tc = (nk + 2) / 3, ksl_tc = (nk + n_sl_tc - 1) / n_sl_tc;
+  int st_tc = TC_STAGES;
+  while (st_tc > 2 && bound_tc_smem_bytes(nk, ksl_tc, st_tc) > 225 * 1024) --st_tc;
+  bool use_tc = bound_tc_smem_bytes(nk, ksl_tc, st_tc) <= 225 * 1024;
   if (const char* env = getenv("OB200_BOUND_TC")) use_tc = use_tc && env[0] != '0';   // (OB200_BOUND_TC=0: the mma.sync kernel)
   if (use_tc) {
     const int n_chunks_tc = (h.n + TC_OBC - 1) / TC_OBC;
-    const int64_t pack_floats = (int64_t)n_chunks_tc * 2 * nk * 2048, aux_floats = (int64_t)n_chunks_tc * (TC_OBC / 2) * 4;
+    const int64_t pack_floats = (int64_t)n_chunks_tc * n_sl_tc * 2 * ksl_tc * 2048, aux_floats = (int64_t)n_chunks_tc * (TC_OBC / 2) * 4;
     if ((rc = ob_reserve(ctx, &ctx->tc_dev, &ctx->tc_cap, pack_floats + aux_floats))) return rc;
     float4* aux2 = reinterpret_cast<float4*>(ctx->tc_dev + pack_floats);
     if (ctx->tc_serial != ctx->fit_serial) {
       bound_pack_tc_kernel<<<ctx->num_sms, 256, 0, ctx->stream>>>(
           reinterpret_cast<const double*>(ctx->blob + lay.off_xs), reinterpret_cast<const double*>(ctx->blob + lay.off_xx),
-          reinterpret_cast<const double*>(ctx->blob + lay.off_alpha), h.n, h.D_pad, nk, n_chunks_tc, scale, ctx->tc_dev, aux2);
+          reinterpret_cast<const double*>(ctx->blob + lay.off_alpha), h.n, h.D_pad, ksl_tc, n_sl_tc, n_chunks_tc, scale, ctx->tc_dev, aux2);
       OB_LAUNCH_CHECK(ctx);
       ctx->tc_serial = ctx->fit_serial;
     }
@@ -850,8 +861,8 @@ int ob200_bound_f32_launch(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, 
     ta.b.c0 = c0 + 70.0 * u;   // FP32 partial sums of up to 128 terms per flush here (64 above)
     ta.b.n_tiles = (M + TC_CT - 1) / TC_CT;
     ta.pack = ctx->tc_dev; ta.aux2 = aux2; ta.n_chunks = n_chunks_tc;
-    ta.stages = nk <= 3 ? TC_STAGES : 2;
-    const size_t smem_tc = bound_tc_smem_bytes(nk, ta.stages);
+    ta.stages = st_tc; ta.ksl = ksl_tc; ta.n_slices = n_sl_tc;
+    const size_t smem_tc = bound_tc_smem_bytes(nk, ksl_tc, st_tc);
     auto kern = a.kind == OB200_KERNEL_MATERN52 ? bound_tc_kernel<OB200_KERNEL_MATERN52> : bound_tc_kernel<OB200_KERNEL_RBF>;
     OB_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_tc));
     const int grid_tc = (int)(ta.b.n_tiles < ctx->num_sms ? ta.b.n_tiles : ctx->num_sms);
