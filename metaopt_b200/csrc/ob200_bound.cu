@@ -168,7 +168,7 @@ __device__ __forceinline__ void epilogue_nb(const float (&acc)[2][4], const floa
 template <int WC, int WO, int KIND, int NKR>
 __global__ void __launch_bounds__((WC * WO + 1) * 32, 1) bound_kernel(bound_args a) {
   constexpr int BD_WARPS = WC * WO, CT = 32 * WC, NB = (BD_OBC / 8) / WO;
-  extern __shared__ __align__(128) unsigned char smem_raw[];
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
   const int nk = NKR > 0 ? NKR : a.nk, ksl = NKR > 0 ? NKR : a.ksl;
   float4* As = reinterpret_cast<float4*>(smem_raw);                                   // [CT/16][nk][hi | lo][32]
   float4* Bs = As + (size_t)(CT / 16) * nk * 64;                                      // stages x [16][ksl][32]
@@ -477,16 +477,23 @@ __global__ void __launch_bounds__(256) bound_pack_kernel(const double* __restric
 // tcgen05 variant of the bound kernel (D <= 32): the 3xTF32 distance contraction runs on the 5th-generation tensor cores
 // (tcgen05.mma kind::tf32, issued by one thread, accumulators in TMEM) instead of in the warps' own instruction stream
 // (mma.sync = legacy HMMA, 2.25 of the 18.4 instructions per 32 kernel evaluations above, and a pipe that was 41 % busy).
-//   CTA = 10 warps: warp 0 streams the observation chunks (bulk async copies), warp 1 allocates TMEM and issues the
-//   MMAs, warps 2..9 evaluate: an accumulator block is 128 candidates (TMEM lanes) x 256 observations (TMEM columns),
-//   double-buffered over the 512 columns; each evaluating thread owns ONE candidate (its TMEM lane) and 128 of the 256
+//   CTA = 18 warps: warp 0 streams the observation chunks (bulk async copies), warp 1 allocates TMEM and issues the
+//   MMAs, warps 2..17 evaluate: an accumulator block is 128 candidates (TMEM lanes) x 256 observations (TMEM columns),
+//   double-buffered over the 512 columns; each evaluating thread owns ONE candidate (its TMEM lane) and 64 of the 256
 //   columns, reads them 32 at a time with tcgen05.ld and keeps mu / S / k_max of its candidate in registers.
+//   (Tried: staging the next candidate tile into a second A buffer two chunks before the end of the current one, so
+//   that the MMA warp never drains -- 1.46 -> 1.68 ms at cfg2: the evaluating warps are the bottleneck and the
+//   staging in mid-stream stalls both accumulator blocks; dropped.)
 //   Operands are in the UMMA canonical K-major no-swizzle layout: 8-row x 16-byte core matrices, SBO = 128 B between
 //   8-row groups, LBO = bytes between the two 16-byte K chunks of a k-step.
 #define TC_CT 128             // candidates per tile = TMEM lanes
 #define TC_OBC 256            // observations per chunk = accumulator columns
 #define TC_STAGES 3
-#define TC_EPI_WARPS 8
+#ifndef TC_EPI_WARPS
+#define TC_EPI_WARPS 16          // evaluating warps: 4 TMEM lane quarters x TC_CG column groups (8 warps: 1.58 ms at cfg2, 16: 1.46)
+#endif
+#define TC_CG (TC_EPI_WARPS / 4)   // column groups of an accumulator block
+#define TC_CW (TC_OBC / TC_CG)     // columns per evaluating thread and chunk
 #define TC_THREADS ((2 + TC_EPI_WARPS) * 32)
 
 struct bound_tc_args {
@@ -530,7 +537,7 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
 
 __host__ __device__ inline size_t bound_tc_smem_bytes(int nk, int ksl, int stages) {
   return 1024 + (size_t)nk * 8192 /* A hi + lo */ + (size_t)stages * ksl * 16384 /* B stages */ + TC_CT * 8 /* cc */ +
-         (size_t)3 * 2 * TC_CT * 8 /* mu, S, kmax of the two column halves */ + 256;
+         (size_t)3 * TC_CG * TC_CT * 8 /* mu, S, kmax of the column groups */ + 256;
 }
 
 template <int KIND>
@@ -543,8 +550,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) bound_tc_kernel(bound_tc_args t
   float* Bst = Alo + (size_t)nk * 1024;                     // stages x ([B hi | B lo] = 2 * 2048 ksl floats)
   const int n_st = ta.stages, ksl = ta.ksl, n_sl = ta.n_slices;
   double* cc = reinterpret_cast<double*>(Bst + (size_t)n_st * ksl * 4096);
-  double* red = cc + TC_CT;                                 // [3][2][TC_CT]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(red + 3 * 2 * TC_CT);
+  double* red = cc + TC_CT;                                 // [3][TC_CG][TC_CT]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(red + 3 * TC_CG * TC_CT);
   uint64_t* full = bars;                  // [TC_STAGES] B stage landed
   uint64_t* empty = full + TC_STAGES;     // [TC_STAGES] B stage consumed by the MMAs
   uint64_t* tfull = empty + TC_STAGES;    // [2] accumulator block complete
@@ -618,19 +625,20 @@ __global__ void __launch_bounds__(TC_THREADS, 1) bound_tc_kernel(bound_tc_args t
     }
   } else {
     // ---- evaluating warps
-    const int ew = warp - 2;                    // 0..7
-    const int q = warp & 3, half = ew >> 2;     // TMEM lane quarter of this warp (hardware: warp index mod 4), column half
+    const int ew = warp - 2;                    // 0 .. TC_EPI_WARPS - 1
+    const int q = warp & 3, half = ew >> 2;     // TMEM lane quarter of this warp (hardware: warp index mod 4), column group
     const int row = q * 32 + lane;              // candidate of this thread inside the tile
-    const int et = ew * 32 + lane;              // 0..255
+    const int et = ew * 32 + lane;
     uint32_t ch = 0;
     for (long long tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
       const long long row0 = tile * TC_CT;
-      {  // stage the tile: two threads per candidate row (even / odd columns)
-        const int r = et >> 1, part = et & 1;
+      {  // stage the tile: TPR threads per candidate row (columns part, part + TPR, ...)
+        constexpr int TPR = TC_EPI_WARPS * 32 / TC_CT;
+        const int r = et / TPR, part = et % TPR;
         const bool live = row0 + r < a.M;
         const double* src = a.cand + (size_t)(row0 + r) * a.ldc;
         double acc = 0.0;
-        for (int d = part; d < nk * 8; d += 2) {
+        for (int d = part; d < nk * 8; d += TPR) {
           double u = 0.0;
           if (live && d < a.D) u = a.scale * src[d] / a.ls[d];
           acc = fma(u, u, acc);
@@ -641,7 +649,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) bound_tc_kernel(bound_tc_args t
           Ahi[idx] = __uint_as_float(hi);
           Alo[idx] = __uint_as_float(lo);
         }
-        acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+#pragma unroll
+        for (int o = 1; o < TPR; o <<= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
         if (part == 0) cc[r] = acc;
       }
       fence_proxy_async();   // generic-proxy writes of A -> the tensor core's (async proxy) reads
@@ -654,12 +663,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) bound_tc_kernel(bound_tc_args t
         const int as = ch & 1;
         mbar_wait(&tfull[as], (ch >> 1) & 1);
         tc_fence_after();
-        const float4* axp = ta.aux2 + (size_t)c * (TC_OBC / 2) + half * 64;
+        const float4* axp = ta.aux2 + (size_t)c * (TC_OBC / 2) + half * (TC_CW / 2);
         float mu32 = 0.f, s32 = 0.f;
 #pragma unroll 1
-        for (int sub = 0; sub < 4; ++sub) {
+        for (int sub = 0; sub < TC_CW / 32; ++sub) {
           float g[32];
-          tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * TC_OBC + half * 128 + sub * 32), g);
+          tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * TC_OBC + half * TC_CW + sub * 32), g);
 #pragma unroll
           for (int j = 0; j < 32; j += 2) {
             const float4 ax = __ldg(axp + sub * 16 + (j >> 1));   // {xx, alpha} of two observations: one address per warp
@@ -679,14 +688,18 @@ __global__ void __launch_bounds__(TC_THREADS, 1) bound_tc_kernel(bound_tc_args t
         mu64 += (double)mu32;
         s64 += (double)s32;
       }
-      red[(0 * 2 + half) * TC_CT + row] = mu64;
-      red[(1 * 2 + half) * TC_CT + row] = s64;
-      red[(2 * 2 + half) * TC_CT + row] = (double)kmx;
+      red[(0 * TC_CG + half) * TC_CT + row] = mu64;
+      red[(1 * TC_CG + half) * TC_CT + row] = s64;
+      red[(2 * TC_CG + half) * TC_CT + row] = (double)kmx;
       asm volatile("bar.sync 1, %0;" ::"n"(TC_EPI_WARPS * 32) : "memory");
       if (half == 0 && row0 + row < a.M) {
-        const double m = red[0 * TC_CT + row] + red[1 * TC_CT + row];
-        const double sS = red[2 * TC_CT + row] + red[3 * TC_CT + row];
-        const double k = fmax(red[4 * TC_CT + row], red[5 * TC_CT + row]);
+        double m = 0.0, sS = 0.0, k = 0.0;
+#pragma unroll
+        for (int cg = 0; cg < TC_CG; ++cg) {
+          m += red[(0 * TC_CG + cg) * TC_CT + row];
+          sS += red[(1 * TC_CG + cg) * TC_CT + row];
+          k = fmax(k, red[(2 * TC_CG + cg) * TC_CT + row]);
+        }
         const double xm = *a.xx_max;
         const double rc = sqrt(cc[row]) + sqrt(xm);
         const double dT = a.g_T * rc * rc;
