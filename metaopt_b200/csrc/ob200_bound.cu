@@ -596,10 +596,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) bound_tc_kernel(bound_tc_args t
       const uint32_t a_hi = smem_u32(Ahi), a_lo = smem_u32(Alo);
       uint32_t it = 0, ch = 0, tl = 0;
       for (long long tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x, ++tl) {
-        mbar_wait(a_ready, tl & 1);
+        mbar_wait_backoff(a_ready, tl & 1);
         for (int c = 0; c < ta.n_chunks; ++c, ++ch) {
           const int as = ch & 1;
-          mbar_wait(&tempty[as], ((ch >> 1) & 1) ^ 1);
+          mbar_wait_backoff(&tempty[as], ((ch >> 1) & 1) ^ 1);   // long wait (the evaluating warps are the bottleneck): do not spin
           const uint32_t d = tmem_base + (uint32_t)as * TC_OBC;
           uint32_t acc = 0;
           for (int sl = 0; sl < n_sl; ++sl, ++it) {
