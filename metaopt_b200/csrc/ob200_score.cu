@@ -1258,6 +1258,7 @@ extern "C" int ob200_score_pruned_multi(ob200_ctx* ctx, const double* cand_dev, 
     if (escalate_at >= 0 && standing > escalate_at && ctx->hdr.n > PR_SUBSET_M) {
       if ((rc = ensure_subset_fit(ctx))) return rc;
       ob200_ctx* sub = ctx->sub;
+      sub->stream = ctx->stream;   // (the caller may have moved the context to another stream since the subset fit was made)
       l2_scope l2s(sub);
       int gs = 0;
       double* sig_s = ub3 + 2 * M;   // (the utility bounds of pass 1 are not needed any more: ub3 = refined mu | sigma | this)
