@@ -613,21 +613,19 @@ def bench_other_configs(torch, eng, comp2, rank, world, multi, dgemm, peaks, pea
     eng.sample(7, 0, 16, out=buf[:16], check=True)  # the latched status of the whole run surfaces here
     bytes5 = n_points * c5.d_out * 8
     gbs_per_gpu = bytes5 / world / ms5 / 1e6
-    traffic5 = None
-    for name in ("r2_sampler_ncu.json", "r1_sampler_ncu.json"):
-        p = os.path.join(ROOT, "profiles", name)
-        if os.path.exists(p):
-            try:
-                j = json.load(open(p))
-                traffic5 = j.get("dram_bytes_per_launch")
-                break
-            except Exception:
-                pass
+    traffic5 = None   # DRAM bytes per launch (one 2^24-point chunk), scaled from the ncu capture's bytes per point
+    tp = os.path.join(ROOT, "profiles", "sampler_traffic.json")
+    if os.path.exists(tp):
+        try:
+            traffic5 = float(json.load(open(tp))["dram_bytes_per_point"]) * min(chunk, p_count)
+        except Exception:
+            traffic5 = None
     out["cfg5"] = {"workload": "cfg5: Space.sample + transform + normalise, 50-D mixed space (17 Real, 17 Integer, 16 Categorical "
                                "k=4) -> 98 float64 columns, 1e9 points over %d GPU(s) in chunks of 2^24" % world,
                    "points": n_points, "ms": ms5, "points_per_s": n_points / ms5 * 1e3,
                    "roofline": {"bound": "hbm", "achieved": gbs_per_gpu, "peak": hbm, "unit": "GB/s", "frac": gbs_per_gpu / hbm,
                                 "traffic": traffic5, "kernel": "sample_transform_kernel", "bytes_per_point": c5.d_out * 8,
+                                "algorithmic_bytes_per_launch": c5.d_out * 8 * min(chunk, p_count),
                                 "per": "GPU", "peak_source": peak_src}}
     del buf
     # ---- cfg3 / cfg4 shape: dense scoring, candidates generated on the device inside the timed call ------------------
