@@ -134,7 +134,7 @@ struct gemm_args {
   int m_last, k_eq_m;  // k_eq_m: K follows the batch entry's M (TRTRI second product)
   double alpha, beta;
   int lower_only;
-  int tri_k;  // both operands lower triangular: only k in [64*tn, 64*(tm+1)) contributes
+  int tri_k;  // bit 0: B is lower triangular, k starts at 64*tn; bit 1: A is lower triangular, k ends at 64*(tm+1); 3: both
 };
 
 template <bool TRANS_B>
@@ -161,8 +161,8 @@ __global__ void __launch_bounds__(128) gemm64_kernel(gemm_args g) {
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
 
-  const int k_begin = g.tri_k ? tn * 64 : 0;
-  if (g.tri_k) { const int k_end = (tm + 1) * 64; if (k_end < K) K = k_end; }
+  const int k_begin = (g.tri_k & 1) ? tn * 64 : 0;
+  if (g.tri_k & 2) { const int k_end = (tm + 1) * 64; if (k_end < K) K = k_end; }
   for (int k0 = k_begin; k0 < K; k0 += GEMM_BK) {
     {  // A tile 64 x 16: thread -> row tid/2, 8 contiguous doubles
       const int r = tid >> 1, c = (tid & 1) * 8;
@@ -1137,13 +1137,10 @@ int fit_impl(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n, in
   if (trail_pending) OB_CUDA(ctx, cudaStreamWaitEvent(st, ctx->ev_trail, 0));
   chol_copy_diag_kernel<<<nb, 256, 0, st>>>(Lm, n_pad, Lfac);
   OB_LAUNCH_CHECK(ctx);
+  // The pivot check is read back with the header at the end of the fit (one host round trip per fit instead of two);
+  // a failed factorisation only costs the NaN-filled remainder of a fit that is discarded anyway.
   int info = 0;
   OB_CUDA(ctx, cudaMemcpyAsync(&info, info_dev, sizeof(int), cudaMemcpyDeviceToHost, st));
-  OB_CUDA(ctx, cudaStreamSynchronize(st));
-  if (info != 0)
-    OB_FAIL(ctx, OB200_ENOTSPD,
-            "The kernel is not returning a positive definite matrix (pivot %d of %d). Try gradually increasing the 'alpha' "
-            "parameter of your GaussianProcessRegressor estimator.", info, n);
 
   const bool serial_solve = getenv("OB200_SERIAL_SOLVE") != nullptr;  // (testing hook: the substitution-based solve)
   if (serial_solve) {
@@ -1165,13 +1162,13 @@ int fit_impl(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n, in
     g1.A = Lm + (size_t)s * n_pad; g1.lda = n_pad; g1.strideA = stride;
     g1.B = Xinv; g1.ldb = n_pad; g1.strideB = stride;
     g1.C = T; g1.ldc = s; g1.strideC = (long long)s * s;
-    g1.M = s; g1.N = s; g1.K = s; g1.m_last = c_last; g1.alpha = 1.0; g1.beta = 0.0;
+    g1.M = s; g1.N = s; g1.K = s; g1.m_last = c_last; g1.alpha = 1.0; g1.beta = 0.0; g1.tri_k = 1;   // X[lo:mid, lo:mid] is lower triangular
     if ((rc = launch_gemm(ctx, false, g1, pairs))) return rc;
     gemm_args g2{};  // X[mid:hi, lo:mid] = -X[mid:hi, mid:hi] * T_z
     g2.A = Xinv + (size_t)s * n_pad + s; g2.lda = n_pad; g2.strideA = stride;
     g2.B = T; g2.ldb = s; g2.strideB = (long long)s * s;
     g2.C = Xinv + (size_t)s * n_pad; g2.ldc = n_pad; g2.strideC = stride;
-    g2.M = s; g2.N = s; g2.K = s; g2.m_last = c_last; g2.k_eq_m = 1; g2.alpha = -1.0; g2.beta = 0.0;
+    g2.M = s; g2.N = s; g2.K = s; g2.m_last = c_last; g2.k_eq_m = 1; g2.alpha = -1.0; g2.beta = 0.0; g2.tri_k = 2;   // so is X[mid:hi, mid:hi]
     if ((rc = launch_gemm(ctx, false, g2, pairs))) return rc;
   }
   mark();
@@ -1181,21 +1178,22 @@ int fit_impl(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n, in
   if (!search && !getenv("OB200_NO_NS")) {  // (testing hook: measure what the refinement buys)
     gemm_args r{};  // T = L X  (lower x lower -> lower tiles, triangular k range)
     r.A = Lm; r.lda = n_pad; r.B = Xinv; r.ldb = n_pad; r.C = T; r.ldc = n_pad;
-    r.M = n_pad; r.N = n_pad; r.K = n_pad; r.alpha = 1.0; r.beta = 0.0; r.lower_only = 1; r.tri_k = 1;
+    r.M = n_pad; r.N = n_pad; r.K = n_pad; r.alpha = 1.0; r.beta = 0.0; r.lower_only = 1; r.tri_k = 3;
     if ((rc = launch_gemm(ctx, false, r, 1))) return rc;
     eye_minus_lower_kernel<<<dim3(n_pad / 32, n_pad / 32), 256, 0, st>>>(T, n_pad);
     OB_LAUNCH_CHECK(ctx);
     OB_CUDA(ctx, cudaMemcpyAsync(X2, Xinv, (size_t)n_pad * n_pad * 8, cudaMemcpyDeviceToDevice, st));
     gemm_args u{};  // X2 = X + X T
     u.A = Xinv; u.lda = n_pad; u.B = T; u.ldb = n_pad; u.C = X2; u.ldc = n_pad;
-    u.M = n_pad; u.N = n_pad; u.K = n_pad; u.alpha = 1.0; u.beta = 1.0; u.lower_only = 1; u.tri_k = 1;
+    u.M = n_pad; u.N = n_pad; u.K = n_pad; u.alpha = 1.0; u.beta = 1.0; u.lower_only = 1; u.tri_k = 3;
     if ((rc = launch_gemm(ctx, false, u, 1))) return rc;
     OB_CUDA(ctx, cudaMemcpyAsync(Xinv, X2, (size_t)n_pad * n_pad * 8, cudaMemcpyDeviceToDevice, st));
   }
   mark();
   // ---- alpha, lml (from the refined inverse factor; T is free again and serves as scratch) -----------------------
   if (!serial_solve) {
-    if ((rc = solve_alpha(ctx, Xinv, Lm, ynorm, n_pad, b_alpha, T, 2))) return rc;
+    // (a search evaluation takes one refinement step: the objective needs ~1e-10, not the last bits)
+    if ((rc = solve_alpha(ctx, Xinv, Lm, ynorm, n_pad, b_alpha, T, search ? 1 : 2))) return rc;
     append_lml_kernel<<<1, 1024, 0, st>>>(Lm, n_pad, n, ynorm, b_alpha, lml_dev);
     OB_LAUNCH_CHECK(ctx);
   }
@@ -1214,6 +1212,11 @@ int fit_impl(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n, in
   OB_LAUNCH_CHECK(ctx);
   OB_CUDA(ctx, cudaMemcpyAsync(&ctx->hdr, blob, sizeof(ob200_fit_header), cudaMemcpyDeviceToHost, st));
   OB_CUDA(ctx, cudaStreamSynchronize(st));
+  if (info != 0) {
+    OB_FAIL(ctx, OB200_ENOTSPD,
+            "The kernel is not returning a positive definite matrix (pivot %d of %d). Try gradually increasing the 'alpha' "
+            "parameter of your GaussianProcessRegressor estimator.", info, n);
+  }
   if (timing) {
     static const char* names[] = {"gram", "cholesky", "trtri", "newton-schulz", "alpha+lml", "pack"};
     float ms = 0.f;
