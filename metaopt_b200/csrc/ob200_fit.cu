@@ -163,25 +163,28 @@ __global__ void __launch_bounds__(128) gemm64_kernel(gemm_args g) {
 
   const int k_begin = (g.tri_k & 1) ? tn * 64 : 0;
   if (g.tri_k & 2) { const int k_end = (tm + 1) * 64; if (k_end < K) K = k_end; }
+  // The next K slab is fetched into registers while the current one is multiplied: at the one or two CTAs per SM the
+  // fit's GEMMs have, the loop is bound by the latency of these loads.
+  const int ar = tid >> 1, ac = (tid & 1) * 8;                          // A tile 64 x 16: row tid/2, 8 contiguous doubles
+  const int br = TRANS_B ? ar : (tid >> 3), bc = TRANS_B ? ac : (tid & 7) * 8;
+  const double* a_src = A + (size_t)ar * g.lda + ac;
+  const double* b_src = TRANS_B ? B + (size_t)br * g.ldb + bc : B + (size_t)br * g.ldb + bc;
+  double2 ra[4], rb[4];
+  auto fetch = [&](int k0) {
+    const double2* pa = reinterpret_cast<const double2*>(a_src + k0);
+    const double2* pb = reinterpret_cast<const double2*>(TRANS_B ? b_src + k0 : b_src + (size_t)k0 * g.ldb);
+#pragma unroll
+    for (int v = 0; v < 4; ++v) { ra[v] = pa[v]; rb[v] = pb[v]; }
+  };
+  if (k_begin < K) fetch(k_begin);
   for (int k0 = k_begin; k0 < K; k0 += GEMM_BK) {
-    {  // A tile 64 x 16: thread -> row tid/2, 8 contiguous doubles
-      const int r = tid >> 1, c = (tid & 1) * 8;
-      const double2* src = reinterpret_cast<const double2*>(A + (size_t)r * g.lda + k0 + c);
 #pragma unroll
-      for (int v = 0; v < 4; ++v) { double2 t = src[v]; As[r][c + 2 * v] = t.x; As[r][c + 2 * v + 1] = t.y; }
-    }
-    if (TRANS_B) {
-      const int r = tid >> 1, c = (tid & 1) * 8;
-      const double2* src = reinterpret_cast<const double2*>(B + (size_t)r * g.ldb + k0 + c);
-#pragma unroll
-      for (int v = 0; v < 4; ++v) { double2 t = src[v]; Bs[r][c + 2 * v] = t.x; Bs[r][c + 2 * v + 1] = t.y; }
-    } else {
-      const int r = tid >> 3, c = (tid & 7) * 8;
-      const double2* src = reinterpret_cast<const double2*>(B + (size_t)(k0 + r) * g.ldb + c);
-#pragma unroll
-      for (int v = 0; v < 4; ++v) { double2 t = src[v]; Bs[r][c + 2 * v] = t.x; Bs[r][c + 2 * v + 1] = t.y; }
+    for (int v = 0; v < 4; ++v) {
+      As[ar][ac + 2 * v] = ra[v].x; As[ar][ac + 2 * v + 1] = ra[v].y;
+      Bs[br][bc + 2 * v] = rb[v].x; Bs[br][bc + 2 * v + 1] = rb[v].y;
     }
     __syncthreads();
+    if (k0 + GEMM_BK < K) fetch(k0 + GEMM_BK);
 #pragma unroll
     for (int kk = 0; kk < GEMM_BK; kk += 4) {
       double a[4], b[4];
