@@ -653,7 +653,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) bound_tc_kernel(bound_tc_args t
         for (int o = 1; o < TPR; o <<= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
         if (part == 0) cc[r] = acc;
       }
-      fence_proxy_async();   // generic-proxy writes of A -> the tensor core's (async proxy) reads
+      fence_proxy_async_smem();   // generic-proxy writes of A -> the tensor core's (async proxy) reads
       asm volatile("bar.sync 1, %0;" ::"n"(TC_EPI_WARPS * 32) : "memory");
       if (lane == 0) mbar_arrive(a_ready);
       const float ccr = (float)cc[row];

@@ -246,6 +246,9 @@ __device__ __forceinline__ void bulk_wait_read1() {
 }
 __device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async;" ::: "memory"); }
+// The same for shared memory only (generic-proxy writes to this CTA's shared memory -> async-proxy reads of it): without the
+// state space the fence covers global memory too and ptxas puts a MEMBAR.ALL.GPU in front of it.
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 // ---- Philox4x32-10 (Salmon et al. 2011); restated bit-for-bit in oracle/philox.py -----------
 struct philox_out { uint32_t r0, r1, r2, r3; };

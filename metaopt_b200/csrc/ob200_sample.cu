@@ -336,6 +336,7 @@ sample_transform_kernel(const dslot* __restrict__ slots_g, int n_dslots, int n_n
   const uint32_t row_bytes = (uint32_t)d_out * 8u;
 
   int buf = 0;
+  int q0 = warp;   // this warp's next item in the round-robin over (tile, row group, Philox call): carried across row groups and tiles
   for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x, buf ^= (ST_NBUF - 1)) {
     double* tile = tile0 + (size_t)buf * tile_elems;
     const uint32_t tile_sa = (uint32_t)__cvta_generic_to_shared(tile);
@@ -350,7 +351,6 @@ sample_transform_kernel(const dslot* __restrict__ slots_g, int n_dslots, int n_n
     // the wide calls (two 53-bit slots each) in two loops of their own, so that each loop's switch holds only its
     // operations and the call's words die right after the conversion (one common loop cost 9 registers and spilled)
     const int n_wide = n_items - n_quads;
-    int q0 = warp, w0 = warp;
     for (int rg = 0; rg < n_rg; ++rg) {
       const int r = rg * 32 + lane;
       row_ctx rc;
@@ -375,9 +375,8 @@ sample_transform_kernel(const dslot* __restrict__ slots_g, int n_dslots, int n_n
         ST_NARROW(sp, 4 * p, u0, u1)
         if (sp[2].op != OP_NONE) { ST_NARROW(sp + 2, 4 * p + 2, u2, u3) }
       }
-      q0 = p - n_quads;  // the round-robin continues into the next row group
 #undef ST_NARROW
-      p = w0;
+      p -= n_quads;  // the round-robin continues into the wide calls, the next row group and the next tile: an even load
       for (; p < n_wide; p += ST_THREADS / 32) {
         const int q = n_narrow + 2 * p;
         const dslot* sp = slots + q;
@@ -395,10 +394,10 @@ sample_transform_kernel(const dslot* __restrict__ slots_g, int n_dslots, int n_n
           default: pair_op<OP_NORMAL_INT, MODE>(sp, cdf, q, n_narrow, rc, rk, ua, ub, normalise, status, exp_tab); break;
         }
       }
-      w0 = p - n_wide;
+      q0 = p - n_wide;
     }
     if (bulk_ok) {
-      fence_proxy_async();  // generic-proxy smem writes -> async-proxy (TMA) reads
+      fence_proxy_async_smem();  // generic-proxy smem writes -> async-proxy (TMA) reads
 #if ST_NBUF == 2
       if (threadIdx.x == 0) bulk_wait_read0();  // the previous tile has left the other buffer (it had a whole tile's time)
 #endif
