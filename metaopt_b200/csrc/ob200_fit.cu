@@ -828,22 +828,30 @@ __global__ void __launch_bounds__(256) pg_v_kernel(const double* __restrict__ Xi
   if (lane == 0) V[(size_t)p * n_pad + i] = acc;
 }
 
-// w = inv(L)^T v = K^-1 k: 32 columns per CTA, 8 row groups walking down the rows (each row segment is one
-// coalesced 256 B read), fixed-order reduction over the groups.
+// w = inv(L)^T v = K^-1 k: 8 columns per CTA (n_pad / 8 CTAs: the 32-column version left half the SMs idle and walked
+// 264 dependent steps per thread), 32 row groups walking down the rows two at a time (each row segment is one 64 B
+// read), fixed-order reduction over the groups.
+#define PG_W_COLS 8
 __global__ void __launch_bounds__(256) pg_w_kernel(const double* __restrict__ Xinv, const double* __restrict__ V, int n_pad,
                                                    double* __restrict__ Wv) {
-  __shared__ double part[8][33];
-  const int c = threadIdx.x & 31, g = threadIdx.x >> 5, j0 = blockIdx.x * 32, j = j0 + c, p = blockIdx.y;
+  __shared__ double part[32][PG_W_COLS + 1];
+  const int c = threadIdx.x & (PG_W_COLS - 1), g = threadIdx.x / PG_W_COLS, j0 = blockIdx.x * PG_W_COLS, j = j0 + c, p = blockIdx.y;
   const double* v = V + (size_t)p * n_pad;
-  double acc = 0.0;
-  if (j < n_pad)
-    for (int i = j0 + g; i < n_pad; i += 8)
-      if (i >= j) acc = fma(Xinv[(size_t)i * n_pad + j], v[i], acc);
-  part[g][c] = acc;
+  double acc0 = 0.0, acc1 = 0.0;
+  if (j < n_pad) {
+    int i = j0 + g;
+    for (; i + 32 < n_pad; i += 64) {
+      const double x0 = Xinv[(size_t)i * n_pad + j], x1 = Xinv[(size_t)(i + 32) * n_pad + j];
+      if (i >= j) acc0 = fma(x0, v[i], acc0);
+      acc1 = fma(x1, v[i + 32], acc1);   // i + 32 >= j0 + 32 > j
+    }
+    if (i < n_pad && i >= j) acc0 = fma(Xinv[(size_t)i * n_pad + j], v[i], acc0);
+  }
+  part[g][c] = acc0 + acc1;
   __syncthreads();
   if (g == 0 && j < n_pad) {
     double t = 0.0;
-    for (int k = 0; k < 8; ++k) t += part[k][c];
+    for (int k = 0; k < 32; ++k) t += part[k][c];
     Wv[(size_t)p * n_pad + j] = t;
   }
 }
@@ -976,7 +984,7 @@ int solve_alpha(ob200_ctx* ctx, const double* Xinv, const double* L, const doubl
                 int refine) {
   cudaStream_t st = ctx->stream;
   double *t = scratch, *r = scratch + n_pad, *d = scratch + 2 * (size_t)n_pad;
-  const dim3 gv((n_pad * 32 + 255) / 256, 1), gw((n_pad + 31) / 32, 1);
+  const dim3 gv((n_pad * 32 + 255) / 256, 1), gw((n_pad + PG_W_COLS - 1) / PG_W_COLS, 1);
   const int gb = (n_pad + 255) / 256;
   pg_v_kernel<<<gv, 256, 0, st>>>(Xinv, y, n_pad, t);
   OB_LAUNCH_CHECK(ctx);
@@ -1350,7 +1358,7 @@ int ob200_gp_predict_grad_host(ob200_ctx* ctx, const double* x_host, int64_t ldx
   OB_LAUNCH_CHECK(ctx);
   pg_v_kernel<<<dim3((n_pad * 32 + 255) / 256, m), 256, 0, st>>>(Xinv, P + p_K, n_pad, P + p_V);
   OB_LAUNCH_CHECK(ctx);
-  pg_w_kernel<<<dim3((n_pad + 31) / 32, m), 256, 0, st>>>(Xinv, P + p_V, n_pad, P + p_W);
+  pg_w_kernel<<<dim3((n_pad + PG_W_COLS - 1) / PG_W_COLS, m), 256, 0, st>>>(Xinv, P + p_V, n_pad, P + p_W);
   OB_LAUNCH_CHECK(ctx);
   pg_final_kernel<<<m, 256, 0, st>>>(P + p_xs, ls, Xs, alpha, P + p_K, P + p_G, P + p_V, P + p_W, n, n_pad, D, D_pad,
                                      ctx->hdr.amplitude, ctx->hdr.y_mean, ctx->hdr.y_std, P + p_out);
@@ -1394,7 +1402,7 @@ int ob200_gp_append(ob200_ctx* ctx, const double* x_new_dev, const double* y_dev
   OB_LAUNCH_CHECK(ctx);
   append_diag_kernel<<<1, 1024, 0, st>>>(lvec, n, n_pad, ctx->hdr.amplitude + ctx->fit_alpha, ctx->L_dev, scal, info_dev);
   OB_LAUNCH_CHECK(ctx);
-  pg_w_kernel<<<dim3((n_pad + 31) / 32, 1), 256, 0, st>>>(Xinv, lvec, n_pad, wvec);         // w = inv(L)^T l
+  pg_w_kernel<<<dim3((n_pad + PG_W_COLS - 1) / PG_W_COLS, 1), 256, 0, st>>>(Xinv, lvec, n_pad, wvec);         // w = inv(L)^T l
   OB_LAUNCH_CHECK(ctx);
   append_row_kernel<<<(n + 256) / 256, 256, 0, st>>>(wvec, scal, n, n_pad, Xinv);
   OB_LAUNCH_CHECK(ctx);
