@@ -643,7 +643,11 @@ def bench_other_configs(torch, eng, comp2, rank, world, multi, dgemm, peaks, pea
         t0 = time.perf_counter()
         eng.fit(Xo, yo, alpha=ALPHA + NOISE, normalize_y=True)
         eng.sync()
-        fit_ms = (time.perf_counter() - t0) * 1e3
+        fit_first_ms = (time.perf_counter() - t0) * 1e3   # includes growing the context's workspaces to this size
+        t0 = time.perf_counter()
+        eng.fit(Xo, yo, alpha=ALPHA + NOISE, normalize_y=True)
+        eng.sync()
+        fit_ms = (time.perf_counter() - t0) * 1e3         # host arrays in, factor + inverse + alpha on the device
         yo_opt = float(yo.min())
         s0, _ = obdist.shard_range(m_gpu * world, rank, world)
         eng.score(None, M=20_000, seed=5, first_index=s0, acq_mask=1, y_opt=yo_opt)
@@ -661,7 +665,7 @@ def bench_other_configs(torch, eng, comp2, rank, world, multi, dgemm, peaks, pea
         d = c.d_out
         tfl = m_gpu * flops_per_candidate(nobs, d) / ms / 1e9
         out[tag] = {"workload": label, "n_obs": nobs, "D": d, "candidates_per_gpu": m_gpu, "candidates_total": m_gpu * world,
-                    "ms": ms, "candidates_per_s": m_gpu * world / ms * 1e3, "fit_ms": fit_ms,
+                    "ms": ms, "candidates_per_s": m_gpu * world / ms * 1e3, "fit_ms": fit_ms, "fit_first_call_ms": fit_first_ms,
                     "includes": "Philox candidate generation + transform + normalise inside the timed call",
                     "roofline": {"bound": "tensor", "achieved": tfl, "peak": dgemm, "unit": "TFLOP/s",
                                  "frac": tfl / dgemm if dgemm else None, "per": "GPU", "flops_per_candidate": flops_per_candidate(nobs, d),

@@ -77,6 +77,8 @@ void ob200_ctx_destroy(ob200_ctx* ctx) {
   if (ctx->fit_stream) cudaStreamDestroy(ctx->fit_stream);
   if (ctx->ev_panel) cudaEventDestroy(ctx->ev_panel);
   if (ctx->ev_trail) cudaEventDestroy(ctx->ev_trail);
+  if (ctx->fit_stream2) cudaStreamDestroy(ctx->fit_stream2);
+  if (ctx->ev_diag) cudaEventDestroy(ctx->ev_diag);
   if (ctx->ev_main) cudaEventDestroy(ctx->ev_main);
   if (ctx->ev_copy) cudaEventDestroy(ctx->ev_copy);
   if (ctx->best_pinned) cudaFreeHost(ctx->best_pinned);

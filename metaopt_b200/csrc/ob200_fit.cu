@@ -502,6 +502,184 @@ __global__ void __launch_bounds__(256) chol_step_compact_kernel(double* __restri
   }
 }
 
+// ---- the step split in two: diagonal block / panel ------------------------------------------------------------------
+// The factorisation of the 64 x 64 diagonal block is a serial chain (~8 us) that every CTA of the fused step kernel
+// repeats before it can touch its panel rows.  Split off, it runs as ONE CTA beside the GEMM that updates the rest of the
+// next block column (it applies that update to the diagonal tile itself), and the panel kernel starts from the finished
+// factor: the chain leaves the critical path of the step.
+//
+// chol_diag_kernel: S = A[kb, kb] - P P^T (P = the previous panel's 64 x 64 block in these rows; kb = 0: no update),
+// factor as in chol_step_compact_kernel, factor -> Lfac[kb], reciprocal pivots -> Rd[kb].
+__global__ void __launch_bounds__(256) chol_diag_kernel(const double* __restrict__ A, int ld, int kb, double* __restrict__ Lfac,
+                                                        double* __restrict__ Rd, int* __restrict__ info) {
+  extern __shared__ double diag_sm[];
+  double* S = diag_sm;                 // [FB][FBS]
+  double* W = diag_sm + FB * FBS;      // [FB][WS] P
+  __shared__ double rdiag[FB];
+  __shared__ int bad;
+  const double* blk = A + (size_t)kb * FB * ld + (size_t)kb * FB;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  for (int e = tid; e < FB * FB; e += 256) { const int r = e >> 6, c = e & 63; S[r * FBS + c] = (c <= r) ? blk[(size_t)r * ld + c] : 0.0; }
+  if (kb > 0) {
+    const double* P = blk - FB;
+    for (int e = tid; e < FB * FB; e += 256) { const int r = e >> 6, c = e & 63; W[r * WS + c] = P[(size_t)r * ld + c]; }
+  }
+  if (tid == 0) bad = 0;
+  __syncthreads();
+  if (*info != 0) return;  // an earlier step already failed
+#ifdef FIT_DEBUG_SKIP_DIAG_UPDATE   // timing experiment only
+  if (false) {
+#else
+  if (kb > 0) {
+#endif
+    // thread (ri, cj) owns the elements (ri + 16 u, cj + 16 v), v <= u (the others lie above the diagonal): rows of P are
+    // read at stride 16, conflict-free with the odd row stride WS
+    const int ri = tid >> 4, cj = tid & 15;
+    double acc[4][4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+#pragma unroll
+      for (int v = 0; v < 4; ++v) acc[u][v] = 0.0;
+    for (int c = 0; c < FB; ++c) {
+      double a[4], b[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) { a[u] = W[(ri + 16 * u) * WS + c]; b[u] = W[(cj + 16 * u) * WS + c]; }
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+#pragma unroll
+        for (int v = 0; v <= u; ++v) acc[u][v] = fma(a[u], b[v], acc[u][v]);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+#pragma unroll
+      for (int v = 0; v <= u; ++v)
+        if (cj + 16 * v <= ri + 16 * u) S[(ri + 16 * u) * FBS + cj + 16 * v] -= acc[u][v];
+    __syncthreads();
+  }
+#ifdef FIT_DEBUG_SKIP_DIAG_FACTOR   // timing experiment only
+  if (tid < FB) rdiag[tid] = 1.0;
+  for (int c0 = FB; c0 < FB; c0 += SB) {
+#else
+  for (int c0 = 0; c0 < FB; c0 += SB) {
+#endif
+    if (warp == 0) {
+      const int r = lane & 15;
+      double a[SB];
+#pragma unroll
+      for (int k = 0; k < SB; ++k) a[k] = S[(c0 + r) * FBS + c0 + k];
+      int fail = 0;
+#pragma unroll
+      for (int j = 0; j < SB; ++j) {
+        double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+        for (int k = 0; k < j; ++k) {
+          const double l = S[(c0 + j) * FBS + c0 + k];
+          if (k & 1) s1 = fma(a[k], l, s1); else s0 = fma(a[k], l, s0);
+        }
+        const double v = a[j] - (s0 + s1);
+        const double piv = __shfl_sync(0xffffffffu, v, j);
+        if (!(piv > 0.0) && !fail) fail = c0 + j + 1;
+        const double rd = (piv > 1e-30 && piv < 1e30) ? rsqrt_pos(piv) : 1.0 / sqrt(piv);
+        a[j] = (r == j) ? piv * rd : v * rd;
+        if (lane < SB && r >= j) S[(c0 + r) * FBS + c0 + j] = a[j];
+        if (lane == j) rdiag[c0 + j] = rd;
+        __syncwarp();
+      }
+      if (fail && lane == 0) bad = fail;
+    }
+    __syncthreads();
+    if (bad) break;
+    const int below = FB - (c0 + SB);
+    if (tid < below) {
+      const int i = c0 + SB + tid;
+      double x[SB];
+#pragma unroll
+      for (int k = 0; k < SB; ++k) x[k] = S[i * FBS + c0 + k];
+      subst16(S, rdiag, c0, x);
+#pragma unroll
+      for (int k = 0; k < SB; ++k) S[i * FBS + c0 + k] = x[k];
+    }
+    __syncthreads();
+    for (int e = tid; e < below * below; e += 256) {
+      const int ii = e / below, kk = e - ii * below;
+      if (kk > ii) continue;
+      const double* pi = S + (c0 + SB + ii) * FBS + c0;
+      const double* pk = S + (c0 + SB + kk) * FBS + c0;
+      double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+      for (int c = 0; c < SB; c += 2) { s0 = fma(pi[c], pk[c], s0); s1 = fma(pi[c + 1], pk[c + 1], s1); }
+      S[(c0 + SB + ii) * FBS + c0 + SB + kk] -= s0 + s1;
+    }
+    __syncthreads();
+  }
+  if (bad) { if (tid == 0) *info = kb * FB + bad; return; }
+  double* lf = Lfac + (size_t)kb * FB * FB;
+  for (int e = tid; e < FB * FB; e += 256) lf[e] = S[(e >> 6) * FBS + (e & 63)];
+  if (tid < FB) Rd[(size_t)kb * FB + tid] = rdiag[tid];
+}
+
+// chol_panel_kernel: X L11^T = A21 for the 64 rows of CTA blockIdx.x - 1, L11 and its reciprocal pivots from
+// chol_diag_kernel; CTA 0 solves for the identity: inv(L11)^T -> Dinv[kb].  The panel code of chol_step_compact_kernel.
+__global__ void __launch_bounds__(256) chol_panel_kernel(double* __restrict__ A, int ld, int kb, double* __restrict__ Dinv,
+                                                         const double* __restrict__ Lfac, const double* __restrict__ Rd,
+                                                         const int* __restrict__ info) {
+  extern __shared__ double diag_sm[];
+  double* S = diag_sm;                 // [FB][FBS] L11
+  double* W = diag_sm + FB * FBS;      // [FB][WS] panel tile (CTA 0: the identity, then inv(L11)^T)
+  __shared__ double rdiag[FB];
+  const int tid = threadIdx.x;
+  double* At = nullptr;
+  const double* lf = Lfac + (size_t)kb * FB * FB;
+  if (blockIdx.x > 0) {
+    At = A + (size_t)(kb + blockIdx.x) * FB * ld + (size_t)kb * FB;
+    for (int e = tid; e < FB * FB; e += 256) { const int r = e >> 6, c = e & 63; W[r * WS + c] = At[(size_t)r * ld + c]; }
+  } else {
+    for (int e = tid; e < FB * FB; e += 256) { const int r = e >> 6, c = e & 63; W[r * WS + c] = (r == c) ? 1.0 : 0.0; }
+  }
+  if (*info != 0) return;  // this or an earlier diagonal block failed (uniform: nothing below is reached by any thread)
+  for (int e = tid; e < FB * FB; e += 256) S[(e >> 6) * FBS + (e & 63)] = lf[e];
+  if (tid < FB) rdiag[tid] = Rd[(size_t)kb * FB + tid];
+  __syncthreads();
+#ifdef FIT_DEBUG_SKIP_PANEL_SOLVE   // timing experiment only
+  for (int c0 = FB; c0 < FB; c0 += SB) {
+#else
+  for (int c0 = 0; c0 < FB; c0 += SB) {
+#endif
+    if (tid < FB) {
+      double x[SB];
+#pragma unroll
+      for (int k = 0; k < SB; ++k) x[k] = W[tid * WS + c0 + k];
+      subst16(S, rdiag, c0, x);
+#pragma unroll
+      for (int k = 0; k < SB; ++k) W[tid * WS + c0 + k] = x[k];
+    }
+    __syncthreads();
+    const int right = FB - (c0 + SB);
+    for (int e = tid; e < FB * right; e += 256) {
+      const int r = e & 63, cc = c0 + SB + (e >> 6);
+      const double* xr = W + r * WS + c0;
+      const double* lc = S + cc * FBS + c0;
+      double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+      for (int c = 0; c < SB; c += 2) { s0 = fma(xr[c], lc[c], s0); s1 = fma(xr[c + 1], lc[c + 1], s1); }
+      W[r * WS + cc] -= s0 + s1;
+    }
+    __syncthreads();
+  }
+  if (blockIdx.x == 0) {
+    double* dinv = Dinv + (size_t)kb * FB * FB;
+    for (int e = tid; e < FB * FB; e += 256) {
+      const int r = e >> 6, c = e & 63;
+      dinv[e] = (c <= r) ? W[c * WS + r] : 0.0;   // inv(L11) = X^T, lower triangular
+    }
+  } else {
+    for (int e = tid; e < FB * FB; e += 256) {
+      const int r = e >> 6, c = e & 63;
+      At[(size_t)r * ld + c] = W[r * WS + c];
+    }
+  }
+}
+
 // the factored diagonal blocks (upper triangle zero) go into L after the last step
 __global__ void __launch_bounds__(256) chol_copy_diag_kernel(double* __restrict__ A, int ld, const double* __restrict__ Lfac) {
   const int kb = blockIdx.x;
@@ -1060,11 +1238,11 @@ int fit_impl(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n, in
   // workspace: X (n_pad^2) | T (n_pad^2 / 2) | Dinv (nb*64*64) | Xs (n_pad*D_pad) | y_norm | tvec | ls | stats(4) | info
   const int64_t w_X = 0, w_T = w_X + (int64_t)n_pad * n_pad, w_X2 = w_T + (int64_t)n_pad * n_pad, w_Dinv = w_X2 + (int64_t)n_pad * n_pad,
                 w_Lf = w_Dinv + (int64_t)nb * FB * FB, w_Xs = w_Lf + (int64_t)nb * FB * FB, w_y = w_Xs + (int64_t)n_pad * D_pad, w_t = w_y + n_pad,
-                w_ls = w_t + n_pad, w_stats = w_ls + D_pad, w_end = w_stats + 8;
+                w_ls = w_t + n_pad, w_stats = w_ls + D_pad, w_Rd = w_stats + 8, w_end = w_Rd + n_pad;
   if ((rc = ob_reserve(ctx, &ctx->work_dev, &ctx->work_cap, w_end))) return rc;
   double* W = ctx->work_dev;
   double *Xinv = W + w_X, *T = W + w_T, *X2 = W + w_X2, *Dinv = W + w_Dinv, *Lfac = W + w_Lf, *Xs = W + w_Xs, *ynorm = W + w_y, *tvec = W + w_t,
-         *ls_dev = W + w_ls, *stats = W + w_stats;
+         *ls_dev = W + w_ls, *stats = W + w_stats, *Rd = W + w_Rd;
   int* info_dev = reinterpret_cast<int*>(stats + 6);
   double* lml_dev = stats + 4;
   cudaStream_t st = ctx->stream;
@@ -1106,16 +1284,73 @@ int fit_impl(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n, in
   const size_t diag_smem = (size_t)2 * FB * (FB + 2) * sizeof(double);
   OB_CUDA(ctx, cudaFuncSetAttribute(chol_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)diag_smem));
   const bool compact_step = getenv("OB200_FIT_UNROLLED_STEP") == nullptr;   // (testing hook: the fully unrolled step kernel of round 2a)
+  // (testing hooks: the fused step kernels -- diagonal block factored inside every CTA of the step -- and their schedule)
+  const bool split_step = compact_step && getenv("OB200_FIT_FUSED_STEP") == nullptr;
   if (!ctx->fit_stream) {
     OB_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->fit_stream, cudaStreamNonBlocking));
+    OB_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->fit_stream2, cudaStreamNonBlocking));
     OB_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_panel, cudaEventDisableTiming));
     OB_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_trail, cudaEventDisableTiming));
+    OB_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_diag, cudaEventDisableTiming));
   }
-  cudaStream_t side = ctx->fit_stream;
+  cudaStream_t side = ctx->fit_stream, side2 = ctx->fit_stream2;
   const bool lookahead = getenv("OB200_FIT_NO_LOOKAHEAD") == nullptr;   // (testing hook: everything on one stream)
   bool trail_pending = false;
   const size_t step_smem = compact_step ? ((size_t)FB * (FB + 2) + (size_t)FB * (FB + 1)) * sizeof(double) : diag_smem;
-  if (compact_step) OB_CUDA(ctx, cudaFuncSetAttribute(chol_step_compact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)step_smem));
+  if (compact_step) {
+    OB_CUDA(ctx, cudaFuncSetAttribute(chol_step_compact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)step_smem));
+    OB_CUDA(ctx, cudaFuncSetAttribute(chol_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)step_smem));
+    OB_CUDA(ctx, cudaFuncSetAttribute(chol_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)step_smem));
+  }
+  if (split_step) {
+    // Per 64-column step: panel(kb) | then, side by side, diag(kb + 1) on its own stream (one CTA: the diagonal tile's
+    // update and factorisation) and GEMM (a') = the rest of block column kb + 1 on the main stream | panel(kb + 1).
+    // (b), the trailing update from block kb + 2 on, runs on the second stream as before; diag(kb + 1) and (a') of step
+    // kb wait for (b) of step kb - 1, which was the last to write their tiles.
+    chol_diag_kernel<<<1, 256, step_smem, st>>>(Lm, n_pad, 0, Lfac, Rd, info_dev);
+    OB_LAUNCH_CHECK(ctx);
+    for (int kb = 0; kb < nb; ++kb) {
+      const int rem = n_pad - (kb + 1) * FB;
+      chol_panel_kernel<<<1 + (rem > 0 ? rem / FB : 0), 256, step_smem, st>>>(Lm, n_pad, kb, Dinv, Lfac, Rd, info_dev);
+      OB_LAUNCH_CHECK(ctx);
+      if (rem <= 0) break;
+      const double* panel = Lm + (size_t)(kb + 1) * FB * n_pad + (size_t)kb * FB;
+      gemm_args a{};   // (a') block column kb + 1 below its diagonal tile: C[(kb+2):, kb+1] -= P[(kb+2):] P[kb+1]^T
+      a.A = panel + (size_t)FB * n_pad; a.lda = n_pad; a.B = panel; a.ldb = n_pad;
+      a.C = Lm + (size_t)(kb + 2) * FB * n_pad + (size_t)(kb + 1) * FB; a.ldc = n_pad;
+      a.M = rem - FB; a.N = FB; a.K = FB; a.alpha = -1.0; a.beta = 1.0; a.lower_only = 0;
+      gemm_args b = a;  // (b) the rest: rows and columns from block kb + 2
+      b.B = b.A;
+      b.C = Lm + (size_t)(kb + 2) * FB * n_pad + (size_t)(kb + 2) * FB;
+      b.N = rem - FB; b.lower_only = 1;
+      if (lookahead) {
+        OB_CUDA(ctx, cudaEventRecord(ctx->ev_panel, st));
+        OB_CUDA(ctx, cudaStreamWaitEvent(side2, ctx->ev_panel, 0));
+        if (trail_pending) {   // (b) of the previous step
+          OB_CUDA(ctx, cudaStreamWaitEvent(side2, ctx->ev_trail, 0));
+          OB_CUDA(ctx, cudaStreamWaitEvent(st, ctx->ev_trail, 0));
+        }
+        chol_diag_kernel<<<1, 256, step_smem, side2>>>(Lm, n_pad, kb + 1, Lfac, Rd, info_dev);
+        OB_LAUNCH_CHECK(ctx);
+        OB_CUDA(ctx, cudaEventRecord(ctx->ev_diag, side2));
+        if ((rc = launch_gemm(ctx, true, a, 1))) return rc;
+        if (b.M > 0) {
+          OB_CUDA(ctx, cudaStreamWaitEvent(side, ctx->ev_panel, 0));
+          if ((rc = launch_gemm(ctx, true, b, 1, side))) return rc;
+          OB_CUDA(ctx, cudaEventRecord(ctx->ev_trail, side));
+          trail_pending = true;
+        } else {
+          trail_pending = false;
+        }
+        OB_CUDA(ctx, cudaStreamWaitEvent(st, ctx->ev_diag, 0));
+      } else {
+        chol_diag_kernel<<<1, 256, step_smem, st>>>(Lm, n_pad, kb + 1, Lfac, Rd, info_dev);
+        OB_LAUNCH_CHECK(ctx);
+        if ((rc = launch_gemm(ctx, true, a, 1))) return rc;
+        if (b.M > 0 && (rc = launch_gemm(ctx, true, b, 1))) return rc;
+      }
+    }
+  } else
   for (int kb = 0; kb < nb; ++kb) {
     const int rem = n_pad - (kb + 1) * FB;
     if (compact_step) chol_step_compact_kernel<<<1 + (rem > 0 ? rem / FB : 0), 256, step_smem, st>>>(Lm, n_pad, kb, Dinv, Lfac, info_dev);

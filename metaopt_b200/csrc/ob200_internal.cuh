@@ -125,6 +125,8 @@ struct ob200_ctx {
   int64_t b32_cap = 0;
   cudaStream_t fit_stream = nullptr;   // trailing updates of the Cholesky look-ahead
   cudaEvent_t ev_panel = nullptr, ev_trail = nullptr;
+  cudaStream_t fit_stream2 = nullptr;  // the next diagonal block's update + factorisation, beside the block column's update
+  cudaEvent_t ev_diag = nullptr;
   cudaStream_t copy_stream = nullptr;  // H2D of the candidate tail overlapped with scoring of the head
   cudaEvent_t ev_main = nullptr, ev_copy = nullptr;
   double* pinned = nullptr;        // pinned staging for host entry points
