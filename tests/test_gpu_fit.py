@@ -63,6 +63,20 @@ def test_not_positive_definite_is_reported(engine):
     engine.fit(X, y, alpha=1e-6)
 
 
+def test_not_positive_definite_in_a_late_block(engine):
+    """The failing pivot lies in the fifth 64-column block: the diagonal kernel of a later step (on its own stream) has to
+    stop the steps after it, and the error names a pivot at or after the duplicated row."""
+    X, y = gp_problem(400, 4, seed=3)
+    X[300] = X[17]
+    with pytest.raises(_lib.NotPositiveDefinite, match="positive definite") as err:
+        engine.fit(X, y, alpha=0.0)
+    pivot = int(str(err.value).split("pivot ")[1].split(" ")[0])
+    assert 300 < pivot <= 400
+    engine.fit(X, y, alpha=1e-6)
+    L, _ = engine.get_factor()
+    assert np.isfinite(L).all()
+
+
 def test_bad_arguments(engine):
     X, y = gp_problem(10, 3)
     with pytest.raises(_lib.Ob200Error):
