@@ -102,7 +102,7 @@ int ob200_space_set(ob200_ctx* ctx, const ob200_slot* slots_host, int n_slots,
  * (:371-391,410-423,542-552) -> TransformedSpace.transform (transformer.py:473-475) -> skopt
  * Normalize.  Point i (global index first_index+i) is a pure function of (seed, index): Philox
  * 4x32-10 counter-based draws, so shards reproduce the same candidates.
- *   out_dev       [count x ld] row-major, ld >= D_out
+ *   out_dev       [count x ld] row-major, ld >= D_out (count = 0: nothing is written, out_dev may be NULL)
  *   normalise     0: transformed values; 1: (x-nlo)/(nhi-nlo)
  *   variates_dev  NULL, or [count x n_slots] host-chosen U (uniform/loguniform/choice) / Z (normal)
  *                 variates: single try per slot (parity mode against the reference's own draws)

@@ -471,8 +471,9 @@ dslot make_dslot(const ob200_slot& s, int src) {
 int ob200_sample_launch(ob200_ctx* ctx, uint64_t seed, uint64_t first_index, int64_t count, int normalise,
                         double* out_dev, int64_t ld, const double* variates_dev) {
   if (ctx->n_slots <= 0) OB_FAIL(ctx, OB200_ESTATE, "ob200_space_set has not been called");
-  if (count < 0 || !out_dev || ld < ctx->d_out) OB_FAIL(ctx, OB200_EINVAL, "bad count/out/ld (ld=%lld, D_out=%d)", (long long)ld, ctx->d_out);
-  if (count == 0) return OB200_OK;
+  if (count < 0) OB_FAIL(ctx, OB200_EINVAL, "count must be >= 0");
+  if (count == 0) return OB200_OK;   // Space.sample(0) is an empty list; an empty tensor has no address
+  if (!out_dev || ld < ctx->d_out) OB_FAIL(ctx, OB200_EINVAL, "bad out/ld (ld=%lld, D_out=%d)", (long long)ld, ctx->d_out);
   const int d_out = ctx->d_out;
   // 16-byte paths need an even width, an even leading dimension and a 16-byte aligned base.  Shared-memory
   // row stride: width padded to 2 (mod 4) doubles (16-byte aligned rows, <= 2-way conflicts); else odd stride.
@@ -618,9 +619,10 @@ int ob200_sample_status(ob200_ctx* ctx) {
 int ob200_sample_transform_host(ob200_ctx* ctx, uint64_t seed, uint64_t first_index, int64_t count, int normalise,
                                 double* out_host, int64_t ld, const double* variates_host) {
   if (!ctx) return OB200_EINVAL;
-  if (!out_host || count < 0 || ld < ctx->d_out) OB_FAIL(ctx, OB200_EINVAL, "bad out/count/ld");
-  OB_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (count < 0) OB_FAIL(ctx, OB200_EINVAL, "count must be >= 0");
   if (count == 0) return OB200_OK;
+  if (!out_host || ld < ctx->d_out) OB_FAIL(ctx, OB200_EINVAL, "bad out/ld");
+  OB_CUDA(ctx, cudaSetDevice(ctx->device));
   const int64_t out_elems = count * ctx->d_out, var_elems = variates_host ? count * ctx->n_slots : 0;
   int rc = ob_reserve(ctx, &ctx->cand_tmp, &ctx->cand_cap, out_elems + var_elems);
   if (rc) return rc;

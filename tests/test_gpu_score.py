@@ -63,6 +63,31 @@ def test_posterior_and_acquisition_match_sklearn(engine, n, d, M, kind, normaliz
     _compare(engine, X, y, C, kind=kind, normalize_y=normalize_y, ls=np.linspace(0.8, 1.6, d), amp=1.7)
 
 
+@pytest.mark.parametrize("n,d,M", [(1, 1, 1), (1, 3, 5), (2, 1, 1), (3, 174, 2)])
+def test_degenerate_sizes(engine, n, d, M):
+    """One observation, one dimension, one candidate, the widest supported space: same contract as any other size."""
+    rs = np.random.RandomState(n * 1000 + d)
+    X = rs.uniform(size=(n, d))
+    y = rs.uniform(size=n) + 1.0
+    C = rs.uniform(size=(M, d))
+    # (normalize_y with one observation divides by a zero standard deviation in the reference: sklearn's guard sets it to 1)
+    _compare(engine, X, y, C, ls=0.7 if d < 100 else 4.0, normalize_y=True)
+    _compare(engine, X, y, C, kind=1, ls=0.7 if d < 100 else 4.0, normalize_y=False)
+
+
+def test_zero_candidates_and_empty_sample(engine):
+    from metaopt_b200 import _lib
+    from helpers import real_space
+    X, y = gp_problem(20, 3, seed=1)
+    engine.fit(X, y, alpha=1e-6)
+    with pytest.raises(_lib.Ob200Error) as err:
+        engine.score(torch.empty((0, 3), dtype=torch.float64, device="cuda"), acq_mask=1, y_opt=0.0)
+    assert err.value.code == _lib.EINVAL
+    comp = compiler.compile_space(transformed(real_space(3)))
+    compiler.upload(engine, comp)
+    assert tuple(engine.sample(1, 0, 0).shape) == (0, 3)
+
+
 def test_cfg2_shape_n2000_d20(engine):
     """BASELINE config 2 recipe at a CPU-checkable candidate count."""
     X, y = gp_problem(2000, 20, seed=0)
