@@ -1284,8 +1284,13 @@ int fit_impl(ob200_ctx* ctx, const double* X_dev, const double* y_dev, int n, in
   const size_t diag_smem = (size_t)2 * FB * (FB + 2) * sizeof(double);
   OB_CUDA(ctx, cudaFuncSetAttribute(chol_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)diag_smem));
   const bool compact_step = getenv("OB200_FIT_UNROLLED_STEP") == nullptr;   // (testing hook: the fully unrolled step kernel of round 2a)
-  // (testing hooks: the fused step kernels -- diagonal block factored inside every CTA of the step -- and their schedule)
-  const bool split_step = compact_step && getenv("OB200_FIT_FUSED_STEP") == nullptr;
+  // Step schedule: below ~3000 observations the fused step (diagonal block factored inside every CTA of the step, two
+  // launches per step on the main stream) wins by a launch and two cross-stream hops per step (n = 2000: 1.61 against
+  // 1.68 ms); above, where the block column's GEMM is long enough to hide the diagonal kernel, the split step does
+  // (n = 4000: 3.57 against 3.79 ms, n = 8000: 12.3 against 13.6).  (Testing hooks force either.)
+  bool split_step = compact_step && n_pad >= 3000;
+  if (getenv("OB200_FIT_FUSED_STEP")) split_step = false;
+  if (getenv("OB200_FIT_SPLIT_STEP")) split_step = compact_step;
   if (!ctx->fit_stream) {
     OB_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->fit_stream, cudaStreamNonBlocking));
     OB_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->fit_stream2, cudaStreamNonBlocking));

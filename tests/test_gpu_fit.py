@@ -63,9 +63,11 @@ def test_not_positive_definite_is_reported(engine):
     engine.fit(X, y, alpha=1e-6)
 
 
-def test_not_positive_definite_in_a_late_block(engine):
-    """The failing pivot lies in the fifth 64-column block: the diagonal kernel of a later step (on its own stream) has to
-    stop the steps after it, and the error names a pivot at or after the duplicated row."""
+@pytest.mark.parametrize("schedule", ["OB200_FIT_FUSED_STEP", "OB200_FIT_SPLIT_STEP"])
+def test_not_positive_definite_in_a_late_block(engine, monkeypatch, schedule):
+    """The failing pivot lies in the fifth 64-column block: under the split schedule the diagonal kernel of a later step
+    (on its own stream) has to stop the steps after it; the error names a pivot at or after the duplicated row."""
+    monkeypatch.setenv(schedule, "1")
     X, y = gp_problem(400, 4, seed=3)
     X[300] = X[17]
     with pytest.raises(_lib.NotPositiveDefinite, match="positive definite") as err:
@@ -75,6 +77,21 @@ def test_not_positive_definite_in_a_late_block(engine):
     engine.fit(X, y, alpha=1e-6)
     L, _ = engine.get_factor()
     assert np.isfinite(L).all()
+
+
+@pytest.mark.parametrize("schedule", ["OB200_FIT_FUSED_STEP", "OB200_FIT_SPLIT_STEP", "OB200_FIT_NO_LOOKAHEAD"])
+def test_step_schedules_agree(engine, monkeypatch, schedule):
+    """The fit picks its Cholesky schedule by size (fused step below ~3000 observations, split step above): each of them,
+    forced at one size, gives the factor of the reference."""
+    X, y = gp_problem(700, 6, seed=4)
+    monkeypatch.setenv(schedule, "1")
+    if schedule == "OB200_FIT_NO_LOOKAHEAD":
+        monkeypatch.setenv("OB200_FIT_SPLIT_STEP", "1")
+    engine.fit(X, y, alpha=1e-6, normalize_y=True)
+    L, al = engine.get_factor()
+    ref = ogp.SklearnGP(0, 1.0, np.ones(6), 1e-6, True).fit(X, y)
+    np.testing.assert_allclose(L, ref.L, rtol=L_RTOL, atol=1e-12)
+    np.testing.assert_allclose(al, ref.alpha_, rtol=ALPHA_RTOL, atol=ALPHA_RTOL * np.abs(ref.alpha_).max())
 
 
 def test_bad_arguments(engine):
