@@ -69,7 +69,11 @@ struct score_args {
 // i.e. below double rounding (<= 1 ulp measured).  x = 0 gives 0; x below 1e-30 gives a tiny finite
 // value <= 1e-15, which the Matern polynomial maps to amplitude * (1 + O(1e-30)).
 __device__ __forceinline__ double sqrt_pos(double x) {
-  const float yf = rsqrtf((float)fmax(x, 1e-30));  // MUFU.RSQ
+  // seed: the clamp in FP32 (one FMNMX; an FP64 max is five instructions) and the bare MUFU.RSQ (rsqrtf() wraps it in a
+  // denormal-input path of three more); same seed bits for every x the clamp lets through
+  const float xf = fmaxf((float)x, 1e-30f);
+  float yf;
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(yf) : "f"(xf));
   const double y0 = (double)yf, hy = (double)(0.5f * yf);
   double s = x * y0;
   s = fma(fma(-s, s, x), hy, s);
