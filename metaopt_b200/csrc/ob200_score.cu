@@ -81,6 +81,14 @@ __device__ __forceinline__ double sqrt_pos(double x) {
   return s;
 }
 
+// max(x, 0) for the squared distance (rounding can leave it a few ulp below zero): an FP64 max costs seven
+// instructions (DSETP.MAX, selects, NaN quieting); masking with the sign takes three and gives the same value for
+// every non-NaN x (a NaN -- a NaN coordinate in a candidate -- now stays a NaN and can never win the argmax).
+__device__ __forceinline__ double clamp_neg(double x) {
+  const int hi = __double2hiint(x), m = ~(hi >> 31);
+  return __hiloint2double(hi & m, __double2loint(x) & m);
+}
+
 __device__ __forceinline__ double kernel_from_d2(int kind, double d2, double amplitude, const double* __restrict__ tab) {
   if (kind == OB200_KERNEL_MATERN52) {
     const double k = sqrt_pos(d2) * 2.23606797749979;  // sqrt(5) * dist
@@ -306,8 +314,8 @@ __global__ void __launch_bounds__(MEAN_ONLY ? SC_MEAN_THREADS : SC_THREADS, MEAN
         double2* dst = reinterpret_cast<double2*>(kslice + (size_t)ob * SC_NCF * 64) + lane;
 #pragma unroll
         for (int cf = 0; cf < SC_NCF; ++cf) {
-          const double d20 = fmax(ccr[cf] + xx0 - 2.0 * acc[cf][0], 0.0);
-          const double d21 = fmax(ccr[cf] + xx1 - 2.0 * acc[cf][1], 0.0);
+          const double d20 = clamp_neg(ccr[cf] + xx0 - 2.0 * acc[cf][0]);
+          const double d21 = clamp_neg(ccr[cf] + xx1 - 2.0 * acc[cf][1]);
           double2 kv;
           kv.x = kernel_from_d2(a.kind, d20, a.amplitude, exp_tab);
           kv.y = kernel_from_d2(a.kind, d21, a.amplitude, exp_tab);
