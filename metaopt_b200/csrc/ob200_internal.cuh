@@ -275,9 +275,13 @@ __device__ __forceinline__ double u53(uint32_t lo, uint32_t hi) {
 // exp(t) = 2^n * 2^(j/32) * exp(r) and a degree-6 Taylor polynomial suffices (truncation 3.5e-18);
 // Cody-Waite two-constant reduction, scaling by exponent-field addition.  ~2 ulp; below 2^-1021 -> 0.
 // `tab` = 2^(j/32), j = 0..31, in shared memory.
+// Constants whose low word is not zero cannot be FP64 immediates; as literals the compiler rebuilds them with two moves
+// per use when registers are short (the mean-only pass runs at 72).  From the constant bank they are operands.
+static __constant__ double ob_kc[3] = {46.16624130844683 /* 32 / ln2 */, 0.3333333333333333, 2.23606797749979 /* sqrt(5) */};
+
 __device__ __forceinline__ double ob_exp_tab(double t, const double* __restrict__ tab) {
   const double magic = 6755399441055744.0;         // 1.5 * 2^52: round-to-nearest-integer trick
-  const double mb = fma(t, 46.16624130844683, magic);  // t * 32 / ln2
+  const double mb = fma(t, ob_kc[0], magic);  // t * 32 / ln2
   const int m = __double2loint(mb);
   const double md = mb - magic;
   double r = fma(md, -2.16608493865351192653e-02, t);   // ln2/32, high part

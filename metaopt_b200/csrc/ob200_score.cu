@@ -91,8 +91,8 @@ __device__ __forceinline__ double clamp_neg(double x) {
 
 __device__ __forceinline__ double kernel_from_d2(int kind, double d2, double amplitude, const double* __restrict__ tab) {
   if (kind == OB200_KERNEL_MATERN52) {
-    const double k = sqrt_pos(d2) * 2.23606797749979;  // sqrt(5) * dist
-    return amplitude * (fma(k, fma(k, 0.3333333333333333, 1.0), 1.0) * ob_exp_tab(-k, tab));
+    const double k = sqrt_pos(d2) * ob_kc[2];  // sqrt(5) * dist
+    return amplitude * (fma(k, fma(k, ob_kc[1], 1.0), 1.0) * ob_exp_tab(-k, tab));
   }
   return amplitude * ob_exp_tab(-0.5 * d2, tab);
 }
@@ -261,12 +261,14 @@ __global__ void __launch_bounds__(MEAN_ONLY ? SC_MEAN_THREADS : SC_THREADS, MEAN
   for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
     const long long row0 = tile * SC_BN;
     SC_PROF_MARK(7)  // (loop overhead / before the first tile)
-    // ---- stage the candidate tile: Cs = cand / ls in A-fragment order, cc = ||Cs||^2
+    // ---- stage the candidate tile: Cs = -2 cand / ls in A-fragment order (the factor makes the DMMA accumulator the
+    // -2 c.x term of the squared distance as it stands -- exact, a power of two -- and saves the doubling per kernel
+    // evaluation), cc = ||cand / ls||^2
     for (int e = tid; e < SC_BN * D_pad; e += SC_CONSUMER_WARPS * 32) {
       const int r = e / D_pad, d = e - r * D_pad;
       double v = 0.0;
       if (d < a.D && row0 + r < n_rows) v = a.cand[(size_t)(a.row_map ? a.row_map[row0 + r] : row0 + r) * a.ldc + d] / a.ls[d];
-      Cs[((size_t)(r >> 3) * nd4 + (d >> 2)) * 32 + (r & 7) * 4 + (d & 3)] = v;
+      Cs[((size_t)(r >> 3) * nd4 + (d >> 2)) * 32 + (r & 7) * 4 + (d & 3)] = -2.0 * v;
     }
     consumer_bar();
     if (tid < SC_BN) {
@@ -276,7 +278,7 @@ __global__ void __launch_bounds__(MEAN_ONLY ? SC_MEAN_THREADS : SC_THREADS, MEAN
         const double v = Cs[((size_t)(r >> 3) * nd4 + (d >> 2)) * 32 + (r & 7) * 4 + (d & 3)];
         acc = fma(v, v, acc);
       }
-      cc[r] = acc;
+      cc[r] = 0.25 * acc;
     }
     consumer_bar();
 
@@ -314,8 +316,8 @@ __global__ void __launch_bounds__(MEAN_ONLY ? SC_MEAN_THREADS : SC_THREADS, MEAN
         double2* dst = reinterpret_cast<double2*>(kslice + (size_t)ob * SC_NCF * 64) + lane;
 #pragma unroll
         for (int cf = 0; cf < SC_NCF; ++cf) {
-          const double d20 = clamp_neg(ccr[cf] + xx0 - 2.0 * acc[cf][0]);
-          const double d21 = clamp_neg(ccr[cf] + xx1 - 2.0 * acc[cf][1]);
+          const double d20 = clamp_neg(ccr[cf] + xx0 + acc[cf][0]);
+          const double d21 = clamp_neg(ccr[cf] + xx1 + acc[cf][1]);
           double2 kv;
           kv.x = kernel_from_d2(a.kind, d20, a.amplitude, exp_tab);
           kv.y = kernel_from_d2(a.kind, d21, a.amplitude, exp_tab);
