@@ -134,7 +134,8 @@ struct gemm_args {
   int m_last, k_eq_m;  // k_eq_m: K follows the batch entry's M (TRTRI second product)
   double alpha, beta;
   int lower_only;
-  int tri_k;  // bit 0: B is lower triangular, k starts at 64*tn; bit 1: A is lower triangular, k ends at 64*(tm+1); 3: both
+  int tri_k;  // bit 0: B is lower triangular, k starts at 64*tn; bit 1: A is lower triangular, k ends at 64*(tm+1); 3: both;
+              // bit 2: A (M x K, row-major) is UPPER triangular, k starts at 64*tm
 };
 
 template <bool TRANS_B>
@@ -161,7 +162,7 @@ __global__ void __launch_bounds__(128) gemm64_kernel(gemm_args g) {
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
 
-  const int k_begin = (g.tri_k & 1) ? tn * 64 : 0;
+  const int k_begin = (g.tri_k & 4) ? tm * 64 : ((g.tri_k & 1) ? tn * 64 : 0);
   if (g.tri_k & 2) { const int k_end = (tm + 1) * 64; if (k_end < K) K = k_end; }
   // The next K slab is fetched into registers while the current one is multiplied: at the one or two CTAs per SM the
   // fit's GEMMs have, the loop is bound by the latency of these loads.
@@ -1546,6 +1547,7 @@ int ob200_gp_lml_grad(ob200_ctx* ctx, double* lml_host, double* grad_host, int n
   gemm_args k{};  // K^-1 = inv(L)^T inv(L) = M M^T, lower tiles
   k.A = G + g_M; k.lda = n_pad; k.B = G + g_M; k.ldb = n_pad; k.C = G + g_Kinv; k.ldc = n_pad;
   k.M = n_pad; k.N = n_pad; k.K = n_pad; k.alpha = 1.0; k.beta = 0.0; k.lower_only = 1;
+  k.tri_k = 4;   // M is upper triangular: row i is zero left of column i, and the lower tiles have i >= j
   if ((rc = launch_gemm(ctx, true, k, 1))) return rc;
   const size_t smem = (size_t)2 * 32 * (D_pad + 1) * sizeof(double);
   OB_CUDA(ctx, cudaFuncSetAttribute(lml_t_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem > 49152 ? smem : 49152)));
