@@ -465,9 +465,9 @@ def run_ours(args):
         pts = [tuple(float(v) for v in row) for row in X]
         rs = np.random.RandomState(5)
 
-        def make(acq_func="EI", **extra):
+        def make(acq_func="EI", n_points=M, **extra):
             algo = BayesianOptimizer(tspace, seed=1, n_initial_points=10, acq_func=acq_func, alpha=ALPHA, noise="gaussian",
-                                     noise_level=NOISE, normalize_y=True, n_points=M, xi=XI, device=local, **extra)
+                                     noise_level=NOISE, normalize_y=True, n_points=n_points, xi=XI, device=local, **extra)
             algo.observe(pts, [{"objective": float(v)} for v in y])
             return algo
 
@@ -500,9 +500,13 @@ def run_ours(args):
         p50_dense, n_dense = cached(max(5, min(20, args.steps * 2)), prune=False)
         p50_pruned, n_calls = cached(50, prune=True)
         p50_hedge, _ = cached(50, acq_func="gp_hedge", prune=True)  # the plugin's default portfolio (EI, LCB, PI)
+        # the plugin's DEFAULT candidate count (n_points = 10 000, skopt's default), EI and the default portfolio
+        p50_10k, _ = cached(50, n_points=10_000, prune=True)
+        p50_10k_hedge, _ = cached(50, n_points=10_000, acq_func="gp_hedge", prune=True)
         p50_fixed, max_fixed, n_cycle = producer_cycle(50, fit_hyperparameters=False, prune=True)
         p50_default, max_default, _ = producer_cycle(50, acq_func="gp_hedge", fit_hyperparameters=True, prune=True)
         suggest_latency = {"p50_ms_dense": p50_dense, "p50_ms_pruned": p50_pruned, "p50_ms_pruned_gp_hedge": p50_hedge,
+                           "p50_ms_n_points_10000": p50_10k, "p50_ms_n_points_10000_gp_hedge": p50_10k_hedge,
                            "p50_ms_observe_then_suggest_fixed_theta": p50_fixed, "max_ms_observe_then_suggest_fixed_theta": max_fixed,
                            "p50_ms_observe_then_suggest_default": p50_default, "max_ms_observe_then_suggest_default": max_default,
                            "calls_dense": n_dense, "calls_pruned": n_calls, "calls_observe_then_suggest": n_cycle, "n_points": M,

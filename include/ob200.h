@@ -209,7 +209,9 @@ int ob200_score_pruned(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int6
  * stays bit-identical to the dense call.  The FP32 pass is used only for fits whose error budget leaves a usable
  * bound (decided once per fit from ||alpha||_1); OB200_BOUND_F32=0 in the environment selects the FP64 bound pass for
  * everything.  When many candidates are still standing after that, a GP on 192 evenly spaced observations bounds
- * their variance from above once more (conditioning on a subset can only raise it) before the O(n^2) scoring.  -LCB with kappa < 0 is not increasing in sigma: such calls take the dense path.  y_opt, xi, kappa must
+ * their variance from above once more (conditioning on a subset can only raise it) before the O(n^2) scoring. 
+ * Calls that take the dense kernel instead: M up to one tile of 32 candidates per SM (a single wave of the dense kernel);
+ * -LCB with kappa < 0, which is not increasing in sigma.  y_opt, xi, kappa must
  * be finite (OB200_EINVAL otherwise, in every score entry point).  One host synchronisation per call. */
 int ob200_score_pruned_multi(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M, uint64_t seed,
                              uint64_t first_index, int acq_mask, double y_opt, double xi, double kappa,

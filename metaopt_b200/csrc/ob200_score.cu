@@ -1201,7 +1201,12 @@ extern "C" int ob200_score_pruned_multi(ob200_ctx* ctx, const double* cand_dev, 
   // DEcreases in sigma, so U(mu_lb, sigma_ub) would not bound it.
   const bool too_big = !cand_dev && (M * (int64_t)D * 8 > ((int64_t)1 << 31));
   const bool lcb_not_monotone = (acq_mask & (1 << OB200_ACQ_LCB)) && kappa < 0.0;
-  if (M <= 4 * batch || too_big || lcb_not_monotone) {
+  // Up to one tile per CTA the dense kernel is one wave (0.68 ms at n = 2000) and nothing can beat it; from the second
+  // wave on the pruned path wins: 0.80 ms flat for 6 000 ... 50 000 candidates against 1.3 / 1.8 / 2.4 / 6.6 ms dense at
+  // 6 000 / 10 000 / 15 000 / 50 000 (tools/small_m_perf.py; the plugin's default n_points is 10 000).
+  int64_t dense_upto = batch;
+  if (const char* env = getenv("OB200_PRUNE_MIN_BATCHES")) { const int v = atoi(env); if (v >= 1 && v <= 64) dense_upto = v * batch; }   // (tuning hook)
+  if (M <= dense_upto || too_big || lcb_not_monotone) {
     rc = ob200_score(ctx, cand_dev, ldc, M, seed, first_index, acq_mask, y_opt, xi, kappa, best_host, nullptr, nullptr, nullptr);
     if (rc) return rc;
     for (int k = 0; k < 3; ++k) if (n_scored_host && (acq_mask & (1 << k))) n_scored_host[k] = M;

@@ -194,7 +194,7 @@ def fuzz_pruned():
     a fraction of the cube to far beyond it (what a fitted GP on a smooth objective looks like)."""
     n = int(rng.choice([13, 192, 193, 500, int(rng.randint(2, 900))]))
     d = int(rng.choice([1, 2, 5, 8, 9, 20, 24, 25, 33, int(rng.randint(1, 70))]))
-    M = int(rng.choice([18945, 19000, 40001, int(rng.randint(18945, 60000))]))
+    M = int(rng.choice([4737, 4768, 9473, 18945, 40001, int(rng.randint(4737, 60000))]))   # above the single-wave dense fallback
     kind = int(rng.randint(0, 2))
     amp = float(10 ** rng.uniform(-1, 3))
     ls_scale = float(10 ** rng.uniform(-0.7, 1.3))
