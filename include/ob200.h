@@ -210,7 +210,8 @@ int ob200_score_pruned(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int6
  * bound (decided once per fit from ||alpha||_1); OB200_BOUND_F32=0 in the environment selects the FP64 bound pass for
  * everything.  When many candidates are still standing after that, a GP on 192 evenly spaced observations bounds
  * their variance from above once more (conditioning on a subset can only raise it) before the O(n^2) scoring. 
- * Calls that take the dense kernel instead: M up to one tile of 32 candidates per SM (a single wave of the dense kernel);
+ * Calls that take the dense kernel instead: M up to a few waves of the dense kernel (one tile of 32 candidates per SM
+ * each; one wave from n_obs ~ 1000, more for smaller fits, where a dense wave is cheaper than the bound pass's fixed cost);
  * -LCB with kappa < 0, which is not increasing in sigma.  y_opt, xi, kappa must
  * be finite (OB200_EINVAL otherwise, in every score entry point).  One host synchronisation per call. */
 int ob200_score_pruned_multi(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M, uint64_t seed,

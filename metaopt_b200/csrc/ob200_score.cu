@@ -1201,10 +1201,16 @@ extern "C" int ob200_score_pruned_multi(ob200_ctx* ctx, const double* cand_dev, 
   // DEcreases in sigma, so U(mu_lb, sigma_ub) would not bound it.
   const bool too_big = !cand_dev && (M * (int64_t)D * 8 > ((int64_t)1 << 31));
   const bool lcb_not_monotone = (acq_mask & (1 << OB200_ACQ_LCB)) && kappa < 0.0;
-  // Up to one tile per CTA the dense kernel is one wave (0.68 ms at n = 2000) and nothing can beat it; from the second
-  // wave on the pruned path wins: 0.80 ms flat for 6 000 ... 50 000 candidates against 1.3 / 1.8 / 2.4 / 6.6 ms dense at
-  // 6 000 / 10 000 / 15 000 / 50 000 (tools/small_m_perf.py; the plugin's default n_points is 10 000).
-  int64_t dense_upto = batch;
+  // Up to one tile per CTA the dense kernel is one wave and nothing can beat it.  Beyond, the pruned path costs one
+  // wave + ~0.10 ms (0.14 ms for a portfolio) whatever M, the dense kernel one wave per `batch` candidates, and a wave
+  // costs ~125 ns per candidate at n_pad = 2112, growing with n_pad^2 (tools/small_m_perf.py, B200): dense while its
+  // extra waves are cheaper than that overhead -- 1 wave from n ~ 1000 (n = 2000: 0.80 ms flat for 6 000 ... 50 000
+  // candidates against 1.3 / 1.8 / 2.4 / 6.6 ms dense at 6 000 / 10 000 / 15 000 / 50 000; the plugin's default
+  // n_points is 10 000), 2 at n = 700, 4 at n = 300, 17 at n = 50.
+  int n_acq_req = 0;
+  for (int k = 0; k < 3; ++k) n_acq_req += (acq_mask >> k) & 1;
+  const double wave_ns = (double)batch * (125.0 * (ctx->hdr.n_pad / 2112.0) * (ctx->hdr.n_pad / 2112.0) + 0.3);
+  int64_t dense_upto = batch * (1 + (int64_t)((n_acq_req > 1 ? 1.4e5 : 1.0e5) / wave_ns));
   if (const char* env = getenv("OB200_PRUNE_MIN_BATCHES")) { const int v = atoi(env); if (v >= 1 && v <= 64) dense_upto = v * batch; }   // (tuning hook)
   if (M <= dense_upto || too_big || lcb_not_monotone) {
     rc = ob200_score(ctx, cand_dev, ldc, M, seed, first_index, acq_mask, y_opt, xi, kappa, best_host, nullptr, nullptr, nullptr);

@@ -172,3 +172,19 @@ def test_subset_variance_bound_is_an_upper_bound(engine, monkeypatch):
     sub = engine.score(C, acq_mask=1, y_opt=0.0, dense=True)["sigma"]
     _, y_std, _ = (None, float(np.std(y)), None)
     assert bool(torch.all(sub * y_std + 1e-9 >= sigma_full))
+
+
+def test_dense_fallback_policy(engine, monkeypatch):
+    """Default policy of the pruned entry points: dense while the extra dense waves cost less than the pruned path's fixed
+    overhead -- one wave at n = 2000, many at n = 50 -- and the same winner either way."""
+    monkeypatch.delenv("OB200_PRUNE_MIN_BATCHES", raising=False)
+    rs = np.random.RandomState(7)
+    C = torch.as_tensor(rs.uniform(size=(30_000, 4))).cuda()
+    for n, expect_dense in ((50, True), (1500, False)):
+        X = rs.uniform(size=(n, 4))
+        y = ((X - 0.5) ** 2).sum(axis=1) + 0.01 * rs.randn(n)
+        engine.fit(X, y, alpha=1e-6, normalize_y=True)
+        dense = engine.score(C, acq_mask=1, y_opt=float(y.min()))
+        pruned, n_scored = engine.score_pruned(C, acq="EI", y_opt=float(y.min()))
+        assert pruned["EI"] == dense["EI"]
+        assert (n_scored == C.shape[0]) == expect_dense, (n, n_scored)

@@ -23,6 +23,7 @@ from oracle import acquisition as oacq  # noqa: E402
 from oracle import gp as ogp  # noqa: E402
 from oracle import sampling as osamp  # noqa: E402
 
+os.environ.setdefault("OB200_PRUNE_MIN_BATCHES", "1")   # the pruned legs want the pruned path at every n
 BUDGET = float(sys.argv[1]) if len(sys.argv) > 1 else 240.0
 rng = np.random.RandomState(int(sys.argv[2]) if len(sys.argv) > 2 else 0)
 eng = get_engine(0)

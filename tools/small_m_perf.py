@@ -5,14 +5,14 @@ import numpy as np, torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from metaopt_b200.engine import get_engine
 
-n, d = 2000, 20
+n, d = (int(sys.argv[1]) if len(sys.argv) > 1 else 2000), 20
 eng = get_engine(0)
 rs = np.random.RandomState(0)
 X = rs.uniform(size=(n, d)); y = ((X - 0.5) ** 2).sum(1) + 0.01 * rs.randn(n)
 eng.fit(X, y, alpha=1e-10 + 1e-4, normalize_y=True)
 y_opt = float(y.min())
 out = {}
-for M in (4736, 6000, 9472, 10000, 14208, 15000, 18944, 25000, 50000):
+for M in (4736, 6000, 10000, 15000, 25000, 50000, 100000, 200000):
     C = torch.rand((M, d), dtype=torch.float64, device="cuda", generator=torch.Generator(device="cuda").manual_seed(1))
     row = {}
     for k in ("64", "1"):
