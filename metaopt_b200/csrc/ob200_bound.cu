@@ -68,11 +68,6 @@ __device__ __forceinline__ float sqrt_approx(float v) {
   asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(v));
   return r;
 }
-__device__ __forceinline__ float rsqrt_approx(float v) {
-  float r;
-  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(v));
-  return r;
-}
 __device__ __forceinline__ float ex2_approx(float v) {
   float r;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(v));
