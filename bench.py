@@ -341,7 +341,11 @@ def run_ours(args):
     host_cand = torch.empty((count, DIM), dtype=torch.float64).pin_memory()
     host_cand.copy_(cand)
     host_np = host_cand.numpy()
+    # untimed warm-up at the timed size: the first full-size call grows the context's candidate buffer (160 MB) and creates
+    # its copy stream, which used to land inside the timed steps (+3 ms per step over five steps)
     eng.score_host(host_np[:4096], acq_mask=1, y_opt=y_opt, xi=XI)
+    for _ in range(min(args.warmup, 2)):
+        eng.score_host(host_np, acq_mask=1, y_opt=y_opt, xi=XI)
     e2e_steps = max(1, min(args.steps, 5))
     barrier()
     t0 = time.perf_counter()

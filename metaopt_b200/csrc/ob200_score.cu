@@ -800,6 +800,9 @@ int ob200_score_host(ob200_ctx* ctx, const double* cand_host, int64_t ldc, int64
   if (ldc < D) OB_FAIL(ctx, OB200_EINVAL, "ldc=%lld < D=%d", (long long)ldc, D);
   OB_CUDA(ctx, cudaSetDevice(ctx->device));
   l2_scope l2(ctx);
+  // Taken here, before any copy is in flight: cudaDeviceSetLimit waits for the device to drain, and inside the first score
+  // launch it used to wait for the tail's H2D copy -- the overlap below was lost (+2.9 ms per 10^6 candidates).
+  ob_l2_acquire(ctx);
   if ((rc = ob_reserve(ctx, &ctx->cand_tmp, &ctx->cand_cap, M * D))) return rc;
   const int64_t dense = (mu_host ? M : 0) + (sigma_host ? M : 0) + (acq_host ? 3 * M : 0);
   if (dense && (rc = ob_reserve(ctx, &ctx->dense_tmp, &ctx->dense_cap, dense))) return rc;
