@@ -682,7 +682,9 @@ int score_launch(ob200_ctx* ctx, const double* cand_dev, int64_t ldc, int64_t M,
   OB_CUDA(ctx, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   // k* slices -> persisting L2 lines for this launch (the window is a launch-time stream attribute)
   const size_t slices = (size_t)grid * h.n_pad * SC_BN * sizeof(double);
-  const bool persist = ctx->l2_persist_max > 0 && !mean_only;
+  // (not for launches of a wave or two -- the first batches of the pruned path: their slices are written and read once
+  // while they are the newest lines in L2 anyway, and the two cudaDeviceSetLimit calls cost ~35 us per call)
+  const bool persist = ctx->l2_persist_max > 0 && !mean_only && (M_dev == nullptr) && n_tiles > 2 * (long long)grid;
   if (persist) {
     ob_l2_acquire(ctx);
     cudaStreamAttrValue attr{};
@@ -802,7 +804,7 @@ int ob200_score_host(ob200_ctx* ctx, const double* cand_host, int64_t ldc, int64
   l2_scope l2(ctx);
   // Taken here, before any copy is in flight: cudaDeviceSetLimit waits for the device to drain, and inside the first score
   // launch it used to wait for the tail's H2D copy -- the overlap below was lost (+2.9 ms per 10^6 candidates).
-  ob_l2_acquire(ctx);
+  if (M > 2 * (int64_t)ctx->num_sms * SC_BN) ob_l2_acquire(ctx);
   if ((rc = ob_reserve(ctx, &ctx->cand_tmp, &ctx->cand_cap, M * D))) return rc;
   const int64_t dense = (mu_host ? M : 0) + (sigma_host ? M : 0) + (acq_host ? 3 * M : 0);
   if (dense && (rc = ob_reserve(ctx, &ctx->dense_tmp, &ctx->dense_cap, dense))) return rc;
